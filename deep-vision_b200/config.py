@@ -1,0 +1,35 @@
+"""Process-wide settings of the B200 path."""
+import torch
+
+_state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0}
+
+
+def compute_dtype():
+    return _state["compute_dtype"]
+
+
+def set_compute_dtype(dtype):
+    """torch.bfloat16 (tensor-core path, the speed configuration) or torch.float32 (CUDA-core path that meets the
+    1e-4 parity bound of BASELINE.json)."""
+    if dtype not in (torch.bfloat16, torch.float32):
+        raise TypeError("compute dtype must be torch.bfloat16 or torch.float32")
+    _state["compute_dtype"] = dtype
+
+
+def weight_epoch():
+    return _state["weight_epoch"]
+
+
+def bump_weight_epoch():
+    """Invalidate every cached compute-dtype filter copy.  Call after parameters were changed behind torch's back
+    (the fused optimiser kernels write through raw pointers and do not move Tensor._version)."""
+    _state["weight_epoch"] += 1
+
+
+def conv_algo():
+    return _state["conv_algo"]
+
+
+def set_conv_algo(algo):
+    """0 = auto (tcgen05 where the shape qualifies), 1 = CUDA-core kernels only, 2 = tensor cores or error."""
+    _state["conv_algo"] = int(algo)

@@ -1,0 +1,356 @@
+// bn.cu — batch normalisation over [M rows][C channels] (NHWC activations flattened), the HBM-bound half of the
+// conv-BN-ReLU block.  All passes stream 16-byte vectors (8 bf16 / 4 fp32 channels per thread, consecutive threads on
+// consecutive channels => fully coalesced 128-byte lines) and keep per-channel statistics in fp32.
+//
+//   stats      : per-channel shifted sums  S1 = sum(x-k), S2 = sum((x-k)^2), k = x[0][c]  -> block partials in scratch
+//                finalize: mean, biased var -> invstd, running stats (unbiased var)          [2 reads of nothing extra]
+//   apply      : y = relu((x-mean)*invstd*gamma + beta [+ residual])
+//   bwd_reduce : dbeta = sum(dz), dgamma = sum(dz*xhat), dz = dy * (y > 0)
+//   bwd_apply  : dx = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M);  dres = dz
+// Partials are reduced in a fixed order, so every result is bit-reproducible run to run.
+#include "common.cuh"
+
+namespace dv {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxBlocks = 592;  // 4 x 148 SMs
+
+struct Plan {
+  int cg;        // channel groups (C / V)
+  int cgb;       // channel groups handled concurrently by a block (<= 256)
+  int rows_par;  // rows handled concurrently by a block
+  int nblk;
+  int64_t rows_per_blk;
+};
+
+static Plan make_plan(int64_t M, int C, int V) {
+  Plan p;
+  p.cg = C / V;
+  p.cgb = p.cg < kThreads ? p.cg : kThreads;
+  p.rows_par = kThreads / p.cgb;
+  int64_t nb = ceil_div64(M, (int64_t)p.rows_par * 32);
+  if (nb > kMaxBlocks) nb = kMaxBlocks;
+  if (nb < 1) nb = 1;
+  p.rows_per_blk = ceil_div64(M, nb);
+  p.nblk = (int)ceil_div64(M, p.rows_per_blk);
+  return p;
+}
+
+// MODE 0: forward statistics of x.  MODE 1: backward sums (dz, dz*xhat).
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kThreads)
+bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, const float* __restrict__ mean,
+                 const float* __restrict__ invstd, float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par,
+                 int64_t rows_per_blk, int relu) {
+  constexpr int V = Vec16<T>::N;
+  __shared__ float red[2][kThreads * V];
+  const int tcg = threadIdx.x % cgb, trow = threadIdx.x / cgb;
+  const bool active = trow < rows_par;
+  const int cg = C / V;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_blk;
+  const int64_t r1 = (r0 + rows_per_blk < M) ? r0 + rows_per_blk : M;
+
+  for (int g0 = 0; g0 < cg; g0 += cgb) {
+    const int g = g0 + tcg;
+    const int c = g * V;
+    float a1[V], a2[V], k0[V], k1[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i) { a1[i] = 0.f; a2[i] = 0.f; k0[i] = 0.f; k1[i] = 1.f; }
+    if (active && g < cg) {
+      if (MODE == 0) {
+        Vec16<T> v0; v0.load(x + c);  // row 0 as the shift
+        v0.unpack(k0);
+      } else {
+#pragma unroll
+        for (int i = 0; i < V; ++i) { k0[i] = mean[c + i]; k1[i] = invstd[c + i]; }
+      }
+      for (int64_t r = r0 + trow; r < r1; r += rows_par) {
+        const size_t off = (size_t)r * C + c;
+        float xv[V];
+        Vec16<T> vx; vx.load(x + off); vx.unpack(xv);
+        if (MODE == 0) {
+#pragma unroll
+          for (int i = 0; i < V; ++i) { const float d = xv[i] - k0[i]; a1[i] += d; a2[i] = fmaf(d, d, a2[i]); }
+        } else {
+          float gv[V];
+          Vec16<T> vg; vg.load(dy + off); vg.unpack(gv);
+          if (relu) {
+            float yv[V];
+            Vec16<T> vy; vy.load(y + off); vy.unpack(yv);
+#pragma unroll
+            for (int i = 0; i < V; ++i) gv[i] = yv[i] > 0.f ? gv[i] : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < V; ++i) { a1[i] += gv[i]; a2[i] = fmaf(gv[i], (xv[i] - k0[i]) * k1[i], a2[i]); }
+        }
+      }
+    }
+    // reduce over the rows_par row lanes of this block
+#pragma unroll
+    for (int i = 0; i < V; ++i) { red[0][threadIdx.x * V + i] = a1[i]; red[1][threadIdx.x * V + i] = a2[i]; }
+    __syncthreads();
+    if (trow == 0 && g < cg) {
+      float s1[V], s2[V];
+#pragma unroll
+      for (int i = 0; i < V; ++i) { s1[i] = 0.f; s2[i] = 0.f; }
+      for (int rr = 0; rr < rows_par; ++rr) {
+        const int t = rr * cgb + tcg;
+#pragma unroll
+        for (int i = 0; i < V; ++i) { s1[i] += red[0][t * V + i]; s2[i] += red[1][t * V + i]; }
+      }
+      float* p1 = partial + ((size_t)blockIdx.x * 2) * C + c;
+      float* p2 = p1 + C;
+#pragma unroll
+      for (int i = 0; i < V; ++i) { p1[i] = s1[i]; p2[i] = s2[i]; }
+    }
+    __syncthreads();
+  }
+}
+
+template <typename T>
+__global__ void bn_stats_finalize_kernel(const T* __restrict__ x, const float* __restrict__ partial, int nblk, int C, int64_t M,
+                                         float eps, float momentum, float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                                         float* __restrict__ running_mean, float* __restrict__ running_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s1 = 0.0, s2 = 0.0;
+  for (int b = 0; b < nblk; ++b) {
+    s1 += (double)partial[((size_t)b * 2) * C + c];
+    s2 += (double)partial[((size_t)b * 2 + 1) * C + c];
+  }
+  const double k = (double)to_f32(x[c]);
+  const double n = (double)M;
+  const double m1 = s1 / n;
+  double var = s2 / n - m1 * m1;
+  if (var < 0.0) var = 0.0;
+  const double mean = k + m1;
+  save_mean[c] = (float)mean;
+  save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+  if (running_mean != nullptr) {
+    const double unbiased = M > 1 ? var * n / (n - 1.0) : var;
+    running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mean);
+    running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+  }
+}
+
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dgamma,
+                                       float* __restrict__ dbeta) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s1 = 0.0, s2 = 0.0;
+  for (int b = 0; b < nblk; ++b) {
+    s1 += (double)partial[((size_t)b * 2) * C + c];
+    s2 += (double)partial[((size_t)b * 2 + 1) * C + c];
+  }
+  dbeta[c] = (float)s1;
+  dgamma[c] = (float)s2;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, const float* __restrict__ gamma,
+                const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
+                int64_t nvec, int C, int relu, int eval_mode, float eps) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = C / V;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cg) * V;
+    float xv[V], rv[V], out[V];
+    Vec16<T> vx; vx.load(x + i * V); vx.unpack(xv);
+    if (res != nullptr) { Vec16<T> vr; vr.load(res + i * V); vr.unpack(rv); }
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float is = eval_mode ? rsqrtf(invstd_or_var[c + j] + eps) : invstd_or_var[c + j];
+      float v = (xv[j] - mean[c + j]) * is * gamma[c + j] + beta[c + j];
+      if (res != nullptr) v += rv[j];
+      if (relu) v = fmaxf(v, 0.f);
+      out[j] = v;
+    }
+    Vec16<T> vo; vo.pack(out); vo.store(y + i * V);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
+                    T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, const float* __restrict__ dgamma, const float* __restrict__ dbeta,
+                    int64_t nvec, int C, int relu, float inv_m) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = C / V;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cg) * V;
+    float xv[V], gv[V], out[V];
+    Vec16<T> vx; vx.load(x + i * V); vx.unpack(xv);
+    Vec16<T> vg; vg.load(dy + i * V); vg.unpack(gv);
+    if (relu) {
+      float yv[V];
+      Vec16<T> vy; vy.load(y + i * V); vy.unpack(yv);
+#pragma unroll
+      for (int j = 0; j < V; ++j) gv[j] = yv[j] > 0.f ? gv[j] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float is = invstd[c + j];
+      const float xhat = (xv[j] - mean[c + j]) * is;
+      out[j] = gamma[c + j] * is * (gv[j] - dbeta[c + j] * inv_m - xhat * dgamma[c + j] * inv_m);
+    }
+    Vec16<T> vo; vo.pack(out); vo.store(dx + i * V);
+    if (dres != nullptr) { Vec16<T> vr; vr.pack(gv); vr.store(dres + i * V); }
+  }
+}
+
+template <typename T>
+__global__ void relu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t nvec) {
+  constexpr int V = Vec16<T>::N;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    float v[V];
+    Vec16<T> a; a.load(x + i * V); a.unpack(v);
+#pragma unroll
+    for (int j = 0; j < V; ++j) v[j] = fmaxf(v[j], 0.f);
+    a.pack(v); a.store(y + i * V);
+  }
+}
+template <typename T>
+__global__ void relu_bwd_kernel(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, int64_t nvec) {
+  constexpr int V = Vec16<T>::N;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    float v[V], g[V];
+    Vec16<T> a; a.load(y + i * V); a.unpack(v);
+    Vec16<T> b; b.load(dy + i * V); b.unpack(g);
+#pragma unroll
+    for (int j = 0; j < V; ++j) g[j] = v[j] > 0.f ? g[j] : 0.f;
+    b.pack(g); b.store(dx + i * V);
+  }
+}
+
+static unsigned stream_grid(int64_t nvec) {
+  int64_t b = ceil_div64(nvec, kThreads);
+  const int64_t cap = (int64_t)num_sms() * 8;
+  return (unsigned)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+template <typename T>
+static int stats_t(const dv_bn_params* p, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
+  Plan pl = make_plan(p->M, p->C, V);
+  const size_t need = (size_t)pl.nblk * 2 * p->C * sizeof(float);
+  DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "bn_stats: workspace %zu bytes required, %zu given", need,
+             p->workspace_bytes);
+  bn_reduce_kernel<T, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, (float*)p->workspace, p->M,
+                                                      p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, 0);
+  DV_LAUNCH_OK("bn_reduce_kernel<stats>");
+  bn_stats_finalize_kernel<T><<<ceil_div(p->C, 128), 128, 0, st>>>((const T*)p->x, (const float*)p->workspace, pl.nblk, p->C, p->M, p->eps,
+                                                                  p->momentum, p->save_mean, p->save_invstd, p->running_mean,
+                                                                  p->running_var);
+  DV_LAUNCH_OK("bn_stats_finalize_kernel");
+  return DV_OK;
+}
+
+template <typename T>
+static int apply_t(const dv_bn_params* p, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
+  const int64_t nvec = p->M * p->C / V;
+  const float* mean = p->eval_mode ? p->running_mean : p->save_mean;
+  const float* is = p->eval_mode ? p->running_var : p->save_invstd;
+  DV_REQUIRE(mean && is, DV_ERR_ARG, "bn_apply: statistics pointers are null");
+  bn_apply_kernel<T><<<stream_grid(nvec), kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is,
+                                                            nvec, p->C, p->relu, p->eval_mode, p->eps);
+  DV_LAUNCH_OK("bn_apply_kernel");
+  return DV_OK;
+}
+
+template <typename T>
+static int bwd_reduce_t(const dv_bn_bwd_params* p, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
+  Plan pl = make_plan(p->M, p->C, V);
+  const size_t need = (size_t)pl.nblk * 2 * p->C * sizeof(float);
+  DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "bn_bwd_reduce: workspace %zu bytes required, %zu given",
+             need, p->workspace_bytes);
+  DV_REQUIRE(!p->relu || p->y, DV_ERR_ARG, "bn_bwd_reduce: y is required when relu is fused");
+  bn_reduce_kernel<T, 1><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, p->save_mean, p->save_invstd,
+                                                      (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, p->relu);
+  DV_LAUNCH_OK("bn_reduce_kernel<bwd>");
+  bn_bwd_finalize_kernel<<<ceil_div(p->C, 128), 128, 0, st>>>((const float*)p->workspace, pl.nblk, p->C, p->dgamma, p->dbeta);
+  DV_LAUNCH_OK("bn_bwd_finalize_kernel");
+  return DV_OK;
+}
+
+template <typename T>
+static int bwd_apply_t(const dv_bn_bwd_params* p, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
+  DV_REQUIRE(!p->relu || p->y, DV_ERR_ARG, "bn_bwd_apply: y is required when relu is fused");
+  const int64_t nvec = p->M * p->C / V;
+  bn_bwd_apply_kernel<T><<<stream_grid(nvec), kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres,
+                                                                p->gamma, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
+                                                                p->relu, 1.0f / (float)p->M);
+  DV_LAUNCH_OK("bn_bwd_apply_kernel");
+  return DV_OK;
+}
+
+}  // namespace
+}  // namespace dv
+
+using namespace dv;
+
+extern "C" size_t dv_bn_workspace_bytes(int64_t M, int C) {
+  // sized for the narrower vector (fp32, 4 channels/thread) so one buffer serves both dtypes
+  Plan a = make_plan(M, C, 4), b = make_plan(M, C, 8);
+  const int nb = a.nblk > b.nblk ? a.nblk : b.nblk;
+  return (size_t)nb * 2 * C * sizeof(float);
+}
+
+extern "C" int dv_bn_stats(const dv_bn_params* p, void* stream) {
+  DV_REQUIRE(p && p->x && p->save_mean && p->save_invstd && p->M > 0 && p->C > 0, DV_ERR_ARG, "dv_bn_stats: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  return p->dtype == DV_BF16 ? stats_t<bf16>(p, st) : stats_t<float>(p, st);
+}
+extern "C" int dv_bn_apply(const dv_bn_params* p, void* stream) {
+  DV_REQUIRE(p && p->x && p->y && p->gamma && p->beta && p->M > 0 && p->C > 0, DV_ERR_ARG, "dv_bn_apply: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  return p->dtype == DV_BF16 ? apply_t<bf16>(p, st) : apply_t<float>(p, st);
+}
+extern "C" int dv_bn_bwd_reduce(const dv_bn_bwd_params* p, void* stream) {
+  DV_REQUIRE(p && p->x && p->dy && p->save_mean && p->save_invstd && p->dgamma && p->dbeta && p->M > 0 && p->C > 0, DV_ERR_ARG,
+             "dv_bn_bwd_reduce: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  return p->dtype == DV_BF16 ? bwd_reduce_t<bf16>(p, st) : bwd_reduce_t<float>(p, st);
+}
+extern "C" int dv_bn_bwd_apply(const dv_bn_bwd_params* p, void* stream) {
+  DV_REQUIRE(p && p->x && p->dy && p->dx && p->gamma && p->save_mean && p->save_invstd && p->dgamma && p->dbeta && p->M > 0 && p->C > 0,
+             DV_ERR_ARG, "dv_bn_bwd_apply: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  return p->dtype == DV_BF16 ? bwd_apply_t<bf16>(p, st) : bwd_apply_t<float>(p, st);
+}
+
+extern "C" int dv_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream) {
+  DV_REQUIRE(x && y && n > 0, DV_ERR_ARG, "dv_relu_fwd: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == DV_BF16) {
+    DV_REQUIRE(n % 8 == 0, DV_ERR_UNSUPPORTED, "dv_relu_fwd: n must be a multiple of 8");
+    relu_fwd_kernel<bf16><<<stream_grid(n / 8), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, n / 8);
+  } else {
+    DV_REQUIRE(n % 4 == 0, DV_ERR_UNSUPPORTED, "dv_relu_fwd: n must be a multiple of 4");
+    relu_fwd_kernel<float><<<stream_grid(n / 4), kThreads, 0, st>>>((const float*)x, (float*)y, n / 4);
+  }
+  DV_LAUNCH_OK("relu_fwd_kernel");
+  return DV_OK;
+}
+extern "C" int dv_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream) {
+  DV_REQUIRE(y && dy && dx && n > 0, DV_ERR_ARG, "dv_relu_bwd: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == DV_BF16) {
+    DV_REQUIRE(n % 8 == 0, DV_ERR_UNSUPPORTED, "dv_relu_bwd: n must be a multiple of 8");
+    relu_bwd_kernel<bf16><<<stream_grid(n / 8), kThreads, 0, st>>>((const bf16*)y, (const bf16*)dy, (bf16*)dx, n / 8);
+  } else {
+    DV_REQUIRE(n % 4 == 0, DV_ERR_UNSUPPORTED, "dv_relu_bwd: n must be a multiple of 4");
+    relu_bwd_kernel<float><<<stream_grid(n / 4), kThreads, 0, st>>>((const float*)y, (const float*)dy, (float*)dx, n / 4);
+  }
+  DV_LAUNCH_OK("relu_bwd_kernel");
+  return DV_OK;
+}

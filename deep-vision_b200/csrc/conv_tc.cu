@@ -1,0 +1,704 @@
+// conv_tc.cu — dense convolution on the Blackwell tensor cores: NHWC implicit GEMM, bf16 operands staged into
+// 128B-swizzled shared memory by TMA (tiled 2-D maps for filters and 1x1 activations, im2col maps for 3x3 /
+// strided activations), tcgen05.mma with the fp32 accumulator in TMEM, tcgen05.ld epilogue.
+//
+//   gemm kernel (fprop, and dgrad as "fprop of dy with flipped/transposed filters"):
+//       D[128 pixels x BN channels] += A[128 px x 64 ch] (K-major) * B[BN x 64 ch] (K-major), K = taps * C/64 blocks
+//   wgrad kernel:
+//       D[128 k x BNC c] += dY[64 px x 128 k]^T (MN-major) * Xtap[64 px x BNC c] (MN-major), reduction over pixels,
+//       split across CTAs, fp32 partials to scratch, deterministic second-stage reduce.
+//
+// Warp roles per CTA (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM owner + MMA issuer (one lane),
+// warps 2..5 = epilogue (each owns the 32 TMEM lanes of its warp_id%4 quarter).  smem ring of STAGES stages,
+// full/empty mbarriers, tcgen05.commit releases a stage and finally signals the epilogue.
+#include "common.cuh"
+#include <cuda.h>  // CUtensorMap + enums only; the two encode entry points are resolved at run time (no -lcuda)
+#include <mutex>
+
+namespace dv {
+namespace {
+
+// ------------------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// Bounded wait: a protocol bug must trap, not hang the GPU (a hung box is a lost box).
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done = 0;
+  long long t0 = 0;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (done) return;
+    if ((spin & 0x3ff) == 0x3ff) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000LL) {  // ~2 s at 2 GHz
+        printf("dv conv_tc: mbarrier wait timed out (block %d,%d thread %d parity %u)\n", blockIdx.x, blockIdx.y,
+               threadIdx.x, parity);
+        __trap();
+      }
+    }
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem, const CUtensorMap* tm, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col(void* smem, const CUtensorMap* tm, uint64_t* bar, int c, int w, int h,
+                                                int n, uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(smem_u32(smem)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// all previously issued MMAs of this thread arrive on `bar` when they complete (implies fence::before_thread_sync)
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// 32 lanes x 32 consecutive fp32 columns: thread i of the warp receives row (lane base + i)
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- descriptors ---------------------------------------------------------------------------------------------
+// Shared-memory matrix descriptor (PTX ISA "tcgen05 matrix descriptor"): start>>4 [0,14), LBO>>4 [16,30),
+// SBO>>4 [32,46), version=1 [46,48), layout type [61,64) with 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// Instruction descriptor for kind::f16: D=f32 (bit 4), A=B=bf16 (bits 7,10), majors (15,16; 1 = MN-major),
+// N>>3 at [17,23), M>>4 at [24,29).
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
+constexpr int kABytes = kBlockM * kBlockK * 2;
+constexpr int kThreads = 192;
+
+// ------------------------------------------------------------------------------------------------------------
+// GEMM-shaped kernel: fprop / dgrad
+// ------------------------------------------------------------------------------------------------------------
+struct GemmArgs {
+  bf16* out;
+  int M;            // output rows (pixels enumerated n,p,q)
+  int Nout;         // output channels
+  int kb_per_tap;   // C_in / 64
+  int taps, S;
+  int a_im2col;     // 0: A is a 2-D [M][C] map, 1: im2col 4-D map
+  int P, Q, stride, pad;
+  int scatter;      // 1: row (n,p,q) is written at pixel (n, p*os, q*os) of an [*, Ho, Wo, Nout] tensor
+  int Ho, Wo, os;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads)
+conv_tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+  constexpr int kBBytes = BN * kBlockK * 2;
+  constexpr int kStageBytes = kABytes + kBBytes;
+  constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_tile = blockIdx.x, m_tile = blockIdx.y;
+  const int m0 = m_tile * kBlockM;
+  const int num_kb = g.taps * g.kb_per_tap;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int n_img = 0, h0 = 0, w0 = 0;
+      if (g.a_im2col) {
+        const int pq = g.P * g.Q;
+        n_img = m0 / pq;
+        const int rem = m0 - n_img * pq;
+        const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
+        h0 = p0 * g.stride - g.pad;
+        w0 = q0 * g.stride - g.pad;
+      }
+      int stage = 0;
+      uint32_t phase = 0;
+      int tap = 0, cb = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sA = smem + stage * kStageBytes;
+        uint8_t* sB = sA + kABytes;
+        mbar_expect_tx(&full_bar[stage], kStageBytes);
+        if (g.a_im2col) {
+          const int r = tap / g.S, s = tap - r * g.S;
+          tma_load_im2col(sA, &tmA, &full_bar[stage], cb * kBlockK, w0, h0, n_img, (uint16_t)s, (uint16_t)r);
+        } else {
+          tma_load_2d(sA, &tmA, &full_bar[stage], cb * kBlockK, m0);
+        }
+        tma_load_2d(sB, &tmB, &full_bar[stage], kb * kBlockK, n_tile * BN);
+        if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sA = smem_u32(smem + stage * kStageBytes);
+        const uint32_t sB = sA + kABytes;
+#pragma unroll
+        for (int k = 0; k < kBlockK / 16; ++k) {
+          // K-major SWIZZLE_128B: 8-row groups 1024 B apart; a 16-element K step is +32 B inside the swizzle row
+          const uint64_t ad = make_smem_desc(sA + k * 32, 16, 1024);
+          const uint64_t bd = make_smem_desc(sB + k * 32, 16, 1024);
+          umma_f16(tmem_base, ad, bd, idesc, (kb | k) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full_bar);
+    }
+    __syncwarp();
+  } else {
+    // epilogue: TMEM -> registers -> bf16 -> global
+    const int quarter = warp & 3;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int m = m0 + quarter * 32 + lane;
+    size_t row_off = 0;
+    if (m < g.M) {
+      if (g.scatter) {
+        const int pq = g.P * g.Q;
+        const int n_img = m / pq, rem = m - n_img * pq;
+        const int p = rem / g.Q, q = rem - p * g.Q;
+        row_off = (((size_t)n_img * g.Ho + (size_t)p * g.os) * g.Wo + (size_t)q * g.os) * g.Nout;
+      } else {
+        row_off = (size_t)m * g.Nout;
+      }
+    }
+    bf16* orow = g.out + row_off + (size_t)n_tile * BN;
+    const int n_left = g.Nout - n_tile * BN;  // valid columns in this tile
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
+      tmem_ld_wait();
+      if (m < g.M) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (c * 32 + j * 8 < n_left) {
+            uint32_t w[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
+              w[e] = *reinterpret_cast<uint32_t*>(&h);
+            }
+            *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// wgrad kernel
+// ------------------------------------------------------------------------------------------------------------
+struct WgradArgs {
+  float* ws;        // [splits][K][taps][C] fp32 partial sums
+  int Mpix;         // N*P*Q
+  int K, C, taps, S;
+  int P, Q, stride, pad;
+  int x_im2col;     // 0: x is a 2-D [Mpix][C] map (1x1 stride 1), 1: im2col 4-D map
+  int kb_per_split; // 64-pixel blocks per split
+  int kb_total;
+  int c_tiles;
+};
+
+template <int BNC, int STAGES>
+__global__ void __launch_bounds__(kThreads)
+conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const WgradArgs g) {
+  constexpr int kPix = 64;                       // pixels per stage (= 4 MMAs of K=16)
+  constexpr int kChunk = kPix * 128;             // one [64 px][64 ch] box = 8 KB
+  constexpr int kABytesW = 2 * kChunk;           // 128 output channels of dY
+  constexpr int kBBytesW = (BNC / 64) * kChunk;  // BNC input channels of x
+  constexpr int kStageBytes = kABytesW + kBBytesW;
+  constexpr uint32_t kTmemCols = BNC <= 32 ? 32 : BNC <= 64 ? 64 : BNC <= 128 ? 128 : 256;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // tile index: tap fastest so the CTAs that share one dY tile are neighbours in launch order (L2 reuse)
+  int t = blockIdx.x;
+  const int tap = t % g.taps; t /= g.taps;
+  const int c_tile = t % g.c_tiles;
+  const int k_tile = t / g.c_tiles;
+  const int split = blockIdx.y;
+  const int kb_begin = split * g.kb_per_split;
+  const int kb_end = min(g.kb_total, kb_begin + g.kb_per_split);
+  const int num_kb = kb_end - kb_begin;  // >= 1 by construction
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmDY);
+    prefetch_tmap(&tmX);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int r = tap / g.S, s = tap - r * g.S;
+      const int pq = g.P * g.Q;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < num_kb; ++i) {
+        const int pix0 = (kb_begin + i) * kPix;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sA = smem + stage * kStageBytes;
+        uint8_t* sB = sA + kABytesW;
+        mbar_expect_tx(&full_bar[stage], kStageBytes);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) tma_load_2d(sA + j * kChunk, &tmDY, &full_bar[stage], k_tile * 128 + j * 64, pix0);
+        if (g.x_im2col) {
+          const int n_img = pix0 / pq, rem = pix0 - n_img * pq;
+          const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
+          const int h0 = p0 * g.stride - g.pad, w0 = q0 * g.stride - g.pad;
+#pragma unroll
+          for (int j = 0; j < BNC / 64; ++j)
+            tma_load_im2col(sB + j * kChunk, &tmX, &full_bar[stage], c_tile * BNC + j * 64, w0, h0, n_img, (uint16_t)s, (uint16_t)r);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BNC / 64; ++j) tma_load_2d(sB + j * kChunk, &tmX, &full_bar[stage], c_tile * BNC + j * 64, pix0);
+        }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(128, BNC, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int i = 0; i < num_kb; ++i) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sA = smem_u32(smem + stage * kStageBytes);
+        const uint32_t sB = sA + kABytesW;
+#pragma unroll
+        for (int k = 0; k < kPix / 16; ++k) {
+          // MN-major SWIZZLE_128B: a row is one pixel (128 B = 64 channels); 8-pixel groups are 1024 B apart (SBO),
+          // 64-channel chunks are kChunk apart (LBO); a 16-pixel K step is +2048 B.
+          const uint64_t ad = make_smem_desc(sA + k * 2048, kChunk, 1024);
+          const uint64_t bd = make_smem_desc(sB + k * 2048, kChunk, 1024);
+          umma_f16(tmem_base, ad, bd, idesc, (i | k) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tmem_full_bar);
+    }
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int k = k_tile * 128 + quarter * 32 + lane;
+    float* orow = g.ws + (((size_t)split * g.K + (size_t)(k < g.K ? k : 0)) * g.taps + tap) * g.C + (size_t)c_tile * BNC;
+#pragma unroll 1
+    for (int c = 0; c < BNC / 32; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
+      tmem_ld_wait();
+      if (k < g.K) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// dw[i] = sum over splits of ws[split][i]   (fixed order => bit-reproducible)
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int64_t n4, int splits) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  float4 acc = reinterpret_cast<const float4*>(ws)[i];
+  for (int s = 1; s < splits; ++s) {
+    const float4 v = reinterpret_cast<const float4*>(ws)[(int64_t)s * n4 + i];
+    acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+  }
+  reinterpret_cast<float4*>(dw)[i] = acc;
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// host side: tensor maps
+// ------------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct DriverApi {
+  EncodeTiledFn tiled = nullptr;
+  EncodeIm2colFn im2col = nullptr;
+  int driver_version = 0;
+  bool ok = false;
+};
+
+static DriverApi& driver_api() {
+  static DriverApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f1 = nullptr;
+    void* f2 = nullptr;
+    cudaDriverEntryPointQueryResult q1, q2;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f1, cudaEnableDefault, &q1) != cudaSuccess ||
+        q1 != cudaDriverEntryPointSuccess)
+      return;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &f2, cudaEnableDefault, &q2) != cudaSuccess ||
+        q2 != cudaDriverEntryPointSuccess)
+      return;
+    api.tiled = (EncodeTiledFn)f1;
+    api.im2col = (EncodeIm2colFn)f2;
+    cudaDriverGetVersion(&api.driver_version);
+    api.ok = true;
+  });
+  return api;
+}
+
+// [rows][cols] bf16 row-major, box = box_rows x 64 columns, 128B swizzle, OOB reads give zeros
+static int make_map_2d(CUtensorMap* tm, const void* ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  DriverApi& api = driver_api();
+  DV_REQUIRE(api.ok, DV_ERR_CUDA, "conv_tc: cuTensorMapEncode* entry points not available from the driver");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {cols * 2};
+  cuuint32_t box[2] = {64, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = api.tiled(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DV_REQUIRE(r == CUDA_SUCCESS, DV_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rows=%llu cols=%llu box_rows=%u", (int)r,
+             (unsigned long long)rows, (unsigned long long)cols, box_rows);
+  return DV_OK;
+}
+
+// NHWC activation, im2col traversal of a R x S window with the given stride / padding; one load = `pixels` output
+// positions (walking q, then p, then n) x 64 channels.  Coordinates passed to the load are the input coordinate of
+// the window's top-left tap for the first output position: (c, q*stride - pad, p*stride - pad, n), offsets = (s, r).
+static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W, int C, int R, int S, int stride, int pad,
+                           uint32_t pixels) {
+  DriverApi& api = driver_api();
+  DV_REQUIRE(api.ok, DV_ERR_CUDA, "conv_tc: cuTensorMapEncode* entry points not available from the driver");
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  // bounding box of window origins: [-pad, dim - 1 + pad - (filter - 1)]  (W first, then H)
+  int lower[2] = {-pad, -pad};
+  int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = api.im2col(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, lower, upper, 64,
+                          pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DV_REQUIRE(r == CUDA_SUCCESS, DV_ERR_CUDA, "cuTensorMapEncodeIm2col failed (%d) NHWC=%d,%d,%d,%d RS=%d,%d stride=%d pad=%d",
+             (int)r, N, H, W, C, R, S, stride, pad);
+  // Drivers up to 13.1 set a descriptor bit that breaks im2col loads of tensors smaller than 128 KiB; clear it
+  // (the same correction CUTLASS applies in make_im2col_tma_copy_desc).
+  if (api.driver_version <= 13010 && (size_t)N * H * W * C * 2 < 131072) {
+    reinterpret_cast<uint64_t*>(tm)[1] &= ~(1ull << 21);
+  }
+  return DV_OK;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <int BN, int STAGES>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, cudaStream_t st) {
+  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + 1024 + 256;
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  dim3 grid((unsigned)ceil_div(g.Nout, BN), (unsigned)ceil_div(g.M, kBlockM));
+  DV_REQUIRE(grid.y <= 65535, DV_ERR_UNSUPPORTED, "conv_tc: %u M tiles exceed grid.y", grid.y);
+  conv_tc_gemm_kernel<BN, STAGES><<<grid, kThreads, smem, st>>>(tmA, tmB, g);
+  DV_LAUNCH_OK("conv_tc_gemm_kernel");
+  return DV_OK;
+}
+
+template <int BNC, int STAGES>
+static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradArgs& g, int tiles, int splits,
+                        cudaStream_t st) {
+  constexpr int smem = STAGES * (2 + BNC / 64) * 8192 + 1024 + 256;
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_wgrad_kernel<BNC, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  dim3 grid((unsigned)tiles, (unsigned)splits);
+  conv_tc_wgrad_kernel<BNC, STAGES><<<grid, kThreads, smem, st>>>(tmDY, tmX, g);
+  DV_LAUNCH_OK("conv_tc_wgrad_kernel");
+  return DV_OK;
+}
+
+struct WgradPlan {
+  int bnc, c_tiles, k_tiles, tiles, kb_total, kb_per_split, splits;
+};
+
+static WgradPlan plan_wgrad(const dv_conv_params* p) {
+  WgradPlan w;
+  const int P = (p->H + 2 * p->pad - p->R) / p->stride + 1, Q = (p->W + 2 * p->pad - p->S) / p->stride + 1;
+  const int64_t mpix = (int64_t)p->N * P * Q;
+  w.bnc = p->C >= 256 ? 256 : p->C;  // C is a multiple of 64; 64, 128, 192 or 256 per tile
+  w.c_tiles = ceil_div(p->C, w.bnc);
+  w.k_tiles = ceil_div(p->K, 128);
+  w.tiles = w.k_tiles * w.c_tiles * p->R * p->S;
+  w.kb_total = (int)ceil_div64(mpix, 64);
+  int want = ceil_div(2 * num_sms(), w.tiles);
+  int max_by_len = w.kb_total / 8 > 0 ? w.kb_total / 8 : 1;  // at least 8 stages of work per CTA
+  int splits = want < max_by_len ? want : max_by_len;
+  if (splits < 1) splits = 1;
+  w.kb_per_split = ceil_div(w.kb_total, splits);
+  w.splits = ceil_div(w.kb_total, w.kb_per_split);
+  return w;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------------------
+// dispatch
+// ------------------------------------------------------------------------------------------------------------
+bool conv_tc_supported(const dv_conv_params* p, int pass, const char** why) {
+  static const char* ok = "";
+  *why = ok;
+  if (p->dtype != DV_BF16) { *why = "tensor-core path is bf16 only"; return false; }
+  if (p->y_f32) { *why = "fp32 output is SIMT only"; return false; }
+  if (p->stride < 1 || p->stride > 8 || p->pad > 64 || p->R > 16 || p->S > 16) { *why = "stride/pad/filter out of TMA im2col range"; return false; }
+  const int P = (p->H + 2 * p->pad - p->R) / p->stride + 1, Q = (p->W + 2 * p->pad - p->S) / p->stride + 1;
+  if ((int64_t)p->N * p->H * p->W >= (1LL << 31) || (int64_t)p->N * P * Q >= (1LL << 31)) { *why = "pixel count exceeds int32"; return false; }
+  if (pass == DV_CONV_FPROP) {
+    if (p->C % 64) { *why = "C must be a multiple of 64"; return false; }
+    if (p->K % 8) { *why = "K must be a multiple of 8"; return false; }
+    return true;
+  }
+  if (pass == DV_CONV_DGRAD) {
+    if (p->K % 64) { *why = "K must be a multiple of 64"; return false; }
+    if (p->C % 8) { *why = "C must be a multiple of 8"; return false; }
+    if (p->stride == 1) {
+      if (p->R - 1 - p->pad < 0 || p->S - 1 - p->pad < 0) { *why = "pad larger than filter-1"; return false; }
+      return true;
+    }
+    if (p->R == 1 && p->S == 1 && p->pad == 0) return true;  // strided 1x1: GEMM + scatter
+    *why = "strided dgrad with R,S>1 is SIMT only";
+    return false;
+  }
+  if (pass == DV_CONV_WGRAD) {
+    if (p->C % 64 || (p->C > 256 && p->C % 256)) { *why = "C must be a multiple of 64 (of 256 above 256)"; return false; }
+    if (p->K % 8) { *why = "K must be a multiple of 8"; return false; }
+    return true;
+  }
+  *why = "bad pass";
+  return false;
+}
+
+size_t conv_tc_workspace(const dv_conv_params* p, int pass) {
+  if (pass != DV_CONV_WGRAD) return 0;
+  WgradPlan w = plan_wgrad(p);
+  return (size_t)w.splits * p->K * p->R * p->S * p->C * sizeof(float);
+}
+
+static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, cudaStream_t st) {
+  switch (bn) {
+    case 64: return launch_gemm<64, 4>(tmA, tmB, g, st);
+    case 128: return launch_gemm<128, 3>(tmA, tmB, g, st);
+    default: return launch_gemm<256, 4>(tmA, tmB, g, st);
+  }
+}
+
+int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
+  const char* why;
+  DV_REQUIRE(conv_tc_supported(p, pass, &why), DV_ERR_UNSUPPORTED, "conv_tc: %s", why);
+  DV_REQUIRE(aligned16(p->x) && aligned16(p->y) && aligned16(p->w), DV_ERR_ARG, "conv_tc: pointers must be 16-byte aligned");
+  const int P = (p->H + 2 * p->pad - p->R) / p->stride + 1, Q = (p->W + 2 * p->pad - p->S) / p->stride + 1;
+  alignas(64) CUtensorMap tmA, tmB;
+  int rc;
+
+  if (pass == DV_CONV_FPROP) {
+    GemmArgs g{};
+    g.out = (bf16*)p->y;
+    g.M = p->N * P * Q;
+    g.Nout = p->K;
+    g.kb_per_tap = p->C / 64;
+    g.taps = p->R * p->S;
+    g.S = p->S;
+    g.P = P; g.Q = Q; g.stride = p->stride; g.pad = p->pad;
+    g.a_im2col = !(p->R == 1 && p->S == 1 && p->stride == 1 && p->pad == 0);
+    const int bn = p->K <= 64 ? 64 : p->K <= 128 ? 128 : 256;
+    if (g.a_im2col) rc = make_map_im2col(&tmA, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, kBlockM);
+    else rc = make_map_2d(&tmA, p->x, (uint64_t)g.M, (uint64_t)p->C, kBlockM);
+    if (rc) return rc;
+    rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, (uint32_t)bn);
+    if (rc) return rc;
+    return gemm_dispatch(tmA, tmB, g, bn, st);
+  }
+
+  if (pass == DV_CONV_DGRAD) {
+    DV_REQUIRE(p->w_t != nullptr && aligned16(p->w_t), DV_ERR_ARG, "conv_tc dgrad: w_t (flipped [C,R,S,K] filters from dv_filter_prep) is required");
+    GemmArgs g{};
+    g.out = (bf16*)p->x;
+    g.Nout = p->C;
+    g.kb_per_tap = p->K / 64;
+    const int bn = p->C <= 64 ? 64 : p->C <= 128 ? 128 : 256;
+    if (p->stride == 1) {
+      // dx = conv(dy, w_t) with pad' = R-1-pad: an fprop whose "input" is dy [N,P,Q,K] and whose output is [N,H,W,C]
+      const int padp = p->R - 1 - p->pad;
+      g.M = p->N * p->H * p->W;
+      g.taps = p->R * p->S;
+      g.S = p->S;
+      g.P = p->H; g.Q = p->W; g.stride = 1; g.pad = padp;
+      g.a_im2col = !(p->R == 1 && p->S == 1);
+      if (g.a_im2col) rc = make_map_im2col(&tmA, p->y, p->N, P, Q, p->K, p->R, p->S, 1, padp, kBlockM);
+      else rc = make_map_2d(&tmA, p->y, (uint64_t)g.M, (uint64_t)p->K, kBlockM);
+    } else {
+      // 1x1 stride s: dx[n, p*s, q*s, :] = dy[n,p,q,:] * w ; every other pixel of dx is zero
+      DV_CUDA_OK(cudaMemsetAsync(p->x, 0, (size_t)p->N * p->H * p->W * p->C * sizeof(bf16), st));
+      g.M = p->N * P * Q;
+      g.taps = 1;
+      g.S = 1;
+      g.P = P; g.Q = Q; g.stride = 1; g.pad = 0;
+      g.a_im2col = 0;
+      g.scatter = 1; g.Ho = p->H; g.Wo = p->W; g.os = p->stride;
+      rc = make_map_2d(&tmA, p->y, (uint64_t)g.M, (uint64_t)p->K, kBlockM);
+    }
+    if (rc) return rc;
+    rc = make_map_2d(&tmB, p->w_t, (uint64_t)p->C, (uint64_t)p->R * p->S * p->K, (uint32_t)bn);
+    if (rc) return rc;
+    return gemm_dispatch(tmA, tmB, g, bn, st);
+  }
+
+  // wgrad
+  WgradPlan w = plan_wgrad(p);
+  const size_t need = (size_t)w.splits * p->K * p->R * p->S * p->C * sizeof(float);
+  DV_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= need, DV_ERR_WORKSPACE,
+             "conv_tc wgrad: workspace of %zu bytes required, %zu given", need, p->workspace_bytes);
+  DV_REQUIRE(aligned16(p->workspace), DV_ERR_ARG, "conv_tc wgrad: workspace must be 16-byte aligned");
+  WgradArgs g{};
+  g.ws = (float*)p->workspace;
+  g.Mpix = p->N * P * Q;
+  g.K = p->K; g.C = p->C; g.taps = p->R * p->S; g.S = p->S;
+  g.P = P; g.Q = Q; g.stride = p->stride; g.pad = p->pad;
+  g.x_im2col = !(p->R == 1 && p->S == 1 && p->stride == 1 && p->pad == 0);
+  g.kb_per_split = w.kb_per_split;
+  g.kb_total = w.kb_total;
+  g.c_tiles = w.c_tiles;
+  rc = make_map_2d(&tmA, p->y, (uint64_t)g.Mpix, (uint64_t)p->K, 64);
+  if (rc) return rc;
+  if (g.x_im2col) rc = make_map_im2col(&tmB, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, 64);
+  else rc = make_map_2d(&tmB, p->x, (uint64_t)g.Mpix, (uint64_t)p->C, 64);
+  if (rc) return rc;
+  switch (w.bnc) {
+    case 64: rc = launch_wgrad<64, 4>(tmA, tmB, g, w.tiles, w.splits, st); break;
+    case 128: rc = launch_wgrad<128, 3>(tmA, tmB, g, w.tiles, w.splits, st); break;
+    case 192: rc = launch_wgrad<192, 4>(tmA, tmB, g, w.tiles, w.splits, st); break;
+    default: rc = launch_wgrad<256, 4>(tmA, tmB, g, w.tiles, w.splits, st); break;
+  }
+  if (rc) return rc;
+  const int64_t n4 = (int64_t)p->K * p->R * p->S * p->C / 4;
+  wgrad_reduce_kernel<<<(unsigned)ceil_div64(n4, 256), 256, 0, st>>>(g.ws, (float*)p->w, n4, w.splits);
+  DV_LAUNCH_OK("wgrad_reduce_kernel");
+  return DV_OK;
+}
+
+}  // namespace dv

@@ -1,0 +1,323 @@
+// pool_misc.cu — the small memory-bound ops around the conv-BN-ReLU stacks: stem max-pool, tail average-pool,
+// layout change at the model entrance, casts, FC bias, filter preparation, optimisers.  All NHWC, 16-byte vectors
+// over channels where the channel count allows it.
+#include "common.cuh"
+#include <math_constants.h>
+
+namespace dv {
+namespace {
+
+constexpr int kThreads = 256;
+
+static unsigned grid_for(int64_t n) {
+  int64_t b = ceil_div64(n, kThreads);
+  const int64_t cap = (int64_t)num_sms() * 8;
+  return (unsigned)(b < cap ? (b < 1 ? 1 : b) : cap);
+}
+
+// ---- max-pool 3x3 stride 2 pad 1 (resnet50.py:34).  Padding behaves as -inf; ties keep the first position in
+//      row-major window order, as torch's kernel does (strict '>' update). ---------------------------------------
+template <typename T>
+__global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ idx, int N, int H, int W, int C,
+                                   int P, int Q) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = C / V;
+  const int64_t total = (int64_t)N * P * Q * cg;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cg) * V;
+    int64_t pix = i / cg;
+    const int q = (int)(pix % Q); pix /= Q;
+    const int p = (int)(pix % P);
+    const int n = (int)(pix / P);
+    float best[V];
+    uint8_t bi[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) { best[j] = -CUDART_INF_F; bi[j] = 0; }
+    bool first = true;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int h = p * 2 + r - 1;
+      if ((unsigned)h >= (unsigned)H) continue;
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int w = q * 2 + s - 1;
+        if ((unsigned)w >= (unsigned)W) continue;
+        float v[V];
+        Vec16<T> a; a.load(x + (((size_t)n * H + h) * W + w) * C + c); a.unpack(v);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          if (first || v[j] > best[j]) { best[j] = v[j]; bi[j] = (uint8_t)(r * 3 + s); }
+        }
+        first = false;
+      }
+    }
+    const size_t o = (size_t)(i / cg) * C + c;
+    Vec16<T> out; out.pack(best); out.store(y + o);
+#pragma unroll
+    for (int j = 0; j < V; ++j) idx[o + j] = bi[j];
+  }
+}
+
+template <typename T>
+__global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ idx, T* __restrict__ dx, int N, int H, int W,
+                                   int C, int P, int Q) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = C / V;
+  const int64_t total = (int64_t)N * H * W * cg;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cg) * V;
+    int64_t pix = i / cg;
+    const int w = (int)(pix % W); pix /= W;
+    const int h = (int)(pix % H);
+    const int n = (int)(pix / H);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    // windows (p,q) whose 3x3 footprint [2p-1, 2p+1] contains h (resp. w)
+    const int plo = h >> 1, phi = (h + 1) >> 1;
+    const int qlo = w >> 1, qhi = (w + 1) >> 1;
+    for (int p = plo; p <= phi; ++p) {
+      if (p >= P) continue;
+      const int r = h - (2 * p - 1);
+      for (int q = qlo; q <= qhi; ++q) {
+        if (q >= Q) continue;
+        const int s = w - (2 * q - 1);
+        const uint8_t tap = (uint8_t)(r * 3 + s);
+        const size_t o = (((size_t)n * P + p) * Q + q) * C + c;
+        float g[V];
+        Vec16<T> a; a.load(dy + o); a.unpack(g);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += (idx[o + j] == tap) ? g[j] : 0.f;
+      }
+    }
+    Vec16<T> out; out.pack(acc); out.store(dx + (size_t)(i / cg) * C + c);
+  }
+}
+
+// ---- global average pool (resnet50.py:43): y[n,c] = mean_hw x[n,hw,c] -----------------------------------------
+template <typename T>
+__global__ void avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int HW, int C) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = C / V;
+  const int64_t total = (int64_t)N * cg;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cg) * V;
+    const int n = (int)(i / cg);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    for (int p = 0; p < HW; ++p) {
+      float v[V];
+      Vec16<T> a; a.load(x + ((size_t)n * HW + p) * C + c); a.unpack(v);
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += v[j];
+    }
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] *= inv;
+    Vec16<T> out; out.pack(acc); out.store(y + (size_t)n * C + c);
+  }
+}
+template <typename T>
+__global__ void avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int N, int HW, int C) {
+  constexpr int V = Vec16<T>::N;
+  const int cg = C / V;
+  const int64_t total = (int64_t)N * HW * cg;
+  const float inv = 1.f / (float)HW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cg) * V;
+    const int n = (int)(i / ((int64_t)HW * cg));
+    float g[V];
+    Vec16<T> a; a.load(dy + (size_t)n * C + c); a.unpack(g);
+#pragma unroll
+    for (int j = 0; j < V; ++j) g[j] *= inv;
+    a.pack(g); a.store(dx + (size_t)(i / cg) * C + c);
+  }
+}
+
+// ---- NCHW fp32 -> NHWC T ------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ y, int N, int C, int H, int W) {
+  const int64_t total = (int64_t)N * H * W;
+  const int64_t hw = (int64_t)H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / hw, p = i % hw;
+    for (int c = 0; c < C; ++c) y[i * C + c] = from_f32<T>(x[(n * C + c) * hw + p]);
+  }
+}
+
+template <typename TS, typename TD>
+__global__ void cast_kernel(const TS* __restrict__ s, TD* __restrict__ d, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    d[i] = from_f32<TD>(to_f32(s[i]));
+}
+
+__global__ void bias_add_kernel(float* __restrict__ y, const float* __restrict__ b, int64_t total, int C) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) y[i] += b[i % C];
+}
+__global__ void bias_grad_kernel(const float* __restrict__ dy, float* __restrict__ db, int64_t M, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f;
+  for (int64_t m = 0; m < M; ++m) s += dy[m * C + c];
+  db[c] = s;
+}
+
+// ---- filters: fp32 KRSC master -> compute dtype KRSC, and [C][R][S][K] with flipped taps for dgrad -----------------
+template <typename T>
+__global__ void filter_prep_kernel(const float* __restrict__ w, T* __restrict__ wo, T* __restrict__ wt, int K, int R, int S, int C) {
+  const int64_t total = (int64_t)K * R * S * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = w[i];
+    if (wo != nullptr) wo[i] = from_f32<T>(v);
+    if (wt != nullptr) {
+      int64_t t = i;
+      const int c = (int)(t % C); t /= C;
+      const int s = (int)(t % S); t /= S;
+      const int r = (int)(t % R);
+      const int k = (int)(t / R);
+      wt[(((size_t)c * R + (R - 1 - r)) * S + (S - 1 - s)) * K + k] = from_f32<T>(v);
+    }
+  }
+}
+
+// ---- optimisers (train.py:166-205) -----------------------------------------------------------------------------------
+__global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, int64_t n, float lr, float mom,
+                           float wd, float gscale, int first) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float pv = p[i];
+    const float gv = fmaf(wd, pv, g[i] * gscale);
+    const float b = first ? gv : fmaf(mom, buf[i], gv);
+    buf[i] = b;
+    p[i] = pv - lr * b;
+  }
+}
+__global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, int64_t n, float lr,
+                               float alpha, float eps, float wd, float gscale) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float pv = p[i];
+    const float gv = fmaf(wd, pv, g[i] * gscale);
+    const float s = alpha * sq[i] + (1.f - alpha) * gv * gv;
+    sq[i] = s;
+    p[i] = pv - lr * gv / (sqrtf(s) + eps);
+  }
+}
+
+}  // namespace
+}  // namespace dv
+
+using namespace dv;
+
+#define DV_DISPATCH_T(dtype, CALL_BF, CALL_F32) \
+  do {                                           \
+    if ((dtype) == DV_BF16) { CALL_BF; } else { CALL_F32; } \
+  } while (0)
+
+static int vec_ok(int C, int dtype, const char* who) {
+  const int V = dtype == DV_BF16 ? 8 : 4;
+  DV_REQUIRE(C % V == 0, DV_ERR_UNSUPPORTED, "%s: C=%d must be a multiple of %d", who, C, V);
+  return DV_OK;
+}
+
+extern "C" int dv_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H, int W, int C, int dtype, void* stream) {
+  DV_REQUIRE(x && y && idx && N > 0 && H > 0 && W > 0 && C > 0, DV_ERR_ARG, "dv_maxpool_fwd: bad arguments");
+  int rc = vec_ok(C, dtype, "dv_maxpool_fwd");
+  if (rc) return rc;
+  const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
+  const int64_t total = (int64_t)N * P * Q * (C / (dtype == DV_BF16 ? 8 : 4));
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (maxpool_fwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, idx, N, H, W, C, P, Q)),
+                (maxpool_fwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)x, (float*)y, idx, N, H, W, C, P, Q)));
+  DV_LAUNCH_OK("maxpool_fwd_kernel");
+  return DV_OK;
+}
+extern "C" int dv_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int N, int H, int W, int C, int dtype, void* stream) {
+  DV_REQUIRE(dy && dx && idx && N > 0 && H > 0 && W > 0 && C > 0, DV_ERR_ARG, "dv_maxpool_bwd: bad arguments");
+  int rc = vec_ok(C, dtype, "dv_maxpool_bwd");
+  if (rc) return rc;
+  const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
+  const int64_t total = (int64_t)N * H * W * (C / (dtype == DV_BF16 ? 8 : 4));
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (maxpool_bwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)dy, idx, (bf16*)dx, N, H, W, C, P, Q)),
+                (maxpool_bwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)dy, idx, (float*)dx, N, H, W, C, P, Q)));
+  DV_LAUNCH_OK("maxpool_bwd_kernel");
+  return DV_OK;
+}
+extern "C" int dv_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int dtype, void* stream) {
+  DV_REQUIRE(x && y && N > 0 && HW > 0 && C > 0, DV_ERR_ARG, "dv_avgpool_fwd: bad arguments");
+  int rc = vec_ok(C, dtype, "dv_avgpool_fwd");
+  if (rc) return rc;
+  const int64_t total = (int64_t)N * (C / (dtype == DV_BF16 ? 8 : 4));
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (avgpool_fwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, N, HW, C)),
+                (avgpool_fwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)x, (float*)y, N, HW, C)));
+  DV_LAUNCH_OK("avgpool_fwd_kernel");
+  return DV_OK;
+}
+extern "C" int dv_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, int dtype, void* stream) {
+  DV_REQUIRE(dy && dx && N > 0 && HW > 0 && C > 0, DV_ERR_ARG, "dv_avgpool_bwd: bad arguments");
+  int rc = vec_ok(C, dtype, "dv_avgpool_bwd");
+  if (rc) return rc;
+  const int64_t total = (int64_t)N * HW * (C / (dtype == DV_BF16 ? 8 : 4));
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (avgpool_bwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)dy, (bf16*)dx, N, HW, C)),
+                (avgpool_bwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)dy, (float*)dx, N, HW, C)));
+  DV_LAUNCH_OK("avgpool_bwd_kernel");
+  return DV_OK;
+}
+extern "C" int dv_nchw_to_nhwc(const float* x, void* y, int N, int C, int H, int W, int dtype, void* stream) {
+  DV_REQUIRE(x && y && N > 0 && H > 0 && W > 0 && C > 0, DV_ERR_ARG, "dv_nchw_to_nhwc: bad arguments");
+  const int64_t total = (int64_t)N * H * W;
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (nchw_to_nhwc_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>(x, (bf16*)y, N, C, H, W)),
+                (nchw_to_nhwc_kernel<float><<<grid_for(total), kThreads, 0, st>>>(x, (float*)y, N, C, H, W)));
+  DV_LAUNCH_OK("nchw_to_nhwc_kernel");
+  return DV_OK;
+}
+extern "C" int dv_cast(const void* src, int sd, void* dst, int dd, int64_t n, void* stream) {
+  DV_REQUIRE(src && dst && n > 0, DV_ERR_ARG, "dv_cast: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned g = grid_for(n);
+  if (sd == DV_F32 && dd == DV_BF16) cast_kernel<float, bf16><<<g, kThreads, 0, st>>>((const float*)src, (bf16*)dst, n);
+  else if (sd == DV_BF16 && dd == DV_F32) cast_kernel<bf16, float><<<g, kThreads, 0, st>>>((const bf16*)src, (float*)dst, n);
+  else if (sd == DV_F32 && dd == DV_F32) cast_kernel<float, float><<<g, kThreads, 0, st>>>((const float*)src, (float*)dst, n);
+  else if (sd == DV_BF16 && dd == DV_BF16) cast_kernel<bf16, bf16><<<g, kThreads, 0, st>>>((const bf16*)src, (bf16*)dst, n);
+  else { set_error("dv_cast: bad dtypes %d -> %d", sd, dd); return DV_ERR_ARG; }
+  DV_LAUNCH_OK("cast_kernel");
+  return DV_OK;
+}
+extern "C" int dv_bias_add(float* y, const float* bias, int64_t M, int C, void* stream) {
+  DV_REQUIRE(y && bias && M > 0 && C > 0, DV_ERR_ARG, "dv_bias_add: bad arguments");
+  bias_add_kernel<<<grid_for(M * C), kThreads, 0, (cudaStream_t)stream>>>(y, bias, M * C, C);
+  DV_LAUNCH_OK("bias_add_kernel");
+  return DV_OK;
+}
+extern "C" int dv_bias_grad(const float* dy, float* dbias, int64_t M, int C, void* stream) {
+  DV_REQUIRE(dy && dbias && M > 0 && C > 0, DV_ERR_ARG, "dv_bias_grad: bad arguments");
+  bias_grad_kernel<<<ceil_div(C, 128), 128, 0, (cudaStream_t)stream>>>(dy, dbias, M, C);
+  DV_LAUNCH_OK("bias_grad_kernel");
+  return DV_OK;
+}
+extern "C" int dv_filter_prep(const float* w, void* wo, void* wt, int K, int R, int S, int C, int dtype, void* stream) {
+  DV_REQUIRE(w && (wo || wt) && K > 0 && R > 0 && S > 0 && C > 0, DV_ERR_ARG, "dv_filter_prep: bad arguments");
+  const int64_t total = (int64_t)K * R * S * C;
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (filter_prep_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>(w, (bf16*)wo, (bf16*)wt, K, R, S, C)),
+                (filter_prep_kernel<float><<<grid_for(total), kThreads, 0, st>>>(w, (float*)wo, (float*)wt, K, R, S, C)));
+  DV_LAUNCH_OK("filter_prep_kernel");
+  return DV_OK;
+}
+extern "C" int dv_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float wd, float gscale, int first,
+                           void* stream) {
+  DV_REQUIRE(p && g && buf && n > 0, DV_ERR_ARG, "dv_sgd_step: bad arguments");
+  sgd_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, buf, n, lr, momentum, wd, gscale, first);
+  DV_LAUNCH_OK("sgd_kernel");
+  return DV_OK;
+}
+extern "C" int dv_rmsprop_step(float* p, const float* g, float* sq, int64_t n, float lr, float alpha, float eps, float wd, float gscale,
+                               void* stream) {
+  DV_REQUIRE(p && g && sq && n > 0, DV_ERR_ARG, "dv_rmsprop_step: bad arguments");
+  rmsprop_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, sq, n, lr, alpha, eps, wd, gscale);
+  DV_LAUNCH_OK("rmsprop_kernel");
+  return DV_OK;
+}

@@ -1,0 +1,466 @@
+"""torch.autograd.Functions over the C ABI (include/dv.h): the replacement for the torch.nn primitives on the
+reference's conv-BN-ReLU hot path (ResNet/pytorch/models/*.py, MobileNet/pytorch/models/mobilenet_v1.py).
+
+Tensors are ordinary torch CUDA tensors with logical shape [N,C,H,W] and ``torch.channels_last`` strides, i.e. NHWC in
+memory; torch only owns the memory and the autograd graph, every byte of arithmetic is done by libdv_b200.so on the
+current CUDA stream.  Nothing here falls back to torch ops or to the CPU.
+"""
+import ctypes as C
+
+import torch
+
+from . import config
+from .lib import (DV_ALGO_AUTO, DV_ALGO_SIMT, DV_ALGO_TC, DV_BF16, DV_CONV_DGRAD, DV_CONV_FPROP, DV_CONV_WGRAD, DV_F32,
+                  BnBwdParams, BnParams, ConvParams, DwConvParams, check, lib)
+
+_CL = torch.channels_last
+
+
+def _dv_dtype(t):
+    if t == torch.float32:
+        return DV_F32
+    if t == torch.bfloat16:
+        return DV_BF16
+    raise TypeError(f"deep_vision_b200 computes in float32 or bfloat16, got {t}")
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _require_cuda(t, what):
+    if not t.is_cuda:
+        raise RuntimeError(f"{what}: deep_vision_b200 runs on CUDA (sm_100a) tensors only; got a {t.device} tensor. "
+                           "There is no CPU path.")
+
+
+def _nhwc(t):
+    """channels_last-contiguous view/copy of a 4-D tensor (a copy only when the layout is wrong)."""
+    return t if t.is_contiguous(memory_format=_CL) else t.contiguous(memory_format=_CL)
+
+
+_workspaces = {}
+
+
+def _workspace(nbytes, device):
+    """Scratch buffer per (device, stream); grown geometrically, never shrunk.  Kernels that share it are ordered by
+    the stream they run on."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    buf = _workspaces.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = buf
+    return buf
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# layout change at the model entrance
+# ----------------------------------------------------------------------------------------------------------------
+class _ToNHWC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, dtype):
+        ctx.in_dtype = x.dtype
+        N, Cc, H, W = x.shape
+        if x.dtype == torch.float32 and x.is_contiguous():
+            y = torch.empty((N, Cc, H, W), dtype=dtype, device=x.device, memory_format=_CL)
+            check(lib.dv_nchw_to_nhwc(x.data_ptr(), y.data_ptr(), N, Cc, H, W, _dv_dtype(dtype), _stream()), "dv_nchw_to_nhwc")
+            return y
+        if x.dtype == dtype:
+            return x.contiguous(memory_format=_CL)
+        # rare entrance (e.g. a half-precision or already channels_last image batch): cast, then lay out
+        xc = x.contiguous(memory_format=_CL)
+        y = torch.empty_like(xc, dtype=dtype)
+        check(lib.dv_cast(xc.data_ptr(), _dv_dtype(xc.dtype), y.data_ptr(), _dv_dtype(dtype), xc.numel(), _stream()), "dv_cast")
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        if dy.dtype == ctx.in_dtype:
+            return dy, None
+        dyc = dy.contiguous(memory_format=_CL)
+        out = torch.empty_like(dyc, dtype=ctx.in_dtype)
+        check(lib.dv_cast(dyc.data_ptr(), _dv_dtype(dyc.dtype), out.data_ptr(), _dv_dtype(ctx.in_dtype), dyc.numel(), _stream()), "dv_cast")
+        return out, None
+
+
+def to_compute_layout(x, dtype=None):
+    """NCHW fp32 batch (what train.py:444-449 feeds the model) -> NHWC compute dtype."""
+    dtype = dtype or config.compute_dtype()
+    _require_cuda(x, "input")
+    if x.dtype == dtype and x.is_contiguous(memory_format=_CL):
+        return x
+    return _ToNHWC.apply(x, dtype)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# dense convolution
+# ----------------------------------------------------------------------------------------------------------------
+class FilterCache:
+    """Compute-dtype copies of one fp32 filter tensor, rebuilt when the parameter's version counter moves
+    (optimizer step, load_state_dict, init)."""
+
+    def __init__(self):
+        self.key = None
+        self.w = None
+        self.w_t = None
+
+    def get(self, weight, dtype, need_t):
+        K, Cc, R, S = weight.shape
+        key = (weight.data_ptr(), weight._version, config.weight_epoch(), dtype, weight.device)
+        if key != self.key or (need_t and self.w_t is None):
+            wm = weight.detach()
+            if not wm.is_contiguous(memory_format=_CL):
+                wm = wm.contiguous(memory_format=_CL)
+            if dtype == torch.float32:
+                self.w, self.w_t = wm, None
+            else:
+                self.w = torch.empty((K, Cc, R, S), dtype=dtype, device=weight.device, memory_format=_CL)
+                self.w_t = torch.empty((Cc, K, R, S), dtype=dtype, device=weight.device, memory_format=_CL) if need_t else None
+                check(lib.dv_filter_prep(wm.data_ptr(), self.w.data_ptr(), self.w_t.data_ptr() if need_t else None,
+                                         K, R, S, Cc, _dv_dtype(dtype), _stream()), "dv_filter_prep")
+            self.key = key
+        return self.w, self.w_t
+
+
+def _conv_params(x_ptr, w_ptr, y_ptr, wt_ptr, N, H, W, Cc, K, R, S, stride, pad, dtype, algo, y_f32=0):
+    p = ConvParams()
+    p.x, p.w, p.y, p.w_t = x_ptr, w_ptr, y_ptr, wt_ptr
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad = N, H, W, Cc, K, R, S, stride, pad
+    p.dtype, p.algo, p.y_f32 = dtype, algo, y_f32
+    return p
+
+
+def _run_conv(fn, p, pass_id, device, what):
+    need = lib.dv_conv_workspace_bytes(C.byref(p), pass_id)
+    if need:
+        ws = _workspace(need, device)
+        p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+    check(fn(C.byref(p), _stream()), what)
+
+
+class _Conv2d(torch.autograd.Function):
+    """y = conv2d(x, weight) without bias — nn.Conv2d at resnet50.py:20-28,101-143; resnet34.py:20-28,96-126;
+    mobilenet_v1.py:30,139-145.  Backward = dgrad + wgrad (autograd of train.py:460)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, stride, pad, cache, algo):
+        _require_cuda(x, "conv2d")
+        x = _nhwc(x)
+        N, Cc, H, W = x.shape
+        K, Cw, R, S = weight.shape
+        if Cw != Cc:
+            raise RuntimeError(f"conv2d: input has {Cc} channels, weight expects {Cw}")
+        P = (H + 2 * pad - R) // stride + 1
+        Q = (W + 2 * pad - S) // stride + 1
+        dt = _dv_dtype(x.dtype)
+        need_t = x.dtype != torch.float32 and ctx.needs_input_grad[0]
+        w_c, w_t = cache.get(weight, x.dtype, need_t)
+        y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
+        _run_conv(lib.dv_conv_fprop, p, DV_CONV_FPROP, x.device, "dv_conv_fprop")
+        ctx.save_for_backward(x, weight)
+        ctx.w_c, ctx.w_t = w_c, w_t
+        ctx.geom = (stride, pad, algo)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        stride, pad, algo = ctx.geom
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        N, Cc, H, W = x.shape
+        K, _, R, S = weight.shape
+        dt = _dv_dtype(x.dtype)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x, memory_format=_CL)
+            p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dy.data_ptr(), ctx.w_t.data_ptr() if ctx.w_t is not None else None,
+                             N, H, W, Cc, K, R, S, stride, pad, dt, algo)
+            _run_conv(lib.dv_conv_dgrad, p, DV_CONV_DGRAD, x.device, "dv_conv_dgrad")
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
+            p = _conv_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
+            _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad")
+        return dx, dw, None, None, None, None
+
+
+def conv2d(x, weight, stride=1, padding=0, cache=None, algo=DV_ALGO_AUTO):
+    return _Conv2d.apply(x, weight, int(stride), int(padding), cache or FilterCache(), algo)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# depth-wise 3x3 convolution
+# ----------------------------------------------------------------------------------------------------------------
+def _dw_params(x_ptr, w_ptr, y_ptr, N, H, W, Cc, stride, dtype):
+    p = DwConvParams()
+    p.x, p.w, p.y = x_ptr, w_ptr, y_ptr
+    p.N, p.H, p.W, p.C, p.stride, p.dtype = N, H, W, Cc, stride, dtype
+    return p
+
+
+class _DwConv3x3(torch.autograd.Function):
+    """nn.Conv2d(C, C, 3, padding=1, stride, groups=C, bias=False) — mobilenet_v1.py:112-122."""
+
+    @staticmethod
+    def forward(ctx, x, weight, stride):
+        _require_cuda(x, "dwconv3x3")
+        x = _nhwc(x)
+        N, Cc, H, W = x.shape
+        P = (H - 1) // stride + 1
+        Q = (W - 1) // stride + 1
+        w = weight.detach().contiguous()  # [C,1,3,3] fp32 == [C][3][3]
+        y = torch.empty((N, Cc, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        p = _dw_params(x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cc, stride, _dv_dtype(x.dtype))
+        check(lib.dv_dwconv_fprop(C.byref(p), _stream()), "dv_dwconv_fprop")
+        ctx.save_for_backward(x, weight)
+        ctx.stride = stride
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        stride = ctx.stride
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        N, Cc, H, W = x.shape
+        dt = _dv_dtype(x.dtype)
+        dx = dw = None
+        w = weight.detach().contiguous()
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x, memory_format=_CL)
+            p = _dw_params(dx.data_ptr(), w.data_ptr(), dy.data_ptr(), N, H, W, Cc, stride, dt)
+            check(lib.dv_dwconv_dgrad(C.byref(p), _stream()), "dv_dwconv_dgrad")
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty_like(w)
+            p = _dw_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), N, H, W, Cc, stride, dt)
+            need = lib.dv_dwconv_workspace_bytes(C.byref(p))
+            ws = _workspace(need, x.device)
+            p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+            check(lib.dv_dwconv_wgrad(C.byref(p), _stream()), "dv_dwconv_wgrad")
+        return dx, dw, None
+
+
+def dwconv3x3(x, weight, stride=1):
+    return _DwConv3x3.apply(x, weight, int(stride))
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# batch norm (+ residual) (+ ReLU)
+# ----------------------------------------------------------------------------------------------------------------
+class _BatchNormAct(torch.autograd.Function):
+    """y = relu(bn(x) [+ residual]) — nn.BatchNorm2d + nn.ReLU(inplace=True) (+ `x + identity`) at
+    resnet50.py:152-164, resnet34.py:135-142, mobilenet_v1.py:129-133,152-156."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
+        _require_cuda(x, "batch_norm")
+        x = _nhwc(x)
+        N, Cc, H, W = x.shape
+        M = N * H * W
+        if residual is not None:
+            residual = _nhwc(residual)
+            if residual.shape != x.shape or residual.dtype != x.dtype:
+                raise RuntimeError("batch_norm: residual must match the input's shape and dtype")
+        y = torch.empty_like(x, memory_format=_CL)
+        p = BnParams()
+        p.x, p.y = x.data_ptr(), y.data_ptr()
+        p.residual = residual.data_ptr() if residual is not None else None
+        p.gamma, p.beta = gamma.data_ptr(), beta.data_ptr()
+        p.running_mean = running_mean.data_ptr() if running_mean is not None else None
+        p.running_var = running_var.data_ptr() if running_var is not None else None
+        p.M, p.C, p.dtype, p.relu = M, Cc, _dv_dtype(x.dtype), int(relu)
+        p.eps, p.momentum = eps, momentum
+        use_batch_stats = training or running_mean is None
+        if use_batch_stats:
+            save_mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            save_invstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            p.save_mean, p.save_invstd = save_mean.data_ptr(), save_invstd.data_ptr()
+            if not training:  # eval without running stats: normalise with batch stats, update nothing
+                p.running_mean = p.running_var = None
+            ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
+            p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+            check(lib.dv_bn_stats(C.byref(p), _stream()), "dv_bn_stats")
+            p.eval_mode = 0
+        else:
+            save_mean = save_invstd = None
+            p.eval_mode = 1
+        check(lib.dv_bn_apply(C.byref(p), _stream()), "dv_bn_apply")
+        ctx.batch_stats = use_batch_stats
+        ctx.relu = bool(relu)
+        ctx.has_res = residual is not None
+        if use_batch_stats:
+            ctx.save_for_backward(x, y if relu else None, gamma, save_mean, save_invstd)
+        else:
+            ctx.save_for_backward(x, y if relu else None, gamma, running_mean, running_var)
+            ctx.eps = eps
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, gamma, mean, second = ctx.saved_tensors
+        if not ctx.batch_stats:
+            raise NotImplementedError("deep_vision_b200: backward through eval-mode BatchNorm2d is not on the hot path")
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        N, Cc, H, W = x.shape
+        M = N * H * W
+        dx = torch.empty_like(x, memory_format=_CL)
+        dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        p = BnBwdParams()
+        p.x, p.y, p.dy, p.dx = x.data_ptr(), (y.data_ptr() if y is not None else None), dy.data_ptr(), dx.data_ptr()
+        p.dres = dres.data_ptr() if dres is not None else None
+        p.gamma, p.save_mean, p.save_invstd = gamma.data_ptr(), mean.data_ptr(), second.data_ptr()
+        p.dgamma, p.dbeta = dgamma.data_ptr(), dbeta.data_ptr()
+        p.M, p.C, p.dtype, p.relu = M, Cc, _dv_dtype(x.dtype), int(ctx.relu)
+        ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
+        p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+        check(lib.dv_bn_bwd_reduce(C.byref(p), _stream()), "dv_bn_bwd_reduce")
+        check(lib.dv_bn_bwd_apply(C.byref(p), _stream()), "dv_bn_bwd_apply")
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+
+
+def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
+    return _BatchNormAct.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum), float(eps), bool(relu))
+
+
+class _ReLU(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _require_cuda(x, "relu")
+        xc = x if (x.is_contiguous() or x.is_contiguous(memory_format=_CL)) else x.contiguous()
+        y = torch.empty_like(xc)
+        check(lib.dv_relu_fwd(xc.data_ptr(), y.data_ptr(), xc.numel(), _dv_dtype(xc.dtype), _stream()), "dv_relu_fwd")
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if dy.stride() != y.stride():
+            dy = dy.contiguous(memory_format=_CL) if y.is_contiguous(memory_format=_CL) and y.dim() == 4 else dy.contiguous()
+        dx = torch.empty_like(y)
+        check(lib.dv_relu_bwd(y.data_ptr(), dy.data_ptr(), dx.data_ptr(), y.numel(), _dv_dtype(y.dtype), _stream()), "dv_relu_bwd")
+        return dx
+
+
+def relu(x):
+    return _ReLU.apply(x)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# stem / tail
+# ----------------------------------------------------------------------------------------------------------------
+class _MaxPool3x3s2(torch.autograd.Function):
+    """nn.MaxPool2d(kernel_size=3, stride=2, padding=1) — resnet50.py:34."""
+
+    @staticmethod
+    def forward(ctx, x):
+        _require_cuda(x, "max_pool")
+        x = _nhwc(x)
+        N, Cc, H, W = x.shape
+        P, Q = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        y = torch.empty((N, Cc, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        idx = torch.empty((N, Cc, P, Q), dtype=torch.uint8, device=x.device, memory_format=_CL)
+        check(lib.dv_maxpool_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, Cc, _dv_dtype(x.dtype), _stream()), "dv_maxpool_fwd")
+        ctx.save_for_backward(idx)
+        ctx.in_shape = (N, Cc, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        N, Cc, H, W = ctx.in_shape
+        dy = _nhwc(dy)
+        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device, memory_format=_CL)
+        check(lib.dv_maxpool_bwd(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, Cc, _dv_dtype(dy.dtype), _stream()), "dv_maxpool_bwd")
+        return dx
+
+
+def max_pool3x3s2(x):
+    return _MaxPool3x3s2.apply(x)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    """nn.AdaptiveAvgPool2d((1, 1)) — resnet50.py:43, mobilenet_v1.py:84."""
+
+    @staticmethod
+    def forward(ctx, x):
+        _require_cuda(x, "avg_pool")
+        x = _nhwc(x)
+        N, Cc, H, W = x.shape
+        y = torch.empty((N, Cc, 1, 1), dtype=x.dtype, device=x.device, memory_format=_CL)
+        check(lib.dv_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, H * W, Cc, _dv_dtype(x.dtype), _stream()), "dv_avgpool_fwd")
+        ctx.in_shape = (N, Cc, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, Cc, H, W = ctx.in_shape
+        dy = dy.reshape(N, Cc).contiguous()
+        dx = torch.empty((N, Cc, H, W), dtype=dy.dtype, device=dy.device, memory_format=_CL)
+        check(lib.dv_avgpool_bwd(dy.data_ptr(), dx.data_ptr(), N, H * W, Cc, _dv_dtype(dy.dtype), _stream()), "dv_avgpool_bwd")
+        return dx
+
+
+def global_avg_pool(x):
+    return _GlobalAvgPool.apply(x)
+
+
+class _Linear(torch.autograd.Function):
+    """y = x W^T + b with fp32 logits — nn.Linear at resnet50.py:44,61; mobilenet_v1.py:87,92.
+    Runs as a 1x1 convolution on [B,1,1,F] (dv_conv_*), bias through dv_bias_add / dv_bias_grad."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, cache):
+        _require_cuda(x, "linear")
+        x = x.contiguous()
+        B, F = x.shape
+        K = weight.shape[0]
+        w_c, _ = cache.get(weight.view(K, F, 1, 1), x.dtype, False)
+        y = torch.empty((B, K), dtype=torch.float32, device=x.device)
+        p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, _dv_dtype(x.dtype), DV_ALGO_SIMT,
+                         y_f32=1)
+        check(lib.dv_conv_fprop(C.byref(p), _stream()), "dv_conv_fprop(linear)")
+        if bias is not None:
+            check(lib.dv_bias_add(y.data_ptr(), bias.data_ptr(), B, K, _stream()), "dv_bias_add")
+        ctx.save_for_backward(x, weight)
+        ctx.w_c = w_c
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        B, F = x.shape
+        K = weight.shape[0]
+        dy = dy.contiguous()
+        dt = _dv_dtype(x.dtype)
+        if dy.dtype != x.dtype:
+            dyc = torch.empty_like(dy, dtype=x.dtype)
+            check(lib.dv_cast(dy.data_ptr(), _dv_dtype(dy.dtype), dyc.data_ptr(), dt, dy.numel(), _stream()), "dv_cast")
+        else:
+            dyc = dy
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dyc.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, dt, DV_ALGO_SIMT)
+            check(lib.dv_conv_dgrad(C.byref(p), _stream()), "dv_conv_dgrad(linear)")
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty((K, F), dtype=torch.float32, device=x.device)
+            p = _conv_params(x.data_ptr(), dw.data_ptr(), dyc.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, dt, DV_ALGO_SIMT)
+            check(lib.dv_conv_wgrad(C.byref(p), _stream()), "dv_conv_wgrad(linear)")
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            dyf = dy if dy.dtype == torch.float32 else dy.float()
+            db = torch.empty(K, dtype=torch.float32, device=x.device)
+            check(lib.dv_bias_grad(dyf.data_ptr(), db.data_ptr(), B, K, _stream()), "dv_bias_grad")
+        return dx, dw, db, None
+
+
+def linear(x, weight, bias=None, cache=None):
+    return _Linear.apply(x, weight, bias, cache or FilterCache())

@@ -1,0 +1,183 @@
+"""Per-rank training step: the B200 restatement of `train()` in ResNet/pytorch/train.py:431-485 and of what
+`nn.DataParallel` (train.py:353-355) does around it.
+
+Reference step:   output = net(image); loss = CrossEntropyLoss()(output, label); optimizer.zero_grad();
+                  loss.backward(); optimizer.step(); loss.item()
+with SGD(lr .1, momentum .9, weight_decay 1e-4) for the ResNets (train.py:166-184) and RMSprop(lr .045, alpha .9,
+eps 1.0) for MobileNet (train.py:185-214); weight decay applies to every parameter (single param group, :363).
+
+Here: one process per GPU.  All parameters live in ONE flat fp32 buffer and all gradients in another, so that
+  * the optimiser is a single fused kernel (dv_sgd_step / dv_rmsprop_step) over the flat buffer,
+  * gradient exchange is an NCCL all-reduce (sum, then 1/world folded into the optimiser) over contiguous BUCKETS of
+    the flat gradient buffer, launched from autograd hooks as soon as the last gradient of a bucket is produced, so
+    the transfer over NVLink overlaps the rest of backward,
+  * BN statistics stay local to the rank (the reference's DataParallel replicas never synchronise BN either),
+  * no per-step parameter broadcast is needed: replicas start identical and apply identical updates.
+The mean cross-entropy over the rank's shard followed by gradient averaging equals DataParallel's mean loss over the
+gathered global batch (train.py:452).  The whole step can be captured in a CUDA graph (static shapes).
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+from . import config
+from .lib import check, lib
+
+# train.py:166-214 — the reference's optimiser settings per model
+TRAINING_CONFIG = {
+    "resnet34": dict(optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4, batch_size=256),
+    "resnet50": dict(optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4, batch_size=256),
+    "resnet152": dict(optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4, batch_size=128),  # no entry in the reference
+    "mobilenet1": dict(optimizer="rmsprop", lr=0.045, alpha=0.9, eps=1.0, weight_decay=0.0, batch_size=128),
+}
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Trainer:
+    def __init__(self, model, optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4, alpha=0.9, eps=1.0,
+                 bucket_bytes=25 << 20, process_group=None, use_cuda_graph=False, **_ignored):
+        self.model = model
+        self.kind = optimizer
+        self.lr, self.momentum, self.weight_decay, self.alpha, self.eps = lr, momentum, weight_decay, alpha, eps
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.use_graph = use_cuda_graph
+        self.steps_done = 0
+        self._graph = None
+        self._flatten(bucket_bytes)
+
+    # ---- flat parameter / gradient storage --------------------------------------------------------------------
+    def _flatten(self, bucket_bytes):
+        params = [p for p in self.model.parameters() if p.requires_grad]
+        dev = params[0].device
+        if dev.type != "cuda":
+            raise RuntimeError("Trainer: move the model to a CUDA device first; there is no CPU path")
+        total = sum(p.numel() for p in params)
+        self.flat_p = torch.empty(total, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_s = torch.zeros(total, dtype=torch.float32, device=dev)  # momentum buffer / squared-grad average
+        self.params, self.offsets = params, []
+        off = 0
+        for p in params:
+            n = p.numel()
+            if p.dim() == 4:  # filters live as KRSC (channels_last) so the kernels read them in place
+                K, Cc, R, S = p.shape
+                pv = self.flat_p[off:off + n].view(K, R, S, Cc).permute(0, 3, 1, 2)
+                gv = self.flat_g[off:off + n].view(K, R, S, Cc).permute(0, 3, 1, 2)
+            else:
+                pv = self.flat_p[off:off + n].view(p.shape)
+                gv = self.flat_g[off:off + n].view(p.shape)
+            pv.copy_(p.data)
+            p.data = pv
+            p.grad = gv
+            self.offsets.append(off)
+            off += n
+        config.bump_weight_epoch()
+        # buckets: contiguous ranges of the flat gradient, cut from the END (gradients of the last layers arrive first)
+        cap = max(1, bucket_bytes // 4)
+        self.buckets = []  # (start, end)
+        end = total
+        i = len(params) - 1
+        while i >= 0:
+            start = end
+            while i >= 0 and (end - start) < cap:
+                start = self.offsets[i]
+                i -= 1
+            self.buckets.append((start, end))
+            end = start
+        self._bucket_of = {}
+        self._bucket_need = []
+        for b, (s, e) in enumerate(self.buckets):
+            members = [j for j, o in enumerate(self.offsets) if s <= o < e]
+            self._bucket_need.append(len(members))
+            for j in members:
+                self._bucket_of[j] = b
+        self._pending = list(self._bucket_need)
+        self._works = []
+        if self.world > 1:
+            for j, p in enumerate(params):
+                p.register_post_accumulate_grad_hook(self._make_hook(j))
+
+    def _make_hook(self, j):
+        def hook(_param):
+            b = self._bucket_of[j]
+            self._pending[b] -= 1
+            if self._pending[b] == 0:
+                s, e = self.buckets[b]
+                self._works.append(dist.all_reduce(self.flat_g[s:e], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+        return hook
+
+    # ---- one step -------------------------------------------------------------------------------------------------
+    def _step_body(self, images, labels):
+        self.flat_g.zero_()
+        self._pending = list(self._bucket_need)
+        self._works = []
+        logits = self.model(images)
+        loss = F.cross_entropy(logits, labels)
+        loss.backward()
+        for w in self._works:
+            w.wait()
+        self._optimizer_step()
+        return loss.detach()
+
+    def _optimizer_step(self):
+        n = self.flat_p.numel()
+        scale = 1.0 / self.world
+        if self.kind == "sgd":
+            first = 1 if self.steps_done == 0 and self._graph is None and not self._capturing else 0
+            check(lib.dv_sgd_step(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(), n, self.lr, self.momentum,
+                                  self.weight_decay, scale, first, _stream()), "dv_sgd_step")
+        elif self.kind == "rmsprop":
+            check(lib.dv_rmsprop_step(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(), n, self.lr, self.alpha,
+                                      self.eps, self.weight_decay, scale, _stream()), "dv_rmsprop_step")
+        else:
+            raise ValueError(f"unknown optimizer {self.kind}")
+        config.bump_weight_epoch()
+
+    _capturing = False
+
+    def step(self, images, labels):
+        """images: [B,3,H,W] fp32 CUDA (NCHW, as the reference's loader yields), labels: [B] int64 CUDA.
+        Returns the loss as a 0-d CUDA tensor (no host sync; call .item() to reproduce train.py:470)."""
+        self.model.train()
+        if not self.use_graph:
+            loss = self._step_body(images, labels)
+            self.steps_done += 1
+            return loss
+        if self._graph is None:
+            self._capture(images, labels)
+        self._static_images.copy_(images, non_blocking=True)
+        self._static_labels.copy_(labels, non_blocking=True)
+        self._graph.replay()
+        self.steps_done += 1
+        return self._static_loss
+
+    def _capture(self, images, labels):
+        """Warm up eagerly on a side stream (allocator, filter caches, NCCL), then record fwd+bwd+exchange+optimiser
+        into one CUDA graph.  The momentum buffer's first-step special case (buf = g) is met by the eager warm-up
+        steps, which are real training steps."""
+        self._static_images = images.clone()
+        self._static_labels = labels.clone()
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(2):
+                self._step_body(self._static_images, self._static_labels)
+                self.steps_done += 1
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self._graph = torch.cuda.CUDAGraph()
+        self._capturing = True
+        try:
+            with torch.cuda.graph(self._graph):
+                self._static_loss = self._step_body(self._static_images, self._static_labels)
+        finally:
+            self._capturing = False
+
+    def state_dict(self):
+        return {"optimizer": self.kind, "steps": self.steps_done, "state": self.flat_s.clone()}

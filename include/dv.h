@@ -1,0 +1,219 @@
+/*
+ * dv.h — C ABI of libdv_b200.so: the B200 (sm_100a) kernels behind the conv-BN-ReLU hot path
+ * of zackdilan/deep-vision (PyTorch ResNet-34/50/152 and MobileNetV1 blocks, forward+backward).
+ *
+ * The reference has no FFI of its own: its hot path is a sequence of torch.nn primitives called
+ * from four model files.  Each entry point below replaces ONE such primitive (the reference call
+ * site is cited beside it) and is what a ctypes / cffi / pybind stub on the reference side binds.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller; the library never allocates device
+ *     memory, never frees, never synchronises the device;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream); calls return after
+ *     enqueue;
+ *   - activations are NHWC ([N][H][W][C], C contiguous); dense filters are KRSC ([K][R][S][C]);
+ *     depth-wise filters are [C][3][3] (== torch [C,1,3,3]);
+ *   - dtype: DV_F32 or DV_BF16 is the storage type of activations / filters; accumulation and
+ *     all per-channel statistics are fp32;
+ *   - return value: 0 on success, a DV_ERR_* code otherwise; dv_last_error() gives the message of
+ *     the last failure on the calling thread.  Nothing throws, nothing calls exit().
+ *   - there is no CPU path: on a machine without an sm_100 GPU every compute entry point fails
+ *     with DV_ERR_CUDA / DV_ERR_ARCH.
+ */
+#ifndef DV_B200_H
+#define DV_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DV_VERSION 100 /* 0.1.0 */
+
+enum { DV_F32 = 0, DV_BF16 = 1 };
+
+enum {
+  DV_OK = 0,
+  DV_ERR_ARG = 1,       /* bad dims / null pointer / misalignment */
+  DV_ERR_UNSUPPORTED = 2,
+  DV_ERR_CUDA = 3,      /* a CUDA runtime/driver call failed */
+  DV_ERR_ARCH = 4,      /* device is not compute capability 10.x */
+  DV_ERR_WORKSPACE = 5  /* workspace too small */
+};
+
+/* conv algorithm selector */
+enum {
+  DV_ALGO_AUTO = 0, /* tensor-core path when the shape qualifies, else SIMT */
+  DV_ALGO_SIMT = 1, /* CUDA-core implicit GEMM (any shape, fp32 or bf16 storage) */
+  DV_ALGO_TC = 2    /* tcgen05/TMEM/TMA implicit GEMM (bf16 only); error if shape unsupported */
+};
+
+/* ------------------------------------------------------------------------------------------
+ * Dense convolution, no bias, zero padding, cross-correlation (torch semantics).
+ * Replaces nn.Conv2d(bias=False) at ResNet/pytorch/models/resnet50.py:20-28,101-107,111-118,
+ * 122-128,137-143; resnet34.py:20-28,96-112,120-126; MobileNet/pytorch/models/mobilenet_v1.py:30,
+ * 139-145 and (as a 1x1 conv on [B,1,1,F]) nn.Linear at resnet50.py:44, mobilenet_v1.py:87.
+ *   fprop:  y[n,p,q,k]  = sum_{r,s,c} x[n, p*stride+r-pad, q*stride+s-pad, c] * w[k,r,s,c]
+ *   dgrad:  dx[n,h,w,c] = sum_{r,s,k} dy[n,p,q,k] * w[k,r,s,c]   over (p,q) with p*stride+r-pad==h ...
+ *   wgrad:  dw[k,r,s,c] = sum_{n,p,q} dy[n,p,q,k] * x[n, p*stride+r-pad, q*stride+s-pad, c]   (fp32 out)
+ * P = (H + 2*pad - R)/stride + 1, Q likewise.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dv_conv_params {
+  /* fprop: x in, w in, y out.  dgrad: y = dy in, w in, x = dx out.  wgrad: x in, y = dy in, w = dw out (fp32 KRSC). */
+  void* x;            /* [N,H,W,C] dtype */
+  void* w;            /* [K,R,S,C] dtype (fprop,dgrad: for DV_ALGO_TC dgrad see w_t) ; wgrad: fp32 out */
+  void* y;            /* [N,P,Q,K] dtype */
+  const void* w_t;    /* dgrad on the tensor-core path only: filters as [C][R][S][K] with taps flipped
+                         (w_t[c,r,s,k] = w[k,R-1-r,S-1-s,c]), made by dv_filter_prep; may be NULL otherwise */
+  void* workspace;    /* scratch, see dv_conv_workspace_bytes; may be NULL when that returns 0 */
+  size_t workspace_bytes;
+  int32_t N, H, W, C, K, R, S, stride, pad;
+  int32_t dtype;      /* DV_F32 | DV_BF16 */
+  int32_t algo;       /* DV_ALGO_* */
+  int32_t y_f32;      /* fprop only, SIMT only: 1 = write y as fp32 even when dtype is bf16 (logits) */
+} dv_conv_params;
+
+enum { DV_CONV_FPROP = 0, DV_CONV_DGRAD = 1, DV_CONV_WGRAD = 2 };
+
+int dv_conv_fprop(const dv_conv_params* p, void* stream);
+int dv_conv_dgrad(const dv_conv_params* p, void* stream);
+int dv_conv_wgrad(const dv_conv_params* p, void* stream);
+/* bytes of scratch the given pass (DV_CONV_*) needs for these params (0 = none) */
+size_t dv_conv_workspace_bytes(const dv_conv_params* p, int pass);
+/* which algorithm DV_ALGO_AUTO resolves to for this pass: DV_ALGO_SIMT or DV_ALGO_TC */
+int dv_conv_algo(const dv_conv_params* p, int pass);
+
+/* fp32 KRSC master filters -> compute-dtype copies: w_out[K,R,S,C] (cast) and, if w_t_out != NULL,
+ * w_t_out[C,R,S,K] with taps flipped (the dgrad operand).  No counterpart call site in the reference
+ * (torch keeps one fp32 OIHW tensor); this is the "NHWC plumbing" of the weight side. */
+int dv_filter_prep(const float* w_f32, void* w_out, void* w_t_out, int K, int R, int S, int C, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Depth-wise 3x3 convolution, pad 1, stride 1 or 2, groups == C.
+ * Replaces nn.Conv2d(C, C, 3, padding=1, stride, groups=C, bias=False) at mobilenet_v1.py:112-122.
+ * w is fp32 [C][3][3] for all three passes (tiny); dw out is fp32 [C][3][3].
+ * wgrad scratch: dv_dwconv_workspace_bytes().
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dv_dwconv_params {
+  void* x;   /* [N,H,W,C] dtype ; dgrad: dx out */
+  void* w;   /* fp32 [C,3,3]    ; wgrad: dw out */
+  void* y;   /* [N,P,Q,C] dtype ; dgrad/wgrad: dy in */
+  void* workspace;
+  size_t workspace_bytes;
+  int32_t N, H, W, C, stride;
+  int32_t dtype;
+} dv_dwconv_params;
+
+int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream);
+int dv_dwconv_dgrad(const dv_dwconv_params* p, void* stream);
+int dv_dwconv_wgrad(const dv_dwconv_params* p, void* stream);
+size_t dv_dwconv_workspace_bytes(const dv_dwconv_params* p);
+
+/* ------------------------------------------------------------------------------------------
+ * Batch normalisation over (N,H,W) per channel, torch defaults (eps 1e-5, momentum 0.1).
+ * Replaces nn.BatchNorm2d at resnet50.py:30,108,119,129,144; resnet34.py:30,104,113,127;
+ * mobilenet_v1.py:31,126,149 — together with the nn.ReLU(inplace=True) that follows it
+ * (resnet50.py:31,131) and the residual add (resnet50.py:163, resnet34.py:141), which are fused
+ * into the apply pass:   y = relu( (x-mean)*invstd*gamma + beta  [+ residual] ).
+ * M = N*H*W rows of C channels.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dv_bn_params {
+  const void* x;        /* [M,C] dtype: conv output */
+  void* y;              /* [M,C] dtype: block output (apply) */
+  const void* residual; /* [M,C] dtype or NULL */
+  const float* gamma;   /* [C] */
+  const float* beta;    /* [C] */
+  float* running_mean;  /* [C] updated by dv_bn_stats when not NULL */
+  float* running_var;   /* [C] (unbiased variance, as torch) */
+  float* save_mean;     /* [C] batch mean     (stats: out; others: in). eval mode: unused */
+  float* save_invstd;   /* [C] 1/sqrt(var+eps) (stats: out; others: in) */
+  void* workspace;      /* dv_bn_workspace_bytes() */
+  size_t workspace_bytes;
+  int64_t M;
+  int32_t C;
+  int32_t dtype;
+  int32_t relu;         /* 1 = fuse ReLU */
+  int32_t eval_mode;    /* apply only: 1 = normalise with running_mean/var instead of save_* */
+  float eps, momentum;
+} dv_bn_params;
+
+/* batch statistics (mean, biased var -> invstd) + running-stat update */
+int dv_bn_stats(const dv_bn_params* p, void* stream);
+/* normalise + affine (+residual) (+ReLU) */
+int dv_bn_apply(const dv_bn_params* p, void* stream);
+
+typedef struct dv_bn_bwd_params {
+  const void* x;        /* [M,C] conv output saved from forward */
+  const void* y;        /* [M,C] block output saved from forward (ReLU mask); may be NULL when relu == 0 */
+  const void* dy;       /* [M,C] gradient w.r.t. block output */
+  void* dx;             /* [M,C] gradient w.r.t. conv output */
+  void* dres;           /* [M,C] gradient w.r.t. residual (== masked dy) or NULL */
+  const float* gamma;
+  const float* save_mean;
+  const float* save_invstd;
+  float* dgamma;        /* [C] out */
+  float* dbeta;         /* [C] out */
+  void* workspace;
+  size_t workspace_bytes;
+  int64_t M;
+  int32_t C;
+  int32_t dtype;
+  int32_t relu;
+} dv_bn_bwd_params;
+
+/* dgamma, dbeta (with the ReLU mask recomputed from y) */
+int dv_bn_bwd_reduce(const dv_bn_bwd_params* p, void* stream);
+/* dx = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M), dres = dz, with dz = dy*(y>0) */
+int dv_bn_bwd_apply(const dv_bn_bwd_params* p, void* stream);
+size_t dv_bn_workspace_bytes(int64_t M, int C);
+
+/* stand-alone ReLU (nn.ReLU at a site that no BN precedes; not used by the four models) */
+int dv_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream);
+int dv_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Stem / tail ops.
+ * ------------------------------------------------------------------------------------------ */
+/* nn.MaxPool2d(3, 2, 1) — resnet50.py:34, resnet34.py:34.  idx: uint8 [N,P,Q,C] window position (0..8) of the max. */
+int dv_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H, int W, int C, int dtype, void* stream);
+int dv_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int N, int H, int W, int C, int dtype, void* stream);
+/* nn.AdaptiveAvgPool2d((1,1)) — resnet50.py:43, mobilenet_v1.py:84.  y: [N,C] */
+int dv_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int dtype, void* stream);
+int dv_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, int dtype, void* stream);
+/* NCHW fp32 image batch -> NHWC compute dtype (the layout change at the model entrance; train.py:444-449) */
+int dv_nchw_to_nhwc(const float* x_nchw, void* y_nhwc, int N, int C, int H, int W, int dtype, void* stream);
+/* plain cast between fp32 and bf16 (n elements) */
+int dv_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);
+/* y[m, :] += bias (fp32 y, fp32 bias) — the bias of nn.Linear, resnet50.py:44 */
+int dv_bias_add(float* y, const float* bias, int64_t M, int C, void* stream);
+/* dbias[c] = sum_m dy[m,c] (fp32) */
+int dv_bias_grad(const float* dy, float* dbias, int64_t M, int C, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Optimisers over a flat fp32 parameter buffer (one launch for the whole model).
+ * optim.SGD(lr, momentum, weight_decay) — ResNet/pytorch/train.py:166-184,361-365,467:
+ *     g' = g*grad_scale + wd*p ; buf = first ? g' : mom*buf + g' ; p -= lr*buf
+ * optim.RMSprop(lr, alpha, eps) — train.py:199-205:
+ *     g' = g*grad_scale + wd*p ; sq = alpha*sq + (1-alpha)*g'^2 ; p -= lr*g'/(sqrt(sq)+eps)
+ * ------------------------------------------------------------------------------------------ */
+int dv_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float weight_decay,
+                float grad_scale, int first_step, void* stream);
+int dv_rmsprop_step(float* p, const float* g, float* sq, int64_t n, float lr, float alpha, float eps,
+                    float weight_decay, float grad_scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Library
+ * ------------------------------------------------------------------------------------------ */
+int dv_version(void);
+const char* dv_last_error(void);
+/* 0 if the current device is compute capability 10.x, else DV_ERR_ARCH / DV_ERR_CUDA */
+int dv_device_check(void);
+/* number of kernels this library has launched since load (all threads); used by bench.py */
+uint64_t dv_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DV_B200_H */

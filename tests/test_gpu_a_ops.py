@@ -1,0 +1,304 @@
+"""GPU parity tests, per op, THROUGH THE C ABI (ctypes on include/dv.h) against the CPU oracle (oracle/ref_ops.py).
+
+Bars (BASELINE.json north_star): fp32 storage <= 1e-4 relative L2 on activations and gradients; bf16 storage
+<= 2e-2 relative L2 (inputs are pre-rounded to bf16 so both sides see identical operands; the error left is
+accumulation order and the final bf16 rounding).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import bf16_round, nchw_to_nhwc, nhwc_to_nchw, rel_l2, stream_ptr
+from oracle import ref_ops
+
+pytestmark = pytest.mark.gpu
+
+TOL = {torch.float32: 1e-4, torch.bfloat16: 2e-2}
+
+
+def _lib():
+    from deep_vision_b200 import lib
+    return lib
+
+
+def _dv(dtype):
+    lib = _lib()
+    return lib.DV_F32 if dtype == torch.float32 else lib.DV_BF16
+
+
+def _dev(a, dtype):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device="cuda", dtype=dtype).contiguous()
+
+
+def _rand(shape, seed, dtype, scale=1.0):
+    g = np.random.default_rng(seed)
+    a = g.standard_normal(shape) * scale
+    return bf16_round(a) if dtype == torch.bfloat16 else a.astype(np.float32).astype(np.float64)
+
+
+def run_conv(pass_id, x_nchw, w_oihw, dy_nchw, stride, pad, dtype, algo):
+    """Calls dv_conv_{fprop,dgrad,wgrad}; numpy NCHW/OIHW in, numpy NCHW/OIHW out (float64)."""
+    lib = _lib()
+    N, Cc, H, W = x_nchw.shape
+    K, _, R, S = w_oihw.shape
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    x = _dev(np.transpose(x_nchw, (0, 2, 3, 1)), dtype)
+    w = _dev(np.transpose(w_oihw, (0, 2, 3, 1)), dtype)
+    p = lib.ConvParams()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad = N, H, W, Cc, K, R, S, stride, pad
+    p.dtype, p.algo = _dv(dtype), algo
+    keep = [x, w]
+    if pass_id == lib.DV_CONV_FPROP:
+        y = torch.full((N, P, Q, K), float("nan"), device="cuda", dtype=dtype)
+        p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
+        fn, out = lib.lib.dv_conv_fprop, y
+    elif pass_id == lib.DV_CONV_DGRAD:
+        dy = _dev(np.transpose(dy_nchw, (0, 2, 3, 1)), dtype)
+        dx = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+        p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), dy.data_ptr()
+        if dtype == torch.bfloat16:
+            wf = _dev(np.transpose(w_oihw, (0, 2, 3, 1)), torch.float32)
+            wt = torch.empty((Cc, R, S, K), device="cuda", dtype=dtype)
+            lib.check(lib.lib.dv_filter_prep(wf.data_ptr(), None, wt.data_ptr(), K, R, S, Cc, _dv(dtype), stream_ptr()), "dv_filter_prep")
+            p.w_t = wt.data_ptr()
+            keep += [wf, wt]
+        keep.append(dy)
+        fn, out = lib.lib.dv_conv_dgrad, dx
+    else:
+        dy = _dev(np.transpose(dy_nchw, (0, 2, 3, 1)), dtype)
+        dw = torch.full((K, R, S, Cc), float("nan"), device="cuda", dtype=torch.float32)
+        p.x, p.w, p.y = x.data_ptr(), dw.data_ptr(), dy.data_ptr()
+        keep.append(dy)
+        fn, out = lib.lib.dv_conv_wgrad, dw
+    need = lib.lib.dv_conv_workspace_bytes(C.byref(p), pass_id)
+    if need:
+        ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+        p.workspace, p.workspace_bytes = ws.data_ptr(), need
+        keep.append(ws)
+    lib.check(fn(C.byref(p), stream_ptr()), "conv")
+    torch.cuda.synchronize()
+    o = out.double().cpu().numpy()
+    return np.transpose(o, (0, 3, 1, 2))
+
+
+CONV_CASES = [
+    # N, C, H, W, K, R, stride, pad
+    (2, 3, 20, 20, 16, 7, 2, 3),      # ResNet stem shape class (C=3, 7x7/2)
+    (2, 3, 16, 16, 32, 3, 2, 1),      # MobileNet stem (3x3/2)
+    (2, 16, 9, 9, 24, 3, 1, 1),
+    (3, 64, 7, 7, 64, 3, 1, 1),       # ragged M (147 rows)
+    (2, 64, 8, 8, 128, 3, 2, 1),      # ResNet-34 3x3 stride 2
+    (2, 128, 8, 8, 64, 1, 1, 0),
+    (2, 64, 8, 8, 256, 1, 2, 0),      # strided 1x1 projection
+    (1, 8, 5, 6, 8, 3, 1, 1),         # H != W
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("case", CONV_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_conv_simt_matches_oracle(case, dtype):
+    lib = _lib()
+    N, Cc, H, W, K, R, stride, pad = case
+    x = _rand((N, Cc, H, W), 1, dtype)
+    w = _rand((K, Cc, R, R), 2, dtype, scale=0.2)
+    y_ref = ref_ops.conv2d(x, w, stride, pad)
+    dy = _rand(y_ref.shape, 3, dtype)
+    dx_ref, dw_ref = ref_ops.conv2d_backward(x, w, dy, stride, pad)
+    tol = TOL[dtype]
+    assert rel_l2(run_conv(lib.DV_CONV_FPROP, x, w, None, stride, pad, dtype, lib.DV_ALGO_SIMT), y_ref) < tol
+    assert rel_l2(run_conv(lib.DV_CONV_DGRAD, x, w, dy, stride, pad, dtype, lib.DV_ALGO_SIMT), dx_ref) < tol
+    assert rel_l2(run_conv(lib.DV_CONV_WGRAD, x, w, dy, stride, pad, dtype, lib.DV_ALGO_SIMT), dw_ref) < 1e-4  # fp32 output
+
+
+def _bn_call(fn_name, x, dtype, **kw):
+    pass
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("shape,residual,relu", [((4, 64, 7, 7), False, True), ((2, 32, 9, 5), True, True),
+                                                 ((3, 256, 4, 4), True, False), ((2, 2048, 2, 2), False, False),
+                                                 ((64, 8, 16, 16), False, True)])
+def test_bn_forward_backward_matches_oracle(shape, residual, relu, dtype):
+    lib = _lib()
+    N, Cc, H, W = shape
+    M = N * H * W
+    x = _rand(shape, 5, dtype, scale=2.0) + (0.0 if dtype == torch.bfloat16 else 3.0)  # fp32: large mean vs std
+    if dtype == torch.bfloat16:
+        x = bf16_round(x + 1.0)
+    res = _rand(shape, 6, dtype) if residual else None
+    gamma = np.random.default_rng(7).uniform(0.5, 1.5, Cc)
+    beta = np.random.default_rng(8).normal(0, 0.3, Cc)
+    rm0, rv0 = np.random.default_rng(9).normal(0, 1, Cc), np.random.default_rng(10).uniform(0.5, 2, Cc)
+    y_ref, rm_ref, rv_ref, mean, invstd = ref_ops.batch_norm_train(x, gamma, beta, rm0, rv0)
+    if residual:
+        y_ref = y_ref + res
+    pre = y_ref.copy()
+    if relu:
+        y_ref = ref_ops.relu(y_ref)
+
+    xd = _dev(np.transpose(x, (0, 2, 3, 1)), dtype)
+    rd = _dev(np.transpose(res, (0, 2, 3, 1)), dtype) if residual else None
+    yd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+    f32 = lambda a: torch.from_numpy(np.asarray(a, np.float32)).cuda()
+    g_d, b_d, rm_d, rv_d = f32(gamma), f32(beta), f32(rm0), f32(rv0)
+    sm, si = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    wsz = lib.lib.dv_bn_workspace_bytes(M, Cc)
+    ws = torch.empty(wsz, dtype=torch.uint8, device="cuda")
+    p = lib.BnParams()
+    p.x, p.y, p.residual = xd.data_ptr(), yd.data_ptr(), (rd.data_ptr() if residual else None)
+    p.gamma, p.beta, p.running_mean, p.running_var = g_d.data_ptr(), b_d.data_ptr(), rm_d.data_ptr(), rv_d.data_ptr()
+    p.save_mean, p.save_invstd, p.workspace, p.workspace_bytes = sm.data_ptr(), si.data_ptr(), ws.data_ptr(), wsz
+    p.M, p.C, p.dtype, p.relu, p.eval_mode, p.eps, p.momentum = M, Cc, _dv(dtype), int(relu), 0, 1e-5, 0.1
+    lib.check(lib.lib.dv_bn_stats(C.byref(p), stream_ptr()), "dv_bn_stats")
+    lib.check(lib.lib.dv_bn_apply(C.byref(p), stream_ptr()), "dv_bn_apply")
+    torch.cuda.synchronize()
+    tol = TOL[dtype]
+    assert rel_l2(sm.cpu().numpy(), mean) < 1e-5
+    assert rel_l2(si.cpu().numpy(), invstd) < 1e-4
+    assert rel_l2(rm_d.cpu().numpy(), rm_ref) < 1e-5 and rel_l2(rv_d.cpu().numpy(), rv_ref) < 1e-4
+    y_gpu = np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2))
+    assert rel_l2(y_gpu, y_ref) < tol
+
+    # backward: the mask comes from the GPU's own stored output (what the kernel sees), statistics from the oracle
+    dy = _rand(shape, 11, dtype)
+    mask = (y_gpu > 0) if relu else np.ones_like(y_gpu, bool)
+    dz = np.where(mask, dy, 0.0)
+    dx_ref, dg_ref, db_ref = ref_ops.batch_norm_backward(x, gamma, mean, invstd, dz)
+    dyd = _dev(np.transpose(dy, (0, 2, 3, 1)), dtype)
+    dxd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+    drd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype) if residual else None
+    dg, db = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    q = lib.BnBwdParams()
+    q.x, q.y, q.dy, q.dx = xd.data_ptr(), yd.data_ptr(), dyd.data_ptr(), dxd.data_ptr()
+    q.dres = drd.data_ptr() if residual else None
+    q.gamma, q.save_mean, q.save_invstd, q.dgamma, q.dbeta = g_d.data_ptr(), sm.data_ptr(), si.data_ptr(), dg.data_ptr(), db.data_ptr()
+    q.workspace, q.workspace_bytes, q.M, q.C, q.dtype, q.relu = ws.data_ptr(), wsz, M, Cc, _dv(dtype), int(relu)
+    lib.check(lib.lib.dv_bn_bwd_reduce(C.byref(q), stream_ptr()), "dv_bn_bwd_reduce")
+    lib.check(lib.lib.dv_bn_bwd_apply(C.byref(q), stream_ptr()), "dv_bn_bwd_apply")
+    torch.cuda.synchronize()
+    assert rel_l2(dg.cpu().numpy(), dg_ref) < 1e-4 and rel_l2(db.cpu().numpy(), db_ref) < 1e-4
+    assert rel_l2(np.transpose(dxd.double().cpu().numpy(), (0, 3, 1, 2)), dx_ref) < tol
+    if residual:
+        assert rel_l2(np.transpose(drd.double().cpu().numpy(), (0, 3, 1, 2)), dz) < tol
+
+    # eval mode uses the running statistics
+    p.eval_mode = 1
+    lib.check(lib.lib.dv_bn_apply(C.byref(p), stream_ptr()), "dv_bn_apply(eval)")
+    torch.cuda.synchronize()
+    ye = ref_ops.batch_norm_eval(x, gamma, beta, rm_d.double().cpu().numpy(), rv_d.double().cpu().numpy())
+    if residual:
+        ye = ye + res
+    if relu:
+        ye = ref_ops.relu(ye)
+    assert rel_l2(np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2)), ye) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("case", [(2, 32, 10, 10, 1), (2, 64, 9, 11, 2), (1, 1024, 7, 7, 1), (3, 128, 8, 8, 2), (2, 2048, 4, 4, 1)],
+                         ids=lambda c: "x".join(map(str, c)))
+def test_dwconv_matches_oracle(case, dtype):
+    lib = _lib()
+    N, Cc, H, W, stride = case
+    x = _rand((N, Cc, H, W), 21, dtype)
+    w = np.random.default_rng(22).standard_normal((Cc, 1, 3, 3)).astype(np.float32).astype(np.float64) * 0.3
+    y_ref = ref_ops.conv2d(x, w, stride, 1, groups=Cc)
+    dy = _rand(y_ref.shape, 23, dtype)
+    dx_ref, dw_ref = ref_ops.conv2d_backward(x, w, dy, stride, 1, groups=Cc)
+    P, Q = y_ref.shape[2:]
+    xd = _dev(np.transpose(x, (0, 2, 3, 1)), dtype)
+    wd = torch.from_numpy(w.astype(np.float32)).cuda().contiguous()
+    yd = torch.full((N, P, Q, Cc), float("nan"), device="cuda", dtype=dtype)
+    p = lib.DwConvParams()
+    p.x, p.w, p.y, p.N, p.H, p.W, p.C, p.stride, p.dtype = xd.data_ptr(), wd.data_ptr(), yd.data_ptr(), N, H, W, Cc, stride, _dv(dtype)
+    lib.check(lib.lib.dv_dwconv_fprop(C.byref(p), stream_ptr()), "dv_dwconv_fprop")
+    torch.cuda.synchronize()
+    tol = TOL[dtype]
+    assert rel_l2(np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2)), y_ref) < tol
+    dyd = _dev(np.transpose(dy, (0, 2, 3, 1)), dtype)
+    dxd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+    p.x, p.y = dxd.data_ptr(), dyd.data_ptr()
+    lib.check(lib.lib.dv_dwconv_dgrad(C.byref(p), stream_ptr()), "dv_dwconv_dgrad")
+    dwd = torch.full((Cc, 1, 3, 3), float("nan"), device="cuda")
+    p.x, p.w = xd.data_ptr(), dwd.data_ptr()
+    need = lib.lib.dv_dwconv_workspace_bytes(C.byref(p))
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    p.workspace, p.workspace_bytes = ws.data_ptr(), need
+    lib.check(lib.lib.dv_dwconv_wgrad(C.byref(p), stream_ptr()), "dv_dwconv_wgrad")
+    torch.cuda.synchronize()
+    assert rel_l2(np.transpose(dxd.double().cpu().numpy(), (0, 3, 1, 2)), dx_ref) < tol
+    assert rel_l2(dwd.double().cpu().numpy(), dw_ref) < 1e-4
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+def test_pools_layout_cast_match_oracle(dtype):
+    lib = _lib()
+    N, Cc, H, W = 3, 64, 11, 9
+    x = ref_ops.relu(_rand((N, Cc, H, W), 31, dtype))  # post-ReLU input: many exact ties at 0
+    y_ref, tap = ref_ops.max_pool_3x3_s2_p1(x)
+    P, Q = y_ref.shape[2:]
+    xd = _dev(np.transpose(x, (0, 2, 3, 1)), dtype)
+    yd = torch.empty((N, P, Q, Cc), device="cuda", dtype=dtype)
+    idx = torch.empty((N, P, Q, Cc), device="cuda", dtype=torch.uint8)
+    lib.check(lib.lib.dv_maxpool_fwd(xd.data_ptr(), yd.data_ptr(), idx.data_ptr(), N, H, W, Cc, _dv(dtype), stream_ptr()), "maxpool_fwd")
+    dy = _rand(y_ref.shape, 32, dtype)
+    dyd = _dev(np.transpose(dy, (0, 2, 3, 1)), dtype)
+    dxd = torch.empty((N, H, W, Cc), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_maxpool_bwd(dyd.data_ptr(), idx.data_ptr(), dxd.data_ptr(), N, H, W, Cc, _dv(dtype), stream_ptr()), "maxpool_bwd")
+    torch.cuda.synchronize()
+    assert np.array_equal(np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2)), y_ref)          # exact: a max of inputs
+    assert np.array_equal(np.transpose(idx.cpu().numpy(), (0, 3, 1, 2)), tap)                     # same tie-breaking
+    assert rel_l2(np.transpose(dxd.double().cpu().numpy(), (0, 3, 1, 2)), ref_ops.max_pool_backward(dy, tap, H, W)) < TOL[dtype]
+
+    ad = torch.empty((N, Cc), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_avgpool_fwd(xd.data_ptr(), ad.data_ptr(), N, H * W, Cc, _dv(dtype), stream_ptr()), "avgpool_fwd")
+    g = _rand((N, Cc), 33, dtype)
+    gd = _dev(g, dtype)
+    gx = torch.empty((N, H, W, Cc), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_avgpool_bwd(gd.data_ptr(), gx.data_ptr(), N, H * W, Cc, _dv(dtype), stream_ptr()), "avgpool_bwd")
+    torch.cuda.synchronize()
+    assert rel_l2(ad.double().cpu().numpy(), ref_ops.global_avg_pool(x)[:, :, 0, 0]) < TOL[dtype]
+    assert rel_l2(np.transpose(gx.double().cpu().numpy(), (0, 3, 1, 2)), np.broadcast_to(g[:, :, None, None] / (H * W), x.shape)) < TOL[dtype]
+
+    img = np.random.default_rng(34).standard_normal((2, 3, 10, 12)).astype(np.float32)
+    imd = torch.from_numpy(img).cuda()
+    out = torch.empty((2, 10, 12, 3), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_nchw_to_nhwc(imd.data_ptr(), out.data_ptr(), 2, 3, 10, 12, _dv(dtype), stream_ptr()), "nchw_to_nhwc")
+    torch.cuda.synchronize()
+    expect = np.transpose(img, (0, 2, 3, 1)).astype(np.float64)
+    if dtype == torch.bfloat16:
+        expect = bf16_round(expect)
+    assert np.array_equal(out.double().cpu().numpy(), expect)
+
+
+def test_optimisers_and_bias_match_oracle():
+    lib = _lib()
+    rng = np.random.default_rng(41)
+    n = 10007
+    p0, g1, g2 = (rng.standard_normal(n).astype(np.float32) for _ in range(3))
+    pd, buf = torch.from_numpy(p0.copy()).cuda(), torch.zeros(n, device="cuda")
+    pn, bn = p0.astype(np.float64), None
+    for step, g in enumerate((g1, g2)):
+        gd = torch.from_numpy(g).cuda()
+        lib.check(lib.lib.dv_sgd_step(pd.data_ptr(), gd.data_ptr(), buf.data_ptr(), n, 0.1, 0.9, 1e-4, 1.0, int(step == 0), stream_ptr()), "sgd")
+        pn, bn = ref_ops.sgd_step(pn, g.astype(np.float64), bn, 0.1, 0.9, 1e-4, first=(step == 0))
+    torch.cuda.synchronize()
+    assert rel_l2(pd.cpu().numpy(), pn) < 1e-6
+    pd, sq = torch.from_numpy(p0.copy()).cuda(), torch.zeros(n, device="cuda")
+    pn, sn = p0.astype(np.float64), np.zeros(n)
+    for g in (g1, g2):
+        gd = torch.from_numpy(g).cuda()
+        lib.check(lib.lib.dv_rmsprop_step(pd.data_ptr(), gd.data_ptr(), sq.data_ptr(), n, 0.045, 0.9, 1.0, 0.0, 1.0, stream_ptr()), "rmsprop")
+        pn, sn = ref_ops.rmsprop_step(pn, g.astype(np.float64), sn, 0.045, 0.9, 1.0)
+    torch.cuda.synchronize()
+    assert rel_l2(pd.cpu().numpy(), pn) < 1e-6
+    y = rng.standard_normal((5, 1000)).astype(np.float32)
+    b = rng.standard_normal(1000).astype(np.float32)
+    yd, bd = torch.from_numpy(y.copy()).cuda(), torch.from_numpy(b).cuda()
+    lib.check(lib.lib.dv_bias_add(yd.data_ptr(), bd.data_ptr(), 5, 1000, stream_ptr()), "bias_add")
+    db = torch.empty(1000, device="cuda")
+    lib.check(lib.lib.dv_bias_grad(yd.data_ptr(), db.data_ptr(), 5, 1000, stream_ptr()), "bias_grad")
+    torch.cuda.synchronize()
+    assert rel_l2(yd.cpu().numpy(), y + b) < 1e-7
+    assert rel_l2(db.cpu().numpy(), (y + b).sum(0)) < 1e-5

@@ -1,0 +1,163 @@
+"""GPU parity tests of the tcgen05/TMEM/TMA convolution kernels (DV_ALGO_TC, bf16) through the C ABI:
+against the CPU oracle at sizes numpy finishes in seconds, and against the independent CUDA-core kernel plus
+size-independent properties (linearity, zero-padding border rows) at BASELINE.json's full sizes."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import bf16_round, rel_l2
+from oracle import ref_ops
+from test_gpu_a_ops import _lib, _rand, run_conv
+
+pytestmark = pytest.mark.gpu
+BF = torch.bfloat16
+
+TC_CASES = [
+    # N, C, H, W, K, R, stride, pad          what it exercises
+    (2, 64, 8, 8, 64, 1, 1, 0),       # 1x1 GEMM, BN=64, M=128 exactly
+    (3, 128, 7, 7, 256, 1, 1, 0),     # ragged M (147), BN=256, two K blocks
+    (2, 256, 8, 8, 128, 1, 1, 0),     # BN=128, four K blocks (ring wraps at 3 stages)
+    (2, 64, 8, 8, 64, 3, 1, 1),       # 3x3 im2col, padding rows
+    (3, 64, 7, 7, 64, 3, 1, 1),       # 3x3, 7x7 image, M-tile spans images
+    (2, 128, 14, 14, 128, 3, 1, 1),   # 3x3, 18 K blocks
+    (2, 64, 8, 8, 128, 1, 2, 0),      # strided 1x1 (Bottleneck conv1 / projection)
+    (2, 64, 9, 9, 128, 3, 2, 1),      # 3x3 stride 2 (ResNet-34), odd size
+    (2, 512, 4, 4, 1000, 1, 1, 0),    # K not a multiple of the N tile (FC-like)
+    (5, 64, 6, 5, 192, 3, 1, 1),      # H != W, K=192
+]
+
+
+@pytest.mark.parametrize("case", TC_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_fprop_matches_oracle(case):
+    lib = _lib()
+    N, Cc, H, W, K, R, stride, pad = case
+    x = _rand((N, Cc, H, W), 1, BF)
+    w = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+    y_ref = ref_ops.conv2d(x, w, stride, pad)
+    y = run_conv(lib.DV_CONV_FPROP, x, w, None, stride, pad, BF, lib.DV_ALGO_TC)
+    assert np.isfinite(y).all()
+    assert rel_l2(y, y_ref) < 2e-2
+    # tighter: identical operands, so only the final bf16 rounding of y separates the two (2^-9 relative per element)
+    assert np.max(np.abs(y - y_ref) / (np.abs(y_ref) + 1e-2)) < 2e-2
+
+
+DGRAD_CASES = [c for c in TC_CASES if not (c[5] == 3 and c[6] == 2) and c[4] % 64 == 0]
+
+
+@pytest.mark.parametrize("case", DGRAD_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_dgrad_matches_oracle(case):
+    lib = _lib()
+    N, Cc, H, W, K, R, stride, pad = case
+    x = _rand((N, Cc, H, W), 1, BF)
+    w = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+    dy = _rand((N, K, P, Q), 3, BF)
+    dx_ref, _ = ref_ops.conv2d_backward(x, w, dy, stride, pad)
+    dx = run_conv(lib.DV_CONV_DGRAD, x, w, dy, stride, pad, BF, lib.DV_ALGO_TC)
+    assert np.isfinite(dx).all()
+    assert rel_l2(dx, dx_ref) < 2e-2
+
+
+WGRAD_CASES = [c for c in TC_CASES if c[1] % 64 == 0] + [(4, 64, 12, 12, 64, 3, 1, 1), (8, 256, 8, 8, 64, 1, 1, 0),
+                                                         (2, 512, 6, 6, 128, 3, 1, 1)]
+
+
+@pytest.mark.parametrize("case", WGRAD_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_wgrad_matches_oracle(case):
+    lib = _lib()
+    N, Cc, H, W, K, R, stride, pad = case
+    x = _rand((N, Cc, H, W), 1, BF)
+    w = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+    dy = _rand((N, K, P, Q), 3, BF)
+    _, dw_ref = ref_ops.conv2d_backward(x, w, dy, stride, pad)
+    dw = run_conv(lib.DV_CONV_WGRAD, x, w, dy, stride, pad, BF, lib.DV_ALGO_TC)
+    assert np.isfinite(dw).all()
+    assert rel_l2(dw, dw_ref) < 1e-4      # bf16 products are exact in fp32; only summation order differs
+    dw2 = run_conv(lib.DV_CONV_WGRAD, x, w, dy, stride, pad, BF, lib.DV_ALGO_TC)
+    assert np.array_equal(dw, dw2)         # fixed-order split reduction: bit-reproducible
+
+
+def _gpu_conv(pass_id, xd, wd, dyd, stride, pad, algo, wt=None):
+    """device tensors in (NHWC / KRSC, bf16) -> device tensor out; for the full-size checks (no host round trip)."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, H, W, Cc = xd.shape
+    K, R, S, _ = wd.shape
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    p = lib.ConvParams()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, W, Cc, K, R, S, stride, pad, lib.DV_BF16, algo
+    if pass_id == lib.DV_CONV_FPROP:
+        out = torch.empty((N, P, Q, K), device="cuda", dtype=BF)
+        p.x, p.w, p.y = xd.data_ptr(), wd.data_ptr(), out.data_ptr()
+        fn = lib.lib.dv_conv_fprop
+    elif pass_id == lib.DV_CONV_DGRAD:
+        out = torch.empty((N, H, W, Cc), device="cuda", dtype=BF)
+        p.x, p.w, p.y = out.data_ptr(), wd.data_ptr(), dyd.data_ptr()
+        p.w_t = wt.data_ptr() if wt is not None else None
+        fn = lib.lib.dv_conv_dgrad
+    else:
+        out = torch.empty((K, R, S, Cc), device="cuda", dtype=torch.float32)
+        p.x, p.w, p.y = xd.data_ptr(), out.data_ptr(), dyd.data_ptr()
+        fn = lib.lib.dv_conv_wgrad
+    need = lib.lib.dv_conv_workspace_bytes(C.byref(p), pass_id)
+    ws = torch.empty(max(need, 16), dtype=torch.uint8, device="cuda")
+    p.workspace, p.workspace_bytes = ws.data_ptr(), need
+    lib.check(fn(C.byref(p), stream_ptr()), "conv")
+    torch.cuda.synchronize()
+    return out
+
+
+FULL_CASES = [
+    # ResNet-50 layer shapes at batch 256; N, C, H, K, R, stride, pad
+    (256, 64, 56, 64, 3, 1, 1),
+    (256, 64, 56, 256, 1, 1, 0),
+    (256, 256, 56, 128, 1, 2, 0),
+    (256, 256, 14, 256, 3, 1, 1),
+    (256, 512, 7, 512, 3, 1, 1),
+    (256, 2048, 7, 512, 1, 1, 0),
+]
+
+
+@pytest.mark.parametrize("case", FULL_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_full_size_against_cuda_core_kernel_and_properties(case):
+    """At BASELINE sizes the numpy oracle is too slow, so: (1) the tensor-core result equals the independent
+    CUDA-core kernel's on the same operands; (2) linearity conv(a*x1 + x2) == a*conv(x1)+conv(x2) with a = 2 (exact in
+    bf16 up to output rounding); (3) sampled output pixels equal the oracle's dot products."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, Cc, H, K, R, stride, pad = case
+    g = torch.Generator(device="cuda").manual_seed(5)
+    xd = torch.randn((N, H, H, Cc), generator=g, device="cuda").to(BF)
+    wd = (torch.randn((K, R, R, Cc), generator=g, device="cuda") * 0.05).to(BF)
+    P = (H + 2 * pad - R) // stride + 1
+    dyd = torch.randn((N, P, P, K), generator=g, device="cuda").to(BF)
+    wf = wd.float().contiguous()
+    wt = torch.empty((Cc, R, R, K), device="cuda", dtype=BF)
+    lib.check(lib.lib.dv_filter_prep(wf.data_ptr(), None, wt.data_ptr(), K, R, R, Cc, lib.DV_BF16, stream_ptr()), "filter_prep")
+
+    y_tc = _gpu_conv(lib.DV_CONV_FPROP, xd, wd, None, stride, pad, lib.DV_ALGO_TC)
+    y_si = _gpu_conv(lib.DV_CONV_FPROP, xd, wd, None, stride, pad, lib.DV_ALGO_SIMT)
+    err = float((y_tc.float() - y_si.float()).norm() / y_si.float().norm())
+    assert err < 4e-3, f"fprop TC vs SIMT {err}"
+    # sampled pixels against the oracle
+    xs = xd[:2].double().cpu().numpy().transpose(0, 3, 1, 2)
+    y_or = ref_ops.conv2d(xs, wd.double().cpu().numpy().transpose(0, 3, 1, 2), stride, pad)
+    assert rel_l2(y_tc[:2].double().cpu().numpy().transpose(0, 3, 1, 2), y_or) < 2e-2
+    # linearity
+    x2 = torch.randn((N, H, H, Cc), generator=g, device="cuda").to(BF)
+    lhs = _gpu_conv(lib.DV_CONV_FPROP, (2 * xd.float() + x2.float()).to(BF), wd, None, stride, pad, lib.DV_ALGO_TC).float()
+    rhs = 2 * y_tc.float() + _gpu_conv(lib.DV_CONV_FPROP, x2, wd, None, stride, pad, lib.DV_ALGO_TC).float()
+    assert float((lhs - rhs).norm() / rhs.norm()) < 2e-2
+
+    dx_tc = _gpu_conv(lib.DV_CONV_DGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_TC, wt)
+    dx_si = _gpu_conv(lib.DV_CONV_DGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_SIMT)
+    err = float((dx_tc.float() - dx_si.float()).norm() / dx_si.float().norm())
+    assert err < 4e-3, f"dgrad TC vs SIMT {err}"
+
+    dw_tc = _gpu_conv(lib.DV_CONV_WGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_TC)
+    dw_si = _gpu_conv(lib.DV_CONV_WGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_SIMT)
+    err = float((dw_tc - dw_si).norm() / dw_si.norm())
+    assert err < 1e-4, f"wgrad TC vs SIMT {err}"

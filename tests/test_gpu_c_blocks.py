@@ -1,0 +1,68 @@
+"""GPU parity of whole blocks (the product's nn.Modules, i.e. autograd Functions over the C ABI) against the golden
+fixtures frozen from the reference's own BasicBlock / BottleneckBlock / DepthwiseSeparableConv.
+
+fp32: output, input gradient and every parameter gradient <= 1e-4 relative L2 (north_star).  bf16: forward <= 2e-2;
+bf16 gradients are reported by torch's own autocast at 6-11e-2 from fp64 and gated at 1.5e-1 here.
+"""
+import numpy as np
+import pytest
+import torch
+
+import deep_vision_b200 as dv
+from helpers import golden_state, load_golden, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "block_bottleneck_256_64_256": lambda: dv.models.BottleneckBlock(256, 64, 256),
+    "block_bottleneck_128_64_256_s2_proj": lambda: dv.models.BottleneckBlock(128, 64, 256, stride=2, downsample=True),
+    "block_bottleneck_64_64_256_s1_proj": lambda: dv.models.BottleneckBlock(64, 64, 256, stride=1, downsample=True),
+    "block_basic_64_64": lambda: dv.models.BasicBlock(64, 64),
+    "block_basic_64_128_s2_proj": lambda: dv.models.BasicBlock(64, 128, stride=2, downsample=True),
+    "block_dwsep_64_128_s2": lambda: dv.models.DepthwiseSeparableConv(64, 128, dw_stride=2, pw_stride=1),
+    "block_dwsep_32_64_s1": lambda: dv.models.DepthwiseSeparableConv(32, 64, dw_stride=1, pw_stride=1),
+}
+
+
+@pytest.fixture(autouse=True)
+def _restore_dtype():
+    yield
+    dv.set_compute_dtype(torch.bfloat16)
+    dv.set_conv_algo(0)
+
+
+def _run(name, dtype, algo=0):
+    rec = load_golden(name)
+    dv.set_compute_dtype(dtype)
+    dv.set_conv_algo(algo)
+    m = CASES[name]()
+    m.load_state_dict(golden_state(rec))
+    m = m.cuda().train()
+    x = torch.from_numpy(rec["x"]).cuda().requires_grad_(True)
+    y = m(x)
+    assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
+    y.backward(torch.from_numpy(rec["dy"]).cuda().to(dtype))
+    torch.cuda.synchronize()
+    out = {"y": rel_l2(y.float().cpu().numpy(), rec["y"]), "dx": rel_l2(x.grad.float().cpu().numpy(), rec["dx"])}
+    for k, p in m.named_parameters():
+        out["grad/" + k] = rel_l2(p.grad.float().cpu().numpy(), rec["grad/" + k])
+    for k, v in m.state_dict().items():
+        if "running_" in k:
+            out["after/" + k] = rel_l2(v.float().cpu().numpy(), rec["after/" + k])
+    return out
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_block_fp32_matches_reference(name):
+    errs = _run(name, torch.float32)
+    bad = {k: v for k, v in errs.items() if v > 1e-4}
+    assert not bad, bad
+
+
+@pytest.mark.parametrize("algo", [0, 1], ids=["auto_tc", "simt"])
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_block_bf16_matches_reference(name, algo):
+    errs = _run(name, torch.bfloat16, algo)
+    assert errs["y"] < 2e-2, errs
+    assert all(v < 1e-3 for k, v in errs.items() if k.startswith("after/")), errs   # statistics are fp32
+    assert errs["dx"] < 1.5e-1 and all(v < 1.5e-1 for k, v in errs.items() if k.startswith("grad/")), errs
