@@ -201,6 +201,13 @@ def run_ours(args):
     for _ in range(max(args.warmup, 3)):
         trainer.step(images, labels)
     barrier()
+    if args.profile:
+        for _ in range(args.steps):
+            trainer.step(images, labels)
+        barrier()
+        if rank == 0:
+            print(json.dumps({"profile": True, "launches_per_step": launches_per_step, "steps": args.steps}), flush=True)
+        return
     with ClockSampler(local_rank) as clk:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
@@ -283,6 +290,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="warm up, run --steps eager steps, print a short line, exit (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

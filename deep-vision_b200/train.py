@@ -38,34 +38,36 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-class Trainer:
-    def __init__(self, model, optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4, alpha=0.9, eps=1.0,
-                 bucket_bytes=25 << 20, process_group=None, use_cuda_graph=False, **_ignored):
-        self.model = model
-        self.kind = optimizer
-        self.lr, self.momentum, self.weight_decay, self.alpha, self.eps = lr, momentum, weight_decay, alpha, eps
-        self.pg = process_group
-        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
-        self.use_graph = use_cuda_graph
-        self.steps_done = 0
-        self._graph = None
-        self._flatten(bucket_bytes)
+def plan_buckets(offsets, total, cap_elems):
+    """Cut [0,total) into contiguous ranges of >= cap_elems elements (the last may be smaller), walking parameters
+    from the END of the flat buffer: backward produces the last layers' gradients first, so bucket 0 is ready first.
+    Returns [(start, end)] in launch order."""
+    buckets, end, i = [], total, len(offsets) - 1
+    while i >= 0:
+        start = end
+        while i >= 0 and (end - start) < cap_elems:
+            start = offsets[i]
+            i -= 1
+        buckets.append((start, end))
+        end = start
+    return buckets
 
-    # ---- flat parameter / gradient storage --------------------------------------------------------------------
-    def _flatten(self, bucket_bytes):
-        params = [p for p in self.model.parameters() if p.requires_grad]
-        dev = params[0].device
-        if dev.type != "cuda":
-            raise RuntimeError("Trainer: move the model to a CUDA device first; there is no CPU path")
-        total = sum(p.numel() for p in params)
+
+class FlatParams:
+    """All trainable parameters of a module as views into ONE flat fp32 buffer (and their gradients into another).
+    4-D filters are laid out KRSC (channels_last) so the convolution kernels read the master copy in place."""
+
+    def __init__(self, module):
+        self.params = [p for p in module.parameters() if p.requires_grad]
+        dev = self.params[0].device
+        total = sum(p.numel() for p in self.params)
         self.flat_p = torch.empty(total, dtype=torch.float32, device=dev)
         self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
-        self.flat_s = torch.zeros(total, dtype=torch.float32, device=dev)  # momentum buffer / squared-grad average
-        self.params, self.offsets = params, []
+        self.offsets = []
         off = 0
-        for p in params:
+        for p in self.params:
             n = p.numel()
-            if p.dim() == 4:  # filters live as KRSC (channels_last) so the kernels read them in place
+            if p.dim() == 4:
                 K, Cc, R, S = p.shape
                 pv = self.flat_p[off:off + n].view(K, R, S, Cc).permute(0, 3, 1, 2)
                 gv = self.flat_g[off:off + n].view(K, R, S, Cc).permute(0, 3, 1, 2)
@@ -77,31 +79,31 @@ class Trainer:
             p.grad = gv
             self.offsets.append(off)
             off += n
-        config.bump_weight_epoch()
-        # buckets: contiguous ranges of the flat gradient, cut from the END (gradients of the last layers arrive first)
-        cap = max(1, bucket_bytes // 4)
-        self.buckets = []  # (start, end)
-        end = total
-        i = len(params) - 1
-        while i >= 0:
-            start = end
-            while i >= 0 and (end - start) < cap:
-                start = self.offsets[i]
-                i -= 1
-            self.buckets.append((start, end))
-            end = start
-        self._bucket_of = {}
-        self._bucket_need = []
+        self.total = total
+
+
+class BucketedAllReduce:
+    """Gradient exchange of the data-parallel step: NCCL (or gloo in the CPU tests) all-reduce SUM over buckets of the
+    flat gradient buffer, each launched asynchronously from the autograd hook of the bucket's last-arriving
+    parameter; `finish()` makes the current stream wait for all of them."""
+
+    def __init__(self, flat, bucket_bytes=25 << 20, process_group=None):
+        self.flat, self.pg = flat, process_group
+        self.buckets = plan_buckets(flat.offsets, flat.total, max(1, bucket_bytes // 4))
+        self._bucket_of, self._need = {}, []
         for b, (s, e) in enumerate(self.buckets):
-            members = [j for j, o in enumerate(self.offsets) if s <= o < e]
-            self._bucket_need.append(len(members))
+            members = [j for j, o in enumerate(flat.offsets) if s <= o < e]
+            self._need.append(len(members))
             for j in members:
                 self._bucket_of[j] = b
-        self._pending = list(self._bucket_need)
+        self.reset()
+        for j, p in enumerate(flat.params):
+            p.register_post_accumulate_grad_hook(self._make_hook(j))
+
+    def reset(self):
+        self._pending = list(self._need)
         self._works = []
-        if self.world > 1:
-            for j, p in enumerate(params):
-                p.register_post_accumulate_grad_hook(self._make_hook(j))
+        self.launch_order = []
 
     def _make_hook(self, j):
         def hook(_param):
@@ -109,19 +111,44 @@ class Trainer:
             self._pending[b] -= 1
             if self._pending[b] == 0:
                 s, e = self.buckets[b]
-                self._works.append(dist.all_reduce(self.flat_g[s:e], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
+                self.launch_order.append(b)
+                self._works.append(dist.all_reduce(self.flat.flat_g[s:e], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
         return hook
+
+    def finish(self):
+        for w in self._works:
+            w.wait()
+        self._works = []
+
+
+class Trainer:
+    def __init__(self, model, optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4, alpha=0.9, eps=1.0,
+                 bucket_bytes=25 << 20, process_group=None, use_cuda_graph=False, **_ignored):
+        self.model = model
+        self.kind = optimizer
+        self.lr, self.momentum, self.weight_decay, self.alpha, self.eps = lr, momentum, weight_decay, alpha, eps
+        self.world = dist.get_world_size(process_group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.use_graph = use_cuda_graph
+        self.steps_done = 0
+        self._graph = None
+        if next(model.parameters()).device.type != "cuda":
+            raise RuntimeError("Trainer: move the model to a CUDA device first; there is no CPU path")
+        self.flat = FlatParams(model)
+        self.flat_p, self.flat_g = self.flat.flat_p, self.flat.flat_g
+        self.flat_s = torch.zeros_like(self.flat_p)  # momentum buffer / squared-gradient average
+        config.bump_weight_epoch()
+        self.exchange = BucketedAllReduce(self.flat, bucket_bytes, process_group) if self.world > 1 else None
 
     # ---- one step -------------------------------------------------------------------------------------------------
     def _step_body(self, images, labels):
         self.flat_g.zero_()
-        self._pending = list(self._bucket_need)
-        self._works = []
+        if self.exchange is not None:
+            self.exchange.reset()
         logits = self.model(images)
         loss = F.cross_entropy(logits, labels)
         loss.backward()
-        for w in self._works:
-            w.wait()
+        if self.exchange is not None:
+            self.exchange.finish()
         self._optimizer_step()
         return loss.detach()
 

@@ -74,10 +74,18 @@ def model_case(name, ctor, in_shape, seed, bn_train):
     m64.train(bn_train)
     with torch.no_grad():
         y64 = m64(x.double())
+    # torch's own bf16 (CPU autocast) on the same reference module: the torch-vs-torch floor reported beside ours
+    torch.manual_seed(seed)
+    mb16 = ctor()
+    mb16.train(bn_train)
+    with torch.no_grad(), torch.autocast("cpu", dtype=torch.bfloat16):
+        yb16 = mb16(x).float()
+    floor_bf16 = float((yb16.double() - y64).norm() / y64.norm())
     np.savez_compressed(os.path.join(OUT, name + ".npz"), seed=seed, in_shape=np.array(in_shape), bn_train=bn_train,
                         logits_fp32=y32.numpy(), logits_fp64=y64.numpy(), param_sum=checksum, param_abs_sum=abssum,
-                        torch_version=torch.__version__)
-    print("wrote", name, y32.shape, "fp32-vs-fp64 rel", float((y32.double() - y64).norm() / y64.norm()))
+                        torch_version=torch.__version__, torch_bf16_autocast_rel=floor_bf16)
+    print("wrote", name, y32.shape, "fp32-vs-fp64 rel", float((y32.double() - y64).norm() / y64.norm()),
+          "torch bf16 autocast vs fp64 rel", floor_bf16)
 
 
 def interface_case(mods):
@@ -108,21 +116,27 @@ def main():
                     (mb, ["MobileNetV1", "DepthwiseSeparableConv", "DepthwiseConv", "PointwiseConv"])])
     if os.environ.get("DV_GOLDEN_INTERFACE_ONLY"):
         return
-    block_case("block_bottleneck_256_64_256", lambda: r50.BottleneckBlock(256, 64, 256), (2, 256, 8, 8), 11)
-    block_case("block_bottleneck_128_64_256_s2_proj", lambda: r50.BottleneckBlock(128, 64, 256, stride=2, downsample=True), (2, 128, 8, 8), 12)
-    block_case("block_bottleneck_64_64_256_s1_proj", lambda: r50.BottleneckBlock(64, 64, 256, stride=1, downsample=True), (3, 64, 7, 7), 13)
-    block_case("block_basic_64_64", lambda: r34.BasicBlock(64, 64), (2, 64, 8, 8), 21)
-    block_case("block_basic_64_128_s2_proj", lambda: r34.BasicBlock(64, 128, stride=2, downsample=True), (2, 64, 8, 8), 22)
-    block_case("block_dwsep_64_128_s2", lambda: mb.DepthwiseSeparableConv(64, 128, dw_stride=2, pw_stride=1), (2, 64, 8, 8), 31)
-    block_case("block_dwsep_32_64_s1", lambda: mb.DepthwiseSeparableConv(32, 64, dw_stride=1, pw_stride=1), (2, 32, 9, 9), 32)
+    if os.environ.get("DV_GOLDEN_MODELS_ONLY"):
+        block_case_enabled = False
+    else:
+        block_case_enabled = True
+    block_case_enabled and block_case("block_bottleneck_256_64_256", lambda: r50.BottleneckBlock(256, 64, 256), (2, 256, 8, 8), 11)
+    block_case_enabled and block_case("block_bottleneck_128_64_256_s2_proj", lambda: r50.BottleneckBlock(128, 64, 256, stride=2, downsample=True), (2, 128, 8, 8), 12)
+    block_case_enabled and block_case("block_bottleneck_64_64_256_s1_proj", lambda: r50.BottleneckBlock(64, 64, 256, stride=1, downsample=True), (3, 64, 7, 7), 13)
+    block_case_enabled and block_case("block_basic_64_64", lambda: r34.BasicBlock(64, 64), (2, 64, 8, 8), 21)
+    block_case_enabled and block_case("block_basic_64_128_s2_proj", lambda: r34.BasicBlock(64, 128, stride=2, downsample=True), (2, 64, 8, 8), 22)
+    block_case_enabled and block_case("block_dwsep_64_128_s2", lambda: mb.DepthwiseSeparableConv(64, 128, dw_stride=2, pw_stride=1), (2, 64, 8, 8), 31)
+    block_case_enabled and block_case("block_dwsep_32_64_s1", lambda: mb.DepthwiseSeparableConv(32, 64, dw_stride=1, pw_stride=1), (2, 32, 9, 9), 32)
 
     # BASELINE.json configs[0]: ResNet-34 fp32 forward, batch 4 of 3x224x224 synthetic, reference model as-is (eval + train BN)
     model_case("model_resnet34_b4_224_eval", r34.ResNet34, (4, 3, 224, 224), 0, bn_train=False)
-    model_case("model_resnet34_b4_64_train", r34.ResNet34, (4, 3, 64, 64), 0, bn_train=True)
-    model_case("model_resnet50_b2_64_train", r50.ResNet50, (2, 3, 64, 64), 0, bn_train=True)
+    # train-mode fixtures: 4 x 128x128 so that the last stage still normalises over 64 samples per channel
+    model_case("model_resnet34_b4_128_train", r34.ResNet34, (4, 3, 128, 128), 0, bn_train=True)
+    model_case("model_resnet50_b4_128_train", r50.ResNet50, (4, 3, 128, 128), 0, bn_train=True)
     model_case("model_resnet50_b2_64_eval", r50.ResNet50, (2, 3, 64, 64), 0, bn_train=False)
-    model_case("model_resnet152_b2_64_train", r152.ResNet152, (2, 3, 64, 64), 0, bn_train=True)
-    model_case("model_mobilenet1_b2_64_train", mb.MobileNetV1, (2, 3, 64, 64), 0, bn_train=True)
+    model_case("model_resnet152_b4_128_train", r152.ResNet152, (4, 3, 128, 128), 0, bn_train=True)
+    model_case("model_resnet152_b2_64_eval", r152.ResNet152, (2, 3, 64, 64), 0, bn_train=False)
+    model_case("model_mobilenet1_b4_128_train", mb.MobileNetV1, (4, 3, 128, 128), 0, bn_train=True)
     model_case("model_mobilenet1_b2_64_eval", mb.MobileNetV1, (2, 3, 64, 64), 0, bn_train=False)
 
 

@@ -43,7 +43,7 @@ def _run(name, dtype, algo=0):
     assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
     y.backward(torch.from_numpy(rec["dy"]).cuda().to(dtype))
     torch.cuda.synchronize()
-    out = {"y": rel_l2(y.float().cpu().numpy(), rec["y"]), "dx": rel_l2(x.grad.float().cpu().numpy(), rec["dx"])}
+    out = {"y": rel_l2(y.detach().float().cpu().numpy(), rec["y"]), "dx": rel_l2(x.grad.float().cpu().numpy(), rec["dx"])}
     for k, p in m.named_parameters():
         out["grad/" + k] = rel_l2(p.grad.float().cpu().numpy(), rec["grad/" + k])
     for k, v in m.state_dict().items():

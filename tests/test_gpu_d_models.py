@@ -3,7 +3,7 @@
 fp32: eval-mode logits <= 1e-4 of the reference's fp64 logits; train-mode logits are gated at the larger of 1e-4 and
 10x the reference's own fp32-vs-fp64 distance on that fixture (random-init BN networks amplify rounding; SURVEY.md
 App. B).  bf16: eval-mode logits <= 2e-2 with identical top-1 (north_star); train-mode is reported against torch
-autocast's own 1.1e-1 floor and gated at 3e-1.
+autocast's own distance on the same fixture (stored in it) and gated at max(3e-1, 2x that).
 """
 import numpy as np
 import pytest
@@ -18,11 +18,12 @@ CTORS = {"resnet34": lambda: dv.models.ResNet34(), "resnet50": lambda: dv.models
          "resnet152": lambda: dv.models.ResNet152(), "mobilenet1": lambda: dv.models.MobileNetV1()}
 FIXTURES = {
     "model_resnet34_b4_224_eval": "resnet34",     # BASELINE.json configs[0]
-    "model_resnet34_b4_64_train": "resnet34",
-    "model_resnet50_b2_64_train": "resnet50",
+    "model_resnet34_b4_128_train": "resnet34",
+    "model_resnet50_b4_128_train": "resnet50",
     "model_resnet50_b2_64_eval": "resnet50",
-    "model_resnet152_b2_64_train": "resnet152",
-    "model_mobilenet1_b2_64_train": "mobilenet1",
+    "model_resnet152_b4_128_train": "resnet152",
+    "model_resnet152_b2_64_eval": "resnet152",
+    "model_mobilenet1_b4_128_train": "mobilenet1",
     "model_mobilenet1_b2_64_eval": "mobilenet1",
 }
 
@@ -66,7 +67,10 @@ def test_model_bf16_logits(name):
     y, rec = _logits(name, torch.bfloat16)
     err = rel_l2(y, rec["logits_fp64"])
     if bool(rec["bn_train"]):
-        assert err < 3e-1, err
+        # chaotic at random init: torch's own bf16 autocast of the reference module sits at `floor` from fp64
+        floor = float(rec["torch_bf16_autocast_rel"])
+        print(f"{name}: ours {err:.3e}  torch bf16 autocast {floor:.3e}")
+        assert err < max(3e-1, 2.0 * floor), (err, floor)
     else:
         assert err < 2e-2, err
         assert np.array_equal(y.argmax(1), rec["logits_fp64"].argmax(1))

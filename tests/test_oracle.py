@@ -150,10 +150,9 @@ def test_numpy_oracle_matches_reference_block():
 
 
 MODELS = {
-    "model_resnet34_b4_64_train": "resnet34",
-    "model_resnet50_b2_64_train": "resnet50",
+    "model_resnet34_b4_128_train": "resnet34",
     "model_resnet50_b2_64_eval": "resnet50",
-    "model_mobilenet1_b2_64_train": "mobilenet1",
+    "model_mobilenet1_b4_128_train": "mobilenet1",
     "model_mobilenet1_b2_64_eval": "mobilenet1",
 }
 
