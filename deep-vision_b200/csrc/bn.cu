@@ -65,6 +65,7 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
 #pragma unroll
         for (int i = 0; i < V; ++i) { k0[i] = mean[c + i]; k1[i] = invstd[c + i]; }
       }
+#pragma unroll 4
       for (int64_t r = r0 + trow; r < r1; r += rows_par) {
         const size_t off = (size_t)r * C + c;
         float xv[V];
@@ -108,17 +109,39 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
   }
 }
 
-template <typename T>
-__global__ void bn_stats_finalize_kernel(const T* __restrict__ x, const float* __restrict__ partial, int nblk, int C, int64_t M,
-                                         float eps, float momentum, float* __restrict__ save_mean, float* __restrict__ save_invstd,
-                                         float* __restrict__ running_mean, float* __restrict__ running_var) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s1 = 0.0, s2 = 0.0;
-  for (int b = 0; b < nblk; ++b) {
-    s1 += (double)partial[((size_t)b * 2) * C + c];
-    s2 += (double)partial[((size_t)b * 2 + 1) * C + c];
+// Finalize: 32 channels x 16 partial-lanes per CTA.  Each thread sums every 16th block partial (fp64), the 16 lanes are
+// combined through shared memory, lane 0 writes the per-channel results.
+constexpr int kFinLanes = 16;
+
+__device__ __forceinline__ void finalize_sums(const float* __restrict__ partial, int nblk, int C, int c, double& s1, double& s2) {
+  __shared__ double sh[2][kFinLanes][32];
+  const int cx = threadIdx.x & 31, ly = threadIdx.x >> 5;
+  double a1 = 0.0, a2 = 0.0;
+  if (c < C) {
+    for (int b = ly; b < nblk; b += kFinLanes) {
+      a1 += (double)partial[((size_t)b * 2) * C + c];
+      a2 += (double)partial[((size_t)b * 2 + 1) * C + c];
+    }
   }
+  sh[0][ly][cx] = a1;
+  sh[1][ly][cx] = a2;
+  __syncthreads();
+  s1 = 0.0; s2 = 0.0;
+  if (ly == 0) {
+#pragma unroll
+    for (int l = 0; l < kFinLanes; ++l) { s1 += sh[0][l][cx]; s2 += sh[1][l][cx]; }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(32 * kFinLanes)
+bn_stats_finalize_kernel(const T* __restrict__ x, const float* __restrict__ partial, int nblk, int C, int64_t M,
+                         float eps, float momentum, float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                         float* __restrict__ running_mean, float* __restrict__ running_var) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  double s1, s2;
+  finalize_sums(partial, nblk, C, c, s1, s2);
+  if ((threadIdx.x >> 5) != 0 || c >= C) return;
   const double k = (double)to_f32(x[c]);
   const double n = (double)M;
   const double m1 = s1 / n;
@@ -134,44 +157,72 @@ __global__ void bn_stats_finalize_kernel(const T* __restrict__ x, const float* _
   }
 }
 
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dgamma,
-                                       float* __restrict__ dbeta) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s1 = 0.0, s2 = 0.0;
-  for (int b = 0; b < nblk; ++b) {
-    s1 += (double)partial[((size_t)b * 2) * C + c];
-    s2 += (double)partial[((size_t)b * 2 + 1) * C + c];
-  }
+__global__ void __launch_bounds__(32 * kFinLanes)
+bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  double s1, s2;
+  finalize_sums(partial, nblk, C, c, s1, s2);
+  if ((threadIdx.x >> 5) != 0 || c >= C) return;
   dbeta[c] = (float)s1;
   dgamma[c] = (float)s2;
 }
 
-template <typename T>
+// The grid-stride is a multiple of the number of channel groups whenever C/V divides the CTA size (every channel count
+// on the path: C/V is a power of two <= 256), so a thread meets the SAME channels on every iteration: the per-channel
+// constants are folded into registers once (FIXED) instead of being re-read per 16-byte vector, and the loop is
+// unrolled four deep so each thread keeps 4-12 independent 16-byte loads in flight.
+constexpr int kUnroll = 4;
+
+template <typename T, bool FIXED>
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, const float* __restrict__ gamma,
                 const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
                 int64_t nvec, int C, int relu, int eval_mode, float eps) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % cg) * V;
-    float xv[V], rv[V], out[V];
-    Vec16<T> vx; vx.load(x + i * V); vx.unpack(xv);
-    if (res != nullptr) { Vec16<T> vr; vr.load(res + i * V); vr.unpack(rv); }
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float sc[V], sh[V];
+  auto load_consts = [&](int c) {
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const float is = eval_mode ? rsqrtf(invstd_or_var[c + j] + eps) : invstd_or_var[c + j];
-      float v = (xv[j] - mean[c + j]) * is * gamma[c + j] + beta[c + j];
-      if (res != nullptr) v += rv[j];
-      if (relu) v = fmaxf(v, 0.f);
-      out[j] = v;
+      sc[j] = is * gamma[c + j];
+      sh[j] = beta[c + j] - mean[c + j] * sc[j];
     }
-    Vec16<T> vo; vo.pack(out); vo.store(y + i * V);
+  };
+  if (FIXED) load_consts((int)(i0 % cg) * V);
+  for (int64_t i = i0; i < nvec; i += stride * kUnroll) {
+    Vec16<T> vx[kUnroll], vr[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t k = i + u * stride;
+      if (k < nvec) {
+        vx[u].load(x + k * V);
+        if (res != nullptr) vr[u].load(res + k * V);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t k = i + u * stride;
+      if (k >= nvec) break;
+      if (!FIXED) load_consts((int)(k % cg) * V);
+      float xv[V], rv[V], out[V];
+      vx[u].unpack(xv);
+      if (res != nullptr) vr[u].unpack(rv);
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float v = fmaf(xv[j], sc[j], sh[j]);
+        if (res != nullptr) v += rv[j];
+        if (relu) v = fmaxf(v, 0.f);
+        out[j] = v;
+      }
+      Vec16<T> vo; vo.pack(out); vo.store(y + k * V);
+    }
   }
 }
 
-template <typename T>
+template <typename T, bool FIXED>
 __global__ void __launch_bounds__(kThreads)
 bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
                     T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ mean,
@@ -179,25 +230,52 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
                     int64_t nvec, int C, int relu, float inv_m) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % cg) * V;
-    float xv[V], gv[V], out[V];
-    Vec16<T> vx; vx.load(x + i * V); vx.unpack(xv);
-    Vec16<T> vg; vg.load(dy + i * V); vg.unpack(gv);
-    if (relu) {
-      float yv[V];
-      Vec16<T> vy; vy.load(y + i * V); vy.unpack(yv);
-#pragma unroll
-      for (int j = 0; j < V; ++j) gv[j] = yv[j] > 0.f ? gv[j] : 0.f;
-    }
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // dx = k1*dz - k2*(x - mean) - k3   with k1 = gamma*invstd, k2 = k1*invstd*dgamma/M, k3 = k1*dbeta/M
+  float k1[V], k2[V], k3[V], mu[V];
+  auto load_consts = [&](int c) {
 #pragma unroll
     for (int j = 0; j < V; ++j) {
       const float is = invstd[c + j];
-      const float xhat = (xv[j] - mean[c + j]) * is;
-      out[j] = gamma[c + j] * is * (gv[j] - dbeta[c + j] * inv_m - xhat * dgamma[c + j] * inv_m);
+      k1[j] = gamma[c + j] * is;
+      k2[j] = k1[j] * is * dgamma[c + j] * inv_m;
+      k3[j] = k1[j] * dbeta[c + j] * inv_m;
+      mu[j] = mean[c + j];
     }
-    Vec16<T> vo; vo.pack(out); vo.store(dx + i * V);
-    if (dres != nullptr) { Vec16<T> vr; vr.pack(gv); vr.store(dres + i * V); }
+  };
+  if (FIXED) load_consts((int)(i0 % cg) * V);
+  constexpr int U = 2;
+  for (int64_t i = i0; i < nvec; i += stride * U) {
+    Vec16<T> vx[U], vg[U], vy[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t k = i + u * stride;
+      if (k < nvec) {
+        vx[u].load(x + k * V);
+        vg[u].load(dy + k * V);
+        if (relu) vy[u].load(y + k * V);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t k = i + u * stride;
+      if (k >= nvec) break;
+      if (!FIXED) load_consts((int)(k % cg) * V);
+      float xv[V], gv[V], out[V];
+      vx[u].unpack(xv);
+      vg[u].unpack(gv);
+      if (relu) {
+        float yv[V];
+        vy[u].unpack(yv);
+#pragma unroll
+        for (int j = 0; j < V; ++j) gv[j] = yv[j] > 0.f ? gv[j] : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) out[j] = fmaf(k1[j], gv[j], -fmaf(k2[j], xv[j] - mu[j], k3[j]));
+      Vec16<T> vo; vo.pack(out); vo.store(dx + k * V);
+      if (dres != nullptr) { Vec16<T> vr; vr.pack(gv); vr.store(dres + k * V); }
+    }
   }
 }
 
@@ -242,7 +320,7 @@ static int stats_t(const dv_bn_params* p, cudaStream_t st) {
   bn_reduce_kernel<T, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, (float*)p->workspace, p->M,
                                                       p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, 0);
   DV_LAUNCH_OK("bn_reduce_kernel<stats>");
-  bn_stats_finalize_kernel<T><<<ceil_div(p->C, 128), 128, 0, st>>>((const T*)p->x, (const float*)p->workspace, pl.nblk, p->C, p->M, p->eps,
+  bn_stats_finalize_kernel<T><<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const T*)p->x, (const float*)p->workspace, pl.nblk, p->C, p->M, p->eps,
                                                                   p->momentum, p->save_mean, p->save_invstd, p->running_mean,
                                                                   p->running_var);
   DV_LAUNCH_OK("bn_stats_finalize_kernel");
@@ -257,8 +335,13 @@ static int apply_t(const dv_bn_params* p, cudaStream_t st) {
   const float* mean = p->eval_mode ? p->running_mean : p->save_mean;
   const float* is = p->eval_mode ? p->running_var : p->save_invstd;
   DV_REQUIRE(mean && is, DV_ERR_ARG, "bn_apply: statistics pointers are null");
-  bn_apply_kernel<T><<<stream_grid(nvec), kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is,
-                                                            nvec, p->C, p->relu, p->eval_mode, p->eps);
+  const unsigned grid = stream_grid(ceil_div64(nvec, kUnroll));
+  if (kThreads % (p->C / V) == 0)
+    bn_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
+                                                       p->C, p->relu, p->eval_mode, p->eps);
+  else
+    bn_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
+                                                        p->C, p->relu, p->eval_mode, p->eps);
   DV_LAUNCH_OK("bn_apply_kernel");
   return DV_OK;
 }
@@ -275,7 +358,7 @@ static int bwd_reduce_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   bn_reduce_kernel<T, 1><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, p->save_mean, p->save_invstd,
                                                       (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, p->relu);
   DV_LAUNCH_OK("bn_reduce_kernel<bwd>");
-  bn_bwd_finalize_kernel<<<ceil_div(p->C, 128), 128, 0, st>>>((const float*)p->workspace, pl.nblk, p->C, p->dgamma, p->dbeta);
+  bn_bwd_finalize_kernel<<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const float*)p->workspace, pl.nblk, p->C, p->dgamma, p->dbeta);
   DV_LAUNCH_OK("bn_bwd_finalize_kernel");
   return DV_OK;
 }
@@ -286,9 +369,15 @@ static int bwd_apply_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
   DV_REQUIRE(!p->relu || p->y, DV_ERR_ARG, "bn_bwd_apply: y is required when relu is fused");
   const int64_t nvec = p->M * p->C / V;
-  bn_bwd_apply_kernel<T><<<stream_grid(nvec), kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres,
-                                                                p->gamma, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
-                                                                p->relu, 1.0f / (float)p->M);
+  const unsigned grid = stream_grid(ceil_div64(nvec, 2));
+  if (kThreads % (p->C / V) == 0)
+    bn_bwd_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
+                                                           p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C, p->relu,
+                                                           1.0f / (float)p->M);
+  else
+    bn_bwd_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
+                                                            p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C, p->relu,
+                                                            1.0f / (float)p->M);
   DV_LAUNCH_OK("bn_bwd_apply_kernel");
   return DV_OK;
 }

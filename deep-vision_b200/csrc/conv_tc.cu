@@ -145,7 +145,8 @@ struct GemmArgs {
   bf16* out;
   int M;            // output rows (pixels enumerated n,p,q)
   int Nout;         // output channels
-  int kb_per_tap;   // C_in / 64
+  int kb_per_tap;   // ceil(C_in / 64); a partial last block is zero-filled by TMA on the A side
+  int Cin;          // reduction channels per tap
   int taps, S;
   int a_im2col;     // 0: A is a 2-D [M][C] map, 1: im2col 4-D map
   int P, Q, stride, pad;
@@ -212,7 +213,7 @@ conv_tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         } else {
           tma_load_2d(sA, &tmA, &full_bar[stage], cb * kBlockK, m0);
         }
-        tma_load_2d(sB, &tmB, &full_bar[stage], kb * kBlockK, n_tile * BN);
+        tma_load_2d(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN);
         if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
@@ -406,9 +407,11 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
       tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
       tmem_ld_wait();
       if (k < g.K) {
+        const int c_left = g.C - c_tile * BNC - c * 32;  // valid input channels from this chunk on
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          if (j * 4 < c_left)
+            *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
       }
     }
   }
@@ -541,7 +544,7 @@ static WgradPlan plan_wgrad(const dv_conv_params* p) {
   WgradPlan w;
   const int P = (p->H + 2 * p->pad - p->R) / p->stride + 1, Q = (p->W + 2 * p->pad - p->S) / p->stride + 1;
   const int64_t mpix = (int64_t)p->N * P * Q;
-  w.bnc = p->C >= 256 ? 256 : p->C;  // C is a multiple of 64; 64, 128, 192 or 256 per tile
+  w.bnc = p->C >= 256 ? 256 : ceil_div(p->C, 64) * 64;  // 64, 128, 192 or 256 input channels per tile
   w.c_tiles = ceil_div(p->C, w.bnc);
   w.k_tiles = ceil_div(p->K, 128);
   w.tiles = w.k_tiles * w.c_tiles * p->R * p->S;
@@ -568,14 +571,18 @@ bool conv_tc_supported(const dv_conv_params* p, int pass, const char** why) {
   if (p->stride < 1 || p->stride > 8 || p->pad > 64 || p->R > 16 || p->S > 16) { *why = "stride/pad/filter out of TMA im2col range"; return false; }
   const int P = (p->H + 2 * p->pad - p->R) / p->stride + 1, Q = (p->W + 2 * p->pad - p->S) / p->stride + 1;
   if ((int64_t)p->N * p->H * p->W >= (1LL << 31) || (int64_t)p->N * P * Q >= (1LL << 31)) { *why = "pixel count exceeds int32"; return false; }
+  // 2-D tiled maps zero-fill a partial last 64-channel block; the im2col maps are only used with whole blocks
+  const bool plain = (p->R == 1 && p->S == 1 && p->pad == 0);
   if (pass == DV_CONV_FPROP) {
-    if (p->C % 64) { *why = "C must be a multiple of 64"; return false; }
+    if (p->C % 8 || p->C < 16) { *why = "C must be a multiple of 8 (and >= 16)"; return false; }
+    if (!(plain && p->stride == 1) && p->C % 64) { *why = "C must be a multiple of 64 for RxS>1 or strided convolutions"; return false; }
     if (p->K % 8) { *why = "K must be a multiple of 8"; return false; }
     return true;
   }
   if (pass == DV_CONV_DGRAD) {
-    if (p->K % 64) { *why = "K must be a multiple of 64"; return false; }
+    if (p->K % 8 || p->K < 16) { *why = "K must be a multiple of 8 (and >= 16)"; return false; }
     if (p->C % 8) { *why = "C must be a multiple of 8"; return false; }
+    if (!plain && p->K % 64) { *why = "K must be a multiple of 64 for RxS>1 dgrad"; return false; }
     if (p->stride == 1) {
       if (p->R - 1 - p->pad < 0 || p->S - 1 - p->pad < 0) { *why = "pad larger than filter-1"; return false; }
       return true;
@@ -585,7 +592,8 @@ bool conv_tc_supported(const dv_conv_params* p, int pass, const char** why) {
     return false;
   }
   if (pass == DV_CONV_WGRAD) {
-    if (p->C % 64 || (p->C > 256 && p->C % 256)) { *why = "C must be a multiple of 64 (of 256 above 256)"; return false; }
+    if (p->C % 8 || p->C < 16) { *why = "C must be a multiple of 8 (and >= 16)"; return false; }
+    if (!(plain && p->stride == 1) && p->C % 64) { *why = "C must be a multiple of 64 for RxS>1 or strided convolutions"; return false; }
     if (p->K % 8) { *why = "K must be a multiple of 8"; return false; }
     return true;
   }
@@ -620,7 +628,8 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     g.out = (bf16*)p->y;
     g.M = p->N * P * Q;
     g.Nout = p->K;
-    g.kb_per_tap = p->C / 64;
+    g.kb_per_tap = ceil_div(p->C, 64);
+    g.Cin = p->C;
     g.taps = p->R * p->S;
     g.S = p->S;
     g.P = P; g.Q = Q; g.stride = p->stride; g.pad = p->pad;
@@ -639,7 +648,8 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     GemmArgs g{};
     g.out = (bf16*)p->x;
     g.Nout = p->C;
-    g.kb_per_tap = p->K / 64;
+    g.kb_per_tap = ceil_div(p->K, 64);
+    g.Cin = p->K;
     const int bn = p->C <= 64 ? 64 : p->C <= 128 ? 128 : 256;
     if (p->stride == 1) {
       // dx = conv(dy, w_t) with pad' = R-1-pad: an fprop whose "input" is dy [N,P,Q,K] and whose output is [N,H,W,C]

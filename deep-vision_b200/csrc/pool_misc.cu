@@ -181,6 +181,62 @@ __global__ void filter_prep_kernel(const float* __restrict__ w, T* __restrict__ 
   }
 }
 
+// ---- explicit patch matrix for the C=3 stems ---------------------------------------------------------------------------
+// one thread per (output pixel, 8-element group of the padded row): 16-byte stores, gathers served by L1/L2
+template <typename T>
+__global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ out, int N, int H, int W, int C, int R, int S, int stride,
+                              int pad, int P, int Q, int Kp) {
+  const int groups = Kp / 8;
+  const int64_t total = (int64_t)N * P * Q * groups;
+  const int rsc = R * S * C;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    int64_t m = i / groups;
+    const int q = (int)(m % Q);
+    int64_t t = m / Q;
+    const int p = (int)(t % P);
+    const int n = (int)(t / P);
+    T v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = g * 8 + j;
+      T val = from_f32<T>(0.f);
+      if (k < rsc) {
+        const int tap = k / C, c = k - tap * C;
+        const int r = tap / S, s2 = tap - r * S;
+        const int h = p * stride + r - pad, w = q * stride + s2 - pad;
+        if ((unsigned)h < (unsigned)H && (unsigned)w < (unsigned)W) val = x[(((size_t)n * H + h) * W + w) * C + c];
+      }
+      v[j] = val;
+    }
+    T* dst = out + (size_t)m * Kp + g * 8;
+    if (sizeof(T) == 2) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+    } else {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+      *reinterpret_cast<uint4*>(dst + 4) = *reinterpret_cast<const uint4*>(v + 4);
+    }
+  }
+}
+
+template <typename T>
+__global__ void pad_rows_kernel(const float* __restrict__ src, T* __restrict__ dst, int rows, int cols, int pitch) {
+  const int64_t total = (int64_t)rows * pitch;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % pitch);
+    const int64_t r = i / pitch;
+    dst[i] = from_f32<T>(c < cols ? src[r * cols + c] : 0.f);
+  }
+}
+__global__ void unpad_rows_kernel(const float* __restrict__ src, float* __restrict__ dst, int rows, int cols, int pitch) {
+  const int64_t total = (int64_t)rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cols);
+    const int64_t r = i / cols;
+    dst[i] = src[r * pitch + c];
+  }
+}
+
 // ---- optimisers (train.py:166-205) -----------------------------------------------------------------------------------
 __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, int64_t n, float lr, float mom,
                            float wd, float gscale, int first) {
@@ -305,6 +361,33 @@ extern "C" int dv_filter_prep(const float* w, void* wo, void* wt, int K, int R, 
   DV_DISPATCH_T(dtype, (filter_prep_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>(w, (bf16*)wo, (bf16*)wt, K, R, S, C)),
                 (filter_prep_kernel<float><<<grid_for(total), kThreads, 0, st>>>(w, (float*)wo, (float*)wt, K, R, S, C)));
   DV_LAUNCH_OK("filter_prep_kernel");
+  return DV_OK;
+}
+extern "C" int dv_im2col(const void* x, void* patches, int N, int H, int W, int C, int R, int S, int stride, int pad, int Kp, int dtype,
+                         void* stream) {
+  DV_REQUIRE(x && patches && N > 0 && H > 0 && W > 0 && C > 0 && R > 0 && S > 0 && stride > 0 && pad >= 0, DV_ERR_ARG, "dv_im2col: bad arguments");
+  DV_REQUIRE(Kp % 8 == 0 && Kp >= R * S * C, DV_ERR_ARG, "dv_im2col: Kp=%d must be a multiple of 8 and >= R*S*C=%d", Kp, R * S * C);
+  const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+  const int64_t total = (int64_t)N * P * Q * (Kp / 8);
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (im2col_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)x, (bf16*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)),
+                (im2col_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)x, (float*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)));
+  DV_LAUNCH_OK("im2col_kernel");
+  return DV_OK;
+}
+extern "C" int dv_pad_rows(const float* src, void* dst, int rows, int cols, int dst_pitch, int dtype, void* stream) {
+  DV_REQUIRE(src && dst && rows > 0 && cols > 0 && dst_pitch >= cols, DV_ERR_ARG, "dv_pad_rows: bad arguments");
+  const int64_t total = (int64_t)rows * dst_pitch;
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_DISPATCH_T(dtype, (pad_rows_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>(src, (bf16*)dst, rows, cols, dst_pitch)),
+                (pad_rows_kernel<float><<<grid_for(total), kThreads, 0, st>>>(src, (float*)dst, rows, cols, dst_pitch)));
+  DV_LAUNCH_OK("pad_rows_kernel");
+  return DV_OK;
+}
+extern "C" int dv_unpad_rows(const float* src, float* dst, int rows, int cols, int src_pitch, void* stream) {
+  DV_REQUIRE(src && dst && rows > 0 && cols > 0 && src_pitch >= cols, DV_ERR_ARG, "dv_unpad_rows: bad arguments");
+  unpad_rows_kernel<<<grid_for((int64_t)rows * cols), kThreads, 0, (cudaStream_t)stream>>>(src, dst, rows, cols, src_pitch);
+  DV_LAUNCH_OK("unpad_rows_kernel");
   return DV_OK;
 }
 extern "C" int dv_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float wd, float gscale, int first,

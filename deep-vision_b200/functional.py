@@ -103,6 +103,21 @@ class FilterCache:
         self.key = None
         self.w = None
         self.w_t = None
+        self.pad_key = None
+        self.w_pad = None
+
+    def get_padded(self, weight, dtype, kp):
+        """[K][Kp] compute-dtype filters (rows zero-padded from R*S*C to Kp) for the patch-matrix path of the stems."""
+        K, Cc, R, S = weight.shape
+        key = (weight.data_ptr(), weight._version, config.weight_epoch(), dtype, weight.device, kp)
+        if key != self.pad_key:
+            wm = weight.detach()
+            if not wm.is_contiguous(memory_format=_CL):
+                wm = wm.contiguous(memory_format=_CL)
+            self.w_pad = torch.empty((K, kp), dtype=dtype, device=weight.device)
+            check(lib.dv_pad_rows(wm.data_ptr(), self.w_pad.data_ptr(), K, R * S * Cc, kp, _dv_dtype(dtype), _stream()), "dv_pad_rows")
+            self.pad_key = key
+        return self.w_pad
 
     def get(self, weight, dtype, need_t):
         K, Cc, R, S = weight.shape
@@ -153,9 +168,24 @@ class _Conv2d(torch.autograd.Function):
         P = (H + 2 * pad - R) // stride + 1
         Q = (W + 2 * pad - S) // stride + 1
         dt = _dv_dtype(x.dtype)
+        y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        # C=3 stems (resnet50.py:20-28, mobilenet_v1.py:30): explicit patch matrix + the tensor-core 1x1 path
+        ctx.patches = None
+        if (x.dtype == torch.bfloat16 and algo != DV_ALGO_SIMT and Cc < 16 and R * S * Cc <= 256 and K % 8 == 0
+                and not ctx.needs_input_grad[0]):
+            kp = -(-(R * S * Cc) // 64) * 64
+            M = N * P * Q
+            patches = torch.empty((M, kp), dtype=x.dtype, device=x.device)
+            check(lib.dv_im2col(x.data_ptr(), patches.data_ptr(), N, H, W, Cc, R, S, stride, pad, kp, dt, _stream()), "dv_im2col")
+            w_pad = cache.get_padded(weight, x.dtype, kp)
+            p = _conv_params(patches.data_ptr(), w_pad.data_ptr(), y.data_ptr(), None, M, 1, 1, kp, K, 1, 1, 1, 0, dt, DV_ALGO_TC)
+            _run_conv(lib.dv_conv_fprop, p, DV_CONV_FPROP, x.device, "dv_conv_fprop(stem)")
+            ctx.save_for_backward(patches, weight)
+            ctx.patches = (M, kp, N, Cc, H, W)
+            ctx.geom = (stride, pad, algo)
+            return y
         need_t = x.dtype != torch.float32 and ctx.needs_input_grad[0]
         w_c, w_t = cache.get(weight, x.dtype, need_t)
-        y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
         p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
         _run_conv(lib.dv_conv_fprop, p, DV_CONV_FPROP, x.device, "dv_conv_fprop")
         ctx.save_for_backward(x, weight)
@@ -170,10 +200,19 @@ class _Conv2d(torch.autograd.Function):
         dy = _nhwc(dy)
         if dy.dtype != x.dtype:
             dy = dy.to(x.dtype)
-        N, Cc, H, W = x.shape
         K, _, R, S = weight.shape
         dt = _dv_dtype(x.dtype)
         dx = dw = None
+        if ctx.patches is not None:
+            M, kp, N, Cc, H, W = ctx.patches
+            if ctx.needs_input_grad[1]:
+                dw_pad = torch.empty((K, kp), dtype=torch.float32, device=x.device)
+                p = _conv_params(x.data_ptr(), dw_pad.data_ptr(), dy.data_ptr(), None, M, 1, 1, kp, K, 1, 1, 1, 0, dt, DV_ALGO_TC)
+                _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad(stem)")
+                dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
+                check(lib.dv_unpad_rows(dw_pad.data_ptr(), dw.data_ptr(), K, R * S * Cc, kp, _stream()), "dv_unpad_rows")
+            return None, dw, None, None, None, None
+        N, Cc, H, W = x.shape
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x, memory_format=_CL)
             p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dy.data_ptr(), ctx.w_t.data_ptr() if ctx.w_t is not None else None,

@@ -65,6 +65,9 @@ _SIG = {
     "dv_conv_workspace_bytes": (C.c_size_t, [C.POINTER(ConvParams), C.c_int]),
     "dv_conv_algo": (C.c_int, [C.POINTER(ConvParams), C.c_int]),
     "dv_filter_prep": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "dv_im2col": (C.c_int, [_P, _P] + [C.c_int] * 10 + [_P]),
+    "dv_pad_rows": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "dv_unpad_rows": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dv_dwconv_fprop": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_dgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_wgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),

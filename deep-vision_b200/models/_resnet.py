@@ -6,6 +6,7 @@ resnet34.py:12-46,93-128) because it fixes both the state_dict key order and the
 """
 import torch.nn as tnn
 
+from .. import functional as F
 from .. import nn as dvnn
 
 
@@ -79,6 +80,7 @@ class BasicBlock(_Residual):
         self._shortcut(in_channels, out_channels, stride, downsample)
 
     def forward(self, x):
+        x = F.to_compute_layout(x)  # no-op inside a network; converts a raw fp32 NCHW tensor fed to a lone block
         identity = self._identity(x)
         x = self.bn1(self.conv1(x), act=self.relu)
         return self.bn2(self.conv2(x), residual=identity, act=self.relu)
@@ -100,6 +102,7 @@ class BottleneckBlock(_Residual):
         self._shortcut(in_channels, out2, stride, downsample)
 
     def forward(self, x):
+        x = F.to_compute_layout(x)
         identity = self._identity(x)
         x = self.bn1(self.conv1(x), act=self.relu)
         x = self.bn2(self.conv2(x), act=self.relu)

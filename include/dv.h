@@ -90,6 +90,18 @@ int dv_conv_algo(const dv_conv_params* p, int pass);
  * (torch keeps one fp32 OIHW tensor); this is the "NHWC plumbing" of the weight side. */
 int dv_filter_prep(const float* w_f32, void* w_out, void* w_t_out, int K, int R, int S, int C, int dtype, void* stream);
 
+/* Small-C convolutions (the C=3 stems: resnet50.py:20-28 7x7/2, mobilenet_v1.py:30 3x3/2) reach the tensor cores
+ * through an explicit patch matrix: patches[m, (r*S+s)*C + c] = x[n, p*stride+r-pad, q*stride+s-pad, c] (zero outside
+ * the image and for columns >= R*S*C), m = (n*P+p)*Q+q, row pitch Kp (a multiple of 64).  The conv is then the 1x1
+ * convolution of `patches` ([M,1,1,Kp]) with the filters padded to [K][Kp] (dv_pad_rows), and wgrad is the 1x1 wgrad
+ * followed by dv_unpad_rows.  No counterpart call in the reference: torch's conv does this internally. */
+int dv_im2col(const void* x, void* patches, int N, int H, int W, int C, int R, int S, int stride, int pad, int Kp, int dtype,
+              void* stream);
+/* dst[r, 0:cols] = src[r, 0:cols] (cast fp32 -> dtype), dst[r, cols:dst_pitch] = 0 */
+int dv_pad_rows(const float* src, void* dst, int rows, int cols, int dst_pitch, int dtype, void* stream);
+/* dst[r, 0:cols] = src[r, 0:cols] with src row pitch src_pitch (fp32 -> fp32) */
+int dv_unpad_rows(const float* src, float* dst, int rows, int cols, int src_pitch, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Depth-wise 3x3 convolution, pad 1, stride 1 or 2, groups == C.
  * Replaces nn.Conv2d(C, C, 3, padding=1, stride, groups=C, bias=False) at mobilenet_v1.py:112-122.

@@ -302,3 +302,31 @@ def test_optimisers_and_bias_match_oracle():
     torch.cuda.synchronize()
     assert rel_l2(yd.cpu().numpy(), y + b) < 1e-7
     assert rel_l2(db.cpu().numpy(), (y + b).sum(0)) < 1e-5
+
+
+@pytest.mark.parametrize("case", [(2, 3, 20, 20, 7, 2, 3), (2, 3, 16, 16, 3, 2, 1), (1, 8, 6, 7, 3, 1, 1)], ids=lambda c: "x".join(map(str, c)))
+def test_im2col_pad_unpad_match_oracle(case):
+    """dv_im2col builds exactly the patch matrix whose product with the padded filter rows is the convolution."""
+    lib = _lib()
+    N, Cc, H, W, R, stride, pad = case
+    dtype = torch.bfloat16
+    x = _rand((N, Cc, H, W), 51, dtype)
+    K = 16
+    w = _rand((K, Cc, R, R), 52, dtype, scale=0.2)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+    kp = -(-(R * R * Cc) // 64) * 64
+    xd = _dev(np.transpose(x, (0, 2, 3, 1)), dtype)
+    pat = torch.full((N * P * Q, kp), float("nan"), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_im2col(xd.data_ptr(), pat.data_ptr(), N, H, W, Cc, R, R, stride, pad, kp, _dv(dtype), stream_ptr()), "im2col")
+    wf = torch.from_numpy(np.ascontiguousarray(np.transpose(w, (0, 2, 3, 1))).astype(np.float32)).cuda()
+    wp = torch.full((K, kp), float("nan"), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_pad_rows(wf.data_ptr(), wp.data_ptr(), K, R * R * Cc, kp, _dv(dtype), stream_ptr()), "pad_rows")
+    torch.cuda.synchronize()
+    y = (pat.double() @ wp.double().t()).cpu().numpy().reshape(N, P, Q, K).transpose(0, 3, 1, 2)
+    assert rel_l2(y, ref_ops.conv2d(x, w, stride, pad)) < 1e-12       # exact operands, fp64 product
+    assert float(pat[:, R * R * Cc:].abs().sum()) == 0.0 and float(wp[:, R * R * Cc:].abs().sum()) == 0.0
+    src = torch.randn(K, kp, device="cuda")
+    dst = torch.empty(K, R * R * Cc, device="cuda")
+    lib.check(lib.lib.dv_unpad_rows(src.data_ptr(), dst.data_ptr(), K, R * R * Cc, kp, stream_ptr()), "unpad_rows")
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src[:, :R * R * Cc])

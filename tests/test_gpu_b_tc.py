@@ -24,6 +24,9 @@ TC_CASES = [
     (2, 64, 9, 9, 128, 3, 2, 1),      # 3x3 stride 2 (ResNet-34), odd size
     (2, 512, 4, 4, 1000, 1, 1, 0),    # K not a multiple of the N tile (FC-like)
     (5, 64, 6, 5, 192, 3, 1, 1),      # H != W, K=192
+    (2, 32, 8, 8, 64, 1, 1, 0),       # C=32: MobileNet's first point-wise conv; TMA zero-fills the half-empty K block
+    (3, 96, 5, 5, 32, 1, 1, 0),       # C=96 (1.5 K blocks), K=32 (tile wider than the tensor)
+    (2, 192, 6, 6, 64, 1, 1, 0),      # patch-matrix shape class of the 7x7 stem (Kp=192)
 ]
 
 
@@ -41,7 +44,7 @@ def test_tc_fprop_matches_oracle(case):
     assert np.max(np.abs(y - y_ref) / (np.abs(y_ref) + 1e-2)) < 2e-2
 
 
-DGRAD_CASES = [c for c in TC_CASES if not (c[5] == 3 and c[6] == 2) and c[4] % 64 == 0]
+DGRAD_CASES = [c for c in TC_CASES if not (c[5] == 3 and c[6] == 2) and (c[4] % 64 == 0 or (c[5] == 1 and c[4] % 8 == 0))]
 
 
 @pytest.mark.parametrize("case", DGRAD_CASES, ids=lambda c: "x".join(map(str, c)))
@@ -58,7 +61,7 @@ def test_tc_dgrad_matches_oracle(case):
     assert rel_l2(dx, dx_ref) < 2e-2
 
 
-WGRAD_CASES = [c for c in TC_CASES if c[1] % 64 == 0] + [(4, 64, 12, 12, 64, 3, 1, 1), (8, 256, 8, 8, 64, 1, 1, 0),
+WGRAD_CASES = TC_CASES + [(4, 64, 12, 12, 64, 3, 1, 1), (8, 256, 8, 8, 64, 1, 1, 0),
                                                          (2, 512, 6, 6, 128, 3, 1, 1)]
 
 
@@ -161,3 +164,24 @@ def test_tc_full_size_against_cuda_core_kernel_and_properties(case):
     dw_si = _gpu_conv(lib.DV_CONV_WGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_SIMT)
     err = float((dw_tc - dw_si).norm() / dw_si.norm())
     assert err < 1e-4, f"wgrad TC vs SIMT {err}"
+
+
+@pytest.mark.parametrize("geom", [(7, 2, 3, 64), (3, 2, 1, 32)], ids=["resnet_stem_7x7", "mobilenet_stem_3x3"])
+def test_stem_conv_module_matches_oracle(geom):
+    """The C=3 stems through the product's nn.Conv2d (patch matrix + tcgen05 GEMM, wgrad through the tensor cores)."""
+    import deep_vision_b200 as dv
+    R, stride, pad, K = geom
+    dv.set_compute_dtype(torch.bfloat16)
+    torch.manual_seed(3)
+    conv = dv.nn.Conv2d(3, K, R, stride=stride, padding=pad, bias=False).cuda()
+    x = torch.randn(4, 3, 30, 30)
+    xr = bf16_round(x.numpy())
+    wr = bf16_round(conv.weight.detach().cpu().numpy())
+    y_ref = ref_ops.conv2d(xr, wr, stride, pad)
+    dy = _rand(y_ref.shape, 9, BF)
+    _, dw_ref = ref_ops.conv2d_backward(xr, wr, dy, stride, pad)
+    y = conv(x.cuda())
+    y.backward(torch.from_numpy(dy).cuda().to(BF))
+    torch.cuda.synchronize()
+    assert rel_l2(y.detach().float().cpu().numpy(), y_ref) < 2e-2
+    assert rel_l2(conv.weight.grad.cpu().numpy(), dw_ref) < 1e-4

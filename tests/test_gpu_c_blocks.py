@@ -64,5 +64,6 @@ def test_block_fp32_matches_reference(name):
 def test_block_bf16_matches_reference(name, algo):
     errs = _run(name, torch.bfloat16, algo)
     assert errs["y"] < 2e-2, errs
-    assert all(v < 1e-3 for k, v in errs.items() if k.startswith("after/")), errs   # statistics are fp32
+    # running statistics: fp32 arithmetic, but taken over the bf16-rounded conv output (as torch autocast does)
+    assert all(v < 2e-2 for k, v in errs.items() if k.startswith("after/")), errs
     assert errs["dx"] < 1.5e-1 and all(v < 1.5e-1 for k, v in errs.items() if k.startswith("grad/")), errs
