@@ -14,7 +14,7 @@ namespace dv {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxBlocks = 592;  // 4 x 148 SMs
+constexpr int kMaxBlocks = 1184;  // 8 x 148 SMs: every SM fully occupied (2048 threads)
 
 struct Plan {
   int cg;        // channel groups (C / V)
@@ -65,25 +65,43 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
 #pragma unroll
         for (int i = 0; i < V; ++i) { k0[i] = mean[c + i]; k1[i] = invstd[c + i]; }
       }
-#pragma unroll 4
-      for (int64_t r = r0 + trow; r < r1; r += rows_par) {
-        const size_t off = (size_t)r * C + c;
-        float xv[V];
-        Vec16<T> vx; vx.load(x + off); vx.unpack(xv);
-        if (MODE == 0) {
+      // U independent 16-byte loads per stream in flight per thread (memory-level parallelism), then the arithmetic
+      constexpr int U = (MODE == 0) ? 4 : 2;
+      for (int64_t r = r0 + trow; r < r1; r += (int64_t)rows_par * U) {
+        Vec16<T> vx[U], vg[U], vy[U];
 #pragma unroll
-          for (int i = 0; i < V; ++i) { const float d = xv[i] - k0[i]; a1[i] += d; a2[i] = fmaf(d, d, a2[i]); }
-        } else {
-          float gv[V];
-          Vec16<T> vg; vg.load(dy + off); vg.unpack(gv);
-          if (relu) {
-            float yv[V];
-            Vec16<T> vy; vy.load(y + off); vy.unpack(yv);
-#pragma unroll
-            for (int i = 0; i < V; ++i) gv[i] = yv[i] > 0.f ? gv[i] : 0.f;
+        for (int u = 0; u < U; ++u) {
+          const int64_t rr = r + (int64_t)u * rows_par;
+          if (rr < r1) {
+            const size_t off = (size_t)rr * C + c;
+            vx[u].load(x + off);
+            if (MODE == 1) {
+              vg[u].load(dy + off);
+              if (relu) vy[u].load(y + off);
+            }
           }
+        }
 #pragma unroll
-          for (int i = 0; i < V; ++i) { a1[i] += gv[i]; a2[i] = fmaf(gv[i], (xv[i] - k0[i]) * k1[i], a2[i]); }
+        for (int u = 0; u < U; ++u) {
+          const int64_t rr = r + (int64_t)u * rows_par;
+          if (rr >= r1) break;
+          float xv[V];
+          vx[u].unpack(xv);
+          if (MODE == 0) {
+#pragma unroll
+            for (int i = 0; i < V; ++i) { const float d = xv[i] - k0[i]; a1[i] += d; a2[i] = fmaf(d, d, a2[i]); }
+          } else {
+            float gv[V];
+            vg[u].unpack(gv);
+            if (relu) {
+              float yv[V];
+              vy[u].unpack(yv);
+#pragma unroll
+              for (int i = 0; i < V; ++i) gv[i] = yv[i] > 0.f ? gv[i] : 0.f;
+            }
+#pragma unroll
+            for (int i = 0; i < V; ++i) { a1[i] += gv[i]; a2[i] = fmaf(gv[i], (xv[i] - k0[i]) * k1[i], a2[i]); }
+          }
         }
       }
     }

@@ -14,6 +14,7 @@
 #include "common.cuh"
 #include <cuda.h>  // CUtensorMap + enums only; the two encode entry points are resolved at run time (no -lcuda)
 #include <mutex>
+#include <stdlib.h>
 
 namespace dv {
 namespace {
@@ -53,6 +54,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       }
     }
   }
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
@@ -279,6 +283,168 @@ conv_tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// Persistent variant: one CTA per SM slot walks output tiles (n fastest, so CTAs running side by side share the same
+// activation tile through L2); the smem ring runs on across tiles and the accumulator is DOUBLE-BUFFERED in TMEM
+// (2 x BN columns), so the epilogue of tile i drains TMEM while the tensor core already works on tile i+1.
+// ------------------------------------------------------------------------------------------------------------
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(kThreads)
+conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+  constexpr int ACC = 2;
+  constexpr int kBBytes = BN * kBlockK * 2;
+  constexpr int kStageBytes = kABytes + kBBytes;
+  constexpr uint32_t kTmemCols = ACC * BN;  // 128, 256 or 512: powers of two
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + ACC;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + ACC);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_n = (g.Nout + BN - 1) / BN;
+  const int num_m = (g.M + kBlockM - 1) / kBlockM;
+  const int total = num_m * num_n;
+  const int num_kb = g.taps * g.kb_per_tap;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < ACC; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 4);  // one arrival per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const int n_tile = tile % num_n, m_tile = tile / num_n;
+        const int m0 = m_tile * kBlockM;
+        int n_img = 0, h0 = 0, w0 = 0;
+        if (g.a_im2col) {
+          const int pq = g.P * g.Q;
+          n_img = m0 / pq;
+          const int rem = m0 - n_img * pq;
+          const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
+          h0 = p0 * g.stride - g.pad;
+          w0 = q0 * g.stride - g.pad;
+        }
+        int tap = 0, cb = 0;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sA = smem + stage * kStageBytes;
+          uint8_t* sB = sA + kABytes;
+          mbar_expect_tx(&full_bar[stage], kStageBytes);
+          if (g.a_im2col) {
+            const int r = tap / g.S, s = tap - r * g.S;
+            tma_load_im2col(sA, &tmA, &full_bar[stage], cb * kBlockK, w0, h0, n_img, (uint16_t)s, (uint16_t)r);
+          } else {
+            tma_load_2d(sA, &tmA, &full_bar[stage], cb * kBlockK, m0);
+          }
+          tma_load_2d(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN);
+          if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, 0);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);  // the epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sA = smem_u32(smem + stage * kStageBytes);
+          const uint32_t sB = sA + kABytes;
+#pragma unroll
+          for (int k = 0; k < kBlockK / 16; ++k) {
+            const uint64_t ad = make_smem_desc(sA + k * 32, 16, 1024);
+            const uint64_t bd = make_smem_desc(sB + k * 32, 16, 1024);
+            umma_f16(d_tmem, ad, bd, idesc, (kb | k) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[acc]);
+        if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const int n_tile = tile % num_n, m_tile = tile / num_n;
+      const int m = m_tile * kBlockM + quarter * 32 + lane;
+      size_t row_off = 0;
+      if (m < g.M) {
+        if (g.scatter) {
+          const int pq = g.P * g.Q;
+          const int n_img = m / pq, rem = m - n_img * pq;
+          const int p = rem / g.Q, q = rem - p * g.Q;
+          row_off = (((size_t)n_img * g.Ho + (size_t)p * g.os) * g.Wo + (size_t)q * g.os) * g.Nout;
+        } else {
+          row_off = (size_t)m * g.Nout;
+        }
+      }
+      bf16* orow = g.out + row_off + (size_t)n_tile * BN;
+      const int n_left = g.Nout - n_tile * BN;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_addr + (uint32_t)(c * 32), v);
+        tmem_ld_wait();
+        if (m < g.M) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (c * 32 + j * 8 < n_left) {
+              uint32_t w[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
+                w[e] = *reinterpret_cast<uint32_t*>(&h);
+              }
+              *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+          }
+        }
+      }
+      // all of this warp's TMEM reads are complete: hand the accumulator back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty_bar[acc]);
+      if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
     }
   }
   tc_fence_before();
@@ -525,6 +691,23 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   return DV_OK;
 }
 
+template <int BN, int STAGES>
+static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, cudaStream_t st) {
+  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + 1024 + 256;
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int total = ceil_div(g.Nout, BN) * ceil_div(g.M, kBlockM);
+  const int slots = num_sms() * (BN == 256 ? 1 : 2);  // 2 x BN TMEM columns and the smem ring bound residency
+  const int grid = total < slots ? total : slots;
+  conv_tc_gemm_persistent_kernel<BN, STAGES><<<grid, kThreads, smem, st>>>(tmA, tmB, g);
+  DV_LAUNCH_OK("conv_tc_gemm_persistent_kernel");
+  return DV_OK;
+}
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
 template <int BNC, int STAGES>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradArgs& g, int tiles, int splits,
                         cudaStream_t st) {
@@ -549,8 +732,10 @@ static WgradPlan plan_wgrad(const dv_conv_params* p) {
   w.k_tiles = ceil_div(p->K, 128);
   w.tiles = w.k_tiles * w.c_tiles * p->R * p->S;
   w.kb_total = (int)ceil_div64(mpix, 64);
-  int want = ceil_div(2 * num_sms(), w.tiles);
-  int max_by_len = w.kb_total / 8 > 0 ? w.kb_total / 8 : 1;  // at least 8 stages of work per CTA
+  // one wave of CTAs: 2 per SM while the ring fits twice (BNC <= 128), else 1; never less than 4 stages of work each
+  const int slots = num_sms() * (w.bnc <= 128 ? 2 : 1);
+  int want = slots / w.tiles;
+  int max_by_len = w.kb_total / 4 > 0 ? w.kb_total / 4 : 1;
   int splits = want < max_by_len ? want : max_by_len;
   if (splits < 1) splits = 1;
   w.kb_per_split = ceil_div(w.kb_total, splits);
@@ -607,7 +792,22 @@ size_t conv_tc_workspace(const dv_conv_params* p, int pass) {
   return (size_t)w.splits * p->K * p->R * p->S * p->C * sizeof(float);
 }
 
+static int pick_bn(int nout) {
+  static const int forced = env_int("DV_TC_BN", 0);  // experiment knob: cap the N tile
+  int bn = nout <= 64 ? 64 : nout <= 128 ? 128 : 256;
+  if (forced && bn > forced) bn = forced;
+  return bn;
+}
+
 static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, cudaStream_t st) {
+  static const int legacy = env_int("DV_TC_LEGACY", 0);  // 1 = one tile per CTA (the first implementation), for A/B runs
+  if (!legacy) {
+    switch (bn) {
+      case 64: return launch_gemm_persistent<64, 4>(tmA, tmB, g, st);
+      case 128: return launch_gemm_persistent<128, 3>(tmA, tmB, g, st);
+      default: return launch_gemm_persistent<256, 4>(tmA, tmB, g, st);
+    }
+  }
   switch (bn) {
     case 64: return launch_gemm<64, 4>(tmA, tmB, g, st);
     case 128: return launch_gemm<128, 3>(tmA, tmB, g, st);
@@ -634,7 +834,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     g.S = p->S;
     g.P = P; g.Q = Q; g.stride = p->stride; g.pad = p->pad;
     g.a_im2col = !(p->R == 1 && p->S == 1 && p->stride == 1 && p->pad == 0);
-    const int bn = p->K <= 64 ? 64 : p->K <= 128 ? 128 : 256;
+    const int bn = pick_bn(p->K);
     if (g.a_im2col) rc = make_map_im2col(&tmA, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, kBlockM);
     else rc = make_map_2d(&tmA, p->x, (uint64_t)g.M, (uint64_t)p->C, kBlockM);
     if (rc) return rc;
@@ -650,7 +850,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     g.Nout = p->C;
     g.kb_per_tap = ceil_div(p->K, 64);
     g.Cin = p->K;
-    const int bn = p->C <= 64 ? 64 : p->C <= 128 ? 128 : 256;
+    const int bn = pick_bn(p->C);
     if (p->stride == 1) {
       // dx = conv(dy, w_t) with pad' = R-1-pad: an fprop whose "input" is dy [N,P,Q,K] and whose output is [N,H,W,C]
       const int padp = p->R - 1 - p->pad;
