@@ -41,8 +41,9 @@ static Plan make_plan(int64_t M, int C, int V) {
 template <typename T, int MODE>
 __global__ void __launch_bounds__(kThreads)
 bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, const float* __restrict__ mean,
-                 const float* __restrict__ invstd, float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par,
-                 int64_t rows_per_blk, int relu) {
+                 const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta,
+                 float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par, int64_t rows_per_blk, int relu) {
+  // relu: 0 = no activation, 1 = mask from the stored output y, 2 = mask recomputed from x exactly as bn_apply computed it
   constexpr int V = Vec16<T>::N;
   __shared__ float red[2][kThreads * V];
   const int tcg = threadIdx.x % cgb, trow = threadIdx.x / cgb;
@@ -54,9 +55,9 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
   for (int g0 = 0; g0 < cg; g0 += cgb) {
     const int g = g0 + tcg;
     const int c = g * V;
-    float a1[V], a2[V], k0[V], k1[V];
+    float a1[V], a2[V], k0[V], k1[V], msc[V], msh[V];
 #pragma unroll
-    for (int i = 0; i < V; ++i) { a1[i] = 0.f; a2[i] = 0.f; k0[i] = 0.f; k1[i] = 1.f; }
+    for (int i = 0; i < V; ++i) { a1[i] = 0.f; a2[i] = 0.f; k0[i] = 0.f; k1[i] = 1.f; msc[i] = 0.f; msh[i] = 0.f; }
     if (active && g < cg) {
       if (MODE == 0) {
         Vec16<T> v0; v0.load(x + c);  // row 0 as the shift
@@ -64,6 +65,10 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
       } else {
 #pragma unroll
         for (int i = 0; i < V; ++i) { k0[i] = mean[c + i]; k1[i] = invstd[c + i]; }
+        if (relu == 2) {
+#pragma unroll
+          for (int i = 0; i < V; ++i) { msc[i] = k1[i] * gamma[c + i]; msh[i] = beta[c + i] - k0[i] * msc[i]; }
+        }
       }
       // U independent 16-byte loads per stream in flight per thread (memory-level parallelism), then the arithmetic
       constexpr int U = (MODE == 0) ? 4 : 2;
@@ -77,7 +82,7 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
             vx[u].load(x + off);
             if (MODE == 1) {
               vg[u].load(dy + off);
-              if (relu) vy[u].load(y + off);
+              if (relu == 1) vy[u].load(y + off);
             }
           }
         }
@@ -93,11 +98,14 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
           } else {
             float gv[V];
             vg[u].unpack(gv);
-            if (relu) {
+            if (relu == 1) {
               float yv[V];
               vy[u].unpack(yv);
 #pragma unroll
               for (int i = 0; i < V; ++i) gv[i] = yv[i] > 0.f ? gv[i] : 0.f;
+            } else if (relu == 2) {
+#pragma unroll
+              for (int i = 0; i < V; ++i) gv[i] = fmaf(xv[i], msc[i], msh[i]) > 0.f ? gv[i] : 0.f;
             }
 #pragma unroll
             for (int i = 0; i < V; ++i) { a1[i] += gv[i]; a2[i] = fmaf(gv[i], (xv[i] - k0[i]) * k1[i], a2[i]); }
@@ -243,15 +251,15 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
 template <typename T, bool FIXED>
 __global__ void __launch_bounds__(kThreads)
 bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
-                    T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ mean,
-                    const float* __restrict__ invstd, const float* __restrict__ dgamma, const float* __restrict__ dbeta,
-                    int64_t nvec, int C, int relu, float inv_m) {
+                    T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ dgamma,
+                    const float* __restrict__ dbeta, int64_t nvec, int C, int relu, float inv_m) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   // dx = k1*dz - k2*(x - mean) - k3   with k1 = gamma*invstd, k2 = k1*invstd*dgamma/M, k3 = k1*dbeta/M
-  float k1[V], k2[V], k3[V], mu[V];
+  float k1[V], k2[V], k3[V], mu[V], msc[V], msh[V];
   auto load_consts = [&](int c) {
 #pragma unroll
     for (int j = 0; j < V; ++j) {
@@ -260,6 +268,10 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
       k2[j] = k1[j] * is * dgamma[c + j] * inv_m;
       k3[j] = k1[j] * dbeta[c + j] * inv_m;
       mu[j] = mean[c + j];
+      if (relu == 2) {  // same expressions as bn_apply_kernel, so the recomputed sign is the forward's
+        msc[j] = is * gamma[c + j];
+        msh[j] = beta[c + j] - mu[j] * msc[j];
+      }
     }
   };
   if (FIXED) load_consts((int)(i0 % cg) * V);
@@ -272,7 +284,7 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
       if (k < nvec) {
         vx[u].load(x + k * V);
         vg[u].load(dy + k * V);
-        if (relu) vy[u].load(y + k * V);
+        if (relu == 1) vy[u].load(y + k * V);
       }
     }
 #pragma unroll
@@ -283,11 +295,14 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
       float xv[V], gv[V], out[V];
       vx[u].unpack(xv);
       vg[u].unpack(gv);
-      if (relu) {
+      if (relu == 1) {
         float yv[V];
         vy[u].unpack(yv);
 #pragma unroll
         for (int j = 0; j < V; ++j) gv[j] = yv[j] > 0.f ? gv[j] : 0.f;
+      } else if (relu == 2) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) gv[j] = fmaf(xv[j], msc[j], msh[j]) > 0.f ? gv[j] : 0.f;
       }
 #pragma unroll
       for (int j = 0; j < V; ++j) out[j] = fmaf(k1[j], gv[j], -fmaf(k2[j], xv[j] - mu[j], k3[j]));
@@ -335,8 +350,8 @@ static int stats_t(const dv_bn_params* p, cudaStream_t st) {
   const size_t need = (size_t)pl.nblk * 2 * p->C * sizeof(float);
   DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "bn_stats: workspace %zu bytes required, %zu given", need,
              p->workspace_bytes);
-  bn_reduce_kernel<T, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, (float*)p->workspace, p->M,
-                                                      p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, 0);
+  bn_reduce_kernel<T, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                                      (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, 0);
   DV_LAUNCH_OK("bn_reduce_kernel<stats>");
   bn_stats_finalize_kernel<T><<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const T*)p->x, (const float*)p->workspace, pl.nblk, p->C, p->M, p->eps,
                                                                   p->momentum, p->save_mean, p->save_invstd, p->running_mean,
@@ -372,9 +387,11 @@ static int bwd_reduce_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   const size_t need = (size_t)pl.nblk * 2 * p->C * sizeof(float);
   DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "bn_bwd_reduce: workspace %zu bytes required, %zu given",
              need, p->workspace_bytes);
-  DV_REQUIRE(!p->relu || p->y, DV_ERR_ARG, "bn_bwd_reduce: y is required when relu is fused");
+  DV_REQUIRE(!p->relu || p->y || p->beta, DV_ERR_ARG, "bn_bwd_reduce: relu needs y (stored mask) or beta (recomputed mask)");
+  const int relu_mode = !p->relu ? 0 : (p->y ? 1 : 2);
   bn_reduce_kernel<T, 1><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, p->save_mean, p->save_invstd,
-                                                      (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, p->relu);
+                                                      p->gamma, p->beta, (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par,
+                                                      pl.rows_per_blk, relu_mode);
   DV_LAUNCH_OK("bn_reduce_kernel<bwd>");
   bn_bwd_finalize_kernel<<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const float*)p->workspace, pl.nblk, p->C, p->dgamma, p->dbeta);
   DV_LAUNCH_OK("bn_bwd_finalize_kernel");
@@ -385,17 +402,18 @@ template <typename T>
 static int bwd_apply_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
-  DV_REQUIRE(!p->relu || p->y, DV_ERR_ARG, "bn_bwd_apply: y is required when relu is fused");
+  DV_REQUIRE(!p->relu || p->y || p->beta, DV_ERR_ARG, "bn_bwd_apply: relu needs y (stored mask) or beta (recomputed mask)");
+  const int relu_mode = !p->relu ? 0 : (p->y ? 1 : 2);
   const int64_t nvec = p->M * p->C / V;
   const unsigned grid = stream_grid(ceil_div64(nvec, 2));
   if (kThreads % (p->C / V) == 0)
     bn_bwd_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
-                                                           p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C, p->relu,
-                                                           1.0f / (float)p->M);
+                                                           p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
+                                                           relu_mode, 1.0f / (float)p->M);
   else
     bn_bwd_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
-                                                            p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C, p->relu,
-                                                            1.0f / (float)p->M);
+                                                            p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
+                                                            relu_mode, 1.0f / (float)p->M);
   DV_LAUNCH_OK("bn_bwd_apply_kernel");
   return DV_OK;
 }

@@ -122,6 +122,8 @@ conv_simt_kernel(Operand<PASS, T> op, TO* __restrict__ out, int64_t M, int64_t N
       if (PASS == DV_CONV_WGRAD) {
         if (atomic) atomicAdd(reinterpret_cast<float*>(out) + m * Ng + n, acc[i][j]);
         else reinterpret_cast<float*>(out)[m * Ng + n] = acc[i][j];
+      } else if (atomic) {  // dgrad with accumulate: dx += result
+        out[m * Ng + n] = from_f32<TO>(acc[i][j] + to_f32(out[m * Ng + n]));
       } else {
         out[m * Ng + n] = from_f32<TO>(acc[i][j]);
       }
@@ -163,7 +165,8 @@ static int launch(const dv_conv_params* p, const ConvDims& d, cudaStream_t st) {
   }
   DV_REQUIRE(gy <= 65535, DV_ERR_UNSUPPORTED, "conv_simt: N tiles %lld exceed grid.y", (long long)gy);
   dim3 grid((unsigned)gx, (unsigned)gy, (unsigned)splits);
-  conv_simt_kernel<PASS, T, TO><<<grid, 256, 0, st>>>(op, (TO*)out, M, Ng, Kg, k_per_split, splits > 1 ? 1 : 0);
+  const int flag = (PASS == DV_CONV_WGRAD) ? (splits > 1 ? 1 : 0) : (PASS == DV_CONV_DGRAD && p->accumulate ? 1 : 0);
+  conv_simt_kernel<PASS, T, TO><<<grid, 256, 0, st>>>(op, (TO*)out, M, Ng, Kg, k_per_split, flag);
   DV_LAUNCH_OK("conv_simt_kernel");
   return DV_OK;
 }

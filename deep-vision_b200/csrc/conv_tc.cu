@@ -156,142 +156,12 @@ struct GemmArgs {
   int P, Q, stride, pad;
   int scatter;      // 1: row (n,p,q) is written at pixel (n, p*os, q*os) of an [*, Ho, Wo, Nout] tensor
   int Ho, Wo, os;
+  int out_f32;      // 1: `out` is float* (fp32 logits of the classifier)
+  int accumulate;   // 1: out += result (bf16 read-modify-write by the owning thread)
 };
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(kThreads)
-conv_tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
-  constexpr int kBBytes = BN * kBlockK * 2;
-  constexpr int kStageBytes = kABytes + kBBytes;
-  constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
-  uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* tmem_full_bar = empty_bar + STAGES;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_tile = blockIdx.x, m_tile = blockIdx.y;
-  const int m0 = m_tile * kBlockM;
-  const int num_kb = g.taps * g.kb_per_tap;
-
-  if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmA);
-    prefetch_tmap(&tmB);
-    for (int i = 0; i < STAGES; ++i) {
-      mbar_init(&full_bar[i], 1);
-      mbar_init(&empty_bar[i], 1);
-    }
-    mbar_init(tmem_full_bar, 1);
-    fence_barrier_init();
-  }
-  if (warp == 1) tmem_alloc(tmem_ptr, kTmemCols);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
-
-  if (warp == 0) {
-    if (lane == 0) {
-      int n_img = 0, h0 = 0, w0 = 0;
-      if (g.a_im2col) {
-        const int pq = g.P * g.Q;
-        n_img = m0 / pq;
-        const int rem = m0 - n_img * pq;
-        const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
-        h0 = p0 * g.stride - g.pad;
-        w0 = q0 * g.stride - g.pad;
-      }
-      int stage = 0;
-      uint32_t phase = 0;
-      int tap = 0, cb = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sA = smem + stage * kStageBytes;
-        uint8_t* sB = sA + kABytes;
-        mbar_expect_tx(&full_bar[stage], kStageBytes);
-        if (g.a_im2col) {
-          const int r = tap / g.S, s = tap - r * g.S;
-          tma_load_im2col(sA, &tmA, &full_bar[stage], cb * kBlockK, w0, h0, n_img, (uint16_t)s, (uint16_t)r);
-        } else {
-          tma_load_2d(sA, &tmA, &full_bar[stage], cb * kBlockK, m0);
-        }
-        tma_load_2d(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN);
-        if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, 0);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t sA = smem_u32(smem + stage * kStageBytes);
-        const uint32_t sB = sA + kABytes;
-#pragma unroll
-        for (int k = 0; k < kBlockK / 16; ++k) {
-          // K-major SWIZZLE_128B: 8-row groups 1024 B apart; a 16-element K step is +32 B inside the swizzle row
-          const uint64_t ad = make_smem_desc(sA + k * 32, 16, 1024);
-          const uint64_t bd = make_smem_desc(sB + k * 32, 16, 1024);
-          umma_f16(tmem_base, ad, bd, idesc, (kb | k) ? 1u : 0u);
-        }
-        umma_commit(&empty_bar[stage]);
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
-      }
-      umma_commit(tmem_full_bar);
-    }
-    __syncwarp();
-  } else {
-    // epilogue: TMEM -> registers -> bf16 -> global
-    const int quarter = warp & 3;
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    const int m = m0 + quarter * 32 + lane;
-    size_t row_off = 0;
-    if (m < g.M) {
-      if (g.scatter) {
-        const int pq = g.P * g.Q;
-        const int n_img = m / pq, rem = m - n_img * pq;
-        const int p = rem / g.Q, q = rem - p * g.Q;
-        row_off = (((size_t)n_img * g.Ho + (size_t)p * g.os) * g.Wo + (size_t)q * g.os) * g.Nout;
-      } else {
-        row_off = (size_t)m * g.Nout;
-      }
-    }
-    bf16* orow = g.out + row_off + (size_t)n_tile * BN;
-    const int n_left = g.Nout - n_tile * BN;  // valid columns in this tile
-#pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      uint32_t v[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
-      tmem_ld_wait();
-      if (m < g.M) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (c * 32 + j * 8 < n_left) {
-            uint32_t w[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
-              w[e] = *reinterpret_cast<uint32_t*>(&h);
-            }
-            *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = make_uint4(w[0], w[1], w[2], w[3]);
-          }
-        }
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
-}
-
 // ------------------------------------------------------------------------------------------------------------
-// Persistent variant: one CTA per SM slot walks output tiles (n fastest, so CTAs running side by side share the same
+// GEMM-shaped kernel (fprop / dgrad), persistent: one CTA per SM slot walks output tiles (n fastest, so CTAs running side by side share the same
 // activation tile through L2); the smem ring runs on across tiles and the accumulator is DOUBLE-BUFFERED in TMEM
 // (2 x BN columns), so the epilogue of tile i drains TMEM while the tensor core already works on tile i+1.
 // ------------------------------------------------------------------------------------------------------------
@@ -416,6 +286,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
         }
       }
       bf16* orow = g.out + row_off + (size_t)n_tile * BN;
+      float* orow32 = reinterpret_cast<float*>(g.out) + row_off + (size_t)n_tile * BN;
       const int n_left = g.Nout - n_tile * BN;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
@@ -426,16 +297,32 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
         tmem_ld_32x32(t_addr + (uint32_t)(c * 32), v);
         tmem_ld_wait();
         if (m < g.M) {
+          if (g.out_f32) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (c * 32 + j * 8 < n_left) {
-              uint32_t w[4];
+            for (int j = 0; j < 8; ++j)
+              if (c * 32 + j * 4 < n_left)
+                *reinterpret_cast<uint4*>(orow32 + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          } else {
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
-                w[e] = *reinterpret_cast<uint32_t*>(&h);
+            for (int j = 0; j < 4; ++j) {
+              if (c * 32 + j * 8 < n_left) {
+                uint32_t w[4];
+                if (g.accumulate) {
+                  const uint4 old = *reinterpret_cast<const uint4*>(orow + c * 32 + j * 8);
+                  const uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    v[j * 8 + 2 * e] = __float_as_uint(__uint_as_float(v[j * 8 + 2 * e]) + __uint_as_float(ow[e] << 16));
+                    v[j * 8 + 2 * e + 1] = __float_as_uint(__uint_as_float(v[j * 8 + 2 * e + 1]) + __uint_as_float(ow[e] & 0xffff0000u));
+                  }
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
+                  w[e] = *reinterpret_cast<uint32_t*>(&h);
+                }
+                *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = make_uint4(w[0], w[1], w[2], w[3]);
               }
-              *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = make_uint4(w[0], w[1], w[2], w[3]);
             }
           }
         }
@@ -681,17 +568,6 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 template <int BN, int STAGES>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, cudaStream_t st) {
-  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + 1024 + 256;
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  dim3 grid((unsigned)ceil_div(g.Nout, BN), (unsigned)ceil_div(g.M, kBlockM));
-  DV_REQUIRE(grid.y <= 65535, DV_ERR_UNSUPPORTED, "conv_tc: %u M tiles exceed grid.y", grid.y);
-  conv_tc_gemm_kernel<BN, STAGES><<<grid, kThreads, smem, st>>>(tmA, tmB, g);
-  DV_LAUNCH_OK("conv_tc_gemm_kernel");
-  return DV_OK;
-}
-
-template <int BN, int STAGES>
 static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + 1024 + 256;
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -752,7 +628,8 @@ bool conv_tc_supported(const dv_conv_params* p, int pass, const char** why) {
   static const char* ok = "";
   *why = ok;
   if (p->dtype != DV_BF16) { *why = "tensor-core path is bf16 only"; return false; }
-  if (p->y_f32) { *why = "fp32 output is SIMT only"; return false; }
+  if (p->y_f32 && pass != DV_CONV_FPROP) { *why = "fp32 output exists for fprop only"; return false; }
+  if (p->y_f32 && p->K % 4) { *why = "fp32 output needs K % 4 == 0"; return false; }
   if (p->stride < 1 || p->stride > 8 || p->pad > 64 || p->R > 16 || p->S > 16) { *why = "stride/pad/filter out of TMA im2col range"; return false; }
   const int P = (p->H + 2 * p->pad - p->R) / p->stride + 1, Q = (p->W + 2 * p->pad - p->S) / p->stride + 1;
   if ((int64_t)p->N * p->H * p->W >= (1LL << 31) || (int64_t)p->N * P * Q >= (1LL << 31)) { *why = "pixel count exceeds int32"; return false; }
@@ -800,18 +677,10 @@ static int pick_bn(int nout) {
 }
 
 static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, cudaStream_t st) {
-  static const int legacy = env_int("DV_TC_LEGACY", 0);  // 1 = one tile per CTA (the first implementation), for A/B runs
-  if (!legacy) {
-    switch (bn) {
-      case 64: return launch_gemm_persistent<64, 4>(tmA, tmB, g, st);
-      case 128: return launch_gemm_persistent<128, 3>(tmA, tmB, g, st);
-      default: return launch_gemm_persistent<256, 4>(tmA, tmB, g, st);
-    }
-  }
   switch (bn) {
-    case 64: return launch_gemm<64, 4>(tmA, tmB, g, st);
-    case 128: return launch_gemm<128, 3>(tmA, tmB, g, st);
-    default: return launch_gemm<256, 4>(tmA, tmB, g, st);
+    case 64: return launch_gemm_persistent<64, 4>(tmA, tmB, g, st);
+    case 128: return launch_gemm_persistent<128, 3>(tmA, tmB, g, st);
+    default: return launch_gemm_persistent<256, 4>(tmA, tmB, g, st);
   }
 }
 
@@ -834,6 +703,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     g.S = p->S;
     g.P = P; g.Q = Q; g.stride = p->stride; g.pad = p->pad;
     g.a_im2col = !(p->R == 1 && p->S == 1 && p->stride == 1 && p->pad == 0);
+    g.out_f32 = p->y_f32 ? 1 : 0;
     const int bn = pick_bn(p->K);
     if (g.a_im2col) rc = make_map_im2col(&tmA, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, kBlockM);
     else rc = make_map_2d(&tmA, p->x, (uint64_t)g.M, (uint64_t)p->C, kBlockM);
@@ -847,6 +717,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     DV_REQUIRE(p->w_t != nullptr && aligned16(p->w_t), DV_ERR_ARG, "conv_tc dgrad: w_t (flipped [C,R,S,K] filters from dv_filter_prep) is required");
     GemmArgs g{};
     g.out = (bf16*)p->x;
+    g.accumulate = p->accumulate ? 1 : 0;
     g.Nout = p->C;
     g.kb_per_tap = ceil_div(p->K, 64);
     g.Cin = p->K;
@@ -863,7 +734,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
       else rc = make_map_2d(&tmA, p->y, (uint64_t)g.M, (uint64_t)p->K, kBlockM);
     } else {
       // 1x1 stride s: dx[n, p*s, q*s, :] = dy[n,p,q,:] * w ; every other pixel of dx is zero
-      DV_CUDA_OK(cudaMemsetAsync(p->x, 0, (size_t)p->N * p->H * p->W * p->C * sizeof(bf16), st));
+      if (!p->accumulate) DV_CUDA_OK(cudaMemsetAsync(p->x, 0, (size_t)p->N * p->H * p->W * p->C * sizeof(bf16), st));
       g.M = p->N * P * Q;
       g.taps = 1;
       g.S = 1;

@@ -30,7 +30,7 @@ __global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, u
     const int p = (int)(pix % P);
     const int n = (int)(pix / P);
     float best[V];
-    uint8_t bi[V];
+    __align__(8) uint8_t bi[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) { best[j] = -CUDART_INF_F; bi[j] = 0; }
     bool first = true;
@@ -53,8 +53,8 @@ __global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, u
     }
     const size_t o = (size_t)(i / cg) * C + c;
     Vec16<T> out; out.pack(best); out.store(y + o);
-#pragma unroll
-    for (int j = 0; j < V; ++j) idx[o + j] = bi[j];
+    if (V == 8) *reinterpret_cast<uint2*>(idx + o) = *reinterpret_cast<const uint2*>(bi);   // o is a multiple of V
+    else *reinterpret_cast<uint32_t*>(idx + o) = *reinterpret_cast<const uint32_t*>(bi);
   }
 }
 
@@ -86,8 +86,11 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __re
         const size_t o = (((size_t)n * P + p) * Q + q) * C + c;
         float g[V];
         Vec16<T> a; a.load(dy + o); a.unpack(g);
+        __align__(8) uint8_t ti[V];
+        if (V == 8) *reinterpret_cast<uint2*>(ti) = *reinterpret_cast<const uint2*>(idx + o);
+        else *reinterpret_cast<uint32_t*>(ti) = *reinterpret_cast<const uint32_t*>(idx + o);
 #pragma unroll
-        for (int j = 0; j < V; ++j) acc[j] += (idx[o + j] == tap) ? g[j] : 0.f;
+        for (int j = 0; j < V; ++j) acc[j] += (ti[j] == tap) ? g[j] : 0.f;
       }
     }
     Vec16<T> out; out.pack(acc); out.store(dx + (size_t)(i / cg) * C + c);
@@ -182,39 +185,47 @@ __global__ void filter_prep_kernel(const float* __restrict__ w, T* __restrict__ 
 }
 
 // ---- explicit patch matrix for the C=3 stems ---------------------------------------------------------------------------
-// one thread per (output pixel, 8-element group of the padded row): 16-byte stores, gathers served by L1/L2
+// One CTA per output row (n,p): the R input rows it touches are staged in shared memory WITH their zero margins
+// (coalesced 2-byte-element rows, whole-row reads), so every filter row of a patch is S*C CONTIGUOUS staged elements
+// and needs no bounds test; a k -> smem-offset table removes all divisions from the inner loop.  Patch rows leave as
+// 16-byte stores.
 template <typename T>
-__global__ void im2col_kernel(const T* __restrict__ x, T* __restrict__ out, int N, int H, int W, int C, int R, int S, int stride,
-                              int pad, int P, int Q, int Kp) {
+__global__ void __launch_bounds__(256)
+im2col_kernel(const T* __restrict__ x, T* __restrict__ out, int N, int H, int W, int C, int R, int S, int stride, int pad, int P,
+              int Q, int Kp) {
+  extern __shared__ __align__(16) unsigned char im2col_smem[];
+  const int Lp = (W + 2 * pad) * C;                    // staged row length incl. margins
+  T* rows = reinterpret_cast<T*>(im2col_smem);        // [R][Lp]
+  int* koff = reinterpret_cast<int*>(im2col_smem + (((size_t)R * Lp * sizeof(T) + 15) & ~(size_t)15));  // [Kp]
+  const int n = blockIdx.x / P, p = blockIdx.x % P;
+  const int rsc = R * S * C, sc = S * C;
+  for (int k = threadIdx.x; k < Kp; k += blockDim.x) koff[k] = k < rsc ? (k / sc) * Lp + (k % sc) : -1;
+  for (int i = threadIdx.x; i < R * Lp; i += blockDim.x) {
+    const int r = i / Lp, e = i - r * Lp;
+    const int h = p * stride + r - pad;
+    const int we = e - pad * C;                        // element index inside the real row
+    T v = from_f32<T>(0.f);
+    if ((unsigned)h < (unsigned)H && (unsigned)we < (unsigned)(W * C)) v = x[((size_t)n * H + h) * W * C + we];
+    rows[i] = v;
+  }
+  __syncthreads();
   const int groups = Kp / 8;
-  const int64_t total = (int64_t)N * P * Q * groups;
-  const int rsc = R * S * C;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int g = (int)(i % groups);
-    int64_t m = i / groups;
-    const int q = (int)(m % Q);
-    int64_t t = m / Q;
-    const int p = (int)(t % P);
-    const int n = (int)(t / P);
-    T v[8];
+  T* orow = out + ((size_t)n * P + p) * Q * Kp;
+  for (int v = threadIdx.x; v < Q * groups; v += blockDim.x) {
+    const int q = v / groups, g = v - q * groups;
+    const int base = q * stride * C;
+    T vals[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int k = g * 8 + j;
-      T val = from_f32<T>(0.f);
-      if (k < rsc) {
-        const int tap = k / C, c = k - tap * C;
-        const int r = tap / S, s2 = tap - r * S;
-        const int h = p * stride + r - pad, w = q * stride + s2 - pad;
-        if ((unsigned)h < (unsigned)H && (unsigned)w < (unsigned)W) val = x[(((size_t)n * H + h) * W + w) * C + c];
-      }
-      v[j] = val;
+      const int o = koff[g * 8 + j];
+      vals[j] = o >= 0 ? rows[o + base] : from_f32<T>(0.f);
     }
-    T* dst = out + (size_t)m * Kp + g * 8;
+    T* dst = orow + (size_t)q * Kp + g * 8;
     if (sizeof(T) == 2) {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(vals);
     } else {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(v);
-      *reinterpret_cast<uint4*>(dst + 4) = *reinterpret_cast<const uint4*>(v + 4);
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(vals);
+      *reinterpret_cast<uint4*>(dst + 4) = *reinterpret_cast<const uint4*>(vals + 4);
     }
   }
 }
@@ -368,10 +379,13 @@ extern "C" int dv_im2col(const void* x, void* patches, int N, int H, int W, int 
   DV_REQUIRE(x && patches && N > 0 && H > 0 && W > 0 && C > 0 && R > 0 && S > 0 && stride > 0 && pad >= 0, DV_ERR_ARG, "dv_im2col: bad arguments");
   DV_REQUIRE(Kp % 8 == 0 && Kp >= R * S * C, DV_ERR_ARG, "dv_im2col: Kp=%d must be a multiple of 8 and >= R*S*C=%d", Kp, R * S * C);
   const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
-  const int64_t total = (int64_t)N * P * Q * (Kp / 8);
   cudaStream_t st = (cudaStream_t)stream;
-  DV_DISPATCH_T(dtype, (im2col_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)x, (bf16*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)),
-                (im2col_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)x, (float*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)));
+  const size_t esz = dtype == DV_BF16 ? 2 : 4;
+  const size_t smem = (((size_t)R * (W + 2 * pad) * C * esz + 15) & ~(size_t)15) + (size_t)Kp * sizeof(int);
+  DV_REQUIRE(smem <= 48 * 1024, DV_ERR_UNSUPPORTED, "dv_im2col: %zu bytes of staging exceed 48 KB (R*(W+2*pad)*C too large)", smem);
+  DV_REQUIRE((int64_t)N * P <= 0x7fffffff, DV_ERR_UNSUPPORTED, "dv_im2col: too many output rows");
+  DV_DISPATCH_T(dtype, (im2col_kernel<bf16><<<(unsigned)(N * P), 256, smem, st>>>((const bf16*)x, (bf16*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)),
+                (im2col_kernel<float><<<(unsigned)(N * P), 256, smem, st>>>((const float*)x, (float*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)));
   DV_LAUNCH_OK("im2col_kernel");
   return DV_OK;
 }

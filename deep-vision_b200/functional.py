@@ -137,12 +137,26 @@ class FilterCache:
         return self.w, self.w_t
 
 
-def _conv_params(x_ptr, w_ptr, y_ptr, wt_ptr, N, H, W, Cc, K, R, S, stride, pad, dtype, algo, y_f32=0):
+def _conv_params(x_ptr, w_ptr, y_ptr, wt_ptr, N, H, W, Cc, K, R, S, stride, pad, dtype, algo, y_f32=0, accumulate=0):
     p = ConvParams()
     p.x, p.w, p.y, p.w_t = x_ptr, w_ptr, y_ptr, wt_ptr
     p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad = N, H, W, Cc, K, R, S, stride, pad
-    p.dtype, p.algo, p.y_f32 = dtype, algo, y_f32
+    p.dtype, p.algo, p.y_f32, p.accumulate = dtype, algo, y_f32, accumulate
     return p
+
+
+class GradSlot:
+    """Hand-over point for the two gradients of a tensor with two consumers (the input of a residual block feeds the
+    first convolution AND the shortcut: resnet50.py:147-163).  The shortcut side DEPOSITS its gradient here instead of
+    returning it to autograd; the main-path convolution COLLECTS it and lets its dgrad kernel accumulate on top
+    (dv_conv_params.accumulate), so the sum costs no extra pass over the tensor.  Autograd runs nodes in reverse creation
+    order, and the blocks create the shortcut's nodes after the main path's, so the deposit always comes first; a
+    collect without a deposit raises instead of silently dropping a gradient."""
+
+    __slots__ = ("t",)
+
+    def __init__(self):
+        self.t = None
 
 
 def _run_conv(fn, p, pass_id, device, what):
@@ -158,7 +172,8 @@ class _Conv2d(torch.autograd.Function):
     mobilenet_v1.py:30,139-145.  Backward = dgrad + wgrad (autograd of train.py:460)."""
 
     @staticmethod
-    def forward(ctx, x, weight, stride, pad, cache, algo):
+    def forward(ctx, x, weight, stride, pad, cache, algo, slot=None, role=None):
+        ctx.slot, ctx.role = slot, role
         _require_cuda(x, "conv2d")
         x = _nhwc(x)
         N, Cc, H, W = x.shape
@@ -211,22 +226,30 @@ class _Conv2d(torch.autograd.Function):
                 _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad(stem)")
                 dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
                 check(lib.dv_unpad_rows(dw_pad.data_ptr(), dw.data_ptr(), K, R * S * Cc, kp, _stream()), "dv_unpad_rows")
-            return None, dw, None, None, None, None
+            return None, dw, None, None, None, None, None, None
         N, Cc, H, W = x.shape
         if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x, memory_format=_CL)
+            acc = 0
+            if ctx.role == "collect":
+                if ctx.slot.t is None:
+                    raise RuntimeError("deep_vision_b200: residual gradient was not deposited before the main path's dgrad")
+                dx, ctx.slot.t, acc = ctx.slot.t, None, 1
+            else:
+                dx = torch.empty_like(x, memory_format=_CL)
             p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dy.data_ptr(), ctx.w_t.data_ptr() if ctx.w_t is not None else None,
-                             N, H, W, Cc, K, R, S, stride, pad, dt, algo)
+                             N, H, W, Cc, K, R, S, stride, pad, dt, algo, accumulate=acc)
             _run_conv(lib.dv_conv_dgrad, p, DV_CONV_DGRAD, x.device, "dv_conv_dgrad")
+            if ctx.role == "deposit":
+                ctx.slot.t, dx = dx, None
         if ctx.needs_input_grad[1]:
             dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
             p = _conv_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
             _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad")
-        return dx, dw, None, None, None, None
+        return dx, dw, None, None, None, None, None, None
 
 
-def conv2d(x, weight, stride=1, padding=0, cache=None, algo=DV_ALGO_AUTO):
-    return _Conv2d.apply(x, weight, int(stride), int(padding), cache or FilterCache(), algo)
+def conv2d(x, weight, stride=1, padding=0, cache=None, algo=DV_ALGO_AUTO, slot=None, role=None):
+    return _Conv2d.apply(x, weight, int(stride), int(padding), cache or FilterCache(), algo, slot, role)
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -294,7 +317,8 @@ class _BatchNormAct(torch.autograd.Function):
     resnet50.py:152-164, resnet34.py:135-142, mobilenet_v1.py:129-133,152-156."""
 
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None):
+        ctx.res_slot = res_slot
         _require_cuda(x, "batch_norm")
         x = _nhwc(x)
         N, Cc, H, W = x.shape
@@ -330,16 +354,18 @@ class _BatchNormAct(torch.autograd.Function):
         ctx.batch_stats = use_batch_stats
         ctx.relu = bool(relu)
         ctx.has_res = residual is not None
+        # the ReLU mask: without a residual it is recomputed bit-exactly from x in backward (y need not be kept or re-read)
+        keep_y = y if (relu and residual is not None) else None
         if use_batch_stats:
-            ctx.save_for_backward(x, y if relu else None, gamma, save_mean, save_invstd)
+            ctx.save_for_backward(x, keep_y, gamma, save_mean, save_invstd, beta)
         else:
-            ctx.save_for_backward(x, y if relu else None, gamma, running_mean, running_var)
+            ctx.save_for_backward(x, keep_y, gamma, running_mean, running_var, beta)
             ctx.eps = eps
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, y, gamma, mean, second = ctx.saved_tensors
+        x, y, gamma, mean, second, beta = ctx.saved_tensors
         if not ctx.batch_stats:
             raise NotImplementedError("deep_vision_b200: backward through eval-mode BatchNorm2d is not on the hot path")
         dy = _nhwc(dy)
@@ -354,18 +380,21 @@ class _BatchNormAct(torch.autograd.Function):
         p = BnBwdParams()
         p.x, p.y, p.dy, p.dx = x.data_ptr(), (y.data_ptr() if y is not None else None), dy.data_ptr(), dx.data_ptr()
         p.dres = dres.data_ptr() if dres is not None else None
-        p.gamma, p.save_mean, p.save_invstd = gamma.data_ptr(), mean.data_ptr(), second.data_ptr()
+        p.gamma, p.beta, p.save_mean, p.save_invstd = gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), second.data_ptr()
         p.dgamma, p.dbeta = dgamma.data_ptr(), dbeta.data_ptr()
         p.M, p.C, p.dtype, p.relu = M, Cc, _dv_dtype(x.dtype), int(ctx.relu)
         ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
         p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
         check(lib.dv_bn_bwd_reduce(C.byref(p), _stream()), "dv_bn_bwd_reduce")
         check(lib.dv_bn_bwd_apply(C.byref(p), _stream()), "dv_bn_bwd_apply")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+        if ctx.res_slot is not None and dres is not None:
+            ctx.res_slot.t, dres = dres, None   # handed to the main path's dgrad, not to autograd
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
 
 
-def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
-    return _BatchNormAct.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum), float(eps), bool(relu))
+def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None):
+    return _BatchNormAct.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum), float(eps),
+                               bool(relu), res_slot)
 
 
 class _ReLU(torch.autograd.Function):
@@ -461,11 +490,13 @@ class _Linear(torch.autograd.Function):
         x = x.contiguous()
         B, F = x.shape
         K = weight.shape[0]
-        w_c, _ = cache.get(weight.view(K, F, 1, 1), x.dtype, False)
+        need_t = x.dtype != torch.float32 and ctx.needs_input_grad[0]
+        w_c, w_t = cache.get(weight.view(K, F, 1, 1), x.dtype, need_t)
         y = torch.empty((B, K), dtype=torch.float32, device=x.device)
-        p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, _dv_dtype(x.dtype), DV_ALGO_SIMT,
-                         y_f32=1)
-        check(lib.dv_conv_fprop(C.byref(p), _stream()), "dv_conv_fprop(linear)")
+        algo = config.conv_algo()
+        p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, _dv_dtype(x.dtype), algo, y_f32=1)
+        _run_conv(lib.dv_conv_fprop, p, DV_CONV_FPROP, x.device, "dv_conv_fprop(linear)")
+        ctx.w_t, ctx.algo = w_t, algo
         if bias is not None:
             check(lib.dv_bias_add(y.data_ptr(), bias.data_ptr(), B, K, _stream()), "dv_bias_add")
         ctx.save_for_backward(x, weight)
@@ -488,12 +519,13 @@ class _Linear(torch.autograd.Function):
         dx = dw = db = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
-            p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dyc.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, dt, DV_ALGO_SIMT)
-            check(lib.dv_conv_dgrad(C.byref(p), _stream()), "dv_conv_dgrad(linear)")
+            p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dyc.data_ptr(), ctx.w_t.data_ptr() if ctx.w_t is not None else None,
+                             B, 1, 1, F, K, 1, 1, 1, 0, dt, ctx.algo)
+            _run_conv(lib.dv_conv_dgrad, p, DV_CONV_DGRAD, x.device, "dv_conv_dgrad(linear)")
         if ctx.needs_input_grad[1]:
             dw = torch.empty((K, F), dtype=torch.float32, device=x.device)
-            p = _conv_params(x.data_ptr(), dw.data_ptr(), dyc.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, dt, DV_ALGO_SIMT)
-            check(lib.dv_conv_wgrad(C.byref(p), _stream()), "dv_conv_wgrad(linear)")
+            p = _conv_params(x.data_ptr(), dw.data_ptr(), dyc.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, dt, ctx.algo)
+            _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad(linear)")
         if ctx.has_bias and ctx.needs_input_grad[2]:
             dyf = dy if dy.dtype == torch.float32 else dy.float()
             db = torch.empty(K, dtype=torch.float32, device=x.device)

@@ -21,7 +21,7 @@ class ConvParams(C.Structure):
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("K", C.c_int32),
         ("R", C.c_int32), ("S", C.c_int32), ("stride", C.c_int32), ("pad", C.c_int32),
-        ("dtype", C.c_int32), ("algo", C.c_int32), ("y_f32", C.c_int32),
+        ("dtype", C.c_int32), ("algo", C.c_int32), ("y_f32", C.c_int32), ("accumulate", C.c_int32),
     ]
 
 
@@ -49,7 +49,7 @@ class BnParams(C.Structure):
 class BnBwdParams(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("y", C.c_void_p), ("dy", C.c_void_p), ("dx", C.c_void_p), ("dres", C.c_void_p),
-        ("gamma", C.c_void_p), ("save_mean", C.c_void_p), ("save_invstd", C.c_void_p),
+        ("gamma", C.c_void_p), ("beta", C.c_void_p), ("save_mean", C.c_void_p), ("save_invstd", C.c_void_p),
         ("dgamma", C.c_void_p), ("dbeta", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("M", C.c_int64), ("C", C.c_int32), ("dtype", C.c_int32), ("relu", C.c_int32),

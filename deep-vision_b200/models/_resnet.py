@@ -60,11 +60,20 @@ class _Residual(tnn.Module):
         if downsample:
             self.projection = tnn.Sequential(_conv(cin, cout, 1, stride=stride), dvnn.BatchNorm2d(cout))
 
-    def _identity(self, x):
-        if not self.downsample:
-            return x
-        conv, bn = self.projection[0], self.projection[1]
-        return bn(conv(x))
+    def _shortcut_and_merge(self, x, main, last_bn, slot):
+        """relu(last_bn(main) + shortcut(x)).  The shortcut is evaluated AFTER the main path on purpose: autograd then
+        runs its backward first, so its gradient w.r.t. x is already in `slot` when the first convolution's dgrad
+        accumulates on top of it (functional.GradSlot)."""
+        if self.downsample:
+            conv, bn = self.projection[0], self.projection[1]
+            identity = bn(conv(x, grad_slot=slot, role="deposit" if slot is not None else None))
+            return last_bn(main, residual=identity, act=self.relu)
+        return last_bn(main, residual=x, act=self.relu, res_slot=slot)
+
+    @staticmethod
+    def _slot_for(x):
+        import torch
+        return F.GradSlot() if (torch.is_grad_enabled() and x.requires_grad) else None
 
 
 class BasicBlock(_Residual):
@@ -81,9 +90,10 @@ class BasicBlock(_Residual):
 
     def forward(self, x):
         x = F.to_compute_layout(x)  # no-op inside a network; converts a raw fp32 NCHW tensor fed to a lone block
-        identity = self._identity(x)
-        x = self.bn1(self.conv1(x), act=self.relu)
-        return self.bn2(self.conv2(x), residual=identity, act=self.relu)
+        slot = self._slot_for(x)
+        out = self.bn1(self.conv1(x, grad_slot=slot, role="collect" if slot is not None else None), act=self.relu)
+        out = self.conv2(out)
+        return self._shortcut_and_merge(x, out, self.bn2, slot)
 
 
 class BottleneckBlock(_Residual):
@@ -103,10 +113,11 @@ class BottleneckBlock(_Residual):
 
     def forward(self, x):
         x = F.to_compute_layout(x)
-        identity = self._identity(x)
-        x = self.bn1(self.conv1(x), act=self.relu)
-        x = self.bn2(self.conv2(x), act=self.relu)
-        return self.bn3(self.conv3(x), residual=identity, act=self.relu)
+        slot = self._slot_for(x)
+        out = self.bn1(self.conv1(x, grad_slot=slot, role="collect" if slot is not None else None), act=self.relu)
+        out = self.bn2(self.conv2(out), act=self.relu)
+        out = self.conv3(out)
+        return self._shortcut_and_merge(x, out, self.bn3, slot)
 
 
 def bottleneck_stage(num_blocks, in_channels, out1, out2, stride):

@@ -27,18 +27,20 @@ class Conv2d(nn.Conv2d):
                                        and self.padding == (1, 1)):
             raise NotImplementedError("deep_vision_b200.nn.Conv2d: grouped convolution is supported as depth-wise 3x3 pad 1 only")
 
-    def forward(self, x):
+    def forward(self, x, grad_slot=None, role=None):
+        """grad_slot/role: see functional.GradSlot — used by the residual blocks to fuse the shortcut's gradient into
+        this convolution's dgrad; plain callers leave them unset."""
         x = F.to_compute_layout(x)
         if self._dv_depthwise:
             return F.dwconv3x3(x, self.weight, self.stride[0])
-        return F.conv2d(x, self.weight, self.stride[0], self.padding[0], self._dv_cache, config.conv_algo())
+        return F.conv2d(x, self.weight, self.stride[0], self.padding[0], self._dv_cache, config.conv_algo(), grad_slot, role)
 
 
 class BatchNorm2d(nn.BatchNorm2d):
     """nn.BatchNorm2d with the following ReLU and the residual add folded into the same pass:
     ``bn(x, residual=identity, act=self.relu)`` == ``relu(bn(x) + identity)``."""
 
-    def forward(self, x, residual=None, act=None):
+    def forward(self, x, residual=None, act=None, res_slot=None):
         if act is not None and not isinstance(act, nn.ReLU):
             raise TypeError("act must be an nn.ReLU module or None")
         x = F.to_compute_layout(x)
@@ -55,7 +57,7 @@ class BatchNorm2d(nn.BatchNorm2d):
             raise NotImplementedError("deep_vision_b200.nn.BatchNorm2d: affine=False is not on the hot path")
         rm = self.running_mean if (not self.training or self.track_running_stats) else None
         rv = self.running_var if (not self.training or self.track_running_stats) else None
-        return F.batch_norm_act(x, residual, self.weight, self.bias, rm, rv, training, eaf, self.eps, act is not None)
+        return F.batch_norm_act(x, residual, self.weight, self.bias, rm, rv, training, eaf, self.eps, act is not None, res_slot)
 
 
 class ReLU(nn.ReLU):

@@ -72,7 +72,9 @@ typedef struct dv_conv_params {
   int32_t N, H, W, C, K, R, S, stride, pad;
   int32_t dtype;      /* DV_F32 | DV_BF16 */
   int32_t algo;       /* DV_ALGO_* */
-  int32_t y_f32;      /* fprop only, SIMT only: 1 = write y as fp32 even when dtype is bf16 (logits) */
+  int32_t y_f32;      /* fprop only: 1 = write y as fp32 even when dtype is bf16 (the logits of nn.Linear) */
+  int32_t accumulate; /* dgrad only: 1 = dx += result instead of dx = result (the second gradient of a tensor that feeds
+                         two consumers, e.g. a residual block's input: resnet50.py:147-163) */
 } dv_conv_params;
 
 enum { DV_CONV_FPROP = 0, DV_CONV_DGRAD = 1, DV_CONV_WGRAD = 2 };
@@ -158,11 +160,14 @@ int dv_bn_apply(const dv_bn_params* p, void* stream);
 
 typedef struct dv_bn_bwd_params {
   const void* x;        /* [M,C] conv output saved from forward */
-  const void* y;        /* [M,C] block output saved from forward (ReLU mask); may be NULL when relu == 0 */
+  const void* y;        /* [M,C] block output saved from forward (ReLU mask).  May be NULL when relu == 0, and also when
+                           relu == 1 and the forward had NO residual: the mask is then recomputed bit-exactly from x
+                           (needs beta), which saves reading y in both backward passes */
   const void* dy;       /* [M,C] gradient w.r.t. block output */
   void* dx;             /* [M,C] gradient w.r.t. conv output */
   void* dres;           /* [M,C] gradient w.r.t. residual (== masked dy) or NULL */
   const float* gamma;
+  const float* beta;    /* [C]; only read when the mask is recomputed (relu == 1, y == NULL) */
   const float* save_mean;
   const float* save_invstd;
   float* dgamma;        /* [C] out */

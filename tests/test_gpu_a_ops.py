@@ -182,6 +182,16 @@ def test_bn_forward_backward_matches_oracle(shape, residual, relu, dtype):
     assert rel_l2(np.transpose(dxd.double().cpu().numpy(), (0, 3, 1, 2)), dx_ref) < tol
     if residual:
         assert rel_l2(np.transpose(drd.double().cpu().numpy(), (0, 3, 1, 2)), dz) < tol
+    if relu and not residual:
+        # mask recomputed from x instead of read from y: must reproduce the stored-mask results bit for bit
+        dx1, dg1, db1 = dxd.clone(), dg.clone(), db.clone()
+        dxd.fill_(float("nan"))
+        q.y, q.beta = None, b_d.data_ptr()
+        lib.check(lib.lib.dv_bn_bwd_reduce(C.byref(q), stream_ptr()), "dv_bn_bwd_reduce(recompute)")
+        lib.check(lib.lib.dv_bn_bwd_apply(C.byref(q), stream_ptr()), "dv_bn_bwd_apply(recompute)")
+        torch.cuda.synchronize()
+        assert torch.equal(dxd, dx1) and torch.equal(dg, dg1) and torch.equal(db, db1)
+        q.y = yd.data_ptr()
 
     # eval mode uses the running statistics
     p.eval_mode = 1

@@ -185,3 +185,47 @@ def test_stem_conv_module_matches_oracle(geom):
     torch.cuda.synchronize()
     assert rel_l2(y.detach().float().cpu().numpy(), y_ref) < 2e-2
     assert rel_l2(conv.weight.grad.cpu().numpy(), dw_ref) < 1e-4
+
+
+def test_tc_fp32_logits_and_dgrad_accumulate():
+    """Two epilogue variants of the tensor-core GEMM: fp32 output (the classifier's logits, nn.Linear at resnet50.py:44)
+    and read-modify-write accumulation of dgrad (second gradient of a residual block's input)."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    # fp32 logits: x [B,1,1,F] * w [1000,F]
+    B, Fdim, K = 48, 512, 1000
+    x = _rand((B, Fdim, 1, 1), 1, BF)
+    w = _rand((K, Fdim, 1, 1), 2, BF, scale=0.05)
+    xd = torch.from_numpy(x.reshape(B, Fdim)).cuda().to(BF)
+    wd = torch.from_numpy(w.reshape(K, Fdim)).cuda().to(BF)
+    y = torch.full((B, K), float("nan"), device="cuda")
+    p = lib.ConvParams()
+    p.x, p.w, p.y = xd.data_ptr(), wd.data_ptr(), y.data_ptr()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo, p.y_f32 = B, 1, 1, Fdim, K, 1, 1, 1, 0, lib.DV_BF16, lib.DV_ALGO_TC, 1
+    lib.check(lib.lib.dv_conv_fprop(C.byref(p), stream_ptr()), "fprop f32")
+    torch.cuda.synchronize()
+    ref = x.reshape(B, Fdim) @ w.reshape(K, Fdim).T
+    assert rel_l2(y.double().cpu().numpy(), ref) < 1e-5       # exact bf16 products, fp32 accumulate, no output rounding
+
+    for case, algo in (((2, 64, 8, 8, 128, 1, 1, 0), lib.DV_ALGO_TC), ((2, 64, 8, 8, 128, 1, 2, 0), lib.DV_ALGO_TC),
+                       ((2, 64, 8, 8, 64, 3, 1, 1), lib.DV_ALGO_TC), ((2, 64, 9, 9, 128, 3, 2, 1), lib.DV_ALGO_SIMT)):
+        N, Cc, H, W, K, R, stride, pad = case
+        xs = _rand((N, Cc, H, W), 1, BF)
+        ws = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+        P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+        dy = _rand((N, K, P, Q), 3, BF)
+        prior = _rand((N, Cc, H, W), 4, BF)
+        dx_ref, _ = ref_ops.conv2d_backward(xs, ws, dy, stride, pad)
+        wk = torch.from_numpy(np.ascontiguousarray(ws.transpose(0, 2, 3, 1))).cuda().to(BF)
+        wt = torch.empty((Cc, R, R, K), device="cuda", dtype=BF)
+        lib.check(lib.lib.dv_filter_prep(wk.float().contiguous().data_ptr(), None, wt.data_ptr(), K, R, R, Cc, lib.DV_BF16, stream_ptr()), "prep")
+        dyd = torch.from_numpy(np.ascontiguousarray(dy.transpose(0, 2, 3, 1))).cuda().to(BF)
+        dxd = torch.from_numpy(np.ascontiguousarray(prior.transpose(0, 2, 3, 1))).cuda().to(BF)
+        q = lib.ConvParams()
+        q.x, q.w, q.y, q.w_t = dxd.data_ptr(), wk.data_ptr(), dyd.data_ptr(), wt.data_ptr()
+        q.N, q.H, q.W, q.C, q.K, q.R, q.S, q.stride, q.pad, q.dtype, q.algo, q.accumulate = N, H, W, Cc, K, R, R, stride, pad, lib.DV_BF16, algo, 1
+        lib.check(lib.lib.dv_conv_dgrad(C.byref(q), stream_ptr()), "dgrad accumulate")
+        torch.cuda.synchronize()
+        got = dxd.double().cpu().numpy().transpose(0, 3, 1, 2)
+        assert rel_l2(got, dx_ref + prior) < 2e-2, case
