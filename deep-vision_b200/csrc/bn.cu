@@ -9,6 +9,7 @@
 //   bwd_apply  : dx = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M);  dres = dz
 // Partials are reduced in a fixed order, so every result is bit-reproducible run to run.
 #include "common.cuh"
+#include <mutex>
 
 namespace dv {
 namespace {
@@ -418,6 +419,66 @@ static int bwd_apply_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   return DV_OK;
 }
 
+// ---- dv_bn_stats_static: the statistics pass for callers that must not allocate -------------------------------------
+// The block partials of bn_reduce_kernel normally live in a caller-provided workspace.  Here they live in a fixed array
+// inside the library image, so the call needs no scratch pointer and performs no allocation of any kind.
+// Capacity: kStaticMaxBlocks partial rows of 2*C floats, C <= kStaticMaxC  ->  148 * 2 * 2048 floats = 2.3 MiB, resident on
+// every GPU that loads the library until the process exits.
+constexpr int kStaticMaxBlocks = 148;
+constexpr int kStaticMaxC = 2048;
+constexpr size_t kStaticFloats = (size_t)kStaticMaxBlocks * 2 * kStaticMaxC;
+static __device__ __align__(256) float g_bn_static_scratch[kStaticFloats];
+
+// In host code `g_bn_static_scratch` is only a handle for the symbol, NOT a device address: a kernel handed that
+// name would read and write wherever the host-side shadow happens to live.  The device address is looked up once per
+// device (with that device current) and cached.
+static int bn_static_scratch(float** out) {
+  constexpr int kMaxDevices = 64;
+  static std::mutex mu;
+  static float* cached[kMaxDevices] = {nullptr};
+  int dev = -1;
+  DV_CUDA_OK(cudaGetDevice(&dev));
+  DV_REQUIRE(dev >= 0 && dev < kMaxDevices, DV_ERR_UNSUPPORTED, "dv_bn_stats_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached[dev] == nullptr) {
+    float* ptr = nullptr;
+    DV_CUDA_OK(cudaGetSymbolAddress((void**)&ptr, g_bn_static_scratch));
+    DV_REQUIRE(ptr != nullptr, DV_ERR_CUDA, "dv_bn_stats_static: cudaGetSymbolAddress returned a null address");
+    cached[dev] = ptr;
+  }
+  *out = cached[dev];
+  return DV_OK;
+}
+
+template <typename T>
+static int stats_static_t(const dv_bn_params* p, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dv_bn_stats_static: C=%d must be a multiple of %d", p->C, V);
+  DV_REQUIRE(p->C <= kStaticMaxC, DV_ERR_UNSUPPORTED,
+             "dv_bn_stats_static: C=%d exceeds the built-in scratch (at most %d channels); use dv_bn_stats with a workspace", p->C,
+             kStaticMaxC);
+  Plan pl = make_plan(p->M, p->C, V);
+  if (pl.nblk > kStaticMaxBlocks) {  // same kernel, fewer and longer row ranges so the partials fit the fixed array
+    pl.rows_per_blk = ceil_div64(p->M, kStaticMaxBlocks);
+    pl.nblk = (int)ceil_div64(p->M, pl.rows_per_blk);
+  }
+  DV_REQUIRE((size_t)pl.nblk * 2 * p->C <= kStaticFloats, DV_ERR_UNSUPPORTED, "dv_bn_stats_static: %d x 2 x %d partials exceed the built-in scratch",
+             pl.nblk, p->C);
+  float* scratch = nullptr;
+  int rc = bn_static_scratch(&scratch);
+  if (rc) return rc;
+  // Every partial the finalize pass reads is overwritten by the reduce pass of the same call, so nothing in the shared
+  // array has to be cleared between calls.
+  bn_reduce_kernel<T, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, scratch, p->M,
+                                                      p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, 0);
+  DV_LAUNCH_OK("bn_reduce_kernel<stats,static>");
+  bn_stats_finalize_kernel<T><<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const T*)p->x, scratch, pl.nblk, p->C, p->M, p->eps,
+                                                                            p->momentum, p->save_mean, p->save_invstd, p->running_mean,
+                                                                            p->running_var);
+  DV_LAUNCH_OK("bn_stats_finalize_kernel<static>");
+  return DV_OK;
+}
+
 }  // namespace
 }  // namespace dv
 
@@ -478,4 +539,10 @@ extern "C" int dv_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, i
   }
   DV_LAUNCH_OK("relu_bwd_kernel");
   return DV_OK;
+}
+
+extern "C" int dv_bn_stats_static(const dv_bn_params* p, void* stream) {
+  DV_REQUIRE(p && p->x && p->save_mean && p->save_invstd && p->M > 0 && p->C > 0, DV_ERR_ARG, "dv_bn_stats_static: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  return p->dtype == DV_BF16 ? stats_static_t<bf16>(p, st) : stats_static_t<float>(p, st);
 }

@@ -74,6 +74,7 @@ _SIG = {
     "dv_dwconv_workspace_bytes": (C.c_size_t, [C.POINTER(DwConvParams)]),
     "dv_bn_stats": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_apply": (C.c_int, [C.POINTER(BnParams), _P]),
+    "dv_bn_stats_static": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_bwd_reduce": (C.c_int, [C.POINTER(BnBwdParams), _P]),
     "dv_bn_bwd_apply": (C.c_int, [C.POINTER(BnBwdParams), _P]),
     "dv_bn_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int]),

@@ -157,6 +157,28 @@ typedef struct dv_bn_params {
 int dv_bn_stats(const dv_bn_params* p, void* stream);
 /* normalise + affine (+residual) (+ReLU) */
 int dv_bn_apply(const dv_bn_params* p, void* stream);
+/* dv_bn_stats for callers that cannot allocate device memory.  (This entry point has no counterpart in the
+ * reference, which leaves every allocation to torch.)
+ *
+ * Who needs it: a host that hands this library tensors but keeps the allocator to itself — an inference or
+ * training runtime that reserves all of its device memory at start-up and forbids cudaMalloc afterwards (an allocation
+ * is a device-wide synchronisation point and can fail late, deep inside a step), or a plug-in that is handed
+ * input/output buffers and has no sanctioned way to ask for a workspace.  Such a caller cannot size and provide the
+ * `workspace` that dv_bn_stats wants.
+ *
+ * Same arguments, same results as dv_bn_stats (the block partials are summed over a different, coarser partition of
+ * the rows, so the statistics agree to rounding, not bit for bit).  `workspace` / `workspace_bytes` are ignored: the
+ * block partials go to a fixed array compiled into the library, 148 x 2 x 2048 floats = 2.3 MiB, which every GPU that
+ * loads the library holds until the process exits.  Neither this call nor anything it calls allocates or frees
+ * (no cudaMalloc / cudaFree, no torch).
+ *   - Limit: C <= 2048 channels (any M).  Larger C is rejected with DV_ERR_UNSUPPORTED and a message; nothing is
+ *     launched in that case.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress, result checked and
+ *     cached per device).  Make that first call before any stream capture begins.
+ *   - All calls on a device share the one array.  It keeps whatever the previous call left there; that is harmless
+ *     because each call overwrites every partial it later reads, so nothing needs clearing.  But two calls that can
+ *     overlap on the GPU (different streams, or two host threads) race on it: serialise them on one stream. */
+int dv_bn_stats_static(const dv_bn_params* p, void* stream);
 
 typedef struct dv_bn_bwd_params {
   const void* x;        /* [M,C] conv output saved from forward */
