@@ -1,0 +1,49 @@
+#!/usr/bin/env python
+"""Launch ONE hot kernel a few times (for `ncu --set full`): the tcgen05 conv fprop on the roofline shape of bench.py
+(3x3, 256->256, 14x14, batch 256), or --which wgrad / bn_apply / bn_bwd."""
+import argparse
+import ctypes as C
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from deep_vision_b200.lib import BnParams, ConvParams, DV_ALGO_TC, DV_BF16, DV_CONV_WGRAD, check, lib  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--which", default="fprop")
+ap.add_argument("--iters", type=int, default=5)
+args = ap.parse_args()
+st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+N, H, Cc, K, R = 256, 14, 256, 256, 3
+x = torch.randn(N, H, H, Cc, device="cuda").to(torch.bfloat16)
+w = (torch.randn(K, R, R, Cc, device="cuda") * 0.05).to(torch.bfloat16)
+y = torch.empty(N, H, H, K, device="cuda", dtype=torch.bfloat16)
+p = ConvParams()
+p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, H, Cc, K, R, R, 1, 1, DV_BF16, DV_ALGO_TC
+if args.which == "fprop":
+    p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
+    fn = lambda: check(lib.dv_conv_fprop(C.byref(p), st), "fprop")
+elif args.which == "wgrad":
+    dw = torch.empty(K, R, R, Cc, device="cuda")
+    p.x, p.w, p.y = x.data_ptr(), dw.data_ptr(), y.normal_().data_ptr()
+    need = lib.dv_conv_workspace_bytes(C.byref(p), DV_CONV_WGRAD)
+    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+    p.workspace, p.workspace_bytes = ws.data_ptr(), need
+    fn = lambda: check(lib.dv_conv_wgrad(C.byref(p), st), "wgrad")
+else:
+    M, Cb = 256 * 56 * 56, 256
+    xb = torch.randn(M, Cb, device="cuda").to(torch.bfloat16)
+    yb = torch.empty_like(xb)
+    v = [torch.ones(Cb, device="cuda") for _ in range(6)]
+    q = BnParams()
+    q.x, q.y, q.gamma, q.beta, q.running_mean, q.running_var, q.save_mean, q.save_invstd = [t.data_ptr() for t in [xb, yb] + v]
+    wsz = lib.dv_bn_workspace_bytes(M, Cb)
+    ws = torch.empty(wsz, dtype=torch.uint8, device="cuda")
+    q.workspace, q.workspace_bytes, q.M, q.C, q.dtype, q.relu, q.eps, q.momentum = ws.data_ptr(), wsz, M, Cb, DV_BF16, 1, 1e-5, 0.1
+    fn = (lambda: check(lib.dv_bn_apply(C.byref(q), st), "apply")) if args.which == "bn_apply" else (lambda: check(lib.dv_bn_stats(C.byref(q), st), "stats"))
+for _ in range(args.iters):
+    fn()
+torch.cuda.synchronize()
+print("ok", args.which)
