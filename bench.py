@@ -207,6 +207,9 @@ def run_ours(args):
         barrier()
         if rank == 0:
             print(json.dumps({"profile": True, "launches_per_step": launches_per_step, "steps": args.steps}), flush=True)
+        if world > 1:
+            sys.stdout.flush()
+            os._exit(0)
         return
     with ClockSampler(local_rank) as clk:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -275,7 +278,13 @@ def run_ours(args):
                                     "sample": f"{nsteps} steps of batch {args.cpu_batch} (fp32, oracle/ref_models.py) after 1 warm-up"}
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # Tearing down a process group whose collectives were captured in a CUDA graph can block for minutes; the numbers
+        # are out, every rank is past the barrier, so leave without the teardown.
+        sys.stdout.flush()
+        sys.stderr.flush()
+        dist.barrier()
+        torch.cuda.synchronize()
+        os._exit(0)
 
 
 def main():

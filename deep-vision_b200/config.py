@@ -1,7 +1,10 @@
 """Process-wide settings of the B200 path."""
+import os
+
 import torch
 
-_state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0}
+_state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
+          "fuse_bn_stats": os.environ.get("DV_FUSE_STATS", "1") != "0"}
 
 
 def compute_dtype():
@@ -33,3 +36,13 @@ def conv_algo():
 def set_conv_algo(algo):
     """0 = auto (tcgen05 where the shape qualifies), 1 = CUDA-core kernels only, 2 = tensor cores or error."""
     _state["conv_algo"] = int(algo)
+
+
+def fuse_bn_stats():
+    return _state["fuse_bn_stats"]
+
+
+def set_fuse_bn_stats(flag):
+    """True (default): tensor-core convolutions accumulate the per-channel sums BatchNorm needs in their epilogue, so the
+    statistics pass never re-reads the activation.  False: BatchNorm runs its own reduction pass."""
+    _state["fuse_bn_stats"] = bool(flag)

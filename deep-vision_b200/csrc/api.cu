@@ -43,7 +43,7 @@ static int check_conv(const dv_conv_params* p, const char* who) {
 static int resolve_algo(const dv_conv_params* p, int pass) {
   if (p->algo == DV_ALGO_SIMT) return DV_ALGO_SIMT;
   const char* why;
-  const bool ok = conv_tc_supported(p, pass, &why) && (pass != DV_CONV_DGRAD || p->w_t != nullptr || p->algo == DV_ALGO_TC);
+  const bool ok = conv_tc_supported(p, pass, &why);
   if (p->algo == DV_ALGO_TC) return DV_ALGO_TC;  // conv_tc reports the reason if unsupported
   return ok ? DV_ALGO_TC : DV_ALGO_SIMT;
 }

@@ -184,6 +184,27 @@ bn_stats_finalize_kernel(const T* __restrict__ x, const float* __restrict__ part
   }
 }
 
+// statistics from sums accumulated by the convolution epilogue; clears the sums for the next step
+__global__ void bn_from_sums_kernel(float* __restrict__ sums, int C, int64_t M, float eps, float momentum, float* __restrict__ save_mean,
+                                    float* __restrict__ save_invstd, float* __restrict__ running_mean, float* __restrict__ running_var) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double s1 = (double)sums[c], s2 = (double)sums[C + c];
+  sums[c] = 0.f;
+  sums[C + c] = 0.f;
+  const double n = (double)M;
+  const double mean = s1 / n;
+  double var = s2 / n - mean * mean;
+  if (var < 0.0) var = 0.0;
+  save_mean[c] = (float)mean;
+  save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+  if (running_mean != nullptr) {
+    const double unbiased = M > 1 ? var * n / (n - 1.0) : var;
+    running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + momentum * mean);
+    running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + momentum * unbiased);
+  }
+}
+
 __global__ void __launch_bounds__(32 * kFinLanes)
 bn_bwd_finalize_kernel(const float* __restrict__ partial, int nblk, int C, float* __restrict__ dgamma, float* __restrict__ dbeta) {
   const int c = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -495,6 +516,13 @@ extern "C" int dv_bn_stats(const dv_bn_params* p, void* stream) {
   DV_REQUIRE(p && p->x && p->save_mean && p->save_invstd && p->M > 0 && p->C > 0, DV_ERR_ARG, "dv_bn_stats: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
   return p->dtype == DV_BF16 ? stats_t<bf16>(p, st) : stats_t<float>(p, st);
+}
+extern "C" int dv_bn_stats_from_sums(const dv_bn_params* p, float* sums, void* stream) {
+  DV_REQUIRE(p && sums && p->save_mean && p->save_invstd && p->M > 0 && p->C > 0, DV_ERR_ARG, "dv_bn_stats_from_sums: bad arguments");
+  bn_from_sums_kernel<<<ceil_div(p->C, 128), 128, 0, (cudaStream_t)stream>>>(sums, p->C, p->M, p->eps, p->momentum, p->save_mean,
+                                                                             p->save_invstd, p->running_mean, p->running_var);
+  DV_LAUNCH_OK("bn_from_sums_kernel");
+  return DV_OK;
 }
 extern "C" int dv_bn_apply(const dv_bn_params* p, void* stream) {
   DV_REQUIRE(p && p->x && p->y && p->gamma && p->beta && p->M > 0 && p->C > 0, DV_ERR_ARG, "dv_bn_apply: bad arguments");

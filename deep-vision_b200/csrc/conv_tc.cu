@@ -141,6 +141,7 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // bf16 elements = one 128-byte swizzle row
 constexpr int kABytes = kBlockM * kBlockK * 2;
 constexpr int kThreads = 192;
+constexpr int kEpiStageBytes = 4 * 32 * 128;  // epilogue transpose buffers
 
 // ------------------------------------------------------------------------------------------------------------
 // GEMM-shaped kernel: fprop / dgrad
@@ -158,6 +159,7 @@ struct GemmArgs {
   int Ho, Wo, os;
   int out_f32;      // 1: `out` is float* (fp32 logits of the classifier)
   int accumulate;   // 1: out += result (bf16 read-modify-write by the owning thread)
+  float* stat_sums; // fprop, optional: [2][Nout] fp32, += per-channel sum and sum of squares of the bf16-rounded output
 };
 
 // ------------------------------------------------------------------------------------------------------------
@@ -165,16 +167,30 @@ struct GemmArgs {
 // activation tile through L2); the smem ring runs on across tiles and the accumulator is DOUBLE-BUFFERED in TMEM
 // (2 x BN columns), so the epilogue of tile i drains TMEM while the tensor core already works on tile i+1.
 // ------------------------------------------------------------------------------------------------------------
-template <int BN, int STAGES>
+// STATS: the fprop-for-training variant whose epilogue also accumulates BatchNorm's per-channel sums.  It stages the
+// output tile through shared memory (16 KB more per CTA); the plain variant stores straight from registers, which
+// measured faster in the full training step (profiles/r01_epilogue_ab.md).
+// B_MN: the B operand is taken as [64 reduction rows][64 output columns] boxes straight from KRSC filters and consumed
+// MN-major — the dgrad case, where the reduction runs over K (filter rows) and the output over C (contiguous), with the
+// tap flipped by index.  No transposed copy of the filters is needed.
+template <int BN, int STAGES, bool STATS, bool B_MN>
 __global__ void __launch_bounds__(kThreads)
 conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
   constexpr int ACC = 2;
   constexpr int kBBytes = BN * kBlockK * 2;
   constexpr int kStageBytes = kABytes + kBBytes;
   constexpr uint32_t kTmemCols = ACC * BN;  // 128, 256 or 512: powers of two
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
+  // SWIZZLE_128B tiles need 1024-byte alignment; the kernel has no static shared memory, so the dynamic window starts
+  // at the CTA's (1 KB-granular) base.  Checked below rather than paid for with a kilobyte of slack: with it, two
+  // CTAs of the BN<=128 variants would no longer fit one SM.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("dv conv_tc: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  uint8_t* stage_out = smem + STAGES * kStageBytes;  // STATS: 4 epilogue warps x [32 rows][128 B], 16-byte chunks XOR-swizzled by row
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + (STATS ? kEpiStageBytes : 0));
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
@@ -233,7 +249,14 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           } else {
             tma_load_2d(sA, &tmA, &full_bar[stage], cb * kBlockK, m0);
           }
-          tma_load_2d(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN);
+          if (B_MN) {
+            // filters [K][taps*Nout]: rows = reduction channels cb*64.., columns = flipped tap's slice of the output channels
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sB + j * 8192, &tmB, &full_bar[stage], (g.taps - 1 - tap) * g.Nout + n_tile * BN + j * 64, cb * kBlockK);
+          } else {
+            tma_load_2d(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN);
+          }
           if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -241,7 +264,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, 0);
+      constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, B_MN ? 1 : 0);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
@@ -256,7 +279,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
             const uint64_t ad = make_smem_desc(sA + k * 32, 16, 1024);
-            const uint64_t bd = make_smem_desc(sB + k * 32, 16, 1024);
+            const uint64_t bd = B_MN ? make_smem_desc(sB + k * 2048, 8192, 1024) : make_smem_desc(sB + k * 32, 16, 1024);
             umma_f16(d_tmem, ad, bd, idesc, (kb | k) ? 1u : 0u);
           }
           umma_commit(&empty_bar[stage]);
@@ -268,41 +291,83 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     }
     __syncwarp();
   } else {
+    // Epilogue.  A TMEM load hands each lane one ROW (32 fp32 columns); storing that directly would make every store
+    // instruction touch 32 different 128-byte lines.  Instead the warp transposes through its private 4 KB of shared
+    // memory, 64 columns at a time: lanes write their row's 8 x 16 B chunks (XOR-swizzled by row), then read back so that
+    // 8 consecutive lanes hold one row's contiguous 128 B, and each store instruction covers 4 whole lines.
     const int quarter = warp & 3;
+    uint8_t* my_stage = stage_out + quarter * (32 * 128);
+    const uint32_t my_stage_u32 = smem_u32(my_stage);
+    const int sub_row = lane >> 3, chunk = lane & 7;  // read-back role: row (it*4 + sub_row), 16-byte chunk `chunk`
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-      const int n_tile = tile % num_n, m_tile = tile / num_n;
-      const int m = m_tile * kBlockM + quarter * 32 + lane;
-      size_t row_off = 0;
-      if (m < g.M) {
-        if (g.scatter) {
-          const int pq = g.P * g.Q;
-          const int n_img = m / pq, rem = m - n_img * pq;
-          const int p = rem / g.Q, q = rem - p * g.Q;
-          row_off = (((size_t)n_img * g.Ho + (size_t)p * g.os) * g.Wo + (size_t)q * g.os) * g.Nout;
-        } else {
-          row_off = (size_t)m * g.Nout;
+    // running per-channel sums of this CTA's tiles (lane owns columns 2*lane, 2*lane+1 of every 64-column group)
+    float s1[BN / 64][2], s2[BN / 64][2];
+    int stat_n_tile = -1;
+#pragma unroll
+    for (int i = 0; i < BN / 64; ++i) { s1[i][0] = s1[i][1] = s2[i][0] = s2[i][1] = 0.f; }
+    auto flush_stats = [&]() {
+      if (g.stat_sums == nullptr || stat_n_tile < 0) return;
+#pragma unroll
+      for (int i = 0; i < BN / 64; ++i) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int col = stat_n_tile * BN + i * 64 + 2 * lane + e;
+          if (col < g.Nout) {
+            atomicAdd(g.stat_sums + col, s1[i][e]);
+            atomicAdd(g.stat_sums + g.Nout + col, s2[i][e]);
+          }
+          s1[i][e] = 0.f;
+          s2[i][e] = 0.f;
         }
       }
-      bf16* orow = g.out + row_off + (size_t)n_tile * BN;
-      float* orow32 = reinterpret_cast<float*>(g.out) + row_off + (size_t)n_tile * BN;
+    };
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const int n_tile = tile % num_n, m_tile = tile / num_n;
+      if (n_tile != stat_n_tile) { flush_stats(); stat_n_tile = n_tile; }
+      const int m_base = m_tile * kBlockM + quarter * 32;
+      // global row offsets of the 8 rows this lane stores (rows it*4 + sub_row)
+      size_t row_off[8];
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int m = m_base + it * 4 + sub_row;
+        size_t off = 0;
+        if (m < g.M) {
+          if (g.scatter) {
+            const int pq = g.P * g.Q;
+            const int n_img = m / pq, rem = m - n_img * pq;
+            const int pp = rem / g.Q, qq = rem - pp * g.Q;
+            off = (((size_t)n_img * g.Ho + (size_t)pp * g.os) * g.Wo + (size_t)qq * g.os) * g.Nout;
+          } else {
+            off = (size_t)m * g.Nout;
+          }
+        }
+        row_off[it] = off;
+      }
       const int n_left = g.Nout - n_tile * BN;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(t_addr + (uint32_t)(c * 32), v);
-        tmem_ld_wait();
+      if (!STATS && !g.out_f32) {
+        const int m = m_base + lane;
+        size_t ro = 0;
         if (m < g.M) {
-          if (g.out_f32) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-              if (c * 32 + j * 4 < n_left)
-                *reinterpret_cast<uint4*>(orow32 + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          if (g.scatter) {
+            const int pq = g.P * g.Q;
+            const int n_img = m / pq, rem = m - n_img * pq;
+            const int pp = rem / g.Q, qq = rem - pp * g.Q;
+            ro = (((size_t)n_img * g.Ho + (size_t)pp * g.os) * g.Wo + (size_t)qq * g.os) * g.Nout;
           } else {
+            ro = (size_t)m * g.Nout;
+          }
+        }
+        bf16* orow = g.out + ro + (size_t)n_tile * BN;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_addr + (uint32_t)(c * 32), v);
+          tmem_ld_wait();
+          if (m < g.M) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               if (c * 32 + j * 8 < n_left) {
@@ -326,6 +391,89 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             }
           }
         }
+      } else if (!STATS) {
+        // fp32 logits (classifier only, tiny): direct row-per-lane stores
+        const int m = m_base + lane;
+        float* orow32 = reinterpret_cast<float*>(g.out) + (size_t)m * g.Nout + (size_t)n_tile * BN;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_addr + (uint32_t)(c * 32), v);
+          tmem_ld_wait();
+          if (m < g.M) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (c * 32 + j * 4 < n_left)
+                *reinterpret_cast<uint4*>(orow32 + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int cgp = 0; cgp < BN / 64; ++cgp) {
+#pragma unroll
+          for (int half = 0; half < 2; ++half) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint32_t w[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
+                w[e] = *reinterpret_cast<uint32_t*>(&h);
+              }
+              const int ch = (half * 4 + j) ^ (lane & 7);
+              asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_stage_u32 + lane * 128 + ch * 16), "r"(w[0]), "r"(w[1]),
+                           "r"(w[2]), "r"(w[3])
+                           : "memory");
+            }
+          }
+          __syncwarp();
+          if (g.stat_sums != nullptr) {
+            // column sums over this warp's 32 rows from the bf16-rounded values (what BN will read back)
+            const int wch = lane >> 2, wof = (lane & 3) * 4;
+            float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+#pragma unroll 8
+            for (int r = 0; r < 32; ++r) {
+              const uint32_t word = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+              const float x0 = __uint_as_float(word << 16), x1 = __uint_as_float(word & 0xffff0000u);
+              a0 += x0; a1 += x1;
+              b0 = fmaf(x0, x0, b0); b1 = fmaf(x1, x1, b1);
+            }
+            s1[cgp][0] += a0; s1[cgp][1] += a1;
+            s2[cgp][0] += b0; s2[cgp][1] += b1;
+          }
+          const int col0 = cgp * 64 + chunk * 8;
+          if (col0 < n_left) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+              const int row = it * 4 + sub_row;
+              if (m_base + row < g.M) {
+                uint4 val;
+                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(val.x), "=r"(val.y), "=r"(val.z), "=r"(val.w)
+                             : "r"(my_stage_u32 + row * 128 + ((chunk ^ (row & 7)) * 16)));
+                bf16* dst = g.out + row_off[it] + (size_t)n_tile * BN + col0;
+                if (g.accumulate) {
+                  const uint4 old = *reinterpret_cast<const uint4*>(dst);
+                  const uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+                  uint32_t nw[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    const float lo = __uint_as_float(nw[e] << 16) + __uint_as_float(ow[e] << 16);
+                    const float hi = __uint_as_float(nw[e] & 0xffff0000u) + __uint_as_float(ow[e] & 0xffff0000u);
+                    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+                    nw[e] = *reinterpret_cast<uint32_t*>(&h);
+                  }
+                  val = make_uint4(nw[0], nw[1], nw[2], nw[3]);
+                }
+                *reinterpret_cast<uint4*>(dst) = val;
+              }
+            }
+          }
+          __syncwarp();  // the staging buffer is rewritten by the next column group
+        }
       }
       // all of this warp's TMEM reads are complete: hand the accumulator back to the MMA warp
       tc_fence_before();
@@ -333,6 +481,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
       if (lane == 0) mbar_arrive(&tempty_bar[acc]);
       if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
     }
+    flush_stats();
   }
   tc_fence_before();
   __syncthreads();
@@ -353,15 +502,19 @@ struct WgradArgs {
   int c_tiles;
 };
 
-template <int BNC, int STAGES>
+// MH = number of 128-row halves of the output tile (1 or 2).  With MH == 2 a CTA owns 256 output channels: two
+// accumulators in TMEM, two MMAs per K step that share ONE staged x tile, so the activation is fetched from L2 once per
+// 256 (not 128) output channels.
+template <int BNC, int STAGES, int MH>
 __global__ void __launch_bounds__(kThreads)
 conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const WgradArgs g) {
   constexpr int kPix = 64;                       // pixels per stage (= 4 MMAs of K=16)
   constexpr int kChunk = kPix * 128;             // one [64 px][64 ch] box = 8 KB
-  constexpr int kABytesW = 2 * kChunk;           // 128 output channels of dY
+  constexpr int kABytesW = MH * 2 * kChunk;      // 128*MH output channels of dY
   constexpr int kBBytesW = (BNC / 64) * kChunk;  // BNC input channels of x
   constexpr int kStageBytes = kABytesW + kBBytesW;
-  constexpr uint32_t kTmemCols = BNC <= 32 ? 32 : BNC <= 64 ? 64 : BNC <= 128 ? 128 : 256;
+  constexpr int kAccCols = MH * BNC;
+  constexpr uint32_t kTmemCols = kAccCols <= 32 ? 32 : kAccCols <= 64 ? 64 : kAccCols <= 128 ? 128 : kAccCols <= 256 ? 256 : 512;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStageBytes);
@@ -409,7 +562,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
         uint8_t* sB = sA + kABytesW;
         mbar_expect_tx(&full_bar[stage], kStageBytes);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) tma_load_2d(sA + j * kChunk, &tmDY, &full_bar[stage], k_tile * 128 + j * 64, pix0);
+        for (int j = 0; j < 2 * MH; ++j) tma_load_2d(sA + j * kChunk, &tmDY, &full_bar[stage], k_tile * (128 * MH) + j * 64, pix0);
         if (g.x_im2col) {
           const int n_img = pix0 / pq, rem = pix0 - n_img * pq;
           const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
@@ -438,9 +591,12 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
         for (int k = 0; k < kPix / 16; ++k) {
           // MN-major SWIZZLE_128B: a row is one pixel (128 B = 64 channels); 8-pixel groups are 1024 B apart (SBO),
           // 64-channel chunks are kChunk apart (LBO); a 16-pixel K step is +2048 B.
-          const uint64_t ad = make_smem_desc(sA + k * 2048, kChunk, 1024);
           const uint64_t bd = make_smem_desc(sB + k * 2048, kChunk, 1024);
-          umma_f16(tmem_base, ad, bd, idesc, (i | k) ? 1u : 0u);
+#pragma unroll
+          for (int h = 0; h < MH; ++h) {
+            const uint64_t ad = make_smem_desc(sA + h * 2 * kChunk + k * 2048, kChunk, 1024);
+            umma_f16(tmem_base + (uint32_t)(h * BNC), ad, bd, idesc, (i | k) ? 1u : 0u);
+          }
         }
         umma_commit(&empty_bar[stage]);
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -452,19 +608,22 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
     const int quarter = warp & 3;
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
-    const int k = k_tile * 128 + quarter * 32 + lane;
-    float* orow = g.ws + (((size_t)split * g.K + (size_t)(k < g.K ? k : 0)) * g.taps + tap) * g.C + (size_t)c_tile * BNC;
 #pragma unroll 1
-    for (int c = 0; c < BNC / 32; ++c) {
-      uint32_t v[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
-      tmem_ld_wait();
-      if (k < g.K) {
-        const int c_left = g.C - c_tile * BNC - c * 32;  // valid input channels from this chunk on
+    for (int h = 0; h < MH; ++h) {
+      const int k = k_tile * (128 * MH) + h * 128 + quarter * 32 + lane;
+      float* orow = g.ws + (((size_t)split * g.K + (size_t)(k < g.K ? k : 0)) * g.taps + tap) * g.C + (size_t)c_tile * BNC;
+#pragma unroll 1
+      for (int c = 0; c < BNC / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(h * BNC + c * 32), v);
+        tmem_ld_wait();
+        if (k < g.K) {
+          const int c_left = g.C - c_tile * BNC - c * 32;  // valid input channels from this chunk on
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (j * 4 < c_left)
-            *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          for (int j = 0; j < 8; ++j)
+            if (j * 4 < c_left)
+              *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
       }
     }
   }
@@ -567,36 +726,55 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int BN, int STAGES>
-static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, cudaStream_t st) {
-  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + 1024 + 256;
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  const int total = ceil_div(g.Nout, BN) * ceil_div(g.M, kBlockM);
-  const int slots = num_sms() * (BN == 256 ? 1 : 2);  // 2 x BN TMEM columns and the smem ring bound residency
-  const int grid = total < slots ? total : slots;
-  conv_tc_gemm_persistent_kernel<BN, STAGES><<<grid, kThreads, smem, st>>>(tmA, tmB, g);
-  DV_LAUNCH_OK("conv_tc_gemm_persistent_kernel");
-  return DV_OK;
-}
-
 static int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
 }
 
-template <int BNC, int STAGES>
+template <int BN, int STAGES, bool STATS, bool B_MN>
+static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, cudaStream_t st) {
+  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + 256;
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  // ask for the whole L1/shared array as shared memory: otherwise the driver sizes the carve-out for ONE CTA of this
+  // kernel and a second CTA never becomes resident (measured: occupancy 1 -> 2 for the 96 KB variants)
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
+  static int occ_cached = 0;  // resident CTAs per SM as the runtime sees it (shared memory and 2 x BN TMEM columns bound it)
+  if (occ_cached == 0) {
+    int occ = 0;
+    DV_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, kThreads, smem));
+    const int tmem_limit = 512 / (2 * BN);
+    occ_cached = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
+    if (env_int("DV_TC_DEBUG", 0))
+      fprintf(stderr, "dv conv_tc: gemm<BN=%d,STAGES=%d,STATS=%d> smem=%d occupancy(api)=%d used=%d\n", BN, STAGES, (int)STATS + 2 * (int)B_MN, smem, occ,
+              occ_cached);
+  }
+  const int num_n = ceil_div(g.Nout, BN);
+  const int total = num_n * ceil_div(g.M, kBlockM);
+  int slots = num_sms() * occ_cached;
+  if (slots > num_n) slots -= slots % num_n;  // a CTA then keeps one n-tile for its whole life (running BN sums stay put)
+  const int grid = total < slots ? total : slots;
+  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, g);
+  DV_LAUNCH_OK("conv_tc_gemm_persistent_kernel");
+  return DV_OK;
+}
+
+template <int BNC, int STAGES, int MH>
 static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradArgs& g, int tiles, int splits,
                         cudaStream_t st) {
-  constexpr int smem = STAGES * (2 + BNC / 64) * 8192 + 1024 + 256;
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_wgrad_kernel<BNC, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  constexpr int smem = STAGES * (2 * MH + BNC / 64) * 8192 + 1024 + 256;
+  static_assert(smem <= 227 * 1024, "wgrad ring exceeds shared memory");
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_wgrad_kernel<BNC, STAGES, MH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_wgrad_kernel<BNC, STAGES, MH>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
   dim3 grid((unsigned)tiles, (unsigned)splits);
-  conv_tc_wgrad_kernel<BNC, STAGES><<<grid, kThreads, smem, st>>>(tmDY, tmX, g);
+  conv_tc_wgrad_kernel<BNC, STAGES, MH><<<grid, kThreads, smem, st>>>(tmDY, tmX, g);
   DV_LAUNCH_OK("conv_tc_wgrad_kernel");
   return DV_OK;
 }
 
 struct WgradPlan {
-  int bnc, c_tiles, k_tiles, tiles, kb_total, kb_per_split, splits;
+  int bnc, mh, c_tiles, k_tiles, tiles, kb_total, kb_per_split, splits;
 };
 
 static WgradPlan plan_wgrad(const dv_conv_params* p) {
@@ -605,11 +783,12 @@ static WgradPlan plan_wgrad(const dv_conv_params* p) {
   const int64_t mpix = (int64_t)p->N * P * Q;
   w.bnc = p->C >= 256 ? 256 : ceil_div(p->C, 64) * 64;  // 64, 128, 192 or 256 input channels per tile
   w.c_tiles = ceil_div(p->C, w.bnc);
-  w.k_tiles = ceil_div(p->K, 128);
+  w.mh = p->K > 128 ? 2 : 1;  // 256 output channels per CTA when there are that many
+  w.k_tiles = ceil_div(p->K, 128 * w.mh);
   w.tiles = w.k_tiles * w.c_tiles * p->R * p->S;
   w.kb_total = (int)ceil_div64(mpix, 64);
-  // one wave of CTAs: 2 per SM while the ring fits twice (BNC <= 128), else 1; never less than 4 stages of work each
-  const int slots = num_sms() * (w.bnc <= 128 ? 2 : 1);
+  // one wave of CTAs: 2 per SM while the ring fits twice (MH == 1, BNC <= 128), else 1; never less than 4 stages of work each
+  const int slots = num_sms() * ((w.mh == 1 && w.bnc <= 128) ? 2 : 1);
   int want = slots / w.tiles;
   int max_by_len = w.kb_total / 4 > 0 ? w.kb_total / 4 : 1;
   int splits = want < max_by_len ? want : max_by_len;
@@ -676,11 +855,25 @@ static int pick_bn(int nout) {
   return bn;
 }
 
-static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, cudaStream_t st) {
+static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, bool b_mn, cudaStream_t st) {
+  if (b_mn) {
+    switch (bn) {
+      case 64: return launch_gemm_persistent<64, 4, false, true>(tmA, tmB, g, st);
+      case 128: return launch_gemm_persistent<128, 3, false, true>(tmA, tmB, g, st);
+      default: return launch_gemm_persistent<256, 4, false, true>(tmA, tmB, g, st);
+    }
+  }
+  if (g.stat_sums != nullptr) {
+    switch (bn) {
+      case 64: return launch_gemm_persistent<64, 4, true, false>(tmA, tmB, g, st);
+      case 128: return launch_gemm_persistent<128, 3, true, false>(tmA, tmB, g, st);
+      default: return launch_gemm_persistent<256, 4, true, false>(tmA, tmB, g, st);
+    }
+  }
   switch (bn) {
-    case 64: return launch_gemm_persistent<64, 4>(tmA, tmB, g, st);
-    case 128: return launch_gemm_persistent<128, 3>(tmA, tmB, g, st);
-    default: return launch_gemm_persistent<256, 4>(tmA, tmB, g, st);
+    case 64: return launch_gemm_persistent<64, 4, false, false>(tmA, tmB, g, st);
+    case 128: return launch_gemm_persistent<128, 3, false, false>(tmA, tmB, g, st);
+    default: return launch_gemm_persistent<256, 4, false, false>(tmA, tmB, g, st);
   }
 }
 
@@ -704,17 +897,19 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     g.P = P; g.Q = Q; g.stride = p->stride; g.pad = p->pad;
     g.a_im2col = !(p->R == 1 && p->S == 1 && p->stride == 1 && p->pad == 0);
     g.out_f32 = p->y_f32 ? 1 : 0;
+    g.stat_sums = p->y_f32 ? nullptr : p->stat_sums;
     const int bn = pick_bn(p->K);
     if (g.a_im2col) rc = make_map_im2col(&tmA, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, kBlockM);
     else rc = make_map_2d(&tmA, p->x, (uint64_t)g.M, (uint64_t)p->C, kBlockM);
     if (rc) return rc;
     rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, (uint32_t)bn);
     if (rc) return rc;
-    return gemm_dispatch(tmA, tmB, g, bn, st);
+    return gemm_dispatch(tmA, tmB, g, bn, false, st);
   }
 
   if (pass == DV_CONV_DGRAD) {
-    DV_REQUIRE(p->w_t != nullptr && aligned16(p->w_t), DV_ERR_ARG, "conv_tc dgrad: w_t (flipped [C,R,S,K] filters from dv_filter_prep) is required");
+    DV_REQUIRE(p->w_t == nullptr || aligned16(p->w_t), DV_ERR_ARG, "conv_tc dgrad: w_t must be 16-byte aligned");
+    const bool b_mn = (p->w_t == nullptr);  // no transposed copy given: read the KRSC filters MN-major, flip taps by index
     GemmArgs g{};
     g.out = (bf16*)p->x;
     g.accumulate = p->accumulate ? 1 : 0;
@@ -744,9 +939,10 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
       rc = make_map_2d(&tmA, p->y, (uint64_t)g.M, (uint64_t)p->K, kBlockM);
     }
     if (rc) return rc;
-    rc = make_map_2d(&tmB, p->w_t, (uint64_t)p->C, (uint64_t)p->R * p->S * p->K, (uint32_t)bn);
+    if (b_mn) rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, 64);
+    else rc = make_map_2d(&tmB, p->w_t, (uint64_t)p->C, (uint64_t)p->R * p->S * p->K, (uint32_t)bn);
     if (rc) return rc;
-    return gemm_dispatch(tmA, tmB, g, bn, st);
+    return gemm_dispatch(tmA, tmB, g, bn, b_mn, st);
   }
 
   // wgrad
@@ -769,11 +965,20 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
   if (g.x_im2col) rc = make_map_im2col(&tmB, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, 64);
   else rc = make_map_2d(&tmB, p->x, (uint64_t)g.Mpix, (uint64_t)p->C, 64);
   if (rc) return rc;
-  switch (w.bnc) {
-    case 64: rc = launch_wgrad<64, 4>(tmA, tmB, g, w.tiles, w.splits, st); break;
-    case 128: rc = launch_wgrad<128, 3>(tmA, tmB, g, w.tiles, w.splits, st); break;
-    case 192: rc = launch_wgrad<192, 4>(tmA, tmB, g, w.tiles, w.splits, st); break;
-    default: rc = launch_wgrad<256, 4>(tmA, tmB, g, w.tiles, w.splits, st); break;
+  if (w.mh == 1) {
+    switch (w.bnc) {
+      case 64: rc = launch_wgrad<64, 4, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      case 128: rc = launch_wgrad<128, 3, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      case 192: rc = launch_wgrad<192, 4, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      default: rc = launch_wgrad<256, 4, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
+    }
+  } else {
+    switch (w.bnc) {
+      case 64: rc = launch_wgrad<64, 5, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      case 128: rc = launch_wgrad<128, 4, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      case 192: rc = launch_wgrad<192, 3, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      default: rc = launch_wgrad<256, 3, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
+    }
   }
   if (rc) return rc;
   const int64_t n4 = (int64_t)p->K * p->R * p->S * p->C / 4;

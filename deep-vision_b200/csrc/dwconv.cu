@@ -1,9 +1,12 @@
 // dwconv.cu — depth-wise 3x3 convolution (pad 1, stride 1|2, groups == C) for MobileNetV1's DepthwiseConv
 // (MobileNet/pytorch/models/mobilenet_v1.py:109-133).  Arithmetic intensity is ~3.5 FLOP/B, so the design target is
 // the HBM roof: NHWC, one 16-byte channel vector per thread, consecutive threads on consecutive channels (coalesced
-// 128 B lines), the 9 taps of a channel slab cached in shared memory, neighbouring pixels' halo served by L1/L2.
+// 128 B lines), the 9 taps of a channel slab cached in shared memory.  Each thread produces a STRIP of 4 neighbouring
+// outputs along W and keeps the input columns they share in registers (18 loads instead of 36 for stride 1), all index
+// arithmetic is 32-bit and the stride is a template constant.
 //   fprop : y[n,p,q,c]  = sum_{r,s} x[n, p*st+r-1, q*st+s-1, c] * w[c,r,s]
-//   dgrad : dx[n,h,w,c] = sum_{r,s} dy[n, (h+1-r)/st, (w+1-s)/st, c] * w[c,r,s]      (divisible & in range)
+//   dgrad : stride 1: the same kernel on dy with the taps flipped;
+//           stride 2: one thread per 2x2 block of dx, which depends on exactly dy[i..i+1][j..j+1]
 //   wgrad : dw[c,r,s]   = sum_{n,p,q} dy[n,p,q,c] * x[n, p*st+r-1, q*st+s-1, c]      (block partials -> fixed-order reduce)
 #include "common.cuh"
 
@@ -28,123 +31,244 @@ static DwPlan dw_plan(int C, int V) {
   return p;
 }
 
-// DGRAD == false: fprop over output pixels (P,Q).  DGRAD == true: dgrad over input pixels (H,W).
-template <typename T, bool DGRAD>
-__global__ void __launch_bounds__(kThreads)
-dwconv_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __restrict__ out, DwDims d, int cgb, int lanes,
-              int64_t pix_per_blk) {
-  constexpr int V = Vec16<T>::N;
-  __shared__ float ws[9][128 * V];
-  const int cg0 = blockIdx.y * cgb;
-  const int nch = min(cgb * V, d.C - cg0 * V);
+template <int V>
+__device__ __forceinline__ void load_taps(float (*ws)[128 * V], const float* __restrict__ w, int c0, int nch, bool flip) {
   for (int i = threadIdx.x; i < 9 * nch; i += kThreads) {
-    const int ch = i / 9, tap = i % 9;
-    ws[tap][ch] = w[(size_t)(cg0 * V + ch) * 9 + tap];
-  }
-  __syncthreads();
-  const int tcg = threadIdx.x % cgb, lane = threadIdx.x / cgb;
-  if (lane >= lanes || (cg0 + tcg) * V >= d.C) return;
-  const int c = (cg0 + tcg) * V;
-  const int OH = DGRAD ? d.H : d.P, OW = DGRAD ? d.W : d.Q;  // extent this kernel writes
-  const int IH = DGRAD ? d.P : d.H, IW = DGRAD ? d.Q : d.W;  // extent it reads
-  const int64_t npix = (int64_t)d.N * OH * OW;
-  const int64_t p0 = (int64_t)blockIdx.x * pix_per_blk;
-  const int64_t p1 = (p0 + pix_per_blk < npix) ? p0 + pix_per_blk : npix;
-  for (int64_t pix = p0 + lane; pix < p1; pix += lanes) {
-    const int n = (int)(pix / (OH * OW)), rem = (int)(pix % (OH * OW));
-    const int oh = rem / OW, ow = rem % OW;
-    float acc[V];
-#pragma unroll
-    for (int j = 0; j < V; ++j) acc[j] = 0.f;
-#pragma unroll
-    for (int r = 0; r < 3; ++r) {
-      int ih;
-      if (DGRAD) {
-        const int t = oh + 1 - r;
-        if (t < 0 || t % d.stride) continue;
-        ih = t / d.stride;
-      } else {
-        ih = oh * d.stride + r - 1;
-      }
-      if ((unsigned)ih >= (unsigned)IH) continue;
-#pragma unroll
-      for (int s = 0; s < 3; ++s) {
-        int iw;
-        if (DGRAD) {
-          const int t = ow + 1 - s;
-          if (t < 0 || t % d.stride) continue;
-          iw = t / d.stride;
-        } else {
-          iw = ow * d.stride + s - 1;
-        }
-        if ((unsigned)iw >= (unsigned)IW) continue;
-        float xv[V];
-        Vec16<T> v; v.load(in + (((size_t)n * IH + ih) * IW + iw) * d.C + c); v.unpack(xv);
-        const float* wt = &ws[r * 3 + s][tcg * V];
-#pragma unroll
-        for (int j = 0; j < V; ++j) acc[j] = fmaf(xv[j], wt[j], acc[j]);
-      }
-    }
-    Vec16<T> o; o.pack(acc); o.store(out + (size_t)pix * d.C + c);
+    const int ch = i / 9, tap = i - ch * 9;
+    ws[flip ? 8 - tap : tap][ch] = w[(size_t)(c0 + ch) * 9 + tap];
   }
 }
 
+// out[n,oh,ow,c] = sum_{r,s} in[n, oh*ST+r-1, ow*ST+s-1, c] * taps[r][s]   (in: [N,IH,IW,C], out: [N,OH,OW,C])
+// outputs per thread along W: 4 for stride 1 (6 input columns), 2 for stride 2 (5 input columns) and for wgrad, whose 72
+// accumulators already fill the register budget
+template <int ST> struct StripW { static constexpr int fwd = ST == 1 ? 4 : 2; static constexpr int wgrad = 2; };
+
+template <typename T, int ST>
+__global__ void __launch_bounds__(kThreads, 2)
+dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __restrict__ out, int N, int IH, int IW, int OH, int OW,
+                    int C, int cgb, int lanes, int strips_per_blk, int flip) {
+  constexpr int V = Vec16<T>::N;
+  constexpr int TW = StripW<ST>::fwd;
+  constexpr int NCOL = (TW - 1) * ST + 3;  // input columns a strip touches
+  __shared__ __align__(16) float ws[9][128 * V];
+  const int cg0 = blockIdx.y * cgb;
+  load_taps<V>(ws, w, cg0 * V, min(cgb * V, C - cg0 * V), flip != 0);
+  __syncthreads();
+  const int tcg = threadIdx.x % cgb, lane = threadIdx.x / cgb;
+  if (lane >= lanes || (cg0 + tcg) * V >= C) return;
+  const int c = (cg0 + tcg) * V;
+  const int strips_w = (OW + TW - 1) / TW;
+  const int nstrips = N * OH * strips_w;
+  const int s0 = blockIdx.x * strips_per_blk;
+  const int s1 = min(nstrips, s0 + strips_per_blk);
+  for (int sidx = s0 + lane; sidx < s1; sidx += lanes) {
+    const int sw = sidx % strips_w;
+    const int t = sidx / strips_w;
+    const int oh = t % OH, n = t / OH;
+    const int ow0 = sw * TW;
+    float acc[TW][V];
+#pragma unroll
+    for (int j = 0; j < TW; ++j)
+#pragma unroll
+      for (int e = 0; e < V; ++e) acc[j][e] = 0.f;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int ih = oh * ST + r - 1;
+      if ((unsigned)ih >= (unsigned)IH) continue;
+      const T* row = in + ((size_t)n * IH + ih) * IW * C + c;
+      Vec16<T> raw[NCOL];
+#pragma unroll
+      for (int k = 0; k < NCOL; ++k) {
+        const int iw = ow0 * ST - 1 + k;
+        if ((unsigned)iw < (unsigned)IW) raw[k].load(row + (size_t)iw * C);
+      }
+      float xv[NCOL][V];
+#pragma unroll
+      for (int k = 0; k < NCOL; ++k) {
+        const int iw = ow0 * ST - 1 + k;
+        if ((unsigned)iw < (unsigned)IW) raw[k].unpack(xv[k]);
+        else {
+#pragma unroll
+          for (int e = 0; e < V; ++e) xv[k][e] = 0.f;
+        }
+      }
+      // one shared-memory read of each tap's weights per strip (not per output): the taps are the outer loop
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        float wv[V];
+        const float* wt = &ws[r * 3 + s][tcg * V];
+#pragma unroll
+        for (int e = 0; e < V; e += 4) {
+          const float4 q4 = *reinterpret_cast<const float4*>(wt + e);
+          wv[e] = q4.x; wv[e + 1] = q4.y; wv[e + 2] = q4.z; wv[e + 3] = q4.w;
+        }
+#pragma unroll
+        for (int j = 0; j < TW; ++j) {
+#pragma unroll
+          for (int e = 0; e < V; ++e) acc[j][e] = fmaf(xv[j * ST + s][e], wv[e], acc[j][e]);
+        }
+      }
+    }
+    T* orow = out + (((size_t)n * OH + oh) * OW + ow0) * C + c;
+#pragma unroll
+    for (int j = 0; j < TW; ++j) {
+      if (ow0 + j < OW) { Vec16<T> o; o.pack(acc[j]); o.store(orow + (size_t)j * C); }
+    }
+  }
+}
+
+// stride-2 dgrad: dx[2i+a, 2j+b] for a,b in {0,1} from dy[i..i+1][j..j+1]
+//   (2i  ,2j  ) = dy[i,j]*w11
+//   (2i  ,2j+1) = dy[i,j]*w12 + dy[i,j+1]*w10
+//   (2i+1,2j  ) = dy[i,j]*w21 + dy[i+1,j]*w01
+//   (2i+1,2j+1) = dy[i,j]*w22 + dy[i,j+1]*w20 + dy[i+1,j]*w02 + dy[i+1,j+1]*w00
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-dwconv_wgrad_kernel(const T* __restrict__ x, const T* __restrict__ dy, float* __restrict__ partial, DwDims d, int cgb, int lanes,
-                    int64_t pix_per_blk) {
+dwconv_dgrad_s2_kernel(const T* __restrict__ dy, const float* __restrict__ w, T* __restrict__ dx, int N, int H, int W, int P, int Q,
+                       int C, int cgb, int lanes, int cells_per_blk) {
   constexpr int V = Vec16<T>::N;
+  __shared__ __align__(16) float ws[9][128 * V];
+  const int cg0 = blockIdx.y * cgb;
+  load_taps<V>(ws, w, cg0 * V, min(cgb * V, C - cg0 * V), false);
+  __syncthreads();
+  const int tcg = threadIdx.x % cgb, lane = threadIdx.x / cgb;
+  if (lane >= lanes || (cg0 + tcg) * V >= C) return;
+  const int c = (cg0 + tcg) * V;
+  const int ch = (H + 1) / 2, cw = (W + 1) / 2;
+  const int ncells = N * ch * cw;
+  const int c0 = blockIdx.x * cells_per_blk;
+  const int c1 = min(ncells, c0 + cells_per_blk);
+  for (int cell = c0 + lane; cell < c1; cell += lanes) {
+    const int j = cell % cw;
+    const int t = cell / cw;
+    const int i = t % ch, n = t / ch;
+    float g[2][2][V];
+    Vec16<T> raw[2][2];
+    bool ok[2][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        ok[a][b] = (i + a < P) && (j + b < Q);
+        if (ok[a][b]) raw[a][b].load(dy + (((size_t)n * P + i + a) * Q + j + b) * C + c);
+      }
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        if (ok[a][b]) raw[a][b].unpack(g[a][b]);
+        else {
+#pragma unroll
+          for (int e = 0; e < V; ++e) g[a][b][e] = 0.f;
+        }
+      }
+    const float* wt = &ws[0][tcg * V];
+    constexpr int WS = 128 * V;  // stride between taps in ws
+    float o00[V], o01[V], o10[V], o11[V];
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+      const float w00 = wt[0 * WS + e], w01 = wt[1 * WS + e], w02 = wt[2 * WS + e];
+      const float w10 = wt[3 * WS + e], w11 = wt[4 * WS + e], w12 = wt[5 * WS + e];
+      const float w20 = wt[6 * WS + e], w21 = wt[7 * WS + e], w22 = wt[8 * WS + e];
+      o00[e] = g[0][0][e] * w11;
+      o01[e] = fmaf(g[0][0][e], w12, g[0][1][e] * w10);
+      o10[e] = fmaf(g[0][0][e], w21, g[1][0][e] * w01);
+      o11[e] = fmaf(g[0][0][e], w22, fmaf(g[0][1][e], w20, fmaf(g[1][0][e], w02, g[1][1][e] * w00)));
+    }
+    const int h = 2 * i, x = 2 * j;
+    T* base = dx + (((size_t)n * H + h) * W + x) * C + c;
+    Vec16<T> o;
+    o.pack(o00); o.store(base);
+    if (x + 1 < W) { o.pack(o01); o.store(base + C); }
+    if (h + 1 < H) {
+      o.pack(o10); o.store(base + (size_t)W * C);
+      if (x + 1 < W) { o.pack(o11); o.store(base + (size_t)W * C + C); }
+    }
+  }
+}
+
+template <typename T, int ST>
+__global__ void __launch_bounds__(kThreads, 2)
+dwconv_wgrad_kernel(const T* __restrict__ x, const T* __restrict__ dy, float* __restrict__ partial, int N, int H, int W, int P, int Q,
+                    int C, int cgb, int lanes, int strips_per_blk) {
+  constexpr int V = Vec16<T>::N;
+  constexpr int TW = StripW<ST>::wgrad;
+  constexpr int NCOL = (TW - 1) * ST + 3;
   __shared__ float red[kThreads * V];
   const int cg0 = blockIdx.y * cgb;
   const int tcg = threadIdx.x % cgb, lane = threadIdx.x / cgb;
-  const bool active = lane < lanes && (cg0 + tcg) * V < d.C;
+  const bool active = lane < lanes && (cg0 + tcg) * V < C;
   const int c = (cg0 + tcg) * V;
   float acc[9][V];
 #pragma unroll
   for (int t = 0; t < 9; ++t)
 #pragma unroll
-    for (int j = 0; j < V; ++j) acc[t][j] = 0.f;
-  const int64_t npix = (int64_t)d.N * d.P * d.Q;
-  const int64_t p0 = (int64_t)blockIdx.x * pix_per_blk;
-  const int64_t p1 = (p0 + pix_per_blk < npix) ? p0 + pix_per_blk : npix;
+    for (int e = 0; e < V; ++e) acc[t][e] = 0.f;
+  const int strips_w = (Q + TW - 1) / TW;
+  const int nstrips = N * P * strips_w;
+  const int s0 = blockIdx.x * strips_per_blk;
+  const int s1 = min(nstrips, s0 + strips_per_blk);
   if (active) {
-    for (int64_t pix = p0 + lane; pix < p1; pix += lanes) {
-      const int n = (int)(pix / (d.P * d.Q)), rem = (int)(pix % (d.P * d.Q));
-      const int p = rem / d.Q, q = rem % d.Q;
-      float g[V];
-      Vec16<T> vg; vg.load(dy + (size_t)pix * d.C + c); vg.unpack(g);
+    for (int sidx = s0 + lane; sidx < s1; sidx += lanes) {
+      const int sw = sidx % strips_w;
+      const int t = sidx / strips_w;
+      const int p = t % P, n = t / P;
+      const int q0 = sw * TW;
+      float g[TW][V];
+      const T* gy = dy + (((size_t)n * P + p) * Q + q0) * C + c;
+#pragma unroll
+      for (int j = 0; j < TW; ++j) {
+        if (q0 + j < Q) { Vec16<T> v; v.load(gy + (size_t)j * C); v.unpack(g[j]); }
+        else {
+#pragma unroll
+          for (int e = 0; e < V; ++e) g[j][e] = 0.f;
+        }
+      }
 #pragma unroll
       for (int r = 0; r < 3; ++r) {
-        const int h = p * d.stride + r - 1;
-        if ((unsigned)h >= (unsigned)d.H) continue;
+        const int h = p * ST + r - 1;
+        if ((unsigned)h >= (unsigned)H) continue;
+        const T* row = x + ((size_t)n * H + h) * W * C + c;
+        Vec16<T> raw[NCOL];
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
-          const int w = q * d.stride + s - 1;
-          if ((unsigned)w >= (unsigned)d.W) continue;
+        for (int k = 0; k < NCOL; ++k) {
+          const int iw = q0 * ST - 1 + k;
+          if ((unsigned)iw < (unsigned)W) raw[k].load(row + (size_t)iw * C);
+        }
+#pragma unroll
+        for (int k = 0; k < NCOL; ++k) {
+          const int iw = q0 * ST - 1 + k;
+          if ((unsigned)iw >= (unsigned)W) continue;
           float xv[V];
-          Vec16<T> vx; vx.load(x + (((size_t)n * d.H + h) * d.W + w) * d.C + c); vx.unpack(xv);
+          raw[k].unpack(xv);
 #pragma unroll
-          for (int j = 0; j < V; ++j) acc[r * 3 + s][j] = fmaf(xv[j], g[j], acc[r * 3 + s][j]);
+          for (int j = 0; j < TW; ++j) {
+            const int s = k - j * ST;
+            if (s < 0 || s > 2) continue;
+#pragma unroll
+            for (int e = 0; e < V; ++e) acc[r * 3 + s][e] = fmaf(xv[e], g[j][e], acc[r * 3 + s][e]);
+          }
         }
       }
     }
   }
-  // reduce the pixel lanes of this block, one tap at a time
+  // reduce the strip lanes of this block, one tap at a time
 #pragma unroll
   for (int t = 0; t < 9; ++t) {
 #pragma unroll
-    for (int j = 0; j < V; ++j) red[threadIdx.x * V + j] = acc[t][j];
+    for (int e = 0; e < V; ++e) red[threadIdx.x * V + e] = acc[t][e];
     __syncthreads();
     if (lane == 0 && active) {
       float s[V];
 #pragma unroll
-      for (int j = 0; j < V; ++j) s[j] = 0.f;
+      for (int e = 0; e < V; ++e) s[e] = 0.f;
       for (int l = 0; l < lanes; ++l)
 #pragma unroll
-        for (int j = 0; j < V; ++j) s[j] += red[(l * cgb + tcg) * V + j];
-      float* dst = partial + ((size_t)blockIdx.x * 9 + t) * d.C + c;
+        for (int e = 0; e < V; ++e) s[e] += red[(l * cgb + tcg) * V + e];
+      float* dst = partial + ((size_t)blockIdx.x * 9 + t) * C + c;
 #pragma unroll
-      for (int j = 0; j < V; ++j) dst[j] = s[j];
+      for (int e = 0; e < V; ++e) dst[e] = s[e];
     }
     __syncthreads();
   }
@@ -160,13 +284,6 @@ __global__ void dwconv_wgrad_finalize_kernel(const float* __restrict__ partial, 
   dw[(size_t)c * 9 + t] = (float)s;
 }
 
-static int wgrad_blocks(int64_t npix, int lanes) {
-  int64_t nb = ceil_div64(npix, (int64_t)lanes * 16);
-  const int64_t cap = (int64_t)num_sms() * 2;
-  if (nb > cap) nb = cap;
-  return (int)(nb < 1 ? 1 : nb);
-}
-
 static DwDims dims_of(const dv_dwconv_params* p) {
   DwDims d;
   d.N = p->N; d.H = p->H; d.W = p->W; d.C = p->C; d.stride = p->stride;
@@ -175,23 +292,69 @@ static DwDims dims_of(const dv_dwconv_params* p) {
   return d;
 }
 
-template <typename T, bool DGRAD>
-static int run_fd(const dv_dwconv_params* p, cudaStream_t st) {
+// blocks over `units` work items (strips / cells) with `lanes` lanes per block, capped at `cap_per_sm` blocks per SM
+static void split_units(int64_t units, int lanes, int per_lane, int cap_per_sm, int* nblk, int* per_blk) {
+  int64_t nb = ceil_div64(units, (int64_t)lanes * per_lane);
+  const int64_t cap = (int64_t)num_sms() * cap_per_sm;
+  if (nb > cap) nb = cap;
+  if (nb < 1) nb = 1;
+  const int64_t pb = ceil_div64(units, nb);
+  *per_blk = (int)pb;
+  *nblk = (int)ceil_div64(units, pb);
+}
+
+static int wgrad_blocks(const DwDims& d, int lanes, int* per_blk) {
+  const int64_t strips = (int64_t)d.N * d.P * ceil_div(d.Q, 2);  // StripW::wgrad
+  int nb;
+  split_units(strips, lanes, 8, 4, &nb, per_blk);
+  return nb;
+}
+
+template <typename T>
+static int run_fprop(const dv_dwconv_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
   DwPlan pl = dw_plan(p->C, V);
-  const int64_t npix = (int64_t)d.N * (DGRAD ? d.H * d.W : d.P * d.Q);
-  int64_t nb = ceil_div64(npix, (int64_t)pl.lanes * 8);
-  const int64_t cap = (int64_t)num_sms() * 16;
-  if (nb > cap) nb = cap;
-  const int64_t ppb = ceil_div64(npix, nb);
-  nb = ceil_div64(npix, ppb);
+  const int64_t strips = (int64_t)d.N * d.P * ceil_div(d.Q, d.stride == 1 ? StripW<1>::fwd : StripW<2>::fwd);
+  DV_REQUIRE(strips < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
+  int nb, per;
+  split_units(strips, pl.lanes, 4, 16, &nb, &per);
   dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
-  const T* in = (const T*)(DGRAD ? p->y : p->x);
-  T* out = (T*)(DGRAD ? p->x : p->y);
-  dwconv_kernel<T, DGRAD><<<grid, kThreads, 0, st>>>(in, (const float*)p->w, out, d, pl.cgb, pl.lanes, ppb);
-  DV_LAUNCH_OK("dwconv_kernel");
+  if (d.stride == 1)
+    dwconv_strip_kernel<T, 1><<<grid, kThreads, 0, st>>>((const T*)p->x, (const float*)p->w, (T*)p->y, d.N, d.H, d.W, d.P, d.Q, d.C, pl.cgb,
+                                                       pl.lanes, per, 0);
+  else
+    dwconv_strip_kernel<T, 2><<<grid, kThreads, 0, st>>>((const T*)p->x, (const float*)p->w, (T*)p->y, d.N, d.H, d.W, d.P, d.Q, d.C, pl.cgb,
+                                                       pl.lanes, per, 0);
+  DV_LAUNCH_OK("dwconv_strip_kernel");
+  return DV_OK;
+}
+
+template <typename T>
+static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
+  DwDims d = dims_of(p);
+  DwPlan pl = dw_plan(p->C, V);
+  int nb, per;
+  if (d.stride == 1) {
+    // dx = "fprop" of dy with the taps flipped (pad 1 both ways)
+    const int64_t strips = (int64_t)d.N * d.H * ceil_div(d.W, StripW<1>::fwd);
+    DV_REQUIRE(strips < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
+    split_units(strips, pl.lanes, 4, 16, &nb, &per);
+    dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
+    dwconv_strip_kernel<T, 1><<<grid, kThreads, 0, st>>>((const T*)p->y, (const float*)p->w, (T*)p->x, d.N, d.P, d.Q, d.H, d.W, d.C, pl.cgb,
+                                                       pl.lanes, per, 1);
+  } else {
+    const int64_t cells = (int64_t)d.N * ((d.H + 1) / 2) * ((d.W + 1) / 2);
+    DV_REQUIRE(cells < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
+    split_units(cells, pl.lanes, 8, 16, &nb, &per);
+    dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
+    dwconv_dgrad_s2_kernel<T><<<grid, kThreads, 0, st>>>((const T*)p->y, (const float*)p->w, (T*)p->x, d.N, d.H, d.W, d.P, d.Q, d.C, pl.cgb,
+                                                       pl.lanes, per);
+  }
+  DV_LAUNCH_OK("dwconv dgrad");
   return DV_OK;
 }
 
@@ -201,15 +364,18 @@ static int run_wgrad(const dv_dwconv_params* p, cudaStream_t st) {
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
   DwPlan pl = dw_plan(p->C, V);
-  const int64_t npix = (int64_t)d.N * d.P * d.Q;
-  const int nb0 = wgrad_blocks(npix, pl.lanes);
-  const int64_t ppb = ceil_div64(npix, nb0);
-  const int nb = (int)ceil_div64(npix, ppb);
+  int per;
+  const int nb = wgrad_blocks(d, pl.lanes, &per);
   const size_t need = (size_t)nb * 9 * p->C * sizeof(float);
   DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "dwconv_wgrad: workspace %zu bytes required, %zu given", need,
              p->workspace_bytes);
   dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
-  dwconv_wgrad_kernel<T><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (float*)p->workspace, d, pl.cgb, pl.lanes, ppb);
+  if (d.stride == 1)
+    dwconv_wgrad_kernel<T, 1><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (float*)p->workspace, d.N, d.H, d.W, d.P, d.Q, d.C,
+                                                       pl.cgb, pl.lanes, per);
+  else
+    dwconv_wgrad_kernel<T, 2><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (float*)p->workspace, d.N, d.H, d.W, d.P, d.Q, d.C,
+                                                       pl.cgb, pl.lanes, per);
   DV_LAUNCH_OK("dwconv_wgrad_kernel");
   dwconv_wgrad_finalize_kernel<<<ceil_div(9 * p->C, 256), 256, 0, st>>>((const float*)p->workspace, (float*)p->w, nb, p->C);
   DV_LAUNCH_OK("dwconv_wgrad_finalize_kernel");
@@ -230,17 +396,14 @@ static int check(const dv_dwconv_params* p, const char* who) {
 using namespace dv;
 
 extern "C" size_t dv_dwconv_workspace_bytes(const dv_dwconv_params* p) {
-  if (!p || p->C <= 0) return 0;
+  if (!p || p->C <= 0 || (p->stride != 1 && p->stride != 2)) return 0;
   DwDims d = dims_of(p);
-  const int64_t npix = (int64_t)d.N * d.P * d.Q;
-  // the fp32 plan has at least as many pixel lanes per channel group as bf16, so size for the larger block count
   size_t best = 0;
-  for (int V : {4, 8}) {
+  for (int V : {4, 8}) {  // sized for whichever dtype's plan needs more blocks
     if (p->C % V) continue;
     DwPlan pl = dw_plan(p->C, V);
-    const int nb0 = wgrad_blocks(npix, pl.lanes);
-    const int64_t ppb = ceil_div64(npix, nb0);
-    const size_t nb = (size_t)ceil_div64(npix, ppb);
+    int per;
+    const size_t nb = (size_t)wgrad_blocks(d, pl.lanes, &per);
     const size_t need = nb * 9 * p->C * sizeof(float);
     if (need > best) best = need;
   }
@@ -249,12 +412,12 @@ extern "C" size_t dv_dwconv_workspace_bytes(const dv_dwconv_params* p) {
 extern "C" int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_fprop");
   if (rc) return rc;
-  return p->dtype == DV_BF16 ? run_fd<bf16, false>(p, (cudaStream_t)stream) : run_fd<float, false>(p, (cudaStream_t)stream);
+  return p->dtype == DV_BF16 ? run_fprop<bf16>(p, (cudaStream_t)stream) : run_fprop<float>(p, (cudaStream_t)stream);
 }
 extern "C" int dv_dwconv_dgrad(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_dgrad");
   if (rc) return rc;
-  return p->dtype == DV_BF16 ? run_fd<bf16, true>(p, (cudaStream_t)stream) : run_fd<float, true>(p, (cudaStream_t)stream);
+  return p->dtype == DV_BF16 ? run_dgrad<bf16>(p, (cudaStream_t)stream) : run_dgrad<float>(p, (cudaStream_t)stream);
 }
 extern "C" int dv_dwconv_wgrad(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_wgrad");

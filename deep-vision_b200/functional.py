@@ -145,6 +145,28 @@ def _conv_params(x_ptr, w_ptr, y_ptr, wt_ptr, N, H, W, Cc, K, R, S, stride, pad,
     return p
 
 
+def grad_sink(param):
+    """(tensor, callback) when the trainer has registered `param` for DIRECT gradient writes: the backward kernel then
+    writes its result straight into the parameter's slice of the flat gradient buffer (no temporary, no accumulate
+    pass) and the callback tells the gradient exchange that the slice is final.  None otherwise (plain autograd)."""
+    sink = getattr(param, "_dv_grad_sink", None)
+    if sink is None or param.grad is None:
+        return None
+    return param.grad, sink
+
+
+class StatSums:
+    """[2][K] fp32 accumulator a convolution's epilogue adds sum(y), sum(y^2) to, owned by the conv module and handed
+    to the BatchNorm that follows through the activation tensor (`y._dv_stat_sums`).  `pending` guards against a
+    producer whose sums were never consumed (they are then cleared before the next use)."""
+
+    __slots__ = ("t", "pending")
+
+    def __init__(self, k, device):
+        self.t = torch.zeros(2 * k, dtype=torch.float32, device=device)
+        self.pending = False
+
+
 class GradSlot:
     """Hand-over point for the two gradients of a tensor with two consumers (the input of a residual block feeds the
     first convolution AND the shortcut: resnet50.py:147-163).  The shortcut side DEPOSITS its gradient here instead of
@@ -172,7 +194,7 @@ class _Conv2d(torch.autograd.Function):
     mobilenet_v1.py:30,139-145.  Backward = dgrad + wgrad (autograd of train.py:460)."""
 
     @staticmethod
-    def forward(ctx, x, weight, stride, pad, cache, algo, slot=None, role=None):
+    def forward(ctx, x, weight, stride, pad, cache, algo, slot=None, role=None, stats=None):
         ctx.slot, ctx.role = slot, role
         _require_cuda(x, "conv2d")
         x = _nhwc(x)
@@ -194,14 +216,15 @@ class _Conv2d(torch.autograd.Function):
             check(lib.dv_im2col(x.data_ptr(), patches.data_ptr(), N, H, W, Cc, R, S, stride, pad, kp, dt, _stream()), "dv_im2col")
             w_pad = cache.get_padded(weight, x.dtype, kp)
             p = _conv_params(patches.data_ptr(), w_pad.data_ptr(), y.data_ptr(), None, M, 1, 1, kp, K, 1, 1, 1, 0, dt, DV_ALGO_TC)
+            _attach_stats(p, stats, y, DV_CONV_FPROP)
             _run_conv(lib.dv_conv_fprop, p, DV_CONV_FPROP, x.device, "dv_conv_fprop(stem)")
             ctx.save_for_backward(patches, weight)
             ctx.patches = (M, kp, N, Cc, H, W)
             ctx.geom = (stride, pad, algo)
             return y
-        need_t = x.dtype != torch.float32 and ctx.needs_input_grad[0]
-        w_c, w_t = cache.get(weight, x.dtype, need_t)
+        w_c, w_t = cache.get(weight, x.dtype, False)  # dgrad reads the KRSC copy MN-major: no transposed filters
         p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
+        _attach_stats(p, stats, y, DV_CONV_FPROP)
         _run_conv(lib.dv_conv_fprop, p, DV_CONV_FPROP, x.device, "dv_conv_fprop")
         ctx.save_for_backward(x, weight)
         ctx.w_c, ctx.w_t = w_c, w_t
@@ -224,9 +247,13 @@ class _Conv2d(torch.autograd.Function):
                 dw_pad = torch.empty((K, kp), dtype=torch.float32, device=x.device)
                 p = _conv_params(x.data_ptr(), dw_pad.data_ptr(), dy.data_ptr(), None, M, 1, 1, kp, K, 1, 1, 1, 0, dt, DV_ALGO_TC)
                 _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad(stem)")
-                dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
+                sink = grad_sink(weight)
+                dw = sink[0] if sink else torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
                 check(lib.dv_unpad_rows(dw_pad.data_ptr(), dw.data_ptr(), K, R * S * Cc, kp, _stream()), "dv_unpad_rows")
-            return None, dw, None, None, None, None, None, None
+                if sink:
+                    sink[1](weight)
+                    dw = None
+            return None, dw, None, None, None, None, None, None, None
         N, Cc, H, W = x.shape
         if ctx.needs_input_grad[0]:
             acc = 0
@@ -242,14 +269,31 @@ class _Conv2d(torch.autograd.Function):
             if ctx.role == "deposit":
                 ctx.slot.t, dx = dx, None
         if ctx.needs_input_grad[1]:
-            dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
+            sink = grad_sink(weight)
+            dw = sink[0] if sink else torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
             p = _conv_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
             _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad")
-        return dx, dw, None, None, None, None, None, None
+            if sink:
+                sink[1](weight)
+                dw = None
+        return dx, dw, None, None, None, None, None, None, None
 
 
-def conv2d(x, weight, stride=1, padding=0, cache=None, algo=DV_ALGO_AUTO, slot=None, role=None):
-    return _Conv2d.apply(x, weight, int(stride), int(padding), cache or FilterCache(), algo, slot, role)
+def _attach_stats(p, stats, y, pass_id):
+    """Let the tensor-core epilogue accumulate BatchNorm's sums; tag the output so the BatchNorm finds them."""
+    if stats is None or lib.dv_conv_algo(C.byref(p), pass_id) != DV_ALGO_TC:
+        return
+    if stats.pending:  # produced earlier and never consumed by a BatchNorm
+        stats.t.zero_()
+    p.stat_sums = stats.t.data_ptr()
+    stats.pending = True
+
+
+def conv2d(x, weight, stride=1, padding=0, cache=None, algo=DV_ALGO_AUTO, slot=None, role=None, stats=None):
+    y = _Conv2d.apply(x, weight, int(stride), int(padding), cache or FilterCache(), algo, slot, role, stats)
+    if stats is not None and stats.pending:
+        y._dv_stat_sums = stats  # picked up by the BatchNorm that consumes y
+    return y
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -317,7 +361,8 @@ class _BatchNormAct(torch.autograd.Function):
     resnet50.py:152-164, resnet34.py:135-142, mobilenet_v1.py:129-133,152-156."""
 
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None):
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None,
+                sums=None):
         ctx.res_slot = res_slot
         _require_cuda(x, "batch_norm")
         x = _nhwc(x)
@@ -343,9 +388,13 @@ class _BatchNormAct(torch.autograd.Function):
             p.save_mean, p.save_invstd = save_mean.data_ptr(), save_invstd.data_ptr()
             if not training:  # eval without running stats: normalise with batch stats, update nothing
                 p.running_mean = p.running_var = None
-            ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
-            p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
-            check(lib.dv_bn_stats(C.byref(p), _stream()), "dv_bn_stats")
+            if sums is not None and sums.pending and sums.t.numel() == 2 * Cc:
+                check(lib.dv_bn_stats_from_sums(C.byref(p), sums.t.data_ptr(), _stream()), "dv_bn_stats_from_sums")
+                sums.pending = False
+            else:
+                ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
+                p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+                check(lib.dv_bn_stats(C.byref(p), _stream()), "dv_bn_stats")
             p.eval_mode = 0
         else:
             save_mean = save_invstd = None
@@ -375,8 +424,9 @@ class _BatchNormAct(torch.autograd.Function):
         M = N * H * W
         dx = torch.empty_like(x, memory_format=_CL)
         dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1]) else None
-        dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
-        dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        sg, sb = grad_sink(gamma), grad_sink(beta)
+        dgamma = sg[0] if sg else torch.empty(Cc, dtype=torch.float32, device=x.device)
+        dbeta = sb[0] if sb else torch.empty(Cc, dtype=torch.float32, device=x.device)
         p = BnBwdParams()
         p.x, p.y, p.dy, p.dx = x.data_ptr(), (y.data_ptr() if y is not None else None), dy.data_ptr(), dx.data_ptr()
         p.dres = dres.data_ptr() if dres is not None else None
@@ -387,14 +437,21 @@ class _BatchNormAct(torch.autograd.Function):
         p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
         check(lib.dv_bn_bwd_reduce(C.byref(p), _stream()), "dv_bn_bwd_reduce")
         check(lib.dv_bn_bwd_apply(C.byref(p), _stream()), "dv_bn_bwd_apply")
+        if sg:
+            sg[1](gamma)
+            dgamma = None
+        if sb:
+            sb[1](beta)
+            dbeta = None
         if ctx.res_slot is not None and dres is not None:
             ctx.res_slot.t, dres = dres, None   # handed to the main path's dgrad, not to autograd
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
 
 
 def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None):
+    sums = getattr(x, "_dv_stat_sums", None)
     return _BatchNormAct.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum), float(eps),
-                               bool(relu), res_slot)
+                               bool(relu), res_slot, sums)
 
 
 class _ReLU(torch.autograd.Function):
@@ -490,8 +547,7 @@ class _Linear(torch.autograd.Function):
         x = x.contiguous()
         B, F = x.shape
         K = weight.shape[0]
-        need_t = x.dtype != torch.float32 and ctx.needs_input_grad[0]
-        w_c, w_t = cache.get(weight.view(K, F, 1, 1), x.dtype, need_t)
+        w_c, w_t = cache.get(weight.view(K, F, 1, 1), x.dtype, False)
         y = torch.empty((B, K), dtype=torch.float32, device=x.device)
         algo = config.conv_algo()
         p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, B, 1, 1, F, K, 1, 1, 1, 0, _dv_dtype(x.dtype), algo, y_f32=1)

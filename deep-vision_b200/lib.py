@@ -18,7 +18,7 @@ DV_CONV_FPROP, DV_CONV_DGRAD, DV_CONV_WGRAD = 0, 1, 2
 class ConvParams(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p), ("w_t", C.c_void_p),
-        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("stat_sums", C.c_void_p),
         ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("K", C.c_int32),
         ("R", C.c_int32), ("S", C.c_int32), ("stride", C.c_int32), ("pad", C.c_int32),
         ("dtype", C.c_int32), ("algo", C.c_int32), ("y_f32", C.c_int32), ("accumulate", C.c_int32),
@@ -74,6 +74,7 @@ _SIG = {
     "dv_dwconv_workspace_bytes": (C.c_size_t, [C.POINTER(DwConvParams)]),
     "dv_bn_stats": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_apply": (C.c_int, [C.POINTER(BnParams), _P]),
+    "dv_bn_stats_from_sums": (C.c_int, [C.POINTER(BnParams), _P, _P]),
     "dv_bn_stats_static": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_bwd_reduce": (C.c_int, [C.POINTER(BnBwdParams), _P]),
     "dv_bn_bwd_apply": (C.c_int, [C.POINTER(BnBwdParams), _P]),

@@ -16,6 +16,7 @@ class Conv2d(nn.Conv2d):
     def __init__(self, *args, **kwargs):
         super().__init__(*args, **kwargs)
         self._dv_cache = F.FilterCache()
+        self._dv_stats = None
         kh, kw = self.kernel_size
         self._dv_depthwise = self.groups > 1
         if self.bias is not None:
@@ -33,7 +34,12 @@ class Conv2d(nn.Conv2d):
         x = F.to_compute_layout(x)
         if self._dv_depthwise:
             return F.dwconv3x3(x, self.weight, self.stride[0])
-        return F.conv2d(x, self.weight, self.stride[0], self.padding[0], self._dv_cache, config.conv_algo(), grad_slot, role)
+        stats = None
+        if self.training and config.fuse_bn_stats() and x.dtype == torch.bfloat16 and config.conv_algo() != 1:
+            if self._dv_stats is None or self._dv_stats.t.device != x.device:
+                self._dv_stats = F.StatSums(self.out_channels, x.device)
+            stats = self._dv_stats
+        return F.conv2d(x, self.weight, self.stride[0], self.padding[0], self._dv_cache, config.conv_algo(), grad_slot, role, stats)
 
 
 class BatchNorm2d(nn.BatchNorm2d):
@@ -49,7 +55,8 @@ class BatchNorm2d(nn.BatchNorm2d):
         else:
             eaf = self.momentum
         if self.training and self.track_running_stats and self.num_batches_tracked is not None:
-            self.num_batches_tracked.add_(1)
+            if not getattr(self, "_dv_external_nbt", False):  # the trainer bumps all counters with one launch
+                self.num_batches_tracked.add_(1)
             if self.momentum is None:
                 eaf = 1.0 / float(self.num_batches_tracked)
         training = self.training or (self.running_mean is None and self.running_var is None)

@@ -97,8 +97,9 @@ class BucketedAllReduce:
             for j in members:
                 self._bucket_of[j] = b
         self.reset()
-        for j, p in enumerate(flat.params):
-            p.register_post_accumulate_grad_hook(self._make_hook(j))
+        self.hooks = [self._make_hook(j) for j in range(len(flat.params))]
+        for p, h in zip(flat.params, self.hooks):
+            p.register_post_accumulate_grad_hook(h)   # gradients that arrive through autograd's accumulation
 
     def reset(self):
         self._pending = list(self._need)
@@ -138,10 +139,43 @@ class Trainer:
         self.flat_s = torch.zeros_like(self.flat_p)  # momentum buffer / squared-gradient average
         config.bump_weight_epoch()
         self.exchange = BucketedAllReduce(self.flat, bucket_bytes, process_group) if self.world > 1 else None
+        self._install_direct_grads()
+        self._flatten_bn_counters()
+
+    def _install_direct_grads(self):
+        """Dense-conv filters and BN affine parameters receive their gradient by a direct kernel write into the flat
+        gradient buffer (functional.grad_sink) instead of autograd's temporary + accumulate pass; the callback is the
+        exchange's bucket hook (a no-op on one GPU).  Each of these parameters is used once per forward."""
+        from . import nn as dvnn
+        index = {id(p): j for j, p in enumerate(self.flat.params)}
+        noop = lambda _p: None
+        for m in self.model.modules():
+            targets = []
+            if isinstance(m, dvnn.Conv2d) and not m._dv_depthwise:
+                targets = [m.weight]
+            elif isinstance(m, dvnn.BatchNorm2d) and m.affine:
+                targets = [m.weight, m.bias]
+            for p in targets:
+                if id(p) in index:
+                    p._dv_grad_sink = self.exchange.hooks[index[id(p)]] if self.exchange is not None else noop
+
+    def _flatten_bn_counters(self):
+        """nn.BatchNorm2d.num_batches_tracked of every layer as views into one int64 vector: one increment per step."""
+        from . import nn as dvnn
+        bns = [m for m in self.model.modules() if isinstance(m, dvnn.BatchNorm2d) and m.num_batches_tracked is not None]
+        self._nbt = None
+        if not bns:
+            return
+        self._nbt = torch.stack([m.num_batches_tracked.detach().clone() for m in bns])
+        for i, m in enumerate(bns):
+            m.num_batches_tracked.data = self._nbt[i]
+            m._dv_external_nbt = True
 
     # ---- one step -------------------------------------------------------------------------------------------------
     def _step_body(self, images, labels):
         self.flat_g.zero_()
+        if self._nbt is not None:
+            self._nbt.add_(1)
         if self.exchange is not None:
             self.exchange.reset()
         logits = self.model(images)

@@ -65,10 +65,15 @@ typedef struct dv_conv_params {
   void* x;            /* [N,H,W,C] dtype */
   void* w;            /* [K,R,S,C] dtype (fprop,dgrad: for DV_ALGO_TC dgrad see w_t) ; wgrad: fp32 out */
   void* y;            /* [N,P,Q,K] dtype */
-  const void* w_t;    /* dgrad on the tensor-core path only: filters as [C][R][S][K] with taps flipped
-                         (w_t[c,r,s,k] = w[k,R-1-r,S-1-s,c]), made by dv_filter_prep; may be NULL otherwise */
+  const void* w_t;    /* dgrad on the tensor-core path only, OPTIONAL: filters as [C][R][S][K] with taps flipped
+                         (w_t[c,r,s,k] = w[k,R-1-r,S-1-s,c]), made by dv_filter_prep.  NULL (the normal case): the kernel reads
+                         the KRSC filters `w` directly as an MN-major operand and flips the taps by index */
   void* workspace;    /* scratch, see dv_conv_workspace_bytes; may be NULL when that returns 0 */
   size_t workspace_bytes;
+  float* stat_sums;   /* fprop on the tensor-core path only, optional: [2][K] fp32 that the epilogue ADDS the per-channel sum
+                         and sum of squares of the (bf16-rounded) output to — the BatchNorm statistics pass that follows the
+                         convolution (resnet50.py:152-153) without re-reading y; see dv_bn_stats_from_sums.  Ignored by the
+                         CUDA-core path (ask dv_conv_algo) */
   int32_t N, H, W, C, K, R, S, stride, pad;
   int32_t dtype;      /* DV_F32 | DV_BF16 */
   int32_t algo;       /* DV_ALGO_* */
@@ -155,6 +160,10 @@ typedef struct dv_bn_params {
 
 /* batch statistics (mean, biased var -> invstd) + running-stat update */
 int dv_bn_stats(const dv_bn_params* p, void* stream);
+/* the same results from sums a convolution's epilogue accumulated (dv_conv_params.stat_sums): sums[0:C] = sum x,
+ * sums[C:2C] = sum x^2 over the M rows.  Writes save_mean / save_invstd, updates the running statistics and CLEARS sums
+ * to zero for the next step.  p->x and the workspace are not used. */
+int dv_bn_stats_from_sums(const dv_bn_params* p, float* sums, void* stream);
 /* normalise + affine (+residual) (+ReLU) */
 int dv_bn_apply(const dv_bn_params* p, void* stream);
 /* dv_bn_stats for callers that cannot allocate device memory.  (This entry point has no counterpart in the

@@ -38,7 +38,7 @@ def _rand(shape, seed, dtype, scale=1.0):
     return bf16_round(a) if dtype == torch.bfloat16 else a.astype(np.float32).astype(np.float64)
 
 
-def run_conv(pass_id, x_nchw, w_oihw, dy_nchw, stride, pad, dtype, algo):
+def run_conv(pass_id, x_nchw, w_oihw, dy_nchw, stride, pad, dtype, algo, use_wt=False):
     """Calls dv_conv_{fprop,dgrad,wgrad}; numpy NCHW/OIHW in, numpy NCHW/OIHW out (float64)."""
     lib = _lib()
     N, Cc, H, W = x_nchw.shape
@@ -58,7 +58,7 @@ def run_conv(pass_id, x_nchw, w_oihw, dy_nchw, stride, pad, dtype, algo):
         dy = _dev(np.transpose(dy_nchw, (0, 2, 3, 1)), dtype)
         dx = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
         p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), dy.data_ptr()
-        if dtype == torch.bfloat16:
+        if dtype == torch.bfloat16 and use_wt:
             wf = _dev(np.transpose(w_oihw, (0, 2, 3, 1)), torch.float32)
             wt = torch.empty((Cc, R, S, K), device="cuda", dtype=dtype)
             lib.check(lib.lib.dv_filter_prep(wf.data_ptr(), None, wt.data_ptr(), K, R, S, Cc, _dv(dtype), stream_ptr()), "dv_filter_prep")

@@ -47,8 +47,9 @@ def test_tc_fprop_matches_oracle(case):
 DGRAD_CASES = [c for c in TC_CASES if not (c[5] == 3 and c[6] == 2) and (c[4] % 64 == 0 or (c[5] == 1 and c[4] % 8 == 0))]
 
 
+@pytest.mark.parametrize("use_wt", [False, True], ids=["krsc_mn_major", "transposed_copy"])
 @pytest.mark.parametrize("case", DGRAD_CASES, ids=lambda c: "x".join(map(str, c)))
-def test_tc_dgrad_matches_oracle(case):
+def test_tc_dgrad_matches_oracle(case, use_wt):
     lib = _lib()
     N, Cc, H, W, K, R, stride, pad = case
     x = _rand((N, Cc, H, W), 1, BF)
@@ -56,7 +57,7 @@ def test_tc_dgrad_matches_oracle(case):
     P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
     dy = _rand((N, K, P, Q), 3, BF)
     dx_ref, _ = ref_ops.conv2d_backward(x, w, dy, stride, pad)
-    dx = run_conv(lib.DV_CONV_DGRAD, x, w, dy, stride, pad, BF, lib.DV_ALGO_TC)
+    dx = run_conv(lib.DV_CONV_DGRAD, x, w, dy, stride, pad, BF, lib.DV_ALGO_TC, use_wt=use_wt)
     assert np.isfinite(dx).all()
     assert rel_l2(dx, dx_ref) < 2e-2
 
@@ -155,7 +156,9 @@ def test_tc_full_size_against_cuda_core_kernel_and_properties(case):
     rhs = 2 * y_tc.float() + _gpu_conv(lib.DV_CONV_FPROP, x2, wd, None, stride, pad, lib.DV_ALGO_TC).float()
     assert float((lhs - rhs).norm() / rhs.norm()) < 2e-2
 
-    dx_tc = _gpu_conv(lib.DV_CONV_DGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_TC, wt)
+    dx_tc = _gpu_conv(lib.DV_CONV_DGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_TC, None)
+    dx_tc2 = _gpu_conv(lib.DV_CONV_DGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_TC, wt)
+    assert float((dx_tc.float() - dx_tc2.float()).abs().max()) <= 1e-2 * float(dx_tc2.float().abs().max())
     dx_si = _gpu_conv(lib.DV_CONV_DGRAD, xd, wd, dyd, stride, pad, lib.DV_ALGO_SIMT)
     err = float((dx_tc.float() - dx_si.float()).norm() / dx_si.float().norm())
     assert err < 4e-3, f"dgrad TC vs SIMT {err}"
@@ -223,9 +226,47 @@ def test_tc_fp32_logits_and_dgrad_accumulate():
         dyd = torch.from_numpy(np.ascontiguousarray(dy.transpose(0, 2, 3, 1))).cuda().to(BF)
         dxd = torch.from_numpy(np.ascontiguousarray(prior.transpose(0, 2, 3, 1))).cuda().to(BF)
         q = lib.ConvParams()
-        q.x, q.w, q.y, q.w_t = dxd.data_ptr(), wk.data_ptr(), dyd.data_ptr(), wt.data_ptr()
+        q.x, q.w, q.y = dxd.data_ptr(), wk.data_ptr(), dyd.data_ptr()
         q.N, q.H, q.W, q.C, q.K, q.R, q.S, q.stride, q.pad, q.dtype, q.algo, q.accumulate = N, H, W, Cc, K, R, R, stride, pad, lib.DV_BF16, algo, 1
         lib.check(lib.lib.dv_conv_dgrad(C.byref(q), stream_ptr()), "dgrad accumulate")
         torch.cuda.synchronize()
         got = dxd.double().cpu().numpy().transpose(0, 3, 1, 2)
         assert rel_l2(got, dx_ref + prior) < 2e-2, case
+
+
+@pytest.mark.parametrize("case", [(2, 64, 8, 8, 64, 3, 1, 1), (3, 128, 7, 7, 256, 1, 1, 0), (4, 64, 12, 12, 512, 1, 1, 0),
+                                  (2, 256, 9, 9, 1000, 1, 1, 0)], ids=lambda c: "x".join(map(str, c)))
+def test_tc_fprop_fused_bn_sums(case):
+    """The epilogue's per-channel sums (dv_conv_params.stat_sums) equal the sums of the stored bf16 output, and
+    dv_bn_stats_from_sums turns them into the statistics dv_bn_stats computes from that output."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, Cc, H, W, K, R, stride, pad = case
+    x = _rand((N, Cc, H, W), 1, BF)
+    w = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+    xd = torch.from_numpy(np.ascontiguousarray(x.transpose(0, 2, 3, 1))).cuda().to(BF)
+    wd = torch.from_numpy(np.ascontiguousarray(w.transpose(0, 2, 3, 1))).cuda().to(BF)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+    y = torch.empty((N, P, Q, K), device="cuda", dtype=BF)
+    sums = torch.zeros(2 * K, device="cuda")
+    p = lib.ConvParams()
+    p.x, p.w, p.y, p.stat_sums = xd.data_ptr(), wd.data_ptr(), y.data_ptr(), sums.data_ptr()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, W, Cc, K, R, R, stride, pad, lib.DV_BF16, lib.DV_ALGO_TC
+    lib.check(lib.lib.dv_conv_fprop(C.byref(p), stream_ptr()), "fprop+sums")
+    torch.cuda.synchronize()
+    yd = y.double().reshape(-1, K)
+    assert rel_l2(sums[:K].cpu().numpy(), yd.sum(0).cpu().numpy()) < 1e-5
+    assert rel_l2(sums[K:].cpu().numpy(), (yd * yd).sum(0).cpu().numpy()) < 1e-5
+    M = N * P * Q
+    f = lambda v: torch.full((K,), float(v), device="cuda")
+    g_, b_, rm, rv, mean, inv = f(1), f(0), f(0), f(1), f(float("nan")), f(float("nan"))
+    q = lib.BnParams()
+    q.x, q.gamma, q.beta, q.running_mean, q.running_var = y.data_ptr(), g_.data_ptr(), b_.data_ptr(), rm.data_ptr(), rv.data_ptr()
+    q.save_mean, q.save_invstd, q.M, q.C, q.dtype, q.eps, q.momentum = mean.data_ptr(), inv.data_ptr(), M, K, lib.DV_BF16, 1e-5, 0.1
+    lib.check(lib.lib.dv_bn_stats_from_sums(C.byref(q), sums.data_ptr(), stream_ptr()), "from_sums")
+    torch.cuda.synchronize()
+    assert float(sums.abs().sum()) == 0.0                                   # cleared for the next step
+    assert rel_l2(mean.cpu().numpy(), yd.mean(0).cpu().numpy()) < 1e-4
+    assert rel_l2(inv.cpu().numpy(), (1.0 / torch.sqrt(yd.var(0, unbiased=False) + 1e-5)).cpu().numpy()) < 1e-4
+    assert rel_l2(rm.cpu().numpy(), (0.1 * yd.mean(0)).cpu().numpy()) < 1e-4

@@ -76,6 +76,9 @@ def conv_rows(batch):
             p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = batch, H, H, Cc, K, R, R, stride, pad, DV_BF16, DV_ALGO_AUTO
             if pass_id == DV_CONV_FPROP:
                 p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
+                if os.environ.get("LB_STATS"):
+                    sums = torch.zeros(2 * K, device="cuda")
+                    p.stat_sums = sums.data_ptr()
             elif pass_id == DV_CONV_DGRAD:
                 p.x, p.w, p.y, p.w_t = dx.data_ptr(), w.data_ptr(), dy.data_ptr(), wt.data_ptr()
             else:
