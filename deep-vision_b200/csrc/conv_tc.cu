@@ -739,15 +739,34 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   // kernel and a second CTA never becomes resident (measured: occupancy 1 -> 2 for the 96 KB variants)
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                   cudaSharedmemCarveoutMaxShared));
-  static int occ_cached = 0;  // resident CTAs per SM as the runtime sees it (shared memory and 2 x BN TMEM columns bound it)
+  // CTAs per SM the grid is sized for: two when two rings (<= 113 KB each) and two accumulator pairs (2 x 2 x BN <= 512 TMEM
+  // columns) fit, else one.  cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for these kernels at ANY shared
+  // memory size, but grids sized for two per SM measured 40-60 % faster on the BN <= 128 layers
+  // (profiles/r01_layer_bench_v2 vs v4), so the answer is not used.
+  static int occ_cached = 0;
   if (occ_cached == 0) {
     int occ = 0;
     DV_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, kThreads, smem));
-    const int tmem_limit = 512 / (2 * BN);
-    occ_cached = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
-    if (env_int("DV_TC_DEBUG", 0))
-      fprintf(stderr, "dv conv_tc: gemm<BN=%d,STAGES=%d,STATS=%d> smem=%d occupancy(api)=%d used=%d\n", BN, STAGES, (int)STATS + 2 * (int)B_MN, smem, occ,
-              occ_cached);
+    occ_cached = (smem <= 115712 && 4 * BN <= 512) ? 2 : 1;
+    const int forced = env_int("DV_TC_OCC", 0);  // experiment knob
+    if (forced > 0) occ_cached = forced;
+    if (env_int("DV_TC_DEBUG", 0)) {
+      cudaFuncAttributes fa;
+      cudaFuncGetAttributes(&fa, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>);
+      int sweep[4] = {0, 0, 0, 0};
+      const int sizes[4] = {32 << 10, 64 << 10, 96 << 10, 110 << 10};
+      for (int i = 0; i < 4; ++i)
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sweep[i], conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, kThreads, sizes[i]);
+      int dev = 0, smem_sm = 0, smem_res = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
+      cudaDeviceGetAttribute(&smem_res, cudaDevAttrReservedSharedMemoryPerBlock, dev);
+      fprintf(stderr,
+              "dv conv_tc: gemm<BN=%d,STAGES=%d,STATS=%d> smem=%d occupancy(api)=%d used=%d regs=%d static_smem=%zu local=%zu maxdyn=%d "
+              "occ@32K/64K/96K/110K=%d/%d/%d/%d smem_per_sm=%d reserved=%d\n",
+              BN, STAGES, (int)STATS + 2 * (int)B_MN, smem, occ, occ_cached, fa.numRegs, fa.sharedSizeBytes, fa.localSizeBytes,
+              fa.maxDynamicSharedSizeBytes, sweep[0], sweep[1], sweep[2], sweep[3], smem_sm, smem_res);
+    }
   }
   const int num_n = ceil_div(g.Nout, BN);
   const int total = num_n * ceil_div(g.M, kBlockM);
@@ -783,11 +802,13 @@ static WgradPlan plan_wgrad(const dv_conv_params* p) {
   const int64_t mpix = (int64_t)p->N * P * Q;
   w.bnc = p->C >= 256 ? 256 : ceil_div(p->C, 64) * 64;  // 64, 128, 192 or 256 input channels per tile
   w.c_tiles = ceil_div(p->C, w.bnc);
-  w.mh = p->K > 128 ? 2 : 1;  // 256 output channels per CTA when there are that many
+  static const int mh_env = env_int("DV_TC_WGRAD_MH", 1);  // 2 = 256 output channels per CTA (measured slower: more split partials)
+  w.mh = (mh_env == 2 && p->K > 128) ? 2 : 1;
   w.k_tiles = ceil_div(p->K, 128 * w.mh);
   w.tiles = w.k_tiles * w.c_tiles * p->R * p->S;
   w.kb_total = (int)ceil_div64(mpix, 64);
-  // one wave of CTAs: 2 per SM while the ring fits twice (MH == 1, BNC <= 128), else 1; never less than 4 stages of work each
+  // ONE wave of CTAs: two per SM while two rings fit (MH == 1, BNC <= 128), else one; at least 4 stages of work each.
+  // (Measured against "2 x SMs CTAs whatever the tile" and against one per SM: this split is 10-40 % faster.)
   const int slots = num_sms() * ((w.mh == 1 && w.bnc <= 128) ? 2 : 1);
   int want = slots / w.tiles;
   int max_by_len = w.kb_total / 4 > 0 ? w.kb_total / 4 : 1;

@@ -249,24 +249,28 @@ __global__ void unpad_rows_kernel(const float* __restrict__ src, float* __restri
 }
 
 // ---- optimisers (train.py:166-205) -----------------------------------------------------------------------------------
-__global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, int64_t n, float lr, float mom,
-                           float wd, float gscale, int first) {
+__global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, bf16* __restrict__ p16, int64_t n,
+                           float lr, float mom, float wd, float gscale, int first) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float pv = p[i];
     const float gv = fmaf(wd, pv, g[i] * gscale);
     const float b = first ? gv : fmaf(mom, buf[i], gv);
     buf[i] = b;
-    p[i] = pv - lr * b;
+    const float pn = pv - lr * b;
+    p[i] = pn;
+    if (p16 != nullptr) p16[i] = __float2bfloat16_rn(pn);
   }
 }
-__global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, int64_t n, float lr,
-                               float alpha, float eps, float wd, float gscale) {
+__global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, bf16* __restrict__ p16, int64_t n,
+                               float lr, float alpha, float eps, float wd, float gscale) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float pv = p[i];
     const float gv = fmaf(wd, pv, g[i] * gscale);
     const float s = alpha * sq[i] + (1.f - alpha) * gv * gv;
     sq[i] = s;
-    p[i] = pv - lr * gv / (sqrtf(s) + eps);
+    const float pn = pv - lr * gv / (sqrtf(s) + eps);
+    p[i] = pn;
+    if (p16 != nullptr) p16[i] = __float2bfloat16_rn(pn);
   }
 }
 
@@ -407,14 +411,28 @@ extern "C" int dv_unpad_rows(const float* src, float* dst, int rows, int cols, i
 extern "C" int dv_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float wd, float gscale, int first,
                            void* stream) {
   DV_REQUIRE(p && g && buf && n > 0, DV_ERR_ARG, "dv_sgd_step: bad arguments");
-  sgd_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, buf, n, lr, momentum, wd, gscale, first);
+  sgd_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, buf, nullptr, n, lr, momentum, wd, gscale, first);
+  DV_LAUNCH_OK("sgd_kernel");
+  return DV_OK;
+}
+extern "C" int dv_sgd_step_bf16(float* p, const float* g, float* buf, void* p16, int64_t n, float lr, float momentum, float wd, float gscale,
+                                int first, void* stream) {
+  DV_REQUIRE(p && g && buf && p16 && n > 0, DV_ERR_ARG, "dv_sgd_step_bf16: bad arguments");
+  sgd_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, buf, (bf16*)p16, n, lr, momentum, wd, gscale, first);
   DV_LAUNCH_OK("sgd_kernel");
   return DV_OK;
 }
 extern "C" int dv_rmsprop_step(float* p, const float* g, float* sq, int64_t n, float lr, float alpha, float eps, float wd, float gscale,
                                void* stream) {
   DV_REQUIRE(p && g && sq && n > 0, DV_ERR_ARG, "dv_rmsprop_step: bad arguments");
-  rmsprop_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, sq, n, lr, alpha, eps, wd, gscale);
+  rmsprop_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, sq, nullptr, n, lr, alpha, eps, wd, gscale);
+  DV_LAUNCH_OK("rmsprop_kernel");
+  return DV_OK;
+}
+extern "C" int dv_rmsprop_step_bf16(float* p, const float* g, float* sq, void* p16, int64_t n, float lr, float alpha, float eps, float wd,
+                                    float gscale, void* stream) {
+  DV_REQUIRE(p && g && sq && p16 && n > 0, DV_ERR_ARG, "dv_rmsprop_step_bf16: bad arguments");
+  rmsprop_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(p, g, sq, (bf16*)p16, n, lr, alpha, eps, wd, gscale);
   DV_LAUNCH_OK("rmsprop_kernel");
   return DV_OK;
 }

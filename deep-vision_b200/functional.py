@@ -105,6 +105,7 @@ class FilterCache:
         self.w_t = None
         self.pad_key = None
         self.w_pad = None
+        self.external = None   # (dtype, tensor): a copy some other kernel keeps current (the trainer's fused optimiser)
 
     def get_padded(self, weight, dtype, kp):
         """[K][Kp] compute-dtype filters (rows zero-padded from R*S*C to Kp) for the patch-matrix path of the stems."""
@@ -121,6 +122,8 @@ class FilterCache:
 
     def get(self, weight, dtype, need_t):
         K, Cc, R, S = weight.shape
+        if self.external is not None and self.external[0] == dtype and not need_t:
+            return self.external[1], None
         key = (weight.data_ptr(), weight._version, config.weight_epoch(), dtype, weight.device)
         if key != self.key or (need_t and self.w_t is None):
             wm = weight.detach()

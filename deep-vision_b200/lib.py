@@ -91,6 +91,8 @@ _SIG = {
     "dv_bias_grad": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P]),
     "dv_sgd_step": (C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, _P]),
     "dv_rmsprop_step": (C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _P]),
+    "dv_sgd_step_bf16": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, _P]),
+    "dv_rmsprop_step_bf16": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _P]),
     "dv_version": (C.c_int, []),
     "dv_last_error": (C.c_char_p, []),
     "dv_device_check": (C.c_int, []),

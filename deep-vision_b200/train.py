@@ -141,6 +141,27 @@ class Trainer:
         self.exchange = BucketedAllReduce(self.flat, bucket_bytes, process_group) if self.world > 1 else None
         self._install_direct_grads()
         self._flatten_bn_counters()
+        self._install_bf16_filters()
+
+    def _install_bf16_filters(self):
+        """One flat bf16 mirror of the parameter buffer, rewritten by the optimiser kernel itself; every dense
+        convolution (and the classifier) reads its compute-dtype filters as a view of it, so no per-layer cast kernel runs."""
+        from . import nn as dvnn
+        self.flat_p16 = None
+        if config.compute_dtype() != torch.bfloat16:
+            return
+        self.flat_p16 = self.flat_p.to(torch.bfloat16)
+        index = {id(p): j for j, p in enumerate(self.flat.params)}
+        for m in self.model.modules():
+            if isinstance(m, dvnn.Conv2d) and not m._dv_depthwise and id(m.weight) in index:
+                off = self.flat.offsets[index[id(m.weight)]]
+                K, Cc, R, S = m.weight.shape
+                view = self.flat_p16[off:off + m.weight.numel()].view(K, R, S, Cc).permute(0, 3, 1, 2)
+                m._dv_cache.external = (torch.bfloat16, view)
+            elif isinstance(m, dvnn.Linear) and id(m.weight) in index:
+                off = self.flat.offsets[index[id(m.weight)]]
+                K, Fdim = m.weight.shape
+                m._dv_cache.external = (torch.bfloat16, self.flat_p16[off:off + K * Fdim].view(K, Fdim, 1, 1))
 
     def _install_direct_grads(self):
         """Dense-conv filters and BN affine parameters receive their gradient by a direct kernel write into the flat
@@ -191,11 +212,20 @@ class Trainer:
         scale = 1.0 / self.world
         if self.kind == "sgd":
             first = 1 if self.steps_done == 0 and self._graph is None and not self._capturing else 0
-            check(lib.dv_sgd_step(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(), n, self.lr, self.momentum,
-                                  self.weight_decay, scale, first, _stream()), "dv_sgd_step")
+            if self.flat_p16 is not None:
+                check(lib.dv_sgd_step_bf16(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(), self.flat_p16.data_ptr(),
+                                           n, self.lr, self.momentum, self.weight_decay, scale, first, _stream()), "dv_sgd_step_bf16")
+            else:
+                check(lib.dv_sgd_step(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(), n, self.lr, self.momentum,
+                                      self.weight_decay, scale, first, _stream()), "dv_sgd_step")
         elif self.kind == "rmsprop":
-            check(lib.dv_rmsprop_step(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(), n, self.lr, self.alpha,
-                                      self.eps, self.weight_decay, scale, _stream()), "dv_rmsprop_step")
+            if self.flat_p16 is not None:
+                check(lib.dv_rmsprop_step_bf16(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(),
+                                               self.flat_p16.data_ptr(), n, self.lr, self.alpha, self.eps, self.weight_decay, scale,
+                                               _stream()), "dv_rmsprop_step_bf16")
+            else:
+                check(lib.dv_rmsprop_step(self.flat_p.data_ptr(), self.flat_g.data_ptr(), self.flat_s.data_ptr(), n, self.lr, self.alpha,
+                                          self.eps, self.weight_decay, scale, _stream()), "dv_rmsprop_step")
         else:
             raise ValueError(f"unknown optimizer {self.kind}")
         config.bump_weight_epoch()

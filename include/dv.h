@@ -250,6 +250,12 @@ int dv_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float
                 float grad_scale, int first_step, void* stream);
 int dv_rmsprop_step(float* p, const float* g, float* sq, int64_t n, float lr, float alpha, float eps,
                     float weight_decay, float grad_scale, void* stream);
+/* the same two updates that ALSO write the new parameters as bf16 into p_bf16[n] (same element order): the
+ * compute-dtype filter copies of every convolution refreshed by the optimiser launch itself */
+int dv_sgd_step_bf16(float* p, const float* g, float* buf, void* p_bf16, int64_t n, float lr, float momentum, float weight_decay,
+                     float grad_scale, int first_step, void* stream);
+int dv_rmsprop_step_bf16(float* p, const float* g, float* sq, void* p_bf16, int64_t n, float lr, float alpha, float eps,
+                         float weight_decay, float grad_scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Library
