@@ -75,6 +75,15 @@ __device__ __forceinline__ void tma_load_im2col(void* smem, const CUtensorMap* t
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
       : "memory");
 }
+// smem tile -> global through the TMA unit (whole 128-byte lines, clipped at the tensor edge, no LSU traffic)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, uint32_t smem_addr, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_addr), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tm)) : "memory");
 }
@@ -167,15 +176,18 @@ struct GemmArgs {
 // activation tile through L2); the smem ring runs on across tiles and the accumulator is DOUBLE-BUFFERED in TMEM
 // (2 x BN columns), so the epilogue of tile i drains TMEM while the tensor core already works on tile i+1.
 // ------------------------------------------------------------------------------------------------------------
-// STATS: the fprop-for-training variant whose epilogue also accumulates BatchNorm's per-channel sums.  It stages the
-// output tile through shared memory (16 KB more per CTA); the plain variant stores straight from registers, which
-// measured faster in the full training step (profiles/r01_epilogue_ab.md).
+// STAGED: the epilogue converts the accumulator to bf16 into a per-warp, 128B-swizzled shared-memory tile ([32 rows][64
+// columns]) and hands it to the TMA unit (cp.async.bulk.tensor store): the SM writes whole 128-byte lines instead of the
+// 16-byte-per-row pieces a TMEM load naturally yields (ncu: those doubled the L2 write sectors and held the memory-bound
+// 1x1 layers at ~50 % of the HBM roof).  The same tile feeds the optional BatchNorm sums.  !STAGED (row-per-lane stores
+// from registers) serves the variants TMA cannot express: strided scatter, read-modify-write accumulate, fp32 logits.
 // B_MN: the B operand is taken as [64 reduction rows][64 output columns] boxes straight from KRSC filters and consumed
 // MN-major — the dgrad case, where the reduction runs over K (filter rows) and the output over C (contiguous), with the
 // tap flipped by index.  No transposed copy of the filters is needed.
 template <int BN, int STAGES, bool STATS, bool B_MN>
 __global__ void __launch_bounds__(kThreads)
-conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                               const __grid_constant__ CUtensorMap tmO, const GemmArgs g) {
   constexpr int ACC = 2;
   constexpr int kBBytes = BN * kBlockK * 2;
   constexpr int kStageBytes = kABytes + kBBytes;
@@ -205,6 +217,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    if (STATS) prefetch_tmap(&tmO);
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
@@ -410,6 +423,9 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
       } else {
 #pragma unroll
         for (int cgp = 0; cgp < BN / 64; ++cgp) {
+          // the TMA store of the previous column group must have finished READING the staging tile
+          if (lane == 0) tma_store_wait_read();
+          __syncwarp();
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             uint32_t v[32];
@@ -423,13 +439,15 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
                 __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
                 w[e] = *reinterpret_cast<uint32_t*>(&h);
               }
-              const int ch = (half * 4 + j) ^ (lane & 7);
+              const int ch = (half * 4 + j) ^ (lane & 7);  // SWIZZLE_128B: 16-byte chunk index XOR (row mod 8)
               asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_stage_u32 + lane * 128 + ch * 16), "r"(w[0]), "r"(w[1]),
                            "r"(w[2]), "r"(w[3])
                            : "memory");
             }
           }
+          fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA (async proxy)
           __syncwarp();
+          if (lane == 0 && cgp * 64 < n_left && m_base < g.M) tma_store_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
           if (g.stat_sums != nullptr) {
             // column sums over this warp's 32 rows from the bf16-rounded values (what BN will read back)
             const int wch = lane >> 2, wof = (lane & 3) * 4;
@@ -444,35 +462,6 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             s1[cgp][0] += a0; s1[cgp][1] += a1;
             s2[cgp][0] += b0; s2[cgp][1] += b1;
           }
-          const int col0 = cgp * 64 + chunk * 8;
-          if (col0 < n_left) {
-#pragma unroll
-            for (int it = 0; it < 8; ++it) {
-              const int row = it * 4 + sub_row;
-              if (m_base + row < g.M) {
-                uint4 val;
-                asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
-                             : "=r"(val.x), "=r"(val.y), "=r"(val.z), "=r"(val.w)
-                             : "r"(my_stage_u32 + row * 128 + ((chunk ^ (row & 7)) * 16)));
-                bf16* dst = g.out + row_off[it] + (size_t)n_tile * BN + col0;
-                if (g.accumulate) {
-                  const uint4 old = *reinterpret_cast<const uint4*>(dst);
-                  const uint32_t ow[4] = {old.x, old.y, old.z, old.w};
-                  uint32_t nw[4] = {val.x, val.y, val.z, val.w};
-#pragma unroll
-                  for (int e = 0; e < 4; ++e) {
-                    const float lo = __uint_as_float(nw[e] << 16) + __uint_as_float(ow[e] << 16);
-                    const float hi = __uint_as_float(nw[e] & 0xffff0000u) + __uint_as_float(ow[e] & 0xffff0000u);
-                    __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
-                    nw[e] = *reinterpret_cast<uint32_t*>(&h);
-                  }
-                  val = make_uint4(nw[0], nw[1], nw[2], nw[3]);
-                }
-                *reinterpret_cast<uint4*>(dst) = val;
-              }
-            }
-          }
-          __syncwarp();  // the staging buffer is rewritten by the next column group
         }
       }
       // all of this warp's TMEM reads are complete: hand the accumulator back to the MMA warp
@@ -482,6 +471,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
       if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
     }
     flush_stats();
+    if (STATS && lane == 0) tma_store_wait_read();  // shared memory must outlive the last bulk store's reads
   }
   tc_fence_before();
   __syncthreads();
@@ -732,7 +722,7 @@ static int env_int(const char* name, int dflt) {
 }
 
 template <int BN, int STAGES, bool STATS, bool B_MN>
-static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, cudaStream_t st) {
+static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const GemmArgs& g, cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + 256;
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   // ask for the whole L1/shared array as shared memory: otherwise the driver sizes the carve-out for ONE CTA of this
@@ -773,7 +763,7 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   int slots = num_sms() * occ_cached;
   if (slots > num_n) slots -= slots % num_n;  // a CTA then keeps one n-tile for its whole life (running BN sums stay put)
   const int grid = total < slots ? total : slots;
-  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, g);
+  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, tmO, g);
   DV_LAUNCH_OK("conv_tc_gemm_persistent_kernel");
   return DV_OK;
 }
@@ -876,26 +866,24 @@ static int pick_bn(int nout) {
   return bn;
 }
 
+// STAGED (TMA-store epilogue, optional BN sums) whenever the output is a plain bf16 [M][Nout] matrix
 static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, bool b_mn, cudaStream_t st) {
+  const bool staged = !g.scatter && !g.accumulate && !g.out_f32;
+  alignas(64) CUtensorMap tmO;
+  if (staged) {
+    int rc = make_map_2d(&tmO, g.out, (uint64_t)g.M, (uint64_t)g.Nout, 32);
+    if (rc) return rc;
+  } else {
+    tmO = tmA;  // unused by the kernel
+  }
+#define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_>(tmA, tmB, tmO, g, st)
   if (b_mn) {
-    switch (bn) {
-      case 64: return launch_gemm_persistent<64, 4, false, true>(tmA, tmB, g, st);
-      case 128: return launch_gemm_persistent<128, 3, false, true>(tmA, tmB, g, st);
-      default: return launch_gemm_persistent<256, 4, false, true>(tmA, tmB, g, st);
-    }
+    if (staged) { switch (bn) { case 64: DV_GEMM_CASE(64, 4, true, true); case 128: DV_GEMM_CASE(128, 3, true, true); default: DV_GEMM_CASE(256, 4, true, true); } }
+    switch (bn) { case 64: DV_GEMM_CASE(64, 4, false, true); case 128: DV_GEMM_CASE(128, 3, false, true); default: DV_GEMM_CASE(256, 4, false, true); }
   }
-  if (g.stat_sums != nullptr) {
-    switch (bn) {
-      case 64: return launch_gemm_persistent<64, 4, true, false>(tmA, tmB, g, st);
-      case 128: return launch_gemm_persistent<128, 3, true, false>(tmA, tmB, g, st);
-      default: return launch_gemm_persistent<256, 4, true, false>(tmA, tmB, g, st);
-    }
-  }
-  switch (bn) {
-    case 64: return launch_gemm_persistent<64, 4, false, false>(tmA, tmB, g, st);
-    case 128: return launch_gemm_persistent<128, 3, false, false>(tmA, tmB, g, st);
-    default: return launch_gemm_persistent<256, 4, false, false>(tmA, tmB, g, st);
-  }
+  if (staged) { switch (bn) { case 64: DV_GEMM_CASE(64, 4, true, false); case 128: DV_GEMM_CASE(128, 3, true, false); default: DV_GEMM_CASE(256, 4, true, false); } }
+  switch (bn) { case 64: DV_GEMM_CASE(64, 4, false, false); case 128: DV_GEMM_CASE(128, 3, false, false); default: DV_GEMM_CASE(256, 4, false, false); }
+#undef DV_GEMM_CASE
 }
 
 int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {

@@ -14,14 +14,15 @@ from deep_vision_b200.lib import BnParams, ConvParams, DV_ALGO_TC, DV_BF16, DV_C
 ap = argparse.ArgumentParser()
 ap.add_argument("--which", default="fprop")
 ap.add_argument("--iters", type=int, default=5)
+ap.add_argument("--shape", default="256,14,256,256,3", help="N,H,C,K,R (stride 1, pad R//2)")
 args = ap.parse_args()
 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-N, H, Cc, K, R = 256, 14, 256, 256, 3
+N, H, Cc, K, R = (int(v) for v in args.shape.split(","))
 x = torch.randn(N, H, H, Cc, device="cuda").to(torch.bfloat16)
 w = (torch.randn(K, R, R, Cc, device="cuda") * 0.05).to(torch.bfloat16)
 y = torch.empty(N, H, H, K, device="cuda", dtype=torch.bfloat16)
 p = ConvParams()
-p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, H, Cc, K, R, R, 1, 1, DV_BF16, DV_ALGO_TC
+p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, H, Cc, K, R, R, 1, R // 2, DV_BF16, DV_ALGO_TC
 if args.which == "fprop":
     p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
     fn = lambda: check(lib.dv_conv_fprop(C.byref(p), st), "fprop")
