@@ -4,7 +4,10 @@ import os
 import torch
 
 _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
-          "fuse_bn_stats": os.environ.get("DV_FUSE_STATS", "1") != "0"}
+          "fuse_bn_stats": os.environ.get("DV_FUSE_STATS", "1") != "0",
+          "deterministic": os.environ.get("DV_DETERMINISTIC", "0") == "1",
+          "atomic_wgrad": os.environ.get("DV_ATOMIC_WGRAD", "1") == "1",
+          "atomic_bn_bwd": os.environ.get("DV_ATOMIC_BN", "0") == "1"}
 
 
 def compute_dtype():
@@ -46,3 +49,26 @@ def set_fuse_bn_stats(flag):
     """True (default): tensor-core convolutions accumulate the per-channel sums BatchNorm needs in their epilogue, so the
     statistics pass never re-reads the activation.  False: BatchNorm runs its own reduction pass."""
     _state["fuse_bn_stats"] = bool(flag)
+
+
+def deterministic():
+    return _state["deterministic"]
+
+
+def set_deterministic(flag):
+    """False (default): split reductions (wgrad tiles, BN backward sums, fused BN statistics) are combined with fp32
+    atomics — fewer launches and less traffic, summation order varies run to run.  True: fixed-order second-stage
+    reductions, bit-reproducible results."""
+    _state["deterministic"] = bool(flag)
+    if flag:
+        _state["fuse_bn_stats"] = False
+
+
+def atomic_wgrad():
+    """Add wgrad tiles straight into dW with fp32 vector reductions instead of split partials + a reduce pass."""
+    return _state["atomic_wgrad"] and not _state["deterministic"]
+
+
+def atomic_bn_bwd():
+    """Add BN-backward block sums straight into dgamma/dbeta with fp32 atomics instead of partials + a finalize pass."""
+    return _state["atomic_bn_bwd"] and not _state["deterministic"]

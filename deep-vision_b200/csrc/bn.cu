@@ -31,7 +31,10 @@ static Plan make_plan(int64_t M, int C, int V) {
   p.cgb = p.cg < kThreads ? p.cg : kThreads;
   p.rows_par = kThreads / p.cgb;
   int64_t nb = ceil_div64(M, (int64_t)p.rows_par * 32);
-  if (nb > kMaxBlocks) nb = kMaxBlocks;
+  // wide layers: a block already spans all C channels, so fewer, longer blocks keep the bytes in flight and shrink the
+  // partial array the finalize pass has to read (nblk x 2 x C floats)
+  const int max_blocks = C >= 512 ? kMaxBlocks / 4 : (C >= 256 ? kMaxBlocks / 2 : kMaxBlocks);
+  if (nb > max_blocks) nb = max_blocks;
   if (nb < 1) nb = 1;
   p.rows_per_blk = ceil_div64(M, nb);
   p.nblk = (int)ceil_div64(M, p.rows_per_blk);
@@ -43,7 +46,8 @@ template <typename T, int MODE>
 __global__ void __launch_bounds__(kThreads)
 bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, const float* __restrict__ mean,
                  const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta,
-                 float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par, int64_t rows_per_blk, int relu) {
+                 float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par, int64_t rows_per_blk, int relu,
+                 float* __restrict__ atomic_s1 = nullptr, float* __restrict__ atomic_s2 = nullptr) {
   // relu: 0 = no activation, 1 = mask from the stored output y, 2 = mask recomputed from x exactly as bn_apply computed it
   constexpr int V = Vec16<T>::N;
   __shared__ float red[2][kThreads * V];
@@ -72,7 +76,7 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
         }
       }
       // U independent 16-byte loads per stream in flight per thread (memory-level parallelism), then the arithmetic
-      constexpr int U = (MODE == 0) ? 4 : 2;
+      constexpr int U = 4;
       for (int64_t r = r0 + trow; r < r1; r += (int64_t)rows_par * U) {
         Vec16<T> vx[U], vg[U], vy[U];
 #pragma unroll
@@ -127,10 +131,15 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
 #pragma unroll
         for (int i = 0; i < V; ++i) { s1[i] += red[0][t * V + i]; s2[i] += red[1][t * V + i]; }
       }
-      float* p1 = partial + ((size_t)blockIdx.x * 2) * C + c;
-      float* p2 = p1 + C;
+      if (atomic_s1 != nullptr) {
 #pragma unroll
-      for (int i = 0; i < V; ++i) { p1[i] = s1[i]; p2[i] = s2[i]; }
+        for (int i = 0; i < V; ++i) { atomicAdd(atomic_s1 + c + i, s1[i]); atomicAdd(atomic_s2 + c + i, s2[i]); }
+      } else {
+        float* p1 = partial + ((size_t)blockIdx.x * 2) * C + c;
+        float* p2 = p1 + C;
+#pragma unroll
+        for (int i = 0; i < V; ++i) { p1[i] = s1[i]; p2[i] = s2[i]; }
+      }
     }
     __syncthreads();
   }
@@ -406,15 +415,17 @@ static int bwd_reduce_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
   Plan pl = make_plan(p->M, p->C, V);
-  const size_t need = (size_t)pl.nblk * 2 * p->C * sizeof(float);
-  DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "bn_bwd_reduce: workspace %zu bytes required, %zu given",
-             need, p->workspace_bytes);
+  const size_t need = p->atomic_sums ? 0 : (size_t)pl.nblk * 2 * p->C * sizeof(float);
+  DV_REQUIRE(need == 0 || (p->workspace && p->workspace_bytes >= need), DV_ERR_WORKSPACE,
+             "bn_bwd_reduce: workspace %zu bytes required, %zu given", need, p->workspace_bytes);
   DV_REQUIRE(!p->relu || p->y || p->beta, DV_ERR_ARG, "bn_bwd_reduce: relu needs y (stored mask) or beta (recomputed mask)");
   const int relu_mode = !p->relu ? 0 : (p->y ? 1 : 2);
   bn_reduce_kernel<T, 1><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, p->save_mean, p->save_invstd,
                                                       p->gamma, p->beta, (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par,
-                                                      pl.rows_per_blk, relu_mode);
+                                                      pl.rows_per_blk, relu_mode, p->atomic_sums ? p->dbeta : nullptr,
+                                                      p->atomic_sums ? p->dgamma : nullptr);
   DV_LAUNCH_OK("bn_reduce_kernel<bwd>");
+  if (p->atomic_sums) return DV_OK;  // dbeta += sum(dz), dgamma += sum(dz*xhat) were accumulated in place
   bn_bwd_finalize_kernel<<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const float*)p->workspace, pl.nblk, p->C, p->dgamma, p->dbeta);
   DV_LAUNCH_OK("bn_bwd_finalize_kernel");
   return DV_OK;

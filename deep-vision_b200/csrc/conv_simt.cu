@@ -160,12 +160,12 @@ static int launch(const dv_conv_params* p, const ConvDims& d, cudaStream_t st) {
   int64_t k_per_split = ceil_div64(Kg, splits);
   k_per_split = ceil_div64(k_per_split, 16) * 16;
   splits = (int)ceil_div64(Kg, k_per_split);
-  if (PASS == DV_CONV_WGRAD && splits > 1) {
+  if (PASS == DV_CONV_WGRAD && splits > 1 && !p->accumulate) {
     DV_CUDA_OK(cudaMemsetAsync(out, 0, (size_t)M * Ng * sizeof(float), st));
   }
   DV_REQUIRE(gy <= 65535, DV_ERR_UNSUPPORTED, "conv_simt: N tiles %lld exceed grid.y", (long long)gy);
   dim3 grid((unsigned)gx, (unsigned)gy, (unsigned)splits);
-  const int flag = (PASS == DV_CONV_WGRAD) ? (splits > 1 ? 1 : 0) : (PASS == DV_CONV_DGRAD && p->accumulate ? 1 : 0);
+  const int flag = (PASS == DV_CONV_WGRAD) ? ((splits > 1 || p->accumulate) ? 1 : 0) : (PASS == DV_CONV_DGRAD && p->accumulate ? 1 : 0);
   conv_simt_kernel<PASS, T, TO><<<grid, 256, 0, st>>>(op, (TO*)out, M, Ng, Kg, k_per_split, flag);
   DV_LAUNCH_OK("conv_simt_kernel");
   return DV_OK;

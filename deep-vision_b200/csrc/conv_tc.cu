@@ -482,6 +482,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 // wgrad kernel
 // ------------------------------------------------------------------------------------------------------------
 struct WgradArgs {
+  float* dw_atomic; // non-null: add the tile straight into dw [K][taps][C] with vector reductions (no partials, no 2nd pass)
   float* ws;        // [splits][K][taps][C] fp32 partial sums
   int Mpix;         // N*P*Q
   int K, C, taps, S;
@@ -601,7 +602,9 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
 #pragma unroll 1
     for (int h = 0; h < MH; ++h) {
       const int k = k_tile * (128 * MH) + h * 128 + quarter * 32 + lane;
-      float* orow = g.ws + (((size_t)split * g.K + (size_t)(k < g.K ? k : 0)) * g.taps + tap) * g.C + (size_t)c_tile * BNC;
+      const size_t kk = (size_t)(k < g.K ? k : 0);
+      float* orow = (g.dw_atomic != nullptr ? g.dw_atomic + (kk * g.taps + tap) * g.C
+                                            : g.ws + (((size_t)split * g.K + kk) * g.taps + tap) * g.C) + (size_t)c_tile * BNC;
 #pragma unroll 1
       for (int c = 0; c < BNC / 32; ++c) {
         uint32_t v[32];
@@ -610,9 +613,16 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
         if (k < g.K) {
           const int c_left = g.C - c_tile * BNC - c * 32;  // valid input channels from this chunk on
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (j * 4 < c_left)
-              *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          for (int j = 0; j < 8; ++j) {
+            if (j * 4 < c_left) {
+              if (g.dw_atomic != nullptr)
+                asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(orow + c * 32 + j * 4), "f"(__uint_as_float(v[4 * j])),
+                             "f"(__uint_as_float(v[4 * j + 1])), "f"(__uint_as_float(v[4 * j + 2])), "f"(__uint_as_float(v[4 * j + 3]))
+                             : "memory");
+              else
+                *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            }
+          }
         }
       }
     }
@@ -854,7 +864,7 @@ bool conv_tc_supported(const dv_conv_params* p, int pass, const char** why) {
 }
 
 size_t conv_tc_workspace(const dv_conv_params* p, int pass) {
-  if (pass != DV_CONV_WGRAD) return 0;
+  if (pass != DV_CONV_WGRAD || p->accumulate) return 0;
   WgradPlan w = plan_wgrad(p);
   return (size_t)w.splits * p->K * p->R * p->S * p->C * sizeof(float);
 }
@@ -956,12 +966,13 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
 
   // wgrad
   WgradPlan w = plan_wgrad(p);
-  const size_t need = (size_t)w.splits * p->K * p->R * p->S * p->C * sizeof(float);
-  DV_REQUIRE(p->workspace != nullptr && p->workspace_bytes >= need, DV_ERR_WORKSPACE,
+  const size_t need = p->accumulate ? 0 : (size_t)w.splits * p->K * p->R * p->S * p->C * sizeof(float);
+  DV_REQUIRE(need == 0 || (p->workspace != nullptr && p->workspace_bytes >= need), DV_ERR_WORKSPACE,
              "conv_tc wgrad: workspace of %zu bytes required, %zu given", need, p->workspace_bytes);
-  DV_REQUIRE(aligned16(p->workspace), DV_ERR_ARG, "conv_tc wgrad: workspace must be 16-byte aligned");
+  DV_REQUIRE(need == 0 || aligned16(p->workspace), DV_ERR_ARG, "conv_tc wgrad: workspace must be 16-byte aligned");
   WgradArgs g{};
   g.ws = (float*)p->workspace;
+  g.dw_atomic = p->accumulate ? (float*)p->w : nullptr;
   g.Mpix = p->N * P * Q;
   g.K = p->K; g.C = p->C; g.taps = p->R * p->S; g.S = p->S;
   g.P = P; g.Q = Q; g.stride = p->stride; g.pad = p->pad;
@@ -990,6 +1001,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     }
   }
   if (rc) return rc;
+  if (p->accumulate) return DV_OK;  // the tiles were added into dw directly
   const int64_t n4 = (int64_t)p->K * p->R * p->S * p->C / 4;
   wgrad_reduce_kernel<<<(unsigned)ceil_div64(n4, 256), 256, 0, st>>>(g.ws, (float*)p->w, n4, w.splits);
   DV_LAUNCH_OK("wgrad_reduce_kernel");

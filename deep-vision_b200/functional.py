@@ -273,8 +273,15 @@ class _Conv2d(torch.autograd.Function):
                 ctx.slot.t, dx = dx, None
         if ctx.needs_input_grad[1]:
             sink = grad_sink(weight)
-            dw = sink[0] if sink else torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
-            p = _conv_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
+            atomic = 1 if config.atomic_wgrad() else 0
+            if sink:
+                dw = sink[0]          # slice of the flat gradient buffer, zeroed at the start of the step
+            elif atomic:
+                dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL).zero_()
+            else:
+                dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
+            p = _conv_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo,
+                             accumulate=atomic)
             _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad")
             if sink:
                 sink[1](weight)
@@ -428,9 +435,12 @@ class _BatchNormAct(torch.autograd.Function):
         dx = torch.empty_like(x, memory_format=_CL)
         dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1]) else None
         sg, sb = grad_sink(gamma), grad_sink(beta)
-        dgamma = sg[0] if sg else torch.empty(Cc, dtype=torch.float32, device=x.device)
-        dbeta = sb[0] if sb else torch.empty(Cc, dtype=torch.float32, device=x.device)
+        atomic = 1 if config.atomic_bn_bwd() else 0
+        mk = torch.zeros if atomic else torch.empty
+        dgamma = sg[0] if sg else mk(Cc, dtype=torch.float32, device=x.device)
+        dbeta = sb[0] if sb else mk(Cc, dtype=torch.float32, device=x.device)
         p = BnBwdParams()
+        p.atomic_sums = atomic
         p.x, p.y, p.dy, p.dx = x.data_ptr(), (y.data_ptr() if y is not None else None), dy.data_ptr(), dx.data_ptr()
         p.dres = dres.data_ptr() if dres is not None else None
         p.gamma, p.beta, p.save_mean, p.save_invstd = gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), second.data_ptr()

@@ -52,7 +52,7 @@ class BnBwdParams(C.Structure):
         ("gamma", C.c_void_p), ("beta", C.c_void_p), ("save_mean", C.c_void_p), ("save_invstd", C.c_void_p),
         ("dgamma", C.c_void_p), ("dbeta", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
-        ("M", C.c_int64), ("C", C.c_int32), ("dtype", C.c_int32), ("relu", C.c_int32),
+        ("M", C.c_int64), ("C", C.c_int32), ("dtype", C.c_int32), ("relu", C.c_int32), ("atomic_sums", C.c_int32),
     ]
 
 

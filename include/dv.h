@@ -78,8 +78,11 @@ typedef struct dv_conv_params {
   int32_t dtype;      /* DV_F32 | DV_BF16 */
   int32_t algo;       /* DV_ALGO_* */
   int32_t y_f32;      /* fprop only: 1 = write y as fp32 even when dtype is bf16 (the logits of nn.Linear) */
-  int32_t accumulate; /* dgrad only: 1 = dx += result instead of dx = result (the second gradient of a tensor that feeds
-                         two consumers, e.g. a residual block's input: resnet50.py:147-163) */
+  int32_t accumulate; /* dgrad: 1 = dx += result instead of dx = result (the second gradient of a tensor that feeds two
+                         consumers, e.g. a residual block's input: resnet50.py:147-163).
+                         wgrad: 1 = dw += result, added straight into dw with fp32 vector reductions — no workspace, no
+                         second pass; the caller provides a zeroed (or to-be-accumulated) dw and accepts a summation order
+                         that varies run to run.  0 = split partials in the workspace + fixed-order reduce (bit-reproducible) */
 } dv_conv_params;
 
 enum { DV_CONV_FPROP = 0, DV_CONV_DGRAD = 1, DV_CONV_WGRAD = 2 };
@@ -209,6 +212,9 @@ typedef struct dv_bn_bwd_params {
   int32_t C;
   int32_t dtype;
   int32_t relu;
+  int32_t atomic_sums;  /* bwd_reduce: 1 = block sums are ADDED into dgamma/dbeta with fp32 atomics (the caller zeroed them):
+                           no workspace, no finalize launch, run-to-run summation order.  0 = partials + fixed-order
+                           finalize (bit-reproducible) */
 } dv_bn_bwd_params;
 
 /* dgamma, dbeta (with the ReLU mask recomputed from y) */
