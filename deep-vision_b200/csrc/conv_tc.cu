@@ -82,6 +82,14 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, uint32_t sme
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
+// the same, but the tile is ADDED to global memory (element-wise bf16 add performed at the L2)
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, uint32_t smem_addr, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_addr), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
@@ -447,7 +455,10 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           }
           fence_proxy_async_smem();  // make the generic-proxy writes visible to the TMA (async proxy)
           __syncwarp();
-          if (lane == 0 && cgp * 64 < n_left && m_base < g.M) tma_store_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
+          if (lane == 0 && cgp * 64 < n_left && m_base < g.M) {
+            if (g.accumulate) tma_reduce_add_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
+            else tma_store_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
+          }
           if (g.stat_sums != nullptr) {
             // column sums over this warp's 32 rows from the bf16-rounded values (what BN will read back)
             const int wch = lane >> 2, wof = (lane & 3) * 4;
@@ -876,9 +887,9 @@ static int pick_bn(int nout) {
   return bn;
 }
 
-// STAGED (TMA-store epilogue, optional BN sums) whenever the output is a plain bf16 [M][Nout] matrix
+// STAGED (TMA store / TMA reduce-add epilogue, optional BN sums) whenever the output is a dense bf16 [M][Nout] matrix
 static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, bool b_mn, cudaStream_t st) {
-  const bool staged = !g.scatter && !g.accumulate && !g.out_f32;
+  const bool staged = !g.scatter && !g.out_f32;
   alignas(64) CUtensorMap tmO;
   if (staged) {
     int rc = make_map_2d(&tmO, g.out, (uint64_t)g.M, (uint64_t)g.Nout, 32);

@@ -22,13 +22,13 @@ __global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, u
                                    int P, int Q) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
-  const int64_t total = (int64_t)N * P * Q * cg;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % cg) * V;
-    int64_t pix = i / cg;
-    const int q = (int)(pix % Q); pix /= Q;
-    const int p = (int)(pix % P);
-    const int n = (int)(pix / P);
+  const int total = N * P * Q * cg;  // < 2^31, checked by the caller
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c = (i % cg) * V;
+    int pix = i / cg;
+    const int q = pix % Q; pix /= Q;
+    const int p = pix % P;
+    const int n = pix / P;
     float best[V];
     __align__(8) uint8_t bi[V];
 #pragma unroll
@@ -63,13 +63,13 @@ __global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __re
                                    int C, int P, int Q) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
-  const int64_t total = (int64_t)N * H * W * cg;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % cg) * V;
-    int64_t pix = i / cg;
-    const int w = (int)(pix % W); pix /= W;
-    const int h = (int)(pix % H);
-    const int n = (int)(pix / H);
+  const int total = N * H * W * cg;  // < 2^31, checked by the caller
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c = (i % cg) * V;
+    int pix = i / cg;
+    const int w = pix % W; pix /= W;
+    const int h = pix % H;
+    const int n = pix / H;
     float acc[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) acc[j] = 0.f;
@@ -248,6 +248,42 @@ __global__ void unpad_rows_kernel(const float* __restrict__ src, float* __restri
   }
 }
 
+// ---- cross entropy, one CTA per row (train.py:358,452) -------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+cross_entropy_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss,
+                     float* __restrict__ dlogits, int B, int C) {
+  __shared__ float red[8];
+  const int b = blockIdx.x;
+  const float* row = logits + (size_t)b * C;
+  float m = -CUDART_INF_F;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) m = fmaxf(m, row[c]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  m = red[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) m = fmaxf(m, red[i]);
+  __syncthreads();
+  float s = 0.f;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) s += expf(row[c] - m);
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s += red[i];
+  const int label = (int)labels[b];
+  const float inv_b = 1.f / (float)B, inv_s = 1.f / s;
+  for (int c = threadIdx.x; c < C; c += blockDim.x)
+    dlogits[(size_t)b * C + c] = (expf(row[c] - m) * inv_s - (c == label ? 1.f : 0.f)) * inv_b;
+  if (threadIdx.x == 0) atomicAdd(loss, (logf(s) + m - row[label]) * inv_b);
+}
+__global__ void scale_by_kernel(float* __restrict__ x, const float* __restrict__ s, int64_t n) {
+  const float f = s[0];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) x[i] *= f;
+}
+
 // ---- optimisers (train.py:166-205) -----------------------------------------------------------------------------------
 __global__ void sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, bf16* __restrict__ p16, int64_t n,
                            float lr, float mom, float wd, float gscale, int first) {
@@ -296,6 +332,7 @@ extern "C" int dv_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H
   if (rc) return rc;
   const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
   const int64_t total = (int64_t)N * P * Q * (C / (dtype == DV_BF16 ? 8 : 4));
+  DV_REQUIRE((int64_t)N * H * W * C < (1LL << 31), DV_ERR_UNSUPPORTED, "dv_maxpool_fwd: tensor exceeds 2^31 elements");
   cudaStream_t st = (cudaStream_t)stream;
   DV_DISPATCH_T(dtype, (maxpool_fwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, idx, N, H, W, C, P, Q)),
                 (maxpool_fwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)x, (float*)y, idx, N, H, W, C, P, Q)));
@@ -308,6 +345,7 @@ extern "C" int dv_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int 
   if (rc) return rc;
   const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
   const int64_t total = (int64_t)N * H * W * (C / (dtype == DV_BF16 ? 8 : 4));
+  DV_REQUIRE((int64_t)N * H * W * C < (1LL << 31), DV_ERR_UNSUPPORTED, "dv_maxpool_bwd: tensor exceeds 2^31 elements");
   cudaStream_t st = (cudaStream_t)stream;
   DV_DISPATCH_T(dtype, (maxpool_bwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)dy, idx, (bf16*)dx, N, H, W, C, P, Q)),
                 (maxpool_bwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)dy, idx, (float*)dx, N, H, W, C, P, Q)));
@@ -406,6 +444,20 @@ extern "C" int dv_unpad_rows(const float* src, float* dst, int rows, int cols, i
   DV_REQUIRE(src && dst && rows > 0 && cols > 0 && src_pitch >= cols, DV_ERR_ARG, "dv_unpad_rows: bad arguments");
   unpad_rows_kernel<<<grid_for((int64_t)rows * cols), kThreads, 0, (cudaStream_t)stream>>>(src, dst, rows, cols, src_pitch);
   DV_LAUNCH_OK("unpad_rows_kernel");
+  return DV_OK;
+}
+extern "C" int dv_cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C, void* stream) {
+  DV_REQUIRE(logits && labels && loss && dlogits && B > 0 && C > 0, DV_ERR_ARG, "dv_cross_entropy: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  DV_CUDA_OK(cudaMemsetAsync(loss, 0, sizeof(float), st));
+  cross_entropy_kernel<<<B, 256, 0, st>>>(logits, labels, loss, dlogits, B, C);
+  DV_LAUNCH_OK("cross_entropy_kernel");
+  return DV_OK;
+}
+extern "C" int dv_scale_by(float* x, const float* s, int64_t n, void* stream) {
+  DV_REQUIRE(x && s && n > 0, DV_ERR_ARG, "dv_scale_by: bad arguments");
+  scale_by_kernel<<<grid_for(n), kThreads, 0, (cudaStream_t)stream>>>(x, s, n);
+  DV_LAUNCH_OK("scale_by_kernel");
   return DV_OK;
 }
 extern "C" int dv_sgd_step(float* p, const float* g, float* buf, int64_t n, float lr, float momentum, float wd, float gscale, int first,

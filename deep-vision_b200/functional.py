@@ -604,3 +604,34 @@ class _Linear(torch.autograd.Function):
 
 def linear(x, weight, bias=None, cache=None):
     return _Linear.apply(x, weight, bias, cache or FilterCache())
+
+
+class _CrossEntropy(torch.autograd.Function):
+    """nn.CrossEntropyLoss() with mean reduction — ResNet/pytorch/train.py:358,452.  Loss and d(loss)/d(logits) come
+    out of one launch; backward only applies the upstream scalar."""
+
+    @staticmethod
+    def forward(ctx, logits, labels):
+        _require_cuda(logits, "cross_entropy")
+        if logits.dtype != torch.float32 or logits.dim() != 2 or labels.dtype != torch.int64:
+            raise TypeError("cross_entropy expects fp32 [B,C] logits and int64 [B] labels")
+        logits = logits.contiguous()
+        labels = labels.contiguous()
+        B, Cn = logits.shape
+        loss = torch.empty((), dtype=torch.float32, device=logits.device)
+        dlogits = torch.empty_like(logits)
+        check(lib.dv_cross_entropy(logits.data_ptr(), labels.data_ptr(), loss.data_ptr(), dlogits.data_ptr(), B, Cn, _stream()),
+              "dv_cross_entropy")
+        ctx.save_for_backward(dlogits)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (dlogits,) = ctx.saved_tensors
+        g = g.contiguous().float()
+        check(lib.dv_scale_by(dlogits.data_ptr(), g.data_ptr(), dlogits.numel(), _stream()), "dv_scale_by")
+        return dlogits, None
+
+
+def cross_entropy(logits, labels):
+    return _CrossEntropy.apply(logits, labels)

@@ -89,6 +89,8 @@ _SIG = {
     "dv_cast": (C.c_int, [_P, C.c_int, _P, C.c_int, C.c_int64, _P]),
     "dv_bias_add": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P]),
     "dv_bias_grad": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P]),
+    "dv_cross_entropy": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P]),
+    "dv_scale_by": (C.c_int, [_P, _P, C.c_int64, _P]),
     "dv_sgd_step": (C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, _P]),
     "dv_rmsprop_step": (C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, _P]),
     "dv_sgd_step_bf16": (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, _P]),

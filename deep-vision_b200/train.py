@@ -23,6 +23,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 
 from . import config
+from . import functional as dvF
 from .lib import check, lib
 
 # train.py:166-214 — the reference's optimiser settings per model
@@ -200,7 +201,7 @@ class Trainer:
         if self.exchange is not None:
             self.exchange.reset()
         logits = self.model(images)
-        loss = F.cross_entropy(logits, labels)
+        loss = dvF.cross_entropy(logits, labels)
         loss.backward()
         if self.exchange is not None:
             self.exchange.finish()
@@ -269,6 +270,12 @@ class Trainer:
                 self._static_loss = self._step_body(self._static_images, self._static_labels)
         finally:
             self._capturing = False
+
+    def refresh_from_parameters(self):
+        """After parameters were written through torch (load_state_dict, manual edits): rebuild the bf16 mirror."""
+        if getattr(self, "flat_p16", None) is not None:
+            self.flat_p16.copy_(self.flat_p)
+        config.bump_weight_epoch()
 
     def state_dict(self):
         return {"optimizer": self.kind, "steps": self.steps_done, "state": self.flat_s.clone()}

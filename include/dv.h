@@ -245,6 +245,14 @@ int dv_bias_add(float* y, const float* bias, int64_t M, int C, void* stream);
 /* dbias[c] = sum_m dy[m,c] (fp32) */
 int dv_bias_grad(const float* dy, float* dbias, int64_t M, int C, void* stream);
 
+/* nn.CrossEntropyLoss() (mean reduction) — ResNet/pytorch/train.py:358,452, forward and backward in one launch:
+ *   loss[0]      = mean_b ( logsumexp(logits[b,:]) - logits[b, labels[b]] )
+ *   dlogits[b,c] = (softmax(logits[b,:])[c] - (c == labels[b])) / B          (the gradient for d(loss) = 1)
+ * logits, dlogits: fp32 [B,C]; labels: int64 [B]; loss: fp32 scalar (zeroed by the call). */
+int dv_cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C, void* stream);
+/* x[i] *= s[0] with s a DEVICE scalar (chain rule for a loss whose upstream gradient is not 1) */
+int dv_scale_by(float* x, const float* s, int64_t n, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Optimisers over a flat fp32 parameter buffer (one launch for the whole model).
  * optim.SGD(lr, momentum, weight_decay) — ResNet/pytorch/train.py:166-184,361-365,467:

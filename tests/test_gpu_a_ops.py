@@ -340,3 +340,25 @@ def test_im2col_pad_unpad_match_oracle(case):
     lib.check(lib.lib.dv_unpad_rows(src.data_ptr(), dst.data_ptr(), K, R * R * Cc, kp, stream_ptr()), "unpad_rows")
     torch.cuda.synchronize()
     assert torch.equal(dst, src[:, :R * R * Cc])
+
+
+def test_cross_entropy_matches_oracle():
+    """dv_cross_entropy: mean loss and d(loss)/d(logits) in one launch (nn.CrossEntropyLoss, train.py:358,452)."""
+    lib = _lib()
+    rng = np.random.default_rng(61)
+    B, Cn = 37, 1000
+    logits = (rng.standard_normal((B, Cn)) * 4).astype(np.float32)
+    labels = rng.integers(0, Cn, B)
+    loss_ref, d_ref = ref_ops.cross_entropy(logits.astype(np.float64), labels)
+    ld = torch.from_numpy(logits).cuda()
+    lab = torch.from_numpy(labels.astype(np.int64)).cuda()
+    loss = torch.full((), float("nan"), device="cuda")
+    d = torch.full((B, Cn), float("nan"), device="cuda")
+    lib.check(lib.lib.dv_cross_entropy(ld.data_ptr(), lab.data_ptr(), loss.data_ptr(), d.data_ptr(), B, Cn, stream_ptr()), "ce")
+    torch.cuda.synchronize()
+    assert abs(float(loss) - loss_ref) < 1e-5 * abs(loss_ref)
+    assert rel_l2(d.cpu().numpy(), d_ref) < 1e-5
+    s = torch.tensor([0.25], device="cuda")
+    lib.check(lib.lib.dv_scale_by(d.data_ptr(), s.data_ptr(), B * Cn, stream_ptr()), "scale")
+    torch.cuda.synchronize()
+    assert rel_l2(d.cpu().numpy(), 0.25 * d_ref) < 1e-5
