@@ -279,3 +279,53 @@ class Trainer:
 
     def state_dict(self):
         return {"optimizer": self.kind, "steps": self.steps_done, "state": self.flat_s.clone()}
+
+
+class HostFeeder:
+    """Host-to-device input path of the training loop (train.py:444-446 moves every batch with `.to(device)`):
+    pinned host batches are copied on a side stream into one of two device buffers while the previous step computes, so
+    the PCIe transfer of batch i+1 hides behind step i.
+
+        feeder = HostFeeder(trainer)
+        feeder.prefetch(images_host, labels_host)            # batch 0
+        for i in range(steps):
+            ready = feeder.take()                            # waits for batch i on the compute stream
+            feeder.prefetch(next_images_host, next_labels_host)
+            loss = trainer.step(*ready).item()
+    """
+
+    def __init__(self, trainer):
+        self.trainer = trainer
+        self.stream = torch.cuda.Stream()
+        self.slots = [None, None]
+        self.events = [torch.cuda.Event(), torch.cuda.Event()]
+        self.free_events = [None, None]
+        self.head = 0   # next slot to fill
+        self.tail = 0   # next slot to hand out
+
+    def prefetch(self, images_host, labels_host):
+        i = self.head
+        if self.slots[i] is None:
+            dev = self.trainer.flat_p.device
+            self.slots[i] = (torch.empty(images_host.shape, dtype=images_host.dtype, device=dev),
+                             torch.empty(labels_host.shape, dtype=labels_host.dtype, device=dev))
+        with torch.cuda.stream(self.stream):
+            if self.free_events[i] is not None:
+                self.stream.wait_event(self.free_events[i])   # the step that read this slot has been enqueued and finished
+            self.slots[i][0].copy_(images_host, non_blocking=True)
+            self.slots[i][1].copy_(labels_host, non_blocking=True)
+            self.events[i].record(self.stream)
+        self.head ^= 1
+
+    def take(self):
+        i = self.tail
+        torch.cuda.current_stream().wait_event(self.events[i])
+        self.tail ^= 1
+        self._last = i
+        return self.slots[i]
+
+    def release(self):
+        """Call after the step that consumed the last `take()` has been enqueued."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.free_events[self._last] = ev
