@@ -136,6 +136,66 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t* v) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- CTA-pair (cta_group::2) helpers -------------------------------------------------------------------------
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address: "the same offset in CTA 0"
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 remote;\n\t"
+      "mapa.shared::cluster.u32 remote, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [remote];\n\t}" ::"r"(smem_u32(bar)),
+      "r"(cta)
+      : "memory");
+}
+// TMA loads issued by either CTA of a pair: data lands in the issuing CTA's shared memory, the bytes are counted on
+// CTA 0's barrier (the MMA issuer waits there for both halves)
+__device__ __forceinline__ void tma_load_2d_pair(void* smem, const CUtensorMap* tm, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_pair(void* smem, const CUtensorMap* tm, uint64_t* bar, int c, int w, int h, int n,
+                                                     uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(smem_u32(smem)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// one MMA over both SMs of the pair: D[256 x N] (128 rows in each SM's TMEM) += A (128 rows per SM) * B (N/2 rows per SM)
+__device__ __forceinline__ void umma_f16_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// completion of all prior MMAs arrives on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+
 // ---- descriptors ---------------------------------------------------------------------------------------------
 // Shared-memory matrix descriptor (PTX ISA "tcgen05 matrix descriptor"): start>>4 [0,14), LBO>>4 [16,30),
 // SBO>>4 [32,46), version=1 [46,48), layout type [61,64) with 2 = SWIZZLE_128B.
@@ -147,6 +207,29 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_
   d |= (uint64_t)2 << 61;
   return d;
 }
+// The issue loop runs on ONE thread and every instruction in it is on the tensor pipe's critical path (ncu: ~95 SASS
+// instructions per 64-wide K block cost ~1000 cycles against 512 cycles of MMA work).  So descriptors are not rebuilt
+// per MMA: the constant high word is a literal and the low word (address >> 4 | LBO) only takes an integer add.
+// Role loops are executed by the WHOLE warp with warp-uniform control flow (the warp index comes through a shuffle so the
+// compiler knows it is uniform) and only the issue itself is predicated on elect.sync: then ptxas keeps descriptors in
+// uniform registers and emits the UTCHMMA / UTMALDG instructions back to back.  Issuing from `if (lane == 0)` instead
+// makes it wrap every such instruction in an ELECT + BRA.U.ANY loop with R2UR moves (10 SASS instructions per MMA).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
+constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (2u << 29);          // SBO 1024 B, version 1, SWIZZLE_128B
+__device__ __forceinline__ uint32_t desc_lo_kmajor(uint32_t saddr) { return ((saddr & 0x3FFFFu) >> 4) | (1u << 16); }
+__device__ __forceinline__ uint32_t desc_lo_mnmajor(uint32_t saddr) { return ((saddr & 0x3FFFFu) >> 4) | ((8192u >> 4) << 16); }
+__device__ __forceinline__ uint64_t desc_pack(uint32_t lo) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(kDescHi));
+  return d;
+}
+
 // Instruction descriptor for kind::f16: D=f32 (bit 4), A=B=bf16 (bits 7,10), majors (15,16; 1 = MN-major),
 // N>>3 at [17,23), M>>4 at [24,29).
 __host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
@@ -216,7 +299,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
   uint64_t* tempty_bar = tfull_bar + ACC;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + ACC);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int num_n = (g.Nout + BN - 1) / BN;
   const int num_m = (g.M + kBlockM - 1) / kBlockM;
   const int total = num_m * num_n;
@@ -243,24 +326,24 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const int n_tile = tile % num_n, m_tile = tile / num_n;
-        const int m0 = m_tile * kBlockM;
-        int n_img = 0, h0 = 0, w0 = 0;
-        if (g.a_im2col) {
-          const int pq = g.P * g.Q;
-          n_img = m0 / pq;
-          const int rem = m0 - n_img * pq;
-          const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
-          h0 = p0 * g.stride - g.pad;
-          w0 = q0 * g.stride - g.pad;
-        }
-        int tap = 0, cb = 0;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const int n_tile = tile % num_n, m_tile = tile / num_n;
+      const int m0 = m_tile * kBlockM;
+      int n_img = 0, h0 = 0, w0 = 0;
+      if (g.a_im2col) {
+        const int pq = g.P * g.Q;
+        n_img = m0 / pq;
+        const int rem = m0 - n_img * pq;
+        const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
+        h0 = p0 * g.stride - g.pad;
+        w0 = q0 * g.stride - g.pad;
+      }
+      int tap = 0, cb = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
           uint8_t* sA = smem + stage * kStageBytes;
           uint8_t* sB = sA + kABytes;
           mbar_expect_tx(&full_bar[stage], kStageBytes);
@@ -278,14 +361,19 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           } else {
             tma_load_2d(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN);
           }
-          if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, B_MN ? 1 : 0);
+      constexpr uint32_t kStageStep = kStageBytes >> 4;            // descriptor units (16 B) between ring stages
+      constexpr uint32_t kBStep = B_MN ? (2048u >> 4) : 2u;       // one K=16 step inside a stage
+      const uint32_t a_lo0 = desc_lo_kmajor(smem_u32(smem));
+      const uint32_t b_lo0 = B_MN ? desc_lo_mnmajor(smem_u32(smem) + kABytes) : desc_lo_kmajor(smem_u32(smem) + kABytes);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
@@ -295,18 +383,19 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sA = smem_u32(smem + stage * kStageBytes);
-          const uint32_t sB = sA + kABytes;
+          if (elect_one()) {
+            const uint32_t a_lo = a_lo0 + (uint32_t)stage * kStageStep;
+            const uint32_t b_lo = b_lo0 + (uint32_t)stage * kStageStep;
+            umma_f16(d_tmem, desc_pack(a_lo), desc_pack(b_lo), idesc, kb ? 1u : 0u);
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k) {
-            const uint64_t ad = make_smem_desc(sA + k * 32, 16, 1024);
-            const uint64_t bd = B_MN ? make_smem_desc(sB + k * 2048, 8192, 1024) : make_smem_desc(sB + k * 32, 16, 1024);
-            umma_f16(d_tmem, ad, bd, idesc, (kb | k) ? 1u : 0u);
+            for (int k = 1; k < kBlockK / 16; ++k)
+              umma_f16(d_tmem, desc_pack(a_lo + k * 2u), desc_pack(b_lo + k * kBStep), idesc, 1u);
+            umma_commit(&empty_bar[stage]);
+            if (kb == num_kb - 1) umma_commit(&tfull_bar[acc]);  // same thread as the MMAs it tracks
           }
-          umma_commit(&empty_bar[stage]);
+          __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tfull_bar[acc]);
         if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -490,6 +579,234 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// CTA-pair variant (BN = 256 layers): two CTAs of a cluster own 256 output pixels x 256 channels.  Each stages ITS 128
+// activation rows and HALF of the filter tile; one thread of CTA 0 issues tcgen05.mma.cta_group::2 (M=256, N=256), which
+// reads A from each SM's own shared memory and the two B halves from both.  Per SM that is 32 KB of TMA fill and 32 KB of
+// operand reads per 512 tensor cycles = 128 B/clk, exactly the shared-memory port, where the single-CTA kernel needs
+// 192 B/clk (ncu: 67 % tensor-pipe ceiling).  Full barriers live in CTA 0 (both CTAs' loads count there); empty and
+// accumulator-ready barriers are signalled in both CTAs by a multicast commit; the peer's epilogue hands accumulators
+// back by a remote arrive.
+// ------------------------------------------------------------------------------------------------------------
+template <int STAGES, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads)
+conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmO, const GemmArgs g) {
+  constexpr int BN = 256, ACC = 2;
+  constexpr int kBHalfBytes = (BN / 2) * kBlockK * 2;  // 16 KB: this CTA's half of the filter tile
+  constexpr int kStageBytes = kABytes + kBHalfBytes;    // 32 KB
+  constexpr uint32_t kTmemCols = ACC * BN;              // 512
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("dv conv_tc: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  uint8_t* stage_out = smem + STAGES * kStageBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + kEpiStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + ACC;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + ACC);
+
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int num_n = (g.Nout + BN - 1) / BN;
+  const int num_m = (g.M + kBlockM - 1) / kBlockM;
+  const int total_pairs = ((num_m + 1) / 2) * num_n;
+  const int num_kb = g.taps * g.kb_per_tap;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmO);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 2);   // CTA 0's expect_tx arrive + the peer's remote arrive
+      mbar_init(&empty_bar[i], 1);  // multicast commit
+    }
+    for (int i = 0; i < ACC; ++i) {
+      mbar_init(&tfull_bar[i], 1);   // multicast commit
+      mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps of each CTA (used in CTA 0 only)
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc_pair(tmem_ptr, kTmemCols);
+  tc_fence_before();
+  cluster_sync_all();  // barriers of both CTAs are initialised before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int pair = cluster_id; pair < total_pairs; pair += num_clusters) {
+      const int n_tile = pair % num_n, m_tile = 2 * (pair / num_n) + (int)rank;
+      const int m0 = m_tile * kBlockM;  // may lie past M for the odd last pair: TMA zero-fills, the epilogue skips
+      int n_img = 0, h0 = 0, w0 = 0;
+      if (g.a_im2col) {
+        const int pq = g.P * g.Q;
+        n_img = m0 / pq;
+        const int rem = m0 - n_img * pq;
+        const int p0 = rem / g.Q, q0 = rem - p0 * g.Q;
+        h0 = p0 * g.stride - g.pad;
+        w0 = q0 * g.stride - g.pad;
+      }
+      int tap = 0, cb = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
+          uint8_t* sA = smem + stage * kStageBytes;
+          uint8_t* sB = sA + kABytes;
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
+          if (g.a_im2col) {
+            const int r = tap / g.S, s = tap - r * g.S;
+            tma_load_im2col_pair(sA, &tmA, &full_bar[stage], cb * kBlockK, w0, h0, n_img, (uint16_t)s, (uint16_t)r);
+          } else {
+            tma_load_2d_pair(sA, &tmA, &full_bar[stage], cb * kBlockK, m0);
+          }
+          if (B_MN) {
+            // this CTA's 128 output columns = two [64 k][64 c] boxes of the KRSC filters (flipped tap)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+              tma_load_2d_pair(sB + j * 8192, &tmB, &full_bar[stage],
+                               (g.taps - 1 - tap) * g.Nout + n_tile * BN + (int)rank * 128 + j * 64, cb * kBlockK);
+          } else {
+            tma_load_2d_pair(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN + (int)rank * 128);
+          }
+          if (rank != 0) mbar_arrive_remote(&full_bar[stage], 0);
+        }
+        __syncwarp();
+        if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc(256, BN, 0, B_MN ? 1 : 0);
+      constexpr uint32_t kStageStep = kStageBytes >> 4;
+      constexpr uint32_t kBStep = B_MN ? (2048u >> 4) : 2u;
+      const uint32_t a_lo0 = desc_lo_kmajor(smem_u32(smem));
+      const uint32_t b_lo0 = B_MN ? desc_lo_mnmajor(smem_u32(smem) + kABytes) : desc_lo_kmajor(smem_u32(smem) + kABytes);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int pair = cluster_id; pair < total_pairs; pair += num_clusters) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);  // both CTAs' epilogues have drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t a_lo = a_lo0 + (uint32_t)stage * kStageStep;
+            const uint32_t b_lo = b_lo0 + (uint32_t)stage * kStageStep;
+            umma_f16_pair(d_tmem, desc_pack(a_lo), desc_pack(b_lo), idesc, kb ? 1u : 0u);
+#pragma unroll
+            for (int k = 1; k < kBlockK / 16; ++k)
+              umma_f16_pair(d_tmem, desc_pack(a_lo + k * 2u), desc_pack(b_lo + k * kBStep), idesc, 1u);
+            umma_commit_pair(&empty_bar[stage]);
+            if (kb == num_kb - 1) umma_commit_pair(&tfull_bar[acc]);
+          }
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    uint8_t* my_stage = stage_out + quarter * (32 * 128);
+    const uint32_t my_stage_u32 = smem_u32(my_stage);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    float s1[BN / 64][2], s2[BN / 64][2];
+    int stat_n_tile = -1;
+#pragma unroll
+    for (int i = 0; i < BN / 64; ++i) { s1[i][0] = s1[i][1] = s2[i][0] = s2[i][1] = 0.f; }
+    auto flush_stats = [&]() {
+      if (g.stat_sums == nullptr || stat_n_tile < 0) return;
+#pragma unroll
+      for (int i = 0; i < BN / 64; ++i) {
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int col = stat_n_tile * BN + i * 64 + 2 * lane + e;
+          if (col < g.Nout) {
+            atomicAdd(g.stat_sums + col, s1[i][e]);
+            atomicAdd(g.stat_sums + g.Nout + col, s2[i][e]);
+          }
+          s1[i][e] = 0.f;
+          s2[i][e] = 0.f;
+        }
+      }
+    };
+    for (int pair = cluster_id; pair < total_pairs; pair += num_clusters) {
+      const int n_tile = pair % num_n, m_tile = 2 * (pair / num_n) + (int)rank;
+      if (n_tile != stat_n_tile) { flush_stats(); stat_n_tile = n_tile; }
+      const int m_base = m_tile * kBlockM + quarter * 32;
+      const int n_left = g.Nout - n_tile * BN;
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll
+      for (int cgp = 0; cgp < BN / 64; ++cgp) {
+        if (lane == 0) tma_store_wait_read();
+        __syncwarp();
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t w[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
+              w[e] = *reinterpret_cast<uint32_t*>(&h);
+            }
+            const int ch = (half * 4 + j) ^ (lane & 7);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_stage_u32 + lane * 128 + ch * 16), "r"(w[0]), "r"(w[1]),
+                         "r"(w[2]), "r"(w[3])
+                         : "memory");
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0 && cgp * 64 < n_left && m_base < g.M) {
+          if (g.accumulate) tma_reduce_add_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
+          else tma_store_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
+        }
+        if (g.stat_sums != nullptr) {
+          const int wch = lane >> 2, wof = (lane & 3) * 4;
+          float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+#pragma unroll 8
+          for (int r = 0; r < 32; ++r) {
+            const uint32_t word = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+            const float x0 = __uint_as_float(word << 16), x1 = __uint_as_float(word & 0xffff0000u);
+            a0 += x0; a1 += x1;
+            b0 = fmaf(x0, x0, b0); b1 = fmaf(x1, x1, b1);
+          }
+          s1[cgp][0] += a0; s1[cgp][1] += a1;
+          s2[cgp][0] += b0; s2[cgp][1] += b1;
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (rank == 0) mbar_arrive(&tempty_bar[acc]);
+        else mbar_arrive_remote(&tempty_bar[acc], 0);
+      }
+      if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
+    }
+    flush_stats();
+    if (lane == 0) tma_store_wait_read();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // neither CTA may retire (or free TMEM) while the pair still issues MMAs / remote arrives
+  if (warp == 1) tmem_dealloc_pair(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // wgrad kernel
 // ------------------------------------------------------------------------------------------------------------
 struct WgradArgs {
@@ -524,7 +841,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   // tile index: tap fastest so the CTAs that share one dY tile are neighbours in launch order (L2 reuse)
   int t = blockIdx.x;
   const int tap = t % g.taps; t /= g.taps;
@@ -552,14 +869,14 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp == 0) {
-    if (lane == 0) {
-      const int r = tap / g.S, s = tap - r * g.S;
-      const int pq = g.P * g.Q;
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int i = 0; i < num_kb; ++i) {
-        const int pix0 = (kb_begin + i) * kPix;
-        mbar_wait(&empty_bar[stage], phase ^ 1);
+    const int r = tap / g.S, s = tap - r * g.S;
+    const int pq = g.P * g.Q;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < num_kb; ++i) {
+      const int pix0 = (kb_begin + i) * kPix;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (elect_one()) {
         uint8_t* sA = smem + stage * kStageBytes;
         uint8_t* sB = sA + kABytesW;
         mbar_expect_tx(&full_bar[stage], kStageBytes);
@@ -576,36 +893,39 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
 #pragma unroll
           for (int j = 0; j < BNC / 64; ++j) tma_load_2d(sB + j * kChunk, &tmX, &full_bar[stage], c_tile * BNC + j * 64, pix0);
         }
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc(128, BNC, 1, 1);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int i = 0; i < num_kb; ++i) {
-        mbar_wait(&full_bar[stage], phase);
-        tc_fence_after();
-        const uint32_t sA = smem_u32(smem + stage * kStageBytes);
-        const uint32_t sB = sA + kABytesW;
+    constexpr uint32_t idesc = make_idesc(128, BNC, 1, 1);
+    constexpr uint32_t kStageStep = kStageBytes >> 4;
+    // MN-major SWIZZLE_128B: a row is one pixel (128 B = 64 channels); 8-pixel groups are 1024 B apart (SBO), 64-channel
+    // chunks are kChunk apart (LBO); a 16-pixel K step is +2048 B; the second 128-row half of dY starts 2*kChunk further.
+    static_assert(kChunk == 8192, "desc_lo_mnmajor encodes LBO = 8192");
+    const uint32_t a_lo0 = desc_lo_mnmajor(smem_u32(smem));
+    const uint32_t b_lo0 = desc_lo_mnmajor(smem_u32(smem) + kABytesW);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int i = 0; i < num_kb; ++i) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t a_lo = a_lo0 + (uint32_t)stage * kStageStep;
+        const uint32_t b_lo = b_lo0 + (uint32_t)stage * kStageStep;
 #pragma unroll
         for (int k = 0; k < kPix / 16; ++k) {
-          // MN-major SWIZZLE_128B: a row is one pixel (128 B = 64 channels); 8-pixel groups are 1024 B apart (SBO),
-          // 64-channel chunks are kChunk apart (LBO); a 16-pixel K step is +2048 B.
-          const uint64_t bd = make_smem_desc(sB + k * 2048, kChunk, 1024);
 #pragma unroll
-          for (int h = 0; h < MH; ++h) {
-            const uint64_t ad = make_smem_desc(sA + h * 2 * kChunk + k * 2048, kChunk, 1024);
-            umma_f16(tmem_base + (uint32_t)(h * BNC), ad, bd, idesc, (i | k) ? 1u : 0u);
-          }
+          for (int h = 0; h < MH; ++h)
+            umma_f16(tmem_base + (uint32_t)(h * BNC), desc_pack(a_lo + (uint32_t)(h * 2 * kChunk + k * 2048) / 16u),
+                     desc_pack(b_lo + (uint32_t)(k * 2048) / 16u), idesc, (k == 0 && i == 0) ? 0u : 1u);
         }
         umma_commit(&empty_bar[stage]);
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (i == num_kb - 1) umma_commit(tmem_full_bar);
       }
-      umma_commit(tmem_full_bar);
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
-    __syncwarp();
   } else {
     const int quarter = warp & 3;
     mbar_wait(tmem_full_bar, 0);
@@ -736,6 +1056,21 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <int STAGES, bool B_MN>
+static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const GemmArgs& g, cudaStream_t st) {
+  constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + kEpiStageBytes + 256;
+  static_assert(smem <= 227 * 1024, "pair kernel ring exceeds shared memory");
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int num_n = ceil_div(g.Nout, 256);
+  const int pairs = ceil_div(ceil_div(g.M, kBlockM), 2) * num_n;
+  int clusters = num_sms() / 2;
+  if (clusters > num_n) clusters -= clusters % num_n;
+  if (clusters > pairs) clusters = pairs;
+  conv_tc_gemm_pair_kernel<STAGES, B_MN><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, g);  // __cluster_dims__(2,1,1)
+  DV_LAUNCH_OK("conv_tc_gemm_pair_kernel");
+  return DV_OK;
+}
 
 static int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
@@ -887,6 +1222,12 @@ static int pick_bn(int nout) {
   return bn;
 }
 
+// the CTA-pair kernel takes the wide (BN = 256), dense-output launches with at least one full pair of M tiles per cluster
+static bool use_pair(const GemmArgs& g, int bn) {
+  static const int enabled = env_int("DV_TC_PAIR", 1);
+  return enabled && bn == 256 && !g.scatter && !g.out_f32 && g.M >= 2 * kBlockM * (num_sms() / 2);
+}
+
 // STAGED (TMA store / TMA reduce-add epilogue, optional BN sums) whenever the output is a dense bf16 [M][Nout] matrix
 static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, bool b_mn, cudaStream_t st) {
   const bool staged = !g.scatter && !g.out_f32;
@@ -897,6 +1238,7 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
   } else {
     tmO = tmA;  // unused by the kernel
   }
+  if (use_pair(g, bn)) return b_mn ? launch_gemm_pair<6, true>(tmA, tmB, tmO, g, st) : launch_gemm_pair<6, false>(tmA, tmB, tmO, g, st);
 #define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_>(tmA, tmB, tmO, g, st)
   if (b_mn) {
     if (staged) { switch (bn) { case 64: DV_GEMM_CASE(64, 4, true, true); case 128: DV_GEMM_CASE(128, 3, true, true); default: DV_GEMM_CASE(256, 4, true, true); } }
@@ -932,7 +1274,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     if (g.a_im2col) rc = make_map_im2col(&tmA, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, kBlockM);
     else rc = make_map_2d(&tmA, p->x, (uint64_t)g.M, (uint64_t)p->C, kBlockM);
     if (rc) return rc;
-    rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, (uint32_t)bn);
+    rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, use_pair(g, bn) ? 128u : (uint32_t)bn);
     if (rc) return rc;
     return gemm_dispatch(tmA, tmB, g, bn, false, st);
   }
@@ -970,7 +1312,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     }
     if (rc) return rc;
     if (b_mn) rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, 64);
-    else rc = make_map_2d(&tmB, p->w_t, (uint64_t)p->C, (uint64_t)p->R * p->S * p->K, (uint32_t)bn);
+    else rc = make_map_2d(&tmB, p->w_t, (uint64_t)p->C, (uint64_t)p->R * p->S * p->K, use_pair(g, bn) ? 128u : (uint32_t)bn);
     if (rc) return rc;
     return gemm_dispatch(tmA, tmB, g, bn, b_mn, st);
   }

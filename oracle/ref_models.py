@@ -132,4 +132,4 @@ def train_step(name, sd, images, labels, opt_state, optimizer="sgd", lr=0.1, mom
                 sq.mul_(alpha).addcmul_(g, g, value=1 - alpha)
                 opt_state[k] = sq
                 p.sub_(lr * g / (sq.sqrt() + eps))
-    return float(loss)
+    return float(loss.detach())
