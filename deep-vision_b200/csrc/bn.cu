@@ -47,8 +47,10 @@ __global__ void __launch_bounds__(kThreads)
 bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, const float* __restrict__ mean,
                  const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta,
                  float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par, int64_t rows_per_blk, int relu,
-                 float* __restrict__ atomic_s1 = nullptr, float* __restrict__ atomic_s2 = nullptr) {
-  // relu: 0 = no activation, 1 = mask from the stored output y, 2 = mask recomputed from x exactly as bn_apply computed it
+                 float* __restrict__ atomic_s1 = nullptr, float* __restrict__ atomic_s2 = nullptr,
+                 const uint8_t* __restrict__ mask = nullptr) {
+  // relu: 0 = no activation, 1 = mask from the stored output y, 2 = mask recomputed from x exactly as bn_apply computed it,
+  //       3 = mask from the bit mask bn_apply wrote (one byte per 16-byte bf16 vector)
   constexpr int V = Vec16<T>::N;
   __shared__ float red[2][kThreads * V];
   const int tcg = threadIdx.x % cgb, trow = threadIdx.x / cgb;
@@ -79,6 +81,7 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
       constexpr int U = 4;
       for (int64_t r = r0 + trow; r < r1; r += (int64_t)rows_par * U) {
         Vec16<T> vx[U], vg[U], vy[U];
+        uint32_t mb[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
           const int64_t rr = r + (int64_t)u * rows_par;
@@ -88,6 +91,7 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
             if (MODE == 1) {
               vg[u].load(dy + off);
               if (relu == 1) vy[u].load(y + off);
+              if (relu == 3) mb[u] = mask[(size_t)rr * cg + g];
             }
           }
         }
@@ -111,6 +115,9 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
             } else if (relu == 2) {
 #pragma unroll
               for (int i = 0; i < V; ++i) gv[i] = fmaf(xv[i], msc[i], msh[i]) > 0.f ? gv[i] : 0.f;
+            } else if (relu == 3) {
+#pragma unroll
+              for (int i = 0; i < V; ++i) gv[i] = ((mb[u] >> i) & 1u) ? gv[i] : 0.f;
             }
 #pragma unroll
             for (int i = 0; i < V; ++i) { a1[i] += gv[i]; a2[i] = fmaf(gv[i], (xv[i] - k0[i]) * k1[i], a2[i]); }
@@ -234,7 +241,7 @@ template <typename T, bool FIXED>
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, const float* __restrict__ gamma,
                 const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
-                int64_t nvec, int C, int relu, int eval_mode, float eps) {
+                int64_t nvec, int C, int relu, int eval_mode, float eps, uint8_t* __restrict__ mask) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -267,6 +274,7 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
       float xv[V], rv[V], out[V];
       vx[u].unpack(xv);
       if (res != nullptr) vr[u].unpack(rv);
+      uint32_t bits = 0;
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         float v = fmaf(xv[j], sc[j], sh[j]);
@@ -275,6 +283,13 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
         out[j] = v;
       }
       Vec16<T> vo; vo.pack(out); vo.store(y + k * V);
+      if (mask != nullptr) {  // the sign of the ROUNDED output, i.e. exactly what `y > 0` reads back
+        float ov[V];
+        vo.unpack(ov);
+#pragma unroll
+        for (int j = 0; j < V; ++j) bits |= (ov[j] > 0.f ? 1u : 0u) << j;
+        mask[k] = (uint8_t)bits;
+      }
     }
   }
 }
@@ -284,7 +299,8 @@ __global__ void __launch_bounds__(kThreads)
 bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
                     T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ dgamma,
-                    const float* __restrict__ dbeta, int64_t nvec, int C, int relu, float inv_m) {
+                    const float* __restrict__ dbeta, int64_t nvec, int C, int relu, float inv_m,
+                    const uint8_t* __restrict__ mask) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -309,6 +325,7 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
   constexpr int U = 2;
   for (int64_t i = i0; i < nvec; i += stride * U) {
     Vec16<T> vx[U], vg[U], vy[U];
+    uint32_t mb[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t k = i + u * stride;
@@ -316,6 +333,7 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
         vx[u].load(x + k * V);
         vg[u].load(dy + k * V);
         if (relu == 1) vy[u].load(y + k * V);
+        if (relu == 3) mb[u] = mask[k];
       }
     }
 #pragma unroll
@@ -334,6 +352,9 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
       } else if (relu == 2) {
 #pragma unroll
         for (int j = 0; j < V; ++j) gv[j] = fmaf(xv[j], msc[j], msh[j]) > 0.f ? gv[j] : 0.f;
+      } else if (relu == 3) {
+#pragma unroll
+        for (int j = 0; j < V; ++j) gv[j] = ((mb[u] >> j) & 1u) ? gv[j] : 0.f;
       }
 #pragma unroll
       for (int j = 0; j < V; ++j) out[j] = fmaf(k1[j], gv[j], -fmaf(k2[j], xv[j] - mu[j], k3[j]));
@@ -400,12 +421,14 @@ static int apply_t(const dv_bn_params* p, cudaStream_t st) {
   const float* is = p->eval_mode ? p->running_var : p->save_invstd;
   DV_REQUIRE(mean && is, DV_ERR_ARG, "bn_apply: statistics pointers are null");
   const unsigned grid = stream_grid(ceil_div64(nvec, kUnroll));
+  DV_REQUIRE(p->relu_mask == nullptr || (V == 8 && p->relu), DV_ERR_UNSUPPORTED, "bn_apply: relu_mask needs bf16 and relu == 1");
+  uint8_t* mask = (uint8_t*)p->relu_mask;
   if (kThreads % (p->C / V) == 0)
     bn_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
-                                                       p->C, p->relu, p->eval_mode, p->eps);
+                                                       p->C, p->relu, p->eval_mode, p->eps, mask);
   else
     bn_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
-                                                        p->C, p->relu, p->eval_mode, p->eps);
+                                                        p->C, p->relu, p->eval_mode, p->eps, mask);
   DV_LAUNCH_OK("bn_apply_kernel");
   return DV_OK;
 }
@@ -418,12 +441,13 @@ static int bwd_reduce_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   const size_t need = p->atomic_sums ? 0 : (size_t)pl.nblk * 2 * p->C * sizeof(float);
   DV_REQUIRE(need == 0 || (p->workspace && p->workspace_bytes >= need), DV_ERR_WORKSPACE,
              "bn_bwd_reduce: workspace %zu bytes required, %zu given", need, p->workspace_bytes);
-  DV_REQUIRE(!p->relu || p->y || p->beta, DV_ERR_ARG, "bn_bwd_reduce: relu needs y (stored mask) or beta (recomputed mask)");
-  const int relu_mode = !p->relu ? 0 : (p->y ? 1 : 2);
+  DV_REQUIRE(!p->relu || p->y || p->beta || p->relu_mask, DV_ERR_ARG, "bn_bwd_reduce: relu needs relu_mask, y (stored mask) or beta (recomputed mask)");
+  DV_REQUIRE(p->relu_mask == nullptr || V == 8, DV_ERR_UNSUPPORTED, "bn_bwd_reduce: relu_mask needs bf16");
+  const int relu_mode = !p->relu ? 0 : (p->relu_mask ? 3 : (p->y ? 1 : 2));
   bn_reduce_kernel<T, 1><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, p->save_mean, p->save_invstd,
                                                       p->gamma, p->beta, (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par,
                                                       pl.rows_per_blk, relu_mode, p->atomic_sums ? p->dbeta : nullptr,
-                                                      p->atomic_sums ? p->dgamma : nullptr);
+                                                      p->atomic_sums ? p->dgamma : nullptr, (const uint8_t*)p->relu_mask);
   DV_LAUNCH_OK("bn_reduce_kernel<bwd>");
   if (p->atomic_sums) return DV_OK;  // dbeta += sum(dz), dgamma += sum(dz*xhat) were accumulated in place
   bn_bwd_finalize_kernel<<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const float*)p->workspace, pl.nblk, p->C, p->dgamma, p->dbeta);
@@ -435,18 +459,19 @@ template <typename T>
 static int bwd_apply_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
-  DV_REQUIRE(!p->relu || p->y || p->beta, DV_ERR_ARG, "bn_bwd_apply: relu needs y (stored mask) or beta (recomputed mask)");
-  const int relu_mode = !p->relu ? 0 : (p->y ? 1 : 2);
+  DV_REQUIRE(!p->relu || p->y || p->beta || p->relu_mask, DV_ERR_ARG, "bn_bwd_apply: relu needs relu_mask, y (stored mask) or beta (recomputed mask)");
+  DV_REQUIRE(p->relu_mask == nullptr || V == 8, DV_ERR_UNSUPPORTED, "bn_bwd_apply: relu_mask needs bf16");
+  const int relu_mode = !p->relu ? 0 : (p->relu_mask ? 3 : (p->y ? 1 : 2));
   const int64_t nvec = p->M * p->C / V;
   const unsigned grid = stream_grid(ceil_div64(nvec, 2));
   if (kThreads % (p->C / V) == 0)
     bn_bwd_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
                                                            p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
-                                                           relu_mode, 1.0f / (float)p->M);
+                                                           relu_mode, 1.0f / (float)p->M, (const uint8_t*)p->relu_mask);
   else
     bn_bwd_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
                                                             p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
-                                                            relu_mode, 1.0f / (float)p->M);
+                                                            relu_mode, 1.0f / (float)p->M, (const uint8_t*)p->relu_mask);
   DV_LAUNCH_OK("bn_bwd_apply_kernel");
   return DV_OK;
 }

@@ -17,83 +17,121 @@ static unsigned grid_for(int64_t n) {
 
 // ---- max-pool 3x3 stride 2 pad 1 (resnet50.py:34).  Padding behaves as -inf; ties keep the first position in
 //      row-major window order, as torch's kernel does (strict '>' update). ---------------------------------------
+// Forward: one thread = one 16-byte channel vector of TWO horizontally adjacent outputs.  Their windows share a column,
+// so the 3x5 input patch is loaded once (15 independent 16-byte loads issued before any compare) instead of 2x9.
 template <typename T>
-__global__ void maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ idx, int N, int H, int W, int C,
-                                   int P, int Q) {
+__global__ void __launch_bounds__(256)
+maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ idx, int N, int H, int W, int C, int P, int Q) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
-  const int total = N * P * Q * cg;  // < 2^31, checked by the caller
+  const int Q2 = (Q + 1) >> 1;
+  const int total = N * P * Q2 * cg;  // < 2^31, checked by the caller
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int c = (i % cg) * V;
     int pix = i / cg;
-    const int q = pix % Q; pix /= Q;
+    const int q0 = (pix % Q2) * 2; pix /= Q2;
     const int p = pix % P;
     const int n = pix / P;
-    float best[V];
-    __align__(8) uint8_t bi[V];
-#pragma unroll
-    for (int j = 0; j < V; ++j) { best[j] = -CUDART_INF_F; bi[j] = 0; }
-    bool first = true;
+    Vec16<T> in[3][5];
+    bool ok[3][5];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
       const int h = p * 2 + r - 1;
-      if ((unsigned)h >= (unsigned)H) continue;
 #pragma unroll
-      for (int s = 0; s < 3; ++s) {
-        const int w = q * 2 + s - 1;
-        if ((unsigned)w >= (unsigned)W) continue;
-        float v[V];
-        Vec16<T> a; a.load(x + (((size_t)n * H + h) * W + w) * C + c); a.unpack(v);
-#pragma unroll
-        for (int j = 0; j < V; ++j) {
-          if (first || v[j] > best[j]) { best[j] = v[j]; bi[j] = (uint8_t)(r * 3 + s); }
-        }
-        first = false;
+      for (int s = 0; s < 5; ++s) {
+        const int w = q0 * 2 + s - 1;
+        ok[r][s] = (unsigned)h < (unsigned)H && (unsigned)w < (unsigned)W;
+        if (ok[r][s]) in[r][s].load(x + (((size_t)n * H + h) * W + w) * C + c);
       }
     }
-    const size_t o = (size_t)(i / cg) * C + c;
-    Vec16<T> out; out.pack(best); out.store(y + o);
-    if (V == 8) *reinterpret_cast<uint2*>(idx + o) = *reinterpret_cast<const uint2*>(bi);   // o is a multiple of V
-    else *reinterpret_cast<uint32_t*>(idx + o) = *reinterpret_cast<const uint32_t*>(bi);
+#pragma unroll
+    for (int o = 0; o < 2; ++o) {
+      const int q = q0 + o;
+      if (q >= Q) break;
+      float best[V];
+      __align__(8) uint8_t bi[V];
+#pragma unroll
+      for (int j = 0; j < V; ++j) { best[j] = -CUDART_INF_F; bi[j] = 0; }
+      bool first = true;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+          if (!ok[r][2 * o + s]) continue;
+          float v[V];
+          in[r][2 * o + s].unpack(v);
+#pragma unroll
+          for (int j = 0; j < V; ++j) {
+            if (first || v[j] > best[j]) { best[j] = v[j]; bi[j] = (uint8_t)(r * 3 + s); }
+          }
+          first = false;
+        }
+      }
+      const size_t off = (((size_t)n * P + p) * Q + q) * C + c;
+      Vec16<T> out; out.pack(best); out.store(y + off);
+      if (V == 8) *reinterpret_cast<uint2*>(idx + off) = *reinterpret_cast<const uint2*>(bi);   // off is a multiple of V
+      else *reinterpret_cast<uint32_t*>(idx + off) = *reinterpret_cast<const uint32_t*>(bi);
+    }
   }
 }
 
+// Backward: one thread = one channel vector of a 2x2 input cell {2p, 2p+1} x {2q, 2q+1}.  The cell is covered by the four
+// windows (p..p+1, q..q+1) only, so 4 gradient + 4 index loads (all independent) produce 4 outputs; a thread per input
+// element would load 2.25 windows per output through data-dependent loops.
 template <typename T>
-__global__ void maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ idx, T* __restrict__ dx, int N, int H, int W,
-                                   int C, int P, int Q) {
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ idx, T* __restrict__ dx, int N, int H, int W, int C, int P, int Q) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
-  const int total = N * H * W * cg;  // < 2^31, checked by the caller
+  const int H2 = (H + 1) >> 1, W2 = (W + 1) >> 1;
+  const int total = N * H2 * W2 * cg;  // < 2^31, checked by the caller
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int c = (i % cg) * V;
     int pix = i / cg;
-    const int w = pix % W; pix /= W;
-    const int h = pix % H;
-    const int n = pix / H;
-    float acc[V];
+    const int q = pix % W2; pix /= W2;
+    const int p = pix % H2;
+    const int n = pix / H2;
+    float g[2][2][V];
+    __align__(8) uint8_t ti[2][2][V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) acc[j] = 0.f;
-    // windows (p,q) whose 3x3 footprint [2p-1, 2p+1] contains h (resp. w)
-    const int plo = h >> 1, phi = (h + 1) >> 1;
-    const int qlo = w >> 1, qhi = (w + 1) >> 1;
-    for (int p = plo; p <= phi; ++p) {
-      if (p >= P) continue;
-      const int r = h - (2 * p - 1);
-      for (int q = qlo; q <= qhi; ++q) {
-        if (q >= Q) continue;
-        const int s = w - (2 * q - 1);
-        const uint8_t tap = (uint8_t)(r * 3 + s);
-        const size_t o = (((size_t)n * P + p) * Q + q) * C + c;
-        float g[V];
-        Vec16<T> a; a.load(dy + o); a.unpack(g);
-        __align__(8) uint8_t ti[V];
-        if (V == 8) *reinterpret_cast<uint2*>(ti) = *reinterpret_cast<const uint2*>(idx + o);
-        else *reinterpret_cast<uint32_t*>(ti) = *reinterpret_cast<const uint32_t*>(idx + o);
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int j = 0; j < V; ++j) acc[j] += (ti[j] == tap) ? g[j] : 0.f;
+      for (int b = 0; b < 2; ++b) {
+        const bool ok = (p + a) < P && (q + b) < Q;
+        if (ok) {
+          const size_t o = (((size_t)n * P + p + a) * Q + q + b) * C + c;
+          Vec16<T> v; v.load(dy + o); v.unpack(g[a][b]);
+          if (V == 8) *reinterpret_cast<uint2*>(ti[a][b]) = *reinterpret_cast<const uint2*>(idx + o);
+          else *reinterpret_cast<uint32_t*>(ti[a][b]) = *reinterpret_cast<const uint32_t*>(idx + o);
+        } else {
+#pragma unroll
+          for (int j = 0; j < V; ++j) { g[a][b][j] = 0.f; ti[a][b][j] = 255; }
+        }
+      }
+    // input (2p+dh, 2q+dw) sits at tap (r,s) = (dh+1-2a, dw+1-2b) of window (p+a, q+b): dh=0 -> a=0 only (r=1);
+    // dh=1 -> a=0 (r=2) and a=1 (r=0); same along w.
+#pragma unroll
+    for (int dh = 0; dh < 2; ++dh) {
+      const int h = 2 * p + dh;
+      if (h >= H) break;
+#pragma unroll
+      for (int dw = 0; dw < 2; ++dw) {
+        const int w = 2 * q + dw;
+        if (w >= W) break;
+        float acc[V];
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int a = 0; a <= dh; ++a)
+#pragma unroll
+          for (int b = 0; b <= dw; ++b) {
+            const uint8_t tap = (uint8_t)((dh + 1 - 2 * a) * 3 + (dw + 1 - 2 * b));
+#pragma unroll
+            for (int j = 0; j < V; ++j) acc[j] += (ti[a][b][j] == tap) ? g[a][b][j] : 0.f;
+          }
+        Vec16<T> out; out.pack(acc); out.store(dx + (((size_t)n * H + h) * W + w) * C + c);
       }
     }
-    Vec16<T> out; out.pack(acc); out.store(dx + (size_t)(i / cg) * C + c);
   }
 }
 
@@ -331,7 +369,7 @@ extern "C" int dv_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H
   int rc = vec_ok(C, dtype, "dv_maxpool_fwd");
   if (rc) return rc;
   const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
-  const int64_t total = (int64_t)N * P * Q * (C / (dtype == DV_BF16 ? 8 : 4));
+  const int64_t total = (int64_t)N * P * ((Q + 1) / 2) * (C / (dtype == DV_BF16 ? 8 : 4));  // two outputs per thread
   DV_REQUIRE((int64_t)N * H * W * C < (1LL << 31), DV_ERR_UNSUPPORTED, "dv_maxpool_fwd: tensor exceeds 2^31 elements");
   cudaStream_t st = (cudaStream_t)stream;
   DV_DISPATCH_T(dtype, (maxpool_fwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, idx, N, H, W, C, P, Q)),
@@ -344,7 +382,7 @@ extern "C" int dv_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int 
   int rc = vec_ok(C, dtype, "dv_maxpool_bwd");
   if (rc) return rc;
   const int P = (H + 2 - 3) / 2 + 1, Q = (W + 2 - 3) / 2 + 1;
-  const int64_t total = (int64_t)N * H * W * (C / (dtype == DV_BF16 ? 8 : 4));
+  const int64_t total = (int64_t)N * ((H + 1) / 2) * ((W + 1) / 2) * (C / (dtype == DV_BF16 ? 8 : 4));  // a 2x2 cell per thread
   DV_REQUIRE((int64_t)N * H * W * C < (1LL << 31), DV_ERR_UNSUPPORTED, "dv_maxpool_bwd: tensor exceeds 2^31 elements");
   cudaStream_t st = (cudaStream_t)stream;
   DV_DISPATCH_T(dtype, (maxpool_bwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)dy, idx, (bf16*)dx, N, H, W, C, P, Q)),

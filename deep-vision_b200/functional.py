@@ -409,12 +409,19 @@ class _BatchNormAct(torch.autograd.Function):
         else:
             save_mean = save_invstd = None
             p.eval_mode = 1
+        # ReLU after a residual add: the sign cannot be recomputed from x alone, so the forward leaves one bit per element
+        # for the backward (bf16) instead of making both backward passes re-read the 16-bit output
+        mask = None
+        if relu and residual is not None and use_batch_stats and x.dtype == torch.bfloat16 and any(ctx.needs_input_grad[:4]):
+            mask = torch.empty((M, Cc // 8), dtype=torch.uint8, device=x.device)
+            p.relu_mask = mask.data_ptr()
         check(lib.dv_bn_apply(C.byref(p), _stream()), "dv_bn_apply")
         ctx.batch_stats = use_batch_stats
         ctx.relu = bool(relu)
         ctx.has_res = residual is not None
         # the ReLU mask: without a residual it is recomputed bit-exactly from x in backward (y need not be kept or re-read)
-        keep_y = y if (relu and residual is not None) else None
+        keep_y = (mask if mask is not None else y) if (relu and residual is not None) else None
+        ctx.bit_mask = mask is not None
         if use_batch_stats:
             ctx.save_for_backward(x, keep_y, gamma, save_mean, save_invstd, beta)
         else:
@@ -441,7 +448,11 @@ class _BatchNormAct(torch.autograd.Function):
         dbeta = sb[0] if sb else mk(Cc, dtype=torch.float32, device=x.device)
         p = BnBwdParams()
         p.atomic_sums = atomic
-        p.x, p.y, p.dy, p.dx = x.data_ptr(), (y.data_ptr() if y is not None else None), dy.data_ptr(), dx.data_ptr()
+        p.x, p.dy, p.dx = x.data_ptr(), dy.data_ptr(), dx.data_ptr()
+        if ctx.bit_mask:
+            p.relu_mask = y.data_ptr()
+        else:
+            p.y = y.data_ptr() if y is not None else None
         p.dres = dres.data_ptr() if dres is not None else None
         p.gamma, p.beta, p.save_mean, p.save_invstd = gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), second.data_ptr()
         p.dgamma, p.dbeta = dgamma.data_ptr(), dbeta.data_ptr()

@@ -159,6 +159,9 @@ typedef struct dv_bn_params {
   int32_t relu;         /* 1 = fuse ReLU */
   int32_t eval_mode;    /* apply only: 1 = normalise with running_mean/var instead of save_* */
   float eps, momentum;
+  void* relu_mask;      /* optional (bf16 only): uint8 [M][C/8] written by dv_bn_apply when relu == 1; bit j of byte
+                           (m, c/8) = (y[m][c+j] > 0).  Lets the backward of a RESIDUAL block read 1 bit instead of 16 per
+                           element for the ReLU mask (see dv_bn_bwd_params.relu_mask) */
 } dv_bn_params;
 
 /* batch statistics (mean, biased var -> invstd) + running-stat update */
@@ -215,6 +218,8 @@ typedef struct dv_bn_bwd_params {
   int32_t atomic_sums;  /* bwd_reduce: 1 = block sums are ADDED into dgamma/dbeta with fp32 atomics (the caller zeroed them):
                            no workspace, no finalize launch, run-to-run summation order.  0 = partials + fixed-order
                            finalize (bit-reproducible) */
+  const void* relu_mask; /* optional (bf16 only): the bit mask dv_bn_apply wrote; when set (and relu == 1) it is used
+                           instead of y, which is then not read by either backward pass */
 } dv_bn_bwd_params;
 
 /* dgamma, dbeta (with the ReLU mask recomputed from y) */

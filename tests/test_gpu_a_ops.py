@@ -192,6 +192,25 @@ def test_bn_forward_backward_matches_oracle(shape, residual, relu, dtype):
         torch.cuda.synchronize()
         assert torch.equal(dxd, dx1) and torch.equal(dg, dg1) and torch.equal(db, db1)
         q.y = yd.data_ptr()
+    if relu and dtype == torch.bfloat16:
+        # one-bit-per-element mask written by the forward: equals (y > 0) and reproduces the stored-mask backward bit for bit
+        mk = torch.full((M, Cc // 8), 0xAA, device="cuda", dtype=torch.uint8)
+        p.relu_mask = mk.data_ptr()
+        lib.check(lib.lib.dv_bn_apply(C.byref(p), stream_ptr()), "dv_bn_apply(mask)")
+        torch.cuda.synchronize()
+        bits = np.unpackbits(mk.cpu().numpy().reshape(N, H, W, Cc // 8, 1), axis=-1, bitorder="little").reshape(N, H, W, Cc)
+        assert np.array_equal(bits.astype(bool), yd.float().cpu().numpy() > 0)
+        dx1, dg1, db1 = dxd.clone(), dg.clone(), db.clone()
+        dr1 = drd.clone() if residual else None
+        dxd.fill_(float("nan"))
+        q.y, q.relu_mask = None, mk.data_ptr()
+        lib.check(lib.lib.dv_bn_bwd_reduce(C.byref(q), stream_ptr()), "dv_bn_bwd_reduce(bit mask)")
+        lib.check(lib.lib.dv_bn_bwd_apply(C.byref(q), stream_ptr()), "dv_bn_bwd_apply(bit mask)")
+        torch.cuda.synchronize()
+        assert torch.equal(dxd, dx1) and torch.equal(dg, dg1) and torch.equal(db, db1)
+        if residual:
+            assert torch.equal(drd, dr1)
+        q.y, q.relu_mask, p.relu_mask = yd.data_ptr(), None, None
 
     # eval mode uses the running statistics
     p.eval_mode = 1
@@ -239,6 +258,30 @@ def test_dwconv_matches_oracle(case, dtype):
     torch.cuda.synchronize()
     assert rel_l2(np.transpose(dxd.double().cpu().numpy(), (0, 3, 1, 2)), dx_ref) < tol
     assert rel_l2(dwd.double().cpu().numpy(), dw_ref) < 1e-4
+
+
+@pytest.mark.parametrize("hw", [(12, 8), (7, 7), (1, 5), (2, 2)], ids=lambda v: f"{v[0]}x{v[1]}")
+def test_maxpool_even_odd_and_tiny_extents(hw):
+    """The kernels work on pairs of outputs (forward) and 2x2 input cells (backward): cover even, odd and 1-wide extents."""
+    lib = _lib()
+    dtype = torch.bfloat16
+    N, Cc = 2, 16
+    H, W = hw
+    x = ref_ops.relu(_rand((N, Cc, H, W), 41, dtype))
+    y_ref, tap = ref_ops.max_pool_3x3_s2_p1(x)
+    P, Q = y_ref.shape[2:]
+    xd = _dev(np.transpose(x, (0, 2, 3, 1)), dtype)
+    yd = torch.full((N, P, Q, Cc), float("nan"), device="cuda", dtype=dtype)
+    idx = torch.full((N, P, Q, Cc), 99, device="cuda", dtype=torch.uint8)
+    lib.check(lib.lib.dv_maxpool_fwd(xd.data_ptr(), yd.data_ptr(), idx.data_ptr(), N, H, W, Cc, _dv(dtype), stream_ptr()), "maxpool_fwd")
+    dy = _rand(y_ref.shape, 42, dtype)
+    dyd = _dev(np.transpose(dy, (0, 2, 3, 1)), dtype)
+    dxd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_maxpool_bwd(dyd.data_ptr(), idx.data_ptr(), dxd.data_ptr(), N, H, W, Cc, _dv(dtype), stream_ptr()), "maxpool_bwd")
+    torch.cuda.synchronize()
+    assert np.array_equal(np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2)), y_ref)
+    assert np.array_equal(np.transpose(idx.cpu().numpy(), (0, 3, 1, 2)), tap)
+    assert rel_l2(np.transpose(dxd.double().cpu().numpy(), (0, 3, 1, 2)), ref_ops.max_pool_backward(dy, tap, H, W)) < TOL[dtype]
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])

@@ -15,36 +15,48 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--which", default="fprop")
 ap.add_argument("--iters", type=int, default=5)
 ap.add_argument("--shape", default="256,14,256,256,3", help="N,H,C,K,R (stride 1, pad R//2)")
+ap.add_argument("--jobs", default="", help="several kernels in one process: 'fprop:256,14,256,256,3;wgrad_acc:256,56,64,256,1'")
 args = ap.parse_args()
 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-N, H, Cc, K, R = (int(v) for v in args.shape.split(","))
-x = torch.randn(N, H, H, Cc, device="cuda").to(torch.bfloat16)
-w = (torch.randn(K, R, R, Cc, device="cuda") * 0.05).to(torch.bfloat16)
-y = torch.empty(N, H, H, K, device="cuda", dtype=torch.bfloat16)
-p = ConvParams()
-p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, H, Cc, K, R, R, 1, R // 2, DV_BF16, DV_ALGO_TC
-if args.which == "fprop":
-    p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
-    fn = lambda: check(lib.dv_conv_fprop(C.byref(p), st), "fprop")
-elif args.which == "wgrad":
-    dw = torch.empty(K, R, R, Cc, device="cuda")
-    p.x, p.w, p.y = x.data_ptr(), dw.data_ptr(), y.normal_().data_ptr()
-    need = lib.dv_conv_workspace_bytes(C.byref(p), DV_CONV_WGRAD)
-    ws = torch.empty(need, dtype=torch.uint8, device="cuda")
-    p.workspace, p.workspace_bytes = ws.data_ptr(), need
-    fn = lambda: check(lib.dv_conv_wgrad(C.byref(p), st), "wgrad")
+
+
+def run_job(which, shape, iters):
+    N, H, Cc, K, R = (int(v) for v in shape.split(","))
+    x = torch.randn(N, H, H, Cc, device="cuda").to(torch.bfloat16)
+    w = (torch.randn(K, R, R, Cc, device="cuda") * 0.05).to(torch.bfloat16)
+    y = torch.empty(N, H, H, K, device="cuda", dtype=torch.bfloat16)
+    p = ConvParams()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, H, Cc, K, R, R, 1, R // 2, DV_BF16, DV_ALGO_TC
+    if which == "fprop":
+        p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
+        fn = lambda: check(lib.dv_conv_fprop(C.byref(p), st), "fprop")
+    elif which in ("wgrad", "wgrad_acc"):
+        dw = torch.zeros(K, R, R, Cc, device="cuda")
+        p.accumulate = 1 if which == "wgrad_acc" else 0
+        p.x, p.w, p.y = x.data_ptr(), dw.data_ptr(), y.normal_().data_ptr()
+        need = lib.dv_conv_workspace_bytes(C.byref(p), DV_CONV_WGRAD)
+        ws = torch.empty(need, dtype=torch.uint8, device="cuda")
+        p.workspace, p.workspace_bytes = ws.data_ptr(), need
+        fn = lambda: check(lib.dv_conv_wgrad(C.byref(p), st), "wgrad")
+    else:
+        M, Cb = 256 * 56 * 56, 256
+        xb = torch.randn(M, Cb, device="cuda").to(torch.bfloat16)
+        yb = torch.empty_like(xb)
+        v = [torch.ones(Cb, device="cuda") for _ in range(6)]
+        q = BnParams()
+        q.x, q.y, q.gamma, q.beta, q.running_mean, q.running_var, q.save_mean, q.save_invstd = [t.data_ptr() for t in [xb, yb] + v]
+        wsz = lib.dv_bn_workspace_bytes(M, Cb)
+        ws = torch.empty(wsz, dtype=torch.uint8, device="cuda")
+        q.workspace, q.workspace_bytes, q.M, q.C, q.dtype, q.relu, q.eps, q.momentum = ws.data_ptr(), wsz, M, Cb, DV_BF16, 1, 1e-5, 0.1
+        fn = (lambda: check(lib.dv_bn_apply(C.byref(q), st), "apply")) if which == "bn_apply" else (lambda: check(lib.dv_bn_stats(C.byref(q), st), "stats"))
+    for _ in range(iters):
+        fn()
+    torch.cuda.synchronize()
+    print("ok", which)
+
+
+if args.jobs:
+    for job in args.jobs.split(";"):
+        run_job(*job.split(":"), args.iters)
 else:
-    M, Cb = 256 * 56 * 56, 256
-    xb = torch.randn(M, Cb, device="cuda").to(torch.bfloat16)
-    yb = torch.empty_like(xb)
-    v = [torch.ones(Cb, device="cuda") for _ in range(6)]
-    q = BnParams()
-    q.x, q.y, q.gamma, q.beta, q.running_mean, q.running_var, q.save_mean, q.save_invstd = [t.data_ptr() for t in [xb, yb] + v]
-    wsz = lib.dv_bn_workspace_bytes(M, Cb)
-    ws = torch.empty(wsz, dtype=torch.uint8, device="cuda")
-    q.workspace, q.workspace_bytes, q.M, q.C, q.dtype, q.relu, q.eps, q.momentum = ws.data_ptr(), wsz, M, Cb, DV_BF16, 1, 1e-5, 0.1
-    fn = (lambda: check(lib.dv_bn_apply(C.byref(q), st), "apply")) if args.which == "bn_apply" else (lambda: check(lib.dv_bn_stats(C.byref(q), st), "stats"))
-for _ in range(args.iters):
-    fn()
-torch.cuda.synchronize()
-print("ok", args.which)
+    run_job(args.which, args.shape, args.iters)
