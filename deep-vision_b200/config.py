@@ -7,7 +7,8 @@ _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
           "fuse_bn_stats": os.environ.get("DV_FUSE_STATS", "1") != "0",
           "deterministic": os.environ.get("DV_DETERMINISTIC", "0") == "1",
           "atomic_wgrad": os.environ.get("DV_ATOMIC_WGRAD", "1") == "1",
-          "atomic_bn_bwd": os.environ.get("DV_ATOMIC_BN", "0") == "1"}
+          "atomic_bn_bwd": os.environ.get("DV_ATOMIC_BN", "0") == "1",
+          "fold_bn": os.environ.get("DV_FOLD_BN", "1") != "0"}
 
 
 def compute_dtype():
@@ -72,3 +73,14 @@ def atomic_wgrad():
 def atomic_bn_bwd():
     """Add BN-backward block sums straight into dgamma/dbeta with fp32 atomics instead of partials + a finalize pass."""
     return _state["atomic_bn_bwd"] and not _state["deterministic"]
+
+
+def fold_bn():
+    return _state["fold_bn"]
+
+
+def set_fold_bn(flag):
+    """True (default): under net.eval() + torch.no_grad() in bf16, each conv -> BatchNorm (-> +identity) (-> ReLU) group of
+    the models runs as ONE kernel: the convolution with the BN folded into its epilogue (inference.py).  False: eval-mode
+    BN stays a separate normalise pass."""
+    _state["fold_bn"] = bool(flag)

@@ -52,7 +52,11 @@ static int run_conv(const dv_conv_params* p, int pass, void* stream, const char*
   int rc = check_conv(p, who);
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  return resolve_algo(p, pass) == DV_ALGO_TC ? conv_tc(p, pass, st) : conv_simt(p, pass, st);
+  const int algo = resolve_algo(p, pass);
+  const bool folded = p->ep_scale || p->ep_shift || p->ep_residual || p->ep_relu;
+  DV_REQUIRE(!folded || (pass == DV_CONV_FPROP && algo == DV_ALGO_TC), DV_ERR_UNSUPPORTED,
+             "%s: the folded-BatchNorm epilogue (ep_*) exists on the tensor-core fprop path only", who);
+  return algo == DV_ALGO_TC ? conv_tc(p, pass, st) : conv_simt(p, pass, st);
 }
 
 }  // namespace dv

@@ -610,3 +610,32 @@ extern "C" int dv_bn_stats_static(const dv_bn_params* p, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   return p->dtype == DV_BF16 ? stats_static_t<bf16>(p, st) : stats_static_t<float>(p, st);
 }
+
+// ---- eval-mode BatchNorm folded into the preceding convolution (dv_conv_params.ep_*, dv_dwconv_params.ep_shift) -----------
+namespace dv {
+namespace {
+__global__ void bn_fold_kernel(const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
+                               const float* __restrict__ var, float eps, float* __restrict__ scale, float* __restrict__ shift, int C,
+                               const float* __restrict__ dw_in, float* __restrict__ dw_out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float sc = gamma[c] * rsqrtf(var[c] + eps);  // the expressions of bn_apply_kernel's eval mode
+  scale[c] = sc;
+  shift[c] = beta[c] - mean[c] * sc;
+  if (dw_in != nullptr) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t) dw_out[c * 9 + t] = dw_in[c * 9 + t] * sc;
+  }
+}
+}  // namespace
+}  // namespace dv
+
+extern "C" int dv_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var, float eps,
+                          float* scale, float* shift, int C, const float* dw_w, float* dw_w_scaled, void* stream) {
+  DV_REQUIRE(gamma && beta && running_mean && running_var && scale && shift && C > 0, DV_ERR_ARG, "dv_bn_fold: bad arguments");
+  DV_REQUIRE((dw_w == nullptr) == (dw_w_scaled == nullptr), DV_ERR_ARG, "dv_bn_fold: dw_w and dw_w_scaled go together");
+  dv::bn_fold_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var, eps, scale, shift, C, dw_w,
+                                                                       dw_w_scaled);
+  DV_LAUNCH_OK("bn_fold_kernel");
+  return DV_OK;
+}

@@ -260,7 +260,44 @@ struct GemmArgs {
   int out_f32;      // 1: `out` is float* (fp32 logits of the classifier)
   int accumulate;   // 1: out += result (bf16 read-modify-write by the owning thread)
   float* stat_sums; // fprop, optional: [2][Nout] fp32, += per-channel sum and sum of squares of the bf16-rounded output
+  // fprop, optional (inference with BatchNorm folded away): out = relu(acc * ep_scale[n] + ep_shift[n] + ep_res[m][n])
+  const float* ep_scale;
+  const float* ep_shift;
+  const bf16* ep_res;
+  int ep_relu;
 };
+
+// Folded-BatchNorm epilogue on the 32 accumulator columns [col0, col0+32) of the output row held by one lane.  The identity
+// tile was brought into the warp's staging buffer by TMA in the layout the result is written back in ([32 rows][128 B],
+// 16-byte chunks XOR-swizzled by row), so a lane finds its row's residual exactly where its result will go: `res_row` is the
+// shared address of the lane's row (0 = no residual), `chunk0` the first of the four 16-byte chunks these columns occupy.
+__device__ __forceinline__ void apply_folded_epilogue(uint32_t* v, const GemmArgs& g, int col0, uint32_t res_row, int chunk0, int lane) {
+  if (col0 >= g.Nout) return;  // Nout is a multiple of 8 and col0 of 32: a partial group ends on an 8-column boundary
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (col0 + j * 8 >= g.Nout) break;
+    const float4 sa = __ldg(reinterpret_cast<const float4*>(g.ep_scale + col0 + j * 8));
+    const float4 sb = __ldg(reinterpret_cast<const float4*>(g.ep_scale + col0 + j * 8 + 4));
+    const float4 ha = __ldg(reinterpret_cast<const float4*>(g.ep_shift + col0 + j * 8));
+    const float4 hb = __ldg(reinterpret_cast<const float4*>(g.ep_shift + col0 + j * 8 + 4));
+    const float sc[8] = {sa.x, sa.y, sa.z, sa.w, sb.x, sb.y, sb.z, sb.w};
+    const float sh[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+    float r[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (res_row != 0) {
+      uint32_t w[4];
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
+                   : "r"(res_row + (uint32_t)(((chunk0 + j) ^ (lane & 7)) * 16)));
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { r[2 * e] = __uint_as_float(w[e] << 16); r[2 * e + 1] = __uint_as_float(w[e] & 0xffff0000u); }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float y = fmaf(__uint_as_float(v[j * 8 + e]), sc[e], sh[e]) + r[e];
+      if (g.ep_relu) y = fmaxf(y, 0.f);
+      v[j * 8 + e] = __float_as_uint(y);
+    }
+  }
+}
 
 // ------------------------------------------------------------------------------------------------------------
 // GEMM-shaped kernel (fprop / dgrad), persistent: one CTA per SM slot walks output tiles (n fastest, so CTAs running side by side share the same
@@ -278,7 +315,7 @@ struct GemmArgs {
 template <int BN, int STAGES, bool STATS, bool B_MN>
 __global__ void __launch_bounds__(kThreads)
 conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                               const __grid_constant__ CUtensorMap tmO, const GemmArgs g) {
+                               const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
   constexpr int ACC = 2;
   constexpr int kBBytes = BN * kBlockK * 2;
   constexpr int kStageBytes = kABytes + kBBytes;
@@ -297,7 +334,8 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + ACC);
+  uint64_t* res_bar = tempty_bar + ACC;  // one per epilogue warp: the identity tile of a folded-BN epilogue has landed
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 4);
 
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const int num_n = (g.Nout + BN - 1) / BN;
@@ -317,6 +355,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
       mbar_init(&tfull_bar[i], 1);
       mbar_init(&tempty_bar[i], 4);  // one arrival per epilogue warp
     }
+    for (int i = 0; i < 4; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_ptr, kTmemCols);
@@ -410,7 +449,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     const uint32_t my_stage_u32 = smem_u32(my_stage);
     const int sub_row = lane >> 3, chunk = lane & 7;  // read-back role: row (it*4 + sub_row), 16-byte chunk `chunk`
     int acc = 0;
-    uint32_t acc_phase = 0;
+    uint32_t acc_phase = 0, res_phase = 0;
     // running per-channel sums of this CTA's tiles (lane owns columns 2*lane, 2*lane+1 of every 64-column group)
     float s1[BN / 64][2], s2[BN / 64][2];
     int stat_n_tile = -1;
@@ -523,11 +562,21 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           // the TMA store of the previous column group must have finished READING the staging tile
           if (lane == 0) tma_store_wait_read();
           __syncwarp();
+          const bool group_live = cgp * 64 < n_left && m_base < g.M;
+          const bool with_res = g.ep_res != nullptr && group_live;
+          if (with_res && lane == 0) {  // identity tile -> staging buffer (rows / columns past the tensor are zero-filled)
+            mbar_expect_tx(&res_bar[quarter], 32 * 128);
+            tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
+          }
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             uint32_t v[32];
             tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
             tmem_ld_wait();
+            if (g.ep_scale != nullptr) {
+              if (with_res && half == 0) { mbar_wait(&res_bar[quarter], res_phase); res_phase ^= 1; }
+              apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? my_stage_u32 + lane * 128 : 0u, half * 4, lane);
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint32_t w[4];
@@ -590,7 +639,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 template <int STAGES, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads)
 conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                         const __grid_constant__ CUtensorMap tmO, const GemmArgs g) {
+                         const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
   constexpr int BN = 256, ACC = 2;
   constexpr int kBHalfBytes = (BN / 2) * kBlockK * 2;  // 16 KB: this CTA's half of the filter tile
   constexpr int kStageBytes = kABytes + kBHalfBytes;    // 32 KB
@@ -606,7 +655,8 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + ACC);
+  uint64_t* res_bar = tempty_bar + ACC;  // one per epilogue warp: the identity tile of a folded-BN epilogue has landed
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 4);
 
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -628,6 +678,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       mbar_init(&tfull_bar[i], 1);   // multicast commit
       mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps of each CTA (used in CTA 0 only)
     }
+    for (int i = 0; i < 4; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc_pair(tmem_ptr, kTmemCols);
@@ -718,7 +769,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     uint8_t* my_stage = stage_out + quarter * (32 * 128);
     const uint32_t my_stage_u32 = smem_u32(my_stage);
     int acc = 0;
-    uint32_t acc_phase = 0;
+    uint32_t acc_phase = 0, res_phase = 0;
     float s1[BN / 64][2], s2[BN / 64][2];
     int stat_n_tile = -1;
 #pragma unroll
@@ -751,11 +802,21 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       for (int cgp = 0; cgp < BN / 64; ++cgp) {
         if (lane == 0) tma_store_wait_read();
         __syncwarp();
+        const bool group_live = cgp * 64 < n_left && m_base < g.M;
+        const bool with_res = g.ep_res != nullptr && group_live;
+        if (with_res && lane == 0) {
+          mbar_expect_tx(&res_bar[quarter], 32 * 128);
+          tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
+        }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
           tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
           tmem_ld_wait();
+          if (g.ep_scale != nullptr) {
+            if (with_res && half == 0) { mbar_wait(&res_bar[quarter], res_phase); res_phase ^= 1; }
+            apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? my_stage_u32 + lane * 128 : 0u, half * 4, lane);
+          }
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint32_t w[4];
@@ -1058,7 +1119,8 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 template <int STAGES, bool B_MN>
-static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const GemmArgs& g, cudaStream_t st) {
+static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
+                            cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + kEpiStageBytes + 256;
   static_assert(smem <= 227 * 1024, "pair kernel ring exceeds shared memory");
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -1067,7 +1129,7 @@ static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
   int clusters = num_sms() / 2;
   if (clusters > num_n) clusters -= clusters % num_n;
   if (clusters > pairs) clusters = pairs;
-  conv_tc_gemm_pair_kernel<STAGES, B_MN><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, g);  // __cluster_dims__(2,1,1)
+  conv_tc_gemm_pair_kernel<STAGES, B_MN><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
   DV_LAUNCH_OK("conv_tc_gemm_pair_kernel");
   return DV_OK;
 }
@@ -1078,7 +1140,8 @@ static int env_int(const char* name, int dflt) {
 }
 
 template <int BN, int STAGES, bool STATS, bool B_MN>
-static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const GemmArgs& g, cudaStream_t st) {
+static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
+                                  cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + 256;
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   // ask for the whole L1/shared array as shared memory: otherwise the driver sizes the carve-out for ONE CTA of this
@@ -1119,7 +1182,7 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   int slots = num_sms() * occ_cached;
   if (slots > num_n) slots -= slots % num_n;  // a CTA then keeps one n-tile for its whole life (running BN sums stay put)
   const int grid = total < slots ? total : slots;
-  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, tmO, g);
+  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);
   DV_LAUNCH_OK("conv_tc_gemm_persistent_kernel");
   return DV_OK;
 }
@@ -1238,8 +1301,14 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
   } else {
     tmO = tmA;  // unused by the kernel
   }
-  if (use_pair(g, bn)) return b_mn ? launch_gemm_pair<6, true>(tmA, tmB, tmO, g, st) : launch_gemm_pair<6, false>(tmA, tmB, tmO, g, st);
-#define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_>(tmA, tmB, tmO, g, st)
+  alignas(64) CUtensorMap tmR = tmO;  // identity tensor of a folded-BN epilogue: same geometry as the output
+  if (g.ep_res != nullptr) {
+    DV_REQUIRE(staged, DV_ERR_UNSUPPORTED, "conv_tc: a residual epilogue needs the TMA-store output path");
+    int rc = make_map_2d(&tmR, g.ep_res, (uint64_t)g.M, (uint64_t)g.Nout, 32);
+    if (rc) return rc;
+  }
+  if (use_pair(g, bn)) return b_mn ? launch_gemm_pair<6, true>(tmA, tmB, tmO, tmR, g, st) : launch_gemm_pair<6, false>(tmA, tmB, tmO, tmR, g, st);
+#define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_>(tmA, tmB, tmO, tmR, g, st)
   if (b_mn) {
     if (staged) { switch (bn) { case 64: DV_GEMM_CASE(64, 4, true, true); case 128: DV_GEMM_CASE(128, 3, true, true); default: DV_GEMM_CASE(256, 4, true, true); } }
     switch (bn) { case 64: DV_GEMM_CASE(64, 4, false, true); case 128: DV_GEMM_CASE(128, 3, false, true); default: DV_GEMM_CASE(256, 4, false, true); }
@@ -1270,6 +1339,13 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     g.a_im2col = !(p->R == 1 && p->S == 1 && p->stride == 1 && p->pad == 0);
     g.out_f32 = p->y_f32 ? 1 : 0;
     g.stat_sums = p->y_f32 ? nullptr : p->stat_sums;
+    if (p->ep_scale != nullptr || p->ep_shift != nullptr || p->ep_residual != nullptr || p->ep_relu) {
+      DV_REQUIRE(p->ep_scale && p->ep_shift, DV_ERR_ARG, "conv_tc fprop: the folded epilogue needs both ep_scale and ep_shift");
+      DV_REQUIRE(!p->y_f32 && p->stat_sums == nullptr, DV_ERR_UNSUPPORTED, "conv_tc fprop: folded epilogue with y_f32 or stat_sums");
+      DV_REQUIRE(aligned16(p->ep_scale) && aligned16(p->ep_shift) && aligned16(p->ep_residual), DV_ERR_ARG,
+                 "conv_tc fprop: ep_scale / ep_shift / ep_residual must be 16-byte aligned");
+      g.ep_scale = p->ep_scale; g.ep_shift = p->ep_shift; g.ep_res = (const bf16*)p->ep_residual; g.ep_relu = p->ep_relu ? 1 : 0;
+    }
     const int bn = pick_bn(p->K);
     if (g.a_im2col) rc = make_map_im2col(&tmA, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, kBlockM);
     else rc = make_map_2d(&tmA, p->x, (uint64_t)g.M, (uint64_t)p->C, kBlockM);

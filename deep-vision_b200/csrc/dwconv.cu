@@ -47,7 +47,7 @@ template <int ST> struct StripW { static constexpr int fwd = ST == 1 ? 4 : 2; st
 template <typename T, int ST>
 __global__ void __launch_bounds__(kThreads, 2)
 dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __restrict__ out, int N, int IH, int IW, int OH, int OW,
-                    int C, int cgb, int lanes, int strips_per_blk, int flip) {
+                    int C, int cgb, int lanes, int strips_per_blk, int flip, const float* __restrict__ ep_shift = nullptr, int ep_relu = 0) {
   constexpr int V = Vec16<T>::N;
   constexpr int TW = StripW<ST>::fwd;
   constexpr int NCOL = (TW - 1) * ST + 3;  // input columns a strip touches
@@ -62,6 +62,9 @@ dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __
   const int nstrips = N * OH * strips_w;
   const int s0 = blockIdx.x * strips_per_blk;
   const int s1 = min(nstrips, s0 + strips_per_blk);
+  float bias[V];  // folded-BatchNorm shift (inference) or zero
+#pragma unroll
+  for (int e = 0; e < V; ++e) bias[e] = ep_shift != nullptr ? ep_shift[c + e] : 0.f;
   for (int sidx = s0 + lane; sidx < s1; sidx += lanes) {
     const int sw = sidx % strips_w;
     const int t = sidx / strips_w;
@@ -71,7 +74,7 @@ dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __
 #pragma unroll
     for (int j = 0; j < TW; ++j)
 #pragma unroll
-      for (int e = 0; e < V; ++e) acc[j][e] = 0.f;
+      for (int e = 0; e < V; ++e) acc[j][e] = bias[e];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
       const int ih = oh * ST + r - 1;
@@ -111,6 +114,12 @@ dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __
       }
     }
     T* orow = out + (((size_t)n * OH + oh) * OW + ow0) * C + c;
+    if (ep_relu) {
+#pragma unroll
+      for (int j = 0; j < TW; ++j)
+#pragma unroll
+        for (int e = 0; e < V; ++e) acc[j][e] = fmaxf(acc[j][e], 0.f);
+    }
 #pragma unroll
     for (int j = 0; j < TW; ++j) {
       if (ow0 + j < OW) { Vec16<T> o; o.pack(acc[j]); o.store(orow + (size_t)j * C); }
@@ -323,10 +332,10 @@ static int run_fprop(const dv_dwconv_params* p, cudaStream_t st) {
   dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
   if (d.stride == 1)
     dwconv_strip_kernel<T, 1><<<grid, kThreads, 0, st>>>((const T*)p->x, (const float*)p->w, (T*)p->y, d.N, d.H, d.W, d.P, d.Q, d.C, pl.cgb,
-                                                       pl.lanes, per, 0);
+                                                       pl.lanes, per, 0, p->ep_shift, p->ep_relu);
   else
     dwconv_strip_kernel<T, 2><<<grid, kThreads, 0, st>>>((const T*)p->x, (const float*)p->w, (T*)p->y, d.N, d.H, d.W, d.P, d.Q, d.C, pl.cgb,
-                                                       pl.lanes, per, 0);
+                                                       pl.lanes, per, 0, p->ep_shift, p->ep_relu);
   DV_LAUNCH_OK("dwconv_strip_kernel");
   return DV_OK;
 }
@@ -417,10 +426,12 @@ extern "C" int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream) {
 extern "C" int dv_dwconv_dgrad(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_dgrad");
   if (rc) return rc;
+  DV_REQUIRE(p->ep_shift == nullptr && p->ep_relu == 0, DV_ERR_UNSUPPORTED, "dv_dwconv_dgrad: the folded epilogue is fprop-only");
   return p->dtype == DV_BF16 ? run_dgrad<bf16>(p, (cudaStream_t)stream) : run_dgrad<float>(p, (cudaStream_t)stream);
 }
 extern "C" int dv_dwconv_wgrad(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_wgrad");
   if (rc) return rc;
+  DV_REQUIRE(p->ep_shift == nullptr && p->ep_relu == 0, DV_ERR_UNSUPPORTED, "dv_dwconv_wgrad: the folded epilogue is fprop-only");
   return p->dtype == DV_BF16 ? run_wgrad<bf16>(p, (cudaStream_t)stream) : run_wgrad<float>(p, (cudaStream_t)stream);
 }

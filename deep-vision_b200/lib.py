@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_HERE, "libdv_b200.so")
 DV_F32, DV_BF16 = 0, 1
 DV_ALGO_AUTO, DV_ALGO_SIMT, DV_ALGO_TC = 0, 1, 2
 DV_CONV_FPROP, DV_CONV_DGRAD, DV_CONV_WGRAD = 0, 1, 2
+DV_OK, DV_ERR_ARG, DV_ERR_UNSUPPORTED, DV_ERR_CUDA, DV_ERR_ARCH, DV_ERR_WORKSPACE = 0, 1, 2, 3, 4, 5
 
 
 class ConvParams(C.Structure):
@@ -22,6 +23,7 @@ class ConvParams(C.Structure):
         ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("K", C.c_int32),
         ("R", C.c_int32), ("S", C.c_int32), ("stride", C.c_int32), ("pad", C.c_int32),
         ("dtype", C.c_int32), ("algo", C.c_int32), ("y_f32", C.c_int32), ("accumulate", C.c_int32),
+        ("ep_scale", C.c_void_p), ("ep_shift", C.c_void_p), ("ep_residual", C.c_void_p), ("ep_relu", C.c_int32),
     ]
 
 
@@ -30,7 +32,7 @@ class DwConvParams(C.Structure):
         ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("stride", C.c_int32),
-        ("dtype", C.c_int32),
+        ("dtype", C.c_int32), ("ep_shift", C.c_void_p), ("ep_relu", C.c_int32),
     ]
 
 
@@ -73,6 +75,7 @@ _SIG = {
     "dv_dwconv_dgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_wgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_workspace_bytes": (C.c_size_t, [C.POINTER(DwConvParams)]),
+    "dv_bn_fold": (C.c_int, [_P, _P, _P, _P, C.c_float, _P, _P, C.c_int, _P, _P, _P]),
     "dv_bn_stats": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_apply": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_stats_from_sums": (C.c_int, [C.POINTER(BnParams), _P, _P]),

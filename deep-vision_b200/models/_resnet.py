@@ -34,7 +34,7 @@ class ResNetScaffold(tnn.Module):
         self._initialize_weights()
 
     def forward(self, x):
-        x = self.bn1(self.conv1(x), act=self.relu)
+        x = self.bn1(self.conv1(x, defer=True), act=self.relu)
         x = self.maxpool(x)
         for stage in (self.conv2x, self.conv3x, self.conv4x, self.conv5x):
             x = stage(x)
@@ -66,7 +66,7 @@ class _Residual(tnn.Module):
         accumulates on top of it (functional.GradSlot)."""
         if self.downsample:
             conv, bn = self.projection[0], self.projection[1]
-            identity = bn(conv(x, grad_slot=slot, role="deposit" if slot is not None else None))
+            identity = bn(conv(x, grad_slot=slot, role="deposit" if slot is not None else None, defer=True))
             return last_bn(main, residual=identity, act=self.relu)
         return last_bn(main, residual=x, act=self.relu, res_slot=slot)
 
@@ -91,8 +91,8 @@ class BasicBlock(_Residual):
     def forward(self, x):
         x = F.to_compute_layout(x)  # no-op inside a network; converts a raw fp32 NCHW tensor fed to a lone block
         slot = self._slot_for(x)
-        out = self.bn1(self.conv1(x, grad_slot=slot, role="collect" if slot is not None else None), act=self.relu)
-        out = self.conv2(out)
+        out = self.bn1(self.conv1(x, grad_slot=slot, role="collect" if slot is not None else None, defer=True), act=self.relu)
+        out = self.conv2(out, defer=True)
         return self._shortcut_and_merge(x, out, self.bn2, slot)
 
 
@@ -114,9 +114,9 @@ class BottleneckBlock(_Residual):
     def forward(self, x):
         x = F.to_compute_layout(x)
         slot = self._slot_for(x)
-        out = self.bn1(self.conv1(x, grad_slot=slot, role="collect" if slot is not None else None), act=self.relu)
-        out = self.bn2(self.conv2(out), act=self.relu)
-        out = self.conv3(out)
+        out = self.bn1(self.conv1(x, grad_slot=slot, role="collect" if slot is not None else None, defer=True), act=self.relu)
+        out = self.bn2(self.conv2(out, defer=True), act=self.relu)
+        out = self.conv3(out, defer=True)
         return self._shortcut_and_merge(x, out, self.bn3, slot)
 
 

@@ -27,7 +27,7 @@ class MobileNetV1(tnn.Module):
 
     def forward(self, x):
         f = self.features
-        x = f[1](f[0](x), act=f[2])          # conv -> BN+ReLU in one pass
+        x = f[1](f[0](x, defer=True), act=f[2])          # conv -> BN+ReLU in one pass
         for i in range(3, len(f)):           # 13 separable blocks, then the pool
             x = f[i](x)
         x = x.view(x.size(0), self.alpha * 1024)
@@ -46,7 +46,7 @@ class DepthwiseSeparableConv(tnn.Module):
 
 class _ConvBnRelu(tnn.Module):
     def forward(self, x):
-        return self.bn(self.conv(x), act=self.relu)
+        return self.bn(self.conv(x, defer=True), act=self.relu)
 
 
 class DepthwiseConv(_ConvBnRelu):

@@ -8,6 +8,7 @@ import torch.nn as nn
 
 from . import config
 from . import functional as F
+from . import inference
 
 
 class Conv2d(nn.Conv2d):
@@ -28,10 +29,13 @@ class Conv2d(nn.Conv2d):
                                        and self.padding == (1, 1)):
             raise NotImplementedError("deep_vision_b200.nn.Conv2d: grouped convolution is supported as depth-wise 3x3 pad 1 only")
 
-    def forward(self, x, grad_slot=None, role=None):
+    def forward(self, x, grad_slot=None, role=None, defer=False):
         """grad_slot/role: see functional.GradSlot — used by the residual blocks to fuse the shortcut's gradient into
-        this convolution's dgrad; plain callers leave them unset."""
+        this convolution's dgrad; plain callers leave them unset.  defer: the caller hands the result straight to a
+        BatchNorm2d; in inference mode the launch is then left to that module (inference.PendingConv)."""
         x = F.to_compute_layout(x)
+        if defer and inference.wanted(self, x):
+            return inference.PendingConv(x, self)
         if self._dv_depthwise:
             return F.dwconv3x3(x, self.weight, self.stride[0])
         stats = None
@@ -49,6 +53,11 @@ class BatchNorm2d(nn.BatchNorm2d):
     def forward(self, x, residual=None, act=None, res_slot=None):
         if act is not None and not isinstance(act, nn.ReLU):
             raise TypeError("act must be an nn.ReLU module or None")
+        if isinstance(x, inference.PendingConv):
+            y = inference.conv_bn_act(x, self, residual, act is not None)
+            if y is not None:
+                return y
+            x = x.materialize()
         x = F.to_compute_layout(x)
         if self.momentum is None:
             eaf = 0.0

@@ -83,6 +83,16 @@ typedef struct dv_conv_params {
                          wgrad: 1 = dw += result, added straight into dw with fp32 vector reductions — no workspace, no
                          second pass; the caller provides a zeroed (or to-be-accumulated) dw and accepts a summation order
                          that varies run to run.  0 = split partials in the workspace + fixed-order reduce (bit-reproducible) */
+  /* fprop on the tensor-core path only, optional — inference with the BatchNorm that follows the convolution folded into
+   * its epilogue (eval-mode nn.BatchNorm2d + nn.ReLU + `x + identity`, resnet50.py:152-164 under net.eval(), train.py:489):
+   *   y = relu( acc * ep_scale[k] + ep_shift[k] + ep_residual[n,p,q,k] )
+   * with ep_scale = gamma / sqrt(running_var + eps), ep_shift = beta - running_mean * ep_scale (fp32 [K], made by the caller).
+   * ep_residual (dtype [N,P,Q,K]) may be NULL; ep_relu 0/1.  All NULL/0 = plain convolution.  Any other path rejects them
+   * with DV_ERR_UNSUPPORTED rather than ignoring them. */
+  const float* ep_scale;
+  const float* ep_shift;
+  const void* ep_residual;
+  int32_t ep_relu;
 } dv_conv_params;
 
 enum { DV_CONV_FPROP = 0, DV_CONV_DGRAD = 1, DV_CONV_WGRAD = 2 };
@@ -126,6 +136,11 @@ typedef struct dv_dwconv_params {
   size_t workspace_bytes;
   int32_t N, H, W, C, stride;
   int32_t dtype;
+  /* fprop only, optional — inference with the following eval-mode BatchNorm + ReLU folded in (mobilenet_v1.py:129-133
+   * under net.eval()):  y = relu(conv(x, w) + ep_shift[c]).  The BN scale needs no field: the taps are fp32 and per
+   * channel, so the caller passes w[c,:,:] * scale[c].  dgrad / wgrad reject a non-NULL ep_shift. */
+  const float* ep_shift;
+  int32_t ep_relu;
 } dv_dwconv_params;
 
 int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream);
@@ -227,6 +242,13 @@ int dv_bn_bwd_reduce(const dv_bn_bwd_params* p, void* stream);
 /* dx = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M), dres = dz, with dz = dy*(y>0) */
 int dv_bn_bwd_apply(const dv_bn_bwd_params* p, void* stream);
 size_t dv_bn_workspace_bytes(int64_t M, int C);
+/* Inference: eval-mode BatchNorm (train.py:489 `net.eval()`, notebooks cell 3) as a per-channel affine map,
+ *   scale[c] = gamma[c] / sqrt(running_var[c] + eps),  shift[c] = beta[c] - running_mean[c] * scale[c]   (fp32 [C]),
+ * for the folded epilogues dv_conv_params.ep_* / dv_dwconv_params.ep_shift.  With dw_w (fp32 [C][3][3], the depth-wise
+ * taps that precede this BN) it also writes dw_w_scaled[c][:] = dw_w[c][:] * scale[c].  No counterpart call in the
+ * reference: torch evaluates eval-mode BN as its own kernel. */
+int dv_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var, float eps,
+               float* scale, float* shift, int C, const float* dw_w, float* dw_w_scaled, void* stream);
 
 /* stand-alone ReLU (nn.ReLU at a site that no BN precedes; not used by the four models) */
 int dv_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream);

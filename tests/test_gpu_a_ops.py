@@ -405,3 +405,33 @@ def test_cross_entropy_matches_oracle():
     lib.check(lib.lib.dv_scale_by(d.data_ptr(), s.data_ptr(), B * Cn, stream_ptr()), "scale")
     torch.cuda.synchronize()
     assert rel_l2(d.cpu().numpy(), 0.25 * d_ref) < 1e-5
+
+
+@pytest.mark.parametrize("stride", [1, 2])
+def test_dwconv_folded_batchnorm_epilogue(stride):
+    """dv_dwconv_params.ep_shift / ep_relu with taps scaled by dv_bn_fold == oracle dwconv -> eval BN -> ReLU."""
+    lib = _lib()
+    dtype = torch.bfloat16
+    N, Cc, H, W = 3, 64, 9, 10
+    x = _rand((N, Cc, H, W), 51, dtype)
+    w = _rand((Cc, 1, 3, 3), 52, torch.float32, scale=0.3)
+    rng = np.random.default_rng(53)
+    gamma, beta, rm, rv = rng.uniform(0.5, 1.5, Cc), rng.normal(0, 0.3, Cc), rng.normal(0, 0.5, Cc), rng.uniform(0.5, 2.0, Cc)
+    ref = ref_ops.relu(ref_ops.batch_norm_eval(ref_ops.conv2d(x, w, stride, 1, groups=Cc), gamma, beta, rm, rv))
+    f32 = lambda a: torch.from_numpy(np.ascontiguousarray(np.asarray(a, np.float32))).cuda()
+    g_d, b_d, rm_d, rv_d, w_d = f32(gamma), f32(beta), f32(rm), f32(rv), f32(w)
+    scale, shift, w_s = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda"), torch.empty_like(w_d)
+    lib.check(lib.lib.dv_bn_fold(g_d.data_ptr(), b_d.data_ptr(), rm_d.data_ptr(), rv_d.data_ptr(), 1e-5, scale.data_ptr(), shift.data_ptr(),
+                                 Cc, w_d.data_ptr(), w_s.data_ptr(), stream_ptr()), "dv_bn_fold")
+    xd = _dev(np.transpose(x, (0, 2, 3, 1)), dtype)
+    P, Q = ref.shape[2:]
+    yd = torch.full((N, P, Q, Cc), float("nan"), device="cuda", dtype=dtype)
+    p = lib.DwConvParams()
+    p.x, p.w, p.y = xd.data_ptr(), w_s.data_ptr(), yd.data_ptr()
+    p.N, p.H, p.W, p.C, p.stride, p.dtype = N, H, W, Cc, stride, _dv(dtype)
+    p.ep_shift, p.ep_relu = shift.data_ptr(), 1
+    lib.check(lib.lib.dv_dwconv_fprop(C.byref(p), stream_ptr()), "dv_dwconv_fprop(folded)")
+    torch.cuda.synchronize()
+    assert rel_l2(w_s.cpu().numpy(), w * (gamma / np.sqrt(rv + 1e-5))[:, None, None, None]) < 1e-6
+    assert rel_l2(np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2)), ref) < 1e-2
+    assert lib.lib.dv_dwconv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED

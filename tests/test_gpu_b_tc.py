@@ -270,3 +270,63 @@ def test_tc_fprop_fused_bn_sums(case):
     assert rel_l2(mean.cpu().numpy(), yd.mean(0).cpu().numpy()) < 1e-4
     assert rel_l2(inv.cpu().numpy(), (1.0 / torch.sqrt(yd.var(0, unbiased=False) + 1e-5)).cpu().numpy()) < 1e-4
     assert rel_l2(rm.cpu().numpy(), (0.1 * yd.mean(0)).cpu().numpy()) < 1e-4
+
+
+FOLD_CASES = [
+    # N, C, H, W, K, R, stride, pad, residual, relu
+    (2, 64, 8, 8, 64, 3, 1, 1, False, True),      # BN=64 tile, conv2 of a bottleneck
+    (3, 128, 7, 7, 256, 1, 1, 0, True, True),     # conv3 + identity + ReLU, ragged M
+    (2, 64, 8, 8, 128, 1, 2, 0, False, False),    # projection shortcut: strided 1x1, BN only
+    (2, 512, 4, 4, 1000, 1, 1, 0, True, True),    # K not a multiple of the N tile
+    (2, 192, 6, 6, 64, 1, 1, 0, False, True),     # patch-matrix shape class of the stem
+    (2, 64, 160, 128, 256, 1, 1, 0, True, True),  # M = 40960 >= 148 x 128 x 2: the CTA-pair kernel's epilogue
+]
+
+
+@pytest.mark.parametrize("case", FOLD_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_fprop_folded_batchnorm_epilogue(case):
+    """dv_conv_params.ep_*: y = relu(conv * scale + shift + identity) against the oracle's conv -> eval BN -> add -> ReLU,
+    with scale/shift made by dv_bn_fold."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, Cc, H, W, K, R, stride, pad, residual, relu = case
+    x = _rand((N, Cc, H, W), 1, BF)
+    w = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+    rng = np.random.default_rng(3)
+    gamma, beta = rng.uniform(0.5, 1.5, K), rng.normal(0, 0.3, K)
+    rm, rv = rng.normal(0, 0.5, K), rng.uniform(0.5, 2.0, K)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+    res = _rand((N, K, P, Q), 4, BF) if residual else None
+    ref = ref_ops.batch_norm_eval(ref_ops.conv2d(x, w, stride, pad), gamma, beta, rm, rv)
+    if residual:
+        ref = ref + res
+    if relu:
+        ref = ref_ops.relu(ref)
+    f32 = lambda a: torch.from_numpy(np.asarray(a, np.float32)).cuda()
+    g_d, b_d, rm_d, rv_d = f32(gamma), f32(beta), f32(rm), f32(rv)
+    scale, shift = torch.empty(K, device="cuda"), torch.empty(K, device="cuda")
+    lib.check(lib.lib.dv_bn_fold(g_d.data_ptr(), b_d.data_ptr(), rm_d.data_ptr(), rv_d.data_ptr(), 1e-5, scale.data_ptr(), shift.data_ptr(),
+                                 K, None, None, stream_ptr()), "dv_bn_fold")
+    torch.cuda.synchronize()
+    assert rel_l2(scale.cpu().numpy(), gamma / np.sqrt(rv + 1e-5)) < 1e-6
+    assert rel_l2(shift.cpu().numpy(), beta - rm * gamma / np.sqrt(rv + 1e-5)) < 1e-5
+    xd = torch.from_numpy(np.ascontiguousarray(x.transpose(0, 2, 3, 1))).cuda().to(BF)
+    wd = torch.from_numpy(np.ascontiguousarray(w.transpose(0, 2, 3, 1))).cuda().to(BF)
+    rd = torch.from_numpy(np.ascontiguousarray(res.transpose(0, 2, 3, 1))).cuda().to(BF) if residual else None
+    y = torch.full((N, P, Q, K), float("nan"), device="cuda", dtype=BF)
+    p = lib.ConvParams()
+    p.x, p.w, p.y = xd.data_ptr(), wd.data_ptr(), y.data_ptr()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, W, Cc, K, R, R, stride, pad, lib.DV_BF16, lib.DV_ALGO_TC
+    p.ep_scale, p.ep_shift, p.ep_relu = scale.data_ptr(), shift.data_ptr(), int(relu)
+    p.ep_residual = rd.data_ptr() if residual else None
+    lib.check(lib.lib.dv_conv_fprop(C.byref(p), stream_ptr()), "fprop(folded)")
+    torch.cuda.synchronize()
+    out = y.double().cpu().numpy().transpose(0, 3, 1, 2)
+    assert np.isfinite(out).all()
+    assert rel_l2(out, ref) < 1e-2   # one bf16 rounding of the final value
+    # the epilogue is refused, not ignored, where it does not exist
+    p.algo = lib.DV_ALGO_SIMT
+    assert lib.lib.dv_conv_fprop(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED
+    p.algo = lib.DV_ALGO_TC
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED

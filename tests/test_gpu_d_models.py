@@ -103,3 +103,54 @@ def test_resnet50_train_step_fp32_matches_oracle_gradients():
     gr = torch.cat([sd[k].grad.flatten() for k, _ in m.named_parameters()]).numpy()
     gg = torch.cat([p.grad.flatten().double().cpu() for _, p in m.named_parameters()]).numpy()
     assert rel_l2(gg, gr) < 5e-2
+
+
+@pytest.mark.parametrize("name", ["model_resnet50_b2_64_eval", "model_resnet34_b4_224_eval", "model_mobilenet1_b2_64_eval"])
+def test_folded_batchnorm_inference_matches_unfused_and_golden(name):
+    """net.eval() + no_grad in bf16 runs every conv->BN(->add)(->ReLU) group as one kernel (inference.py).  Same bar as
+    the unfused path against the frozen reference logits, one launch fewer per BatchNorm2d, and the two paths agree."""
+    from deep_vision_b200.lib import lib
+    rec = load_golden(name)
+    torch.manual_seed(int(rec["seed"]))
+    m = CTORS[FIXTURES[name]]()
+    psum = float(sum(p.detach().double().sum() for p in m.parameters()))
+    if abs(psum - float(rec["param_sum"])) > 1e-9 * float(rec["param_abs_sum"]):
+        pytest.skip("torch RNG differs from the build that froze the fixture")
+    g = torch.Generator().manual_seed(int(rec["seed"]) + 1)
+    x = torch.randn(tuple(int(v) for v in rec["in_shape"]), generator=g).cuda()
+    dv.set_compute_dtype(torch.bfloat16)
+    m = m.cuda().eval()
+
+    def run():
+        n0 = lib.dv_launch_count()
+        with torch.no_grad():
+            y = m(x)
+        torch.cuda.synchronize()
+        return y.cpu().numpy(), lib.dv_launch_count() - n0
+
+    run()                                   # first call also launches one dv_bn_fold per BatchNorm2d
+    y_fold, n_fold = run()
+    dv.set_fold_bn(False)
+    try:
+        y_plain, n_plain = run()
+    finally:
+        dv.set_fold_bn(True)
+    n_bn = sum(isinstance(mod, torch.nn.BatchNorm2d) for mod in m.modules())
+    assert n_plain - n_fold == n_bn, (n_plain, n_fold, n_bn)
+    err = rel_l2(y_fold, rec["logits_fp64"])
+    print(f"{name}: folded {err:.3e}  unfused {rel_l2(y_plain, rec['logits_fp64']):.3e}  launches {n_fold} vs {n_plain}")
+    assert err < 2e-2
+    assert np.array_equal(y_fold.argmax(1), rec["logits_fp64"].argmax(1))
+    assert rel_l2(y_fold, y_plain) < 2e-2
+    # a changed running statistic invalidates the cached scale/shift
+    bn = next(mod for mod in m.modules() if isinstance(mod, torch.nn.BatchNorm2d))
+    bn.running_var.mul_(4.0)
+    y2, _ = run()
+    dv.set_fold_bn(False)
+    try:
+        y2_plain, _ = run()
+    finally:
+        dv.set_fold_bn(True)
+    assert rel_l2(y2, y2_plain) < 2e-2
+    if "mobilenet" not in name:   # (a fresh MobileNetV1 in eval mode has logits ~ the classifier bias: nothing to see there)
+        assert rel_l2(y2, y_fold) > 1e-3

@@ -1,0 +1,61 @@
+#!/usr/bin/env python
+"""In-step kernel timeline of the CUDA-graph training step (CUPTI through torch.profiler, no ncu): per-kernel time with
+the caches as they are in the real step, plus the idle time between kernels.  Writes a markdown table.
+A number read from this trace is an attribution aid, not a bench value."""
+import argparse
+import collections
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import deep_vision_b200 as dv  # noqa: E402
+from deep_vision_b200.train import TRAINING_CONFIG, Trainer  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--model", default="resnet50")
+ap.add_argument("--batch", type=int, default=256)
+ap.add_argument("--out", default="gpurun_out/step_trace.md")
+args = ap.parse_args()
+torch.cuda.set_device(0)
+dv.set_compute_dtype(torch.bfloat16)
+torch.manual_seed(0)
+ctor = {"resnet50": "ResNet50", "resnet34": "ResNet34", "resnet152": "ResNet152", "mobilenet_v1": "MobileNetV1"}[args.model]
+net = getattr(dv.models, ctor)().cuda()
+cfg = dict(TRAINING_CONFIG[args.model])
+cfg.pop("batch_size")
+trainer = Trainer(net, use_cuda_graph=True, **cfg)
+x = torch.randn(args.batch, 3, 224, 224, device="cuda")
+y = torch.randint(0, 1000, (args.batch,), device="cuda")
+for _ in range(5):
+    trainer.step(x, y)
+torch.cuda.synchronize()
+from torch.profiler import ProfilerActivity, profile  # noqa: E402
+
+STEPS = 3
+with profile(activities=[ProfilerActivity.CUDA]) as prof:
+    for _ in range(STEPS):
+        trainer.step(x, y)
+    torch.cuda.synchronize()
+ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and e.time_range.end > e.time_range.start]
+ev.sort(key=lambda e: e.time_range.start)
+span = (ev[-1].time_range.end - ev[0].time_range.start) / STEPS
+busy = sum(e.time_range.end - e.time_range.start for e in ev) / STEPS
+gaps = []
+for a, b in zip(ev, ev[1:]):
+    gaps.append(max(0.0, b.time_range.start - a.time_range.end))
+agg = collections.defaultdict(lambda: [0, 0.0])
+for e in ev:
+    k = e.name.replace("(anonymous namespace)::", "").replace("void ", "").split("(")[0][:90]
+    agg[k][0] += 1
+    agg[k][1] += e.time_range.end - e.time_range.start
+rows = sorted(agg.items(), key=lambda kv: -kv[1][1])
+with open(args.out, "w") as f:
+    f.write(f"# In-step kernel timeline, {args.model} batch {args.batch} bf16, CUDA graph, {STEPS} steps averaged (CUPTI)\n\n")
+    f.write(f"span per step {span / 1e3:.3f} ms, kernels busy {busy / 1e3:.3f} ms, idle between kernels {(span - busy) / 1e3:.3f} ms "
+            f"({len(ev) // STEPS} launches per step, median gap {sorted(gaps)[len(gaps) // 2]:.2f} us)\n\n")
+    f.write("| kernel | launches/step | us/step | share |\n|---|---|---|---|\n")
+    for k, (n, t) in rows:
+        f.write(f"| `{k}` | {n / STEPS:.0f} | {t / STEPS:.1f} | {100 * t / STEPS / span:.1f}% |\n")
+print(open(args.out).read()[:3000])
