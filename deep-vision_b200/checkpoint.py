@@ -16,14 +16,37 @@ def _strip_module_prefix(state):
     return state
 
 
+def _load_torch_optimizer_state(trainer, opt):
+    """torch.optim.SGD keeps 'momentum_buffer', RMSprop 'square_avg', keyed by the parameter's index in
+    net.parameters() order — the order FlatParams lays the flat buffers out in."""
+    key = {"sgd": "momentum_buffer", "rmsprop": "square_avg"}[trainer.kind]
+    params = [p for p in trainer.model.parameters()]
+    steps = 0
+    for idx, p in enumerate(params):
+        st = opt["state"].get(idx)
+        if not st or st.get(key) is None:
+            continue
+        buf = st[key].to(device=trainer.flat_s.device, dtype=torch.float32)
+        off = (p.data_ptr() - trainer.flat_p.data_ptr()) // 4
+        view = trainer.flat_s[off:off + p.numel()].view(p.shape)
+        view.copy_(buf.reshape(p.shape))
+        steps = max(steps, int(st.get("step", 1)) if not torch.is_tensor(st.get("step", 1)) else int(st["step"].item()))
+    trainer.steps_done = max(trainer.steps_done, steps, 1 if opt["state"] else 0)
+    groups = opt.get("param_groups") or []
+    if groups and "lr" in groups[0]:
+        trainer.set_lr(groups[0]["lr"])
+
+
 def save_checkpoint(path, net, epoch, trainer=None, scheduler=None, loggers=None):
     model_state = {k: (v.detach().contiguous().cpu() if torch.is_tensor(v) else v) for k, v in net.state_dict().items()}
     torch.save({"epoch": epoch, "model": model_state, "optimizer": trainer.state_dict() if trainer is not None else None,
                 "scheduler": scheduler.state_dict() if scheduler is not None else None, "loggers": loggers or {}}, path)
 
 
-def load_checkpoint(path, net, trainer=None, map_location="cpu"):
-    """Loads a checkpoint written by save_checkpoint OR by the reference's train.py.  Returns (next epoch, loggers)."""
+def load_checkpoint(path, net, trainer=None, map_location="cpu", scheduler=None):
+    """Loads a checkpoint written by save_checkpoint OR by the reference's train.py.  Returns (next epoch, loggers).
+    A reference checkpoint's 'optimizer' entry is torch.optim's per-parameter state_dict (train.py:295-302): its momentum
+    / squared-average buffers are copied into the trainer's flat state in parameter order."""
     ckpt = torch.load(path, map_location=map_location, weights_only=False)
     net.load_state_dict(_strip_module_prefix(ckpt["model"]))
     config.bump_weight_epoch()  # cached compute-dtype filter copies are stale now
@@ -33,4 +56,10 @@ def load_checkpoint(path, net, trainer=None, map_location="cpu"):
         if isinstance(opt, dict) and "state" in opt and opt.get("optimizer") == trainer.kind:
             trainer.flat_s.copy_(opt["state"].to(trainer.flat_s.device))
             trainer.steps_done = int(opt.get("steps", 0))
+            if "lr" in opt:
+                trainer.set_lr(opt["lr"])
+        elif isinstance(opt, dict) and "param_groups" in opt and isinstance(opt.get("state"), dict):
+            _load_torch_optimizer_state(trainer, opt)
+    if scheduler is not None and ckpt.get("scheduler") is not None:
+        scheduler.load_state_dict(ckpt["scheduler"])
     return int(ckpt.get("epoch", 0)) + 1, ckpt.get("loggers", {})

@@ -312,7 +312,7 @@ __device__ __forceinline__ void apply_folded_epilogue(uint32_t* v, const GemmArg
 // B_MN: the B operand is taken as [64 reduction rows][64 output columns] boxes straight from KRSC filters and consumed
 // MN-major — the dgrad case, where the reduction runs over K (filter rows) and the output over C (contiguous), with the
 // tap flipped by index.  No transposed copy of the filters is needed.
-template <int BN, int STAGES, bool STATS, bool B_MN>
+template <int BN, int STAGES, bool STATS, bool B_MN, bool FOLD>
 __global__ void __launch_bounds__(kThreads)
 conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
@@ -563,7 +563,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           if (lane == 0) tma_store_wait_read();
           __syncwarp();
           const bool group_live = cgp * 64 < n_left && m_base < g.M;
-          const bool with_res = g.ep_res != nullptr && group_live;
+          const bool with_res = FOLD && g.ep_res != nullptr && group_live;
           if (with_res && lane == 0) {  // identity tile -> staging buffer (rows / columns past the tensor are zero-filled)
             mbar_expect_tx(&res_bar[quarter], 32 * 128);
             tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
@@ -573,7 +573,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             uint32_t v[32];
             tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
             tmem_ld_wait();
-            if (g.ep_scale != nullptr) {
+            if (FOLD) {
               if (with_res && half == 0) { mbar_wait(&res_bar[quarter], res_phase); res_phase ^= 1; }
               apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? my_stage_u32 + lane * 128 : 0u, half * 4, lane);
             }
@@ -636,7 +636,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 // accumulator-ready barriers are signalled in both CTAs by a multicast commit; the peer's epilogue hands accumulators
 // back by a remote arrive.
 // ------------------------------------------------------------------------------------------------------------
-template <int STAGES, bool B_MN>
+template <int STAGES, bool B_MN, bool FOLD>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads)
 conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
@@ -803,7 +803,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (lane == 0) tma_store_wait_read();
         __syncwarp();
         const bool group_live = cgp * 64 < n_left && m_base < g.M;
-        const bool with_res = g.ep_res != nullptr && group_live;
+        const bool with_res = FOLD && g.ep_res != nullptr && group_live;
         if (with_res && lane == 0) {
           mbar_expect_tx(&res_bar[quarter], 32 * 128);
           tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
@@ -813,7 +813,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           uint32_t v[32];
           tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
           tmem_ld_wait();
-          if (g.ep_scale != nullptr) {
+          if (FOLD) {
             if (with_res && half == 0) { mbar_wait(&res_bar[quarter], res_phase); res_phase ^= 1; }
             apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? my_stage_u32 + lane * 128 : 0u, half * 4, lane);
           }
@@ -1118,18 +1118,18 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int STAGES, bool B_MN>
+template <int STAGES, bool B_MN, bool FOLD>
 static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                             cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + kEpiStageBytes + 256;
   static_assert(smem <= 227 * 1024, "pair kernel ring exceeds shared memory");
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int num_n = ceil_div(g.Nout, 256);
   const int pairs = ceil_div(ceil_div(g.M, kBlockM), 2) * num_n;
   int clusters = num_sms() / 2;
   if (clusters > num_n) clusters -= clusters % num_n;
   if (clusters > pairs) clusters = pairs;
-  conv_tc_gemm_pair_kernel<STAGES, B_MN><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
+  conv_tc_gemm_pair_kernel<STAGES, B_MN, FOLD><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
   DV_LAUNCH_OK("conv_tc_gemm_pair_kernel");
   return DV_OK;
 }
@@ -1139,14 +1139,14 @@ static int env_int(const char* name, int dflt) {
   return v ? atoi(v) : dflt;
 }
 
-template <int BN, int STAGES, bool STATS, bool B_MN>
+template <int BN, int STAGES, bool STATS, bool B_MN, bool FOLD>
 static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                                   cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + 256;
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   // ask for the whole L1/shared array as shared memory: otherwise the driver sizes the carve-out for ONE CTA of this
   // kernel and a second CTA never becomes resident (measured: occupancy 1 -> 2 for the 96 KB variants)
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, cudaFuncAttributePreferredSharedMemoryCarveout,
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                   cudaSharedmemCarveoutMaxShared));
   // CTAs per SM the grid is sized for: two when two rings (<= 113 KB each) and two accumulator pairs (2 x 2 x BN <= 512 TMEM
   // columns) fit, else one.  cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for these kernels at ANY shared
@@ -1155,17 +1155,17 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   static int occ_cached = 0;
   if (occ_cached == 0) {
     int occ = 0;
-    DV_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, kThreads, smem));
+    DV_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, kThreads, smem));
     occ_cached = (smem <= 115712 && 4 * BN <= 512) ? 2 : 1;
     const int forced = env_int("DV_TC_OCC", 0);  // experiment knob
     if (forced > 0) occ_cached = forced;
     if (env_int("DV_TC_DEBUG", 0)) {
       cudaFuncAttributes fa;
-      cudaFuncGetAttributes(&fa, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>);
+      cudaFuncGetAttributes(&fa, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>);
       int sweep[4] = {0, 0, 0, 0};
       const int sizes[4] = {32 << 10, 64 << 10, 96 << 10, 110 << 10};
       for (int i = 0; i < 4; ++i)
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sweep[i], conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN>, kThreads, sizes[i]);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sweep[i], conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, kThreads, sizes[i]);
       int dev = 0, smem_sm = 0, smem_res = 0;
       cudaGetDevice(&dev);
       cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
@@ -1182,7 +1182,7 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   int slots = num_sms() * occ_cached;
   if (slots > num_n) slots -= slots % num_n;  // a CTA then keeps one n-tile for its whole life (running BN sums stay put)
   const int grid = total < slots ? total : slots;
-  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN><<<grid, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);
+  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD><<<grid, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);
   DV_LAUNCH_OK("conv_tc_gemm_persistent_kernel");
   return DV_OK;
 }
@@ -1307,8 +1307,18 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
     int rc = make_map_2d(&tmR, g.ep_res, (uint64_t)g.M, (uint64_t)g.Nout, 32);
     if (rc) return rc;
   }
-  if (use_pair(g, bn)) return b_mn ? launch_gemm_pair<6, true>(tmA, tmB, tmO, tmR, g, st) : launch_gemm_pair<6, false>(tmA, tmB, tmO, tmR, g, st);
-#define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_>(tmA, tmB, tmO, tmR, g, st)
+  const bool fold = g.ep_scale != nullptr;  // fprop only (conv_tc checks): staged, K-major B
+  if (fold) {
+    DV_REQUIRE(staged && !b_mn, DV_ERR_UNSUPPORTED, "conv_tc: the folded epilogue exists on the fprop TMA-store path only");
+    if (use_pair(g, bn)) return launch_gemm_pair<6, false, true>(tmA, tmB, tmO, tmR, g, st);
+    switch (bn) {
+      case 64: return launch_gemm_persistent<64, 4, true, false, true>(tmA, tmB, tmO, tmR, g, st);
+      case 128: return launch_gemm_persistent<128, 3, true, false, true>(tmA, tmB, tmO, tmR, g, st);
+      default: return launch_gemm_persistent<256, 4, true, false, true>(tmA, tmB, tmO, tmR, g, st);
+    }
+  }
+  if (use_pair(g, bn)) return b_mn ? launch_gemm_pair<6, true, false>(tmA, tmB, tmO, tmR, g, st) : launch_gemm_pair<6, false, false>(tmA, tmB, tmO, tmR, g, st);
+#define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_, false>(tmA, tmB, tmO, tmR, g, st)
   if (b_mn) {
     if (staged) { switch (bn) { case 64: DV_GEMM_CASE(64, 4, true, true); case 128: DV_GEMM_CASE(128, 3, true, true); default: DV_GEMM_CASE(256, 4, true, true); } }
     switch (bn) { case 64: DV_GEMM_CASE(64, 4, false, true); case 128: DV_GEMM_CASE(128, 3, false, true); default: DV_GEMM_CASE(256, 4, false, true); }

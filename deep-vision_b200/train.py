@@ -232,6 +232,15 @@ class Trainer:
         config.bump_weight_epoch()
 
     _capturing = False
+    _warmed = False
+
+    def set_lr(self, lr):
+        """Learning-rate schedulers call this (epochs.SchedulerTarget).  The rate is a by-value kernel argument, so a
+        captured step is re-recorded on the next call to `step` (once per change, i.e. at most once per epoch)."""
+        lr = float(lr)
+        if lr != self.lr:
+            self.lr = lr
+            self._graph = None
 
     def step(self, images, labels):
         """images: [B,3,H,W] fp32 CUDA (NCHW, as the reference's loader yields), labels: [B] int64 CUDA.
@@ -243,6 +252,9 @@ class Trainer:
             return loss
         if self._graph is None:
             self._capture(images, labels)
+        if images.shape != self._static_images.shape:
+            raise RuntimeError(f"Trainer(use_cuda_graph=True): batch shape changed from {tuple(self._static_images.shape)} to "
+                               f"{tuple(images.shape)}; feed full batches (drop_last) or use use_cuda_graph=False")
         self._static_images.copy_(images, non_blocking=True)
         self._static_labels.copy_(labels, non_blocking=True)
         self._graph.replay()
@@ -255,13 +267,15 @@ class Trainer:
         steps, which are real training steps."""
         self._static_images = images.clone()
         self._static_labels = labels.clone()
-        s = torch.cuda.Stream()
-        s.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(s):
-            for _ in range(2):
-                self._step_body(self._static_images, self._static_labels)
-                self.steps_done += 1
-        torch.cuda.current_stream().wait_stream(s)
+        if not self._warmed:   # a re-capture (set_lr) records straight away: nothing is executed, no batch is trained twice
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(2):
+                    self._step_body(self._static_images, self._static_labels)
+                    self.steps_done += 1
+            torch.cuda.current_stream().wait_stream(s)
+            self._warmed = True
         torch.cuda.synchronize()
         self._graph = torch.cuda.CUDAGraph()
         self._capturing = True
@@ -278,7 +292,7 @@ class Trainer:
         config.bump_weight_epoch()
 
     def state_dict(self):
-        return {"optimizer": self.kind, "steps": self.steps_done, "state": self.flat_s.clone()}
+        return {"optimizer": self.kind, "steps": self.steps_done, "lr": self.lr, "state": self.flat_s.clone()}
 
 
 class HostFeeder:

@@ -111,3 +111,33 @@ def test_validate_matches_oracle_eval_pass():
         ref5 += float(a5)
     assert abs(loss - ref_loss / 2) < 1e-4 * abs(ref_loss / 2)
     assert abs(top1 - ref1 / 2) < 1e-6 and abs(top5 - ref5 / 2) < 1e-6
+
+
+def test_run_epochs_schedules_checkpoints_and_resumes(tmp_path):
+    """epochs.run_epochs (train.py:310-428) on a toy loader: validate at epoch 0, train/validate per epoch, StepLR moves the
+    rate of the captured step, one checkpoint per epoch in the reference's format, and a resumed run continues from it."""
+    import glob
+    import os
+    from torch import optim
+    torch.manual_seed(0)
+    dv.set_compute_dtype(torch.bfloat16)
+    g = torch.Generator().manual_seed(5)
+    batches = [{"image": torch.randn(8, 3, 64, 64, generator=g), "annotation": torch.randint(0, 1000, (8,), generator=g)} for _ in range(4)]
+    cfg = dict(dv.epochs.training_config["mobilenet1"])
+    cfg.update(scheduler=optim.lr_scheduler.StepLR, scheduler_params={"step_size": 1, "gamma": 0.5}, total_epochs=2)
+    net, trainer, sched, loggers = dv.epochs.run_epochs(cfg, None, batches, batches[:2], model_dir=str(tmp_path) + "/", verbose=False)
+    assert abs(trainer.lr - 0.045 * 0.25) < 1e-12
+    assert loggers["val_loss"]["epochs"] == [0, 1, 2] and len(loggers["val_top5_acc"]["value"]) == 3
+    files = sorted(glob.glob(os.path.join(tmp_path, "mobilenet1-*-epoch-*.pt")))
+    assert len(files) == 2
+    ck = torch.load(files[-1], weights_only=False)
+    assert set(ck) == {"epoch", "model", "optimizer", "scheduler", "loggers"} and ck["epoch"] == 2
+    assert set(ck["model"]) == set(net.state_dict())
+    assert all(np.isfinite(v) for v in loggers["val_loss"]["value"])
+    # resume: epoch 3 only, starting from the saved rate and optimiser state
+    cfg["total_epochs"] = 3
+    net2, trainer2, sched2, loggers2 = dv.epochs.run_epochs(cfg, files[-1], batches, batches[:2], model_dir=str(tmp_path) + "/r/",
+                                                             verbose=False)
+    assert loggers2["val_loss"]["epochs"] == [0, 1, 2, 0, 3]
+    assert abs(trainer2.lr - 0.045 * 0.125) < 1e-12
+    assert trainer2.steps_done > 0 and float(trainer2.flat_s.abs().sum()) > 0
