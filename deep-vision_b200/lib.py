@@ -36,6 +36,15 @@ class DwConvParams(C.Structure):
     ]
 
 
+class AugmentParams(C.Structure):
+    _fields_ = [
+        ("src", C.c_void_p), ("dst", C.c_void_p), ("geom", C.c_void_p), ("factors", C.c_void_p), ("widths", C.c_void_p),
+        ("gray_sums", C.c_void_p),
+        ("B", C.c_int32), ("Hs", C.c_int32), ("Ws", C.c_int32), ("crop", C.c_int32), ("dtype", C.c_int32), ("nchw", C.c_int32),
+        ("mean", C.c_float * 3), ("std", C.c_float * 3),
+    ]
+
+
 class BnParams(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("y", C.c_void_p), ("residual", C.c_void_p),
@@ -75,6 +84,7 @@ _SIG = {
     "dv_dwconv_dgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_wgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_workspace_bytes": (C.c_size_t, [C.POINTER(DwConvParams)]),
+    "dv_augment": (C.c_int, [C.POINTER(AugmentParams), _P]),
     "dv_bn_fold": (C.c_int, [_P, _P, _P, _P, C.c_float, _P, _P, C.c_int, _P, _P, _P]),
     "dv_bn_stats": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_apply": (C.c_int, [C.POINTER(BnParams), _P]),

@@ -255,6 +255,31 @@ int dv_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream);
 int dv_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Input pipeline after decode + rescale: the reference's per-image transforms
+ *   RandomHorizontalFlip -> RandomCrop | CenterCrop -> ColorJitter(brightness, contrast, saturation; hue 0)
+ *   -> ToTensor (float, NOT divided by 255) -> Normalize(mean, std)
+ * ResNet/pytorch/data_load.py:102-297 as composed at train.py:315-331, for a whole uint8 batch in two launches,
+ * writing the model's input directly (NHWC compute dtype, or NCHW fp32 as the reference's loader yields).
+ * The uint8 stages are Pillow's arithmetic bit for bit (oracle/ref_augment.py); the random draws stay with the caller.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct dv_augment_params {
+  const uint8_t* src;     /* [B][Hs][Ws][3] uint8 RGB: decoded and Rescale'd images (data_load.py:49-99), each in the
+                             top-left corner of its Hs x Ws slot */
+  void* dst;              /* [B][crop][crop][3] dtype (NHWC), or [B][3][crop][crop] when nchw != 0 */
+  const int32_t* geom;    /* device [B][4]: top, left, flip (0/1), order = index into the permutations
+                             (b,c,s) (b,s,c) (c,b,s) (c,s,b) (s,b,c) (s,c,b) of brightness/contrast/saturation
+                             (data_load.py:270 shuffles them); order < 0 = no colour jitter (validation) */
+  const float* factors;   /* device [B][3]: brightness, contrast, saturation factors (data_load.py:248-262) */
+  const int32_t* widths;  /* device [B] true image widths (the flip mirrors the image, not the slot) or NULL = Ws */
+  uint32_t* gray_sums;    /* device [B] scratch */
+  int32_t B, Hs, Ws, crop;
+  int32_t dtype;          /* of dst */
+  int32_t nchw;
+  float mean[3], std[3];  /* train.py:324: 0.485,0.456,0.406 / 0.229,0.224,0.225 applied to 0..255 values */
+} dv_augment_params;
+int dv_augment(const dv_augment_params* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Stem / tail ops.
  * ------------------------------------------------------------------------------------------ */
 /* nn.MaxPool2d(3, 2, 1) — resnet50.py:34, resnet34.py:34.  idx: uint8 [N,P,Q,C] window position (0..8) of the max. */
