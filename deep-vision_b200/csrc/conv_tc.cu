@@ -257,6 +257,9 @@ struct GemmArgs {
   int P, Q, stride, pad;
   int scatter;      // 1: row (n,p,q) is written at pixel (n, p*os, q*os) of an [*, Ho, Wo, Nout] tensor
   int Ho, Wo, os;
+  int oa, ob;       // scatter: row/column offset added to (p*os, q*os) — the parity class of a stride-2 dgrad
+  int use_btap;     // 1: the filter tap of reduction step `tap` is btap[tap] (sub-sampled taps of a parity class)
+  signed char btap[12];
   int out_f32;      // 1: `out` is float* (fp32 logits of the classifier)
   int accumulate;   // 1: out += result (bf16 read-modify-write by the owning thread)
   float* stat_sums; // fprop, optional: [2][Nout] fp32, += per-channel sum and sum of squares of the bf16-rounded output
@@ -396,9 +399,10 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             // filters [K][taps*Nout]: rows = reduction channels cb*64.., columns = flipped tap's slice of the output channels
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(sB + j * 8192, &tmB, &full_bar[stage], (g.taps - 1 - tap) * g.Nout + n_tile * BN + j * 64, cb * kBlockK);
+              tma_load_2d(sB + j * 8192, &tmB, &full_bar[stage], (g.use_btap ? g.btap[tap] : g.taps - 1 - tap) * g.Nout + n_tile * BN + j * 64,
+                          cb * kBlockK);
           } else {
-            tma_load_2d(sB, &tmB, &full_bar[stage], tap * g.Cin + cb * kBlockK, n_tile * BN);
+            tma_load_2d(sB, &tmB, &full_bar[stage], (g.use_btap ? g.btap[tap] : tap) * g.Cin + cb * kBlockK, n_tile * BN);
           }
         }
         __syncwarp();
@@ -486,7 +490,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             const int pq = g.P * g.Q;
             const int n_img = m / pq, rem = m - n_img * pq;
             const int pp = rem / g.Q, qq = rem - pp * g.Q;
-            off = (((size_t)n_img * g.Ho + (size_t)pp * g.os) * g.Wo + (size_t)qq * g.os) * g.Nout;
+            off = (((size_t)n_img * g.Ho + (size_t)pp * g.os + g.oa) * g.Wo + (size_t)qq * g.os + g.ob) * g.Nout;
           } else {
             off = (size_t)m * g.Nout;
           }
@@ -505,7 +509,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             const int pq = g.P * g.Q;
             const int n_img = m / pq, rem = m - n_img * pq;
             const int pp = rem / g.Q, qq = rem - pp * g.Q;
-            ro = (((size_t)n_img * g.Ho + (size_t)pp * g.os) * g.Wo + (size_t)qq * g.os) * g.Nout;
+            ro = (((size_t)n_img * g.Ho + (size_t)pp * g.os + g.oa) * g.Wo + (size_t)qq * g.os + g.ob) * g.Nout;
           } else {
             ro = (size_t)m * g.Nout;
           }
@@ -1093,8 +1097,9 @@ static int make_map_2d(CUtensorMap* tm, const void* ptr, uint64_t rows, uint64_t
 // NHWC activation, im2col traversal of a R x S window with the given stride / padding; one load = `pixels` output
 // positions (walking q, then p, then n) x 64 channels.  Coordinates passed to the load are the input coordinate of
 // the window's top-left tap for the first output position: (c, q*stride - pad, p*stride - pad, n), offsets = (s, r).
+// corners != nullptr: {lower_w, lower_h, upper_w, upper_h} given explicitly (window origins run over [lower, dim - 1 + upper])
 static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W, int C, int R, int S, int stride, int pad,
-                           uint32_t pixels) {
+                           uint32_t pixels, const int* corners = nullptr) {
   DriverApi& api = driver_api();
   DV_REQUIRE(api.ok, DV_ERR_CUDA, "conv_tc: cuTensorMapEncode* entry points not available from the driver");
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
@@ -1102,6 +1107,7 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
   // bounding box of window origins: [-pad, dim - 1 + pad - (filter - 1)]  (W first, then H)
   int lower[2] = {-pad, -pad};
   int upper[2] = {pad - (S - 1), pad - (R - 1)};
+  if (corners) { lower[0] = corners[0]; lower[1] = corners[1]; upper[0] = corners[2]; upper[1] = corners[3]; }
   cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   CUresult r = api.im2col(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, lower, upper, 64,
                           pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -1259,7 +1265,8 @@ bool conv_tc_supported(const dv_conv_params* p, int pass, const char** why) {
       return true;
     }
     if (p->R == 1 && p->S == 1 && p->pad == 0) return true;  // strided 1x1: GEMM + scatter
-    *why = "strided dgrad with R,S>1 is SIMT only";
+    if (p->R == 3 && p->S == 3 && p->pad == 1 && p->stride == 2) return true;  // four parity-class sub-convolutions
+    *why = "strided dgrad with R,S>1 exists for 3x3 stride 2 pad 1 only";
     return false;
   }
   if (pass == DV_CONV_WGRAD) {
@@ -1385,6 +1392,44 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
       g.a_im2col = !(p->R == 1 && p->S == 1);
       if (g.a_im2col) rc = make_map_im2col(&tmA, p->y, p->N, P, Q, p->K, p->R, p->S, 1, padp, kBlockM);
       else rc = make_map_2d(&tmA, p->y, (uint64_t)g.M, (uint64_t)p->K, kBlockM);
+    } else if (p->R == 3) {
+      // 3x3 stride 2 pad 1 (ResNet-34's down-sampling convs, resnet34.py:96-103): h = 2p + r - 1 ties the parity of h to the
+      // filter row — even h only meets r = 1, odd h meets r = 2 (p = (h-1)/2) and r = 0 (p = (h+1)/2); the same along w.
+      // So dx splits into four parity classes, each a STRIDE-1 convolution of dy with 1, 2, 2 or 4 of the nine taps: four
+      // launches with exactly the useful FLOPs, the im2col map walking a 1x1 / 1x2 / 2x1 / 2x2 window over dy (one past the
+      // edge reads as zero), rows scattered to (2i + a, 2j + b).  Every dx pixel belongs to one class: no memset.
+      // (accumulate: the scatter epilogue reads-modifies-writes its own pixels, as for the strided 1x1 case)
+      if (b_mn) rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, 64);
+      else rc = make_map_2d(&tmB, p->w_t, (uint64_t)p->C, (uint64_t)p->R * p->S * p->K, (uint32_t)bn);
+      if (rc) return rc;
+      for (int a = 0; a < 2; ++a) {
+        for (int b = 0; b < 2; ++b) {
+          const int Hc = (p->H - a + 1) / 2, Wc = (p->W - b + 1) / 2;
+          if (Hc <= 0 || Wc <= 0) continue;
+          const int Ta = a ? 2 : 1, Tb = b ? 2 : 1;
+          GemmArgs gc = g;
+          gc.M = p->N * Hc * Wc;
+          gc.taps = Ta * Tb;
+          gc.S = Tb;
+          gc.P = Hc; gc.Q = Wc; gc.stride = 1; gc.pad = 0;
+          gc.a_im2col = 1;
+          gc.scatter = 1; gc.Ho = p->H; gc.Wo = p->W; gc.os = 2; gc.oa = a; gc.ob = b;
+          gc.use_btap = 1;
+          for (int dp = 0; dp < Ta; ++dp) {
+            for (int dq = 0; dq < Tb; ++dq) {
+              const int r = a ? 2 - 2 * dp : 1, s2 = b ? 2 - 2 * dq : 1;
+              const int fr = r * 3 + s2;
+              gc.btap[dp * Tb + dq] = (signed char)(b_mn ? fr : 8 - fr);  // w_t holds the taps flipped
+            }
+          }
+          const int corners[4] = {0, 0, Wc - Q, Hc - P};  // origins 0..Wc-1 / 0..Hc-1; the second tap may read column Q / row P = zero
+          rc = make_map_im2col(&tmA, p->y, p->N, P, Q, p->K, Ta, Tb, 1, 0, kBlockM, corners);
+          if (rc) return rc;
+          rc = gemm_dispatch(tmA, tmB, gc, bn, b_mn, st);
+          if (rc) return rc;
+        }
+      }
+      return DV_OK;
     } else {
       // 1x1 stride s: dx[n, p*s, q*s, :] = dy[n,p,q,:] * w ; every other pixel of dx is zero
       if (!p->accumulate) DV_CUDA_OK(cudaMemsetAsync(p->x, 0, (size_t)p->N * p->H * p->W * p->C * sizeof(bf16), st));

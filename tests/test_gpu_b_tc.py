@@ -44,7 +44,11 @@ def test_tc_fprop_matches_oracle(case):
     assert np.max(np.abs(y - y_ref) / (np.abs(y_ref) + 1e-2)) < 2e-2
 
 
-DGRAD_CASES = [c for c in TC_CASES if not (c[5] == 3 and c[6] == 2) and (c[4] % 64 == 0 or (c[5] == 1 and c[4] % 8 == 0))]
+DGRAD_CASES = [c for c in TC_CASES if (c[4] % 64 == 0 or (c[5] == 1 and c[4] % 8 == 0))] + [
+    (2, 64, 8, 8, 128, 3, 2, 1),      # 3x3 stride 2, even size: four parity classes of equal extent
+    (3, 128, 10, 7, 64, 3, 2, 1),     # H != W, even/odd mix: the odd classes are one row / column shorter
+    (2, 64, 2, 3, 64, 3, 2, 1),       # tiny: a class with a single row
+]
 
 
 @pytest.mark.parametrize("use_wt", [False, True], ids=["krsc_mn_major", "transposed_copy"])
@@ -121,6 +125,7 @@ FULL_CASES = [
     (256, 256, 14, 256, 3, 1, 1),
     (256, 512, 7, 512, 3, 1, 1),
     (256, 2048, 7, 512, 1, 1, 0),
+    (256, 64, 56, 128, 3, 2, 1),      # ResNet-34's first down-sampling 3x3 (resnet34.py:96-103): dgrad = four parity classes
 ]
 
 
@@ -212,7 +217,8 @@ def test_tc_fp32_logits_and_dgrad_accumulate():
     assert rel_l2(y.double().cpu().numpy(), ref) < 1e-5       # exact bf16 products, fp32 accumulate, no output rounding
 
     for case, algo in (((2, 64, 8, 8, 128, 1, 1, 0), lib.DV_ALGO_TC), ((2, 64, 8, 8, 128, 1, 2, 0), lib.DV_ALGO_TC),
-                       ((2, 64, 8, 8, 64, 3, 1, 1), lib.DV_ALGO_TC), ((2, 64, 9, 9, 128, 3, 2, 1), lib.DV_ALGO_SIMT)):
+                       ((2, 64, 8, 8, 64, 3, 1, 1), lib.DV_ALGO_TC), ((2, 64, 9, 9, 128, 3, 2, 1), lib.DV_ALGO_SIMT),
+                       ((2, 64, 9, 9, 128, 3, 2, 1), lib.DV_ALGO_TC), ((2, 128, 12, 10, 64, 3, 2, 1), lib.DV_ALGO_TC)):
         N, Cc, H, W, K, R, stride, pad = case
         xs = _rand((N, Cc, H, W), 1, BF)
         ws = _rand((K, Cc, R, R), 2, BF, scale=0.1)
