@@ -9,7 +9,7 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from deep_vision_b200.lib import BnParams, ConvParams, DV_ALGO_TC, DV_BF16, DV_CONV_WGRAD, check, lib  # noqa: E402
+from deep_vision_b200.lib import BnParams, ConvParams, DwConvParams, DV_ALGO_TC, DV_BF16, DV_CONV_WGRAD, check, lib  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--which", default="fprop")
@@ -20,7 +20,27 @@ args = ap.parse_args()
 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def run_dw(which, shape, iters):
+    N, H, Cc, stride = (int(v) for v in shape.split(","))
+    P = (H - 1) // stride + 1
+    x = torch.randn(N, H, H, Cc, device="cuda").to(torch.bfloat16)
+    y = torch.randn(N, P, P, Cc, device="cuda").to(torch.bfloat16)
+    w = torch.randn(Cc, 3, 3, device="cuda")
+    p = DwConvParams()
+    p.x, p.w, p.y, p.N, p.H, p.W, p.C, p.stride, p.dtype = x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, H, Cc, stride, DV_BF16
+    need = lib.dv_dwconv_workspace_bytes(C.byref(p))
+    ws = torch.empty(max(need, 16), dtype=torch.uint8, device="cuda")
+    p.workspace, p.workspace_bytes = ws.data_ptr(), need
+    fn = {"dw_fprop": lib.dv_dwconv_fprop, "dw_dgrad": lib.dv_dwconv_dgrad, "dw_wgrad": lib.dv_dwconv_wgrad}[which]
+    for _ in range(iters):
+        check(fn(C.byref(p), st), which)
+    torch.cuda.synchronize()
+    print("ok", which)
+
+
 def run_job(which, shape, iters):
+    if which.startswith("dw_"):
+        return run_dw(which, shape, iters)
     N, H, Cc, K, R = (int(v) for v in shape.split(","))
     x = torch.randn(N, H, H, Cc, device="cuda").to(torch.bfloat16)
     w = (torch.randn(K, R, R, Cc, device="cuda") * 0.05).to(torch.bfloat16)

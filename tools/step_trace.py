@@ -21,7 +21,7 @@ args = ap.parse_args()
 torch.cuda.set_device(0)
 dv.set_compute_dtype(torch.bfloat16)
 torch.manual_seed(0)
-ctor = {"resnet50": "ResNet50", "resnet34": "ResNet34", "resnet152": "ResNet152", "mobilenet_v1": "MobileNetV1"}[args.model]
+ctor = {"resnet50": "ResNet50", "resnet34": "ResNet34", "resnet152": "ResNet152", "mobilenet1": "MobileNetV1"}[args.model]
 net = getattr(dv.models, ctor)().cuda()
 cfg = dict(TRAINING_CONFIG[args.model])
 cfg.pop("batch_size")
