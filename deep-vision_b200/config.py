@@ -8,7 +8,8 @@ _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
           "deterministic": os.environ.get("DV_DETERMINISTIC", "0") == "1",
           "atomic_wgrad": os.environ.get("DV_ATOMIC_WGRAD", "1") == "1",
           "atomic_bn_bwd": os.environ.get("DV_ATOMIC_BN", "0") == "1",
-          "fold_bn": os.environ.get("DV_FOLD_BN", "1") != "0"}
+          "fold_bn": os.environ.get("DV_FOLD_BN", "1") != "0",
+          "side_wgrad": os.environ.get("DV_SIDE_WGRAD", "1") == "1"}
 
 
 def compute_dtype():
@@ -84,3 +85,8 @@ def set_fold_bn(flag):
     the models runs as ONE kernel: the convolution with the BN folded into its epilogue (inference.py).  False: eval-mode
     BN stays a separate normalise pass."""
     _state["fold_bn"] = bool(flag)
+
+
+def side_wgrad():
+    """Trainer: launch dense weight-gradient kernels on a second stream beside the dgrad -> BN-backward chain."""
+    return _state["side_wgrad"] and not _state["deterministic"]

@@ -192,6 +192,41 @@ def _run_conv(fn, p, pass_id, device, what):
     check(fn(C.byref(p), _stream()), what)
 
 
+class SideWgrad:
+    """Weight-gradient kernels on a second stream.  A layer's wgrad depends only on tensors that exist before its dgrad
+    starts and nothing in the backward chain waits for it, so the trainer lets it run beside the chain
+    dgrad -> BN backward -> dgrad: a tensor-bound 3x3 wgrad then shares the SMs with the HBM-bound BatchNorm passes.
+    `fork` makes the side stream wait for the producer of dy; the tensors it reads are kept alive until `join`, which
+    the trainer calls once after backward (before the gradient exchange finishes and the optimiser runs)."""
+
+    def __init__(self, device):
+        self.stream = torch.cuda.Stream(device=device)
+        self.keep = []
+        self.used = False
+
+    def fork(self, *tensors):
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream())
+        self.stream.wait_event(ev)
+        self.keep.extend(tensors)
+        self.used = True
+        return self.stream
+
+    def join(self):
+        if self.used:
+            torch.cuda.current_stream().wait_stream(self.stream)
+        self.keep.clear()
+        self.used = False
+
+
+_side_wgrad = {"obj": None}
+
+
+def set_side_wgrad(obj):
+    """Installed by the Trainer around loss.backward(); None = weight gradients on the current stream."""
+    _side_wgrad["obj"] = obj
+
+
 class _Conv2d(torch.autograd.Function):
     """y = conv2d(x, weight) without bias — nn.Conv2d at resnet50.py:20-28,101-143; resnet34.py:20-28,96-126;
     mobilenet_v1.py:30,139-145.  Backward = dgrad + wgrad (autograd of train.py:460)."""
@@ -282,7 +317,12 @@ class _Conv2d(torch.autograd.Function):
                 dw = torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
             p = _conv_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo,
                              accumulate=atomic)
-            _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad")
+            side = _side_wgrad["obj"] if (sink and atomic) else None   # direct write into the flat buffer, no workspace
+            if side is not None:
+                with torch.cuda.stream(side.fork(x, dy)):
+                    _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad")
+            else:
+                _run_conv(lib.dv_conv_wgrad, p, DV_CONV_WGRAD, x.device, "dv_conv_wgrad")
             if sink:
                 sink[1](weight)
                 dw = None

@@ -114,6 +114,9 @@ class BucketedAllReduce:
             if self._pending[b] == 0:
                 s, e = self.buckets[b]
                 self.launch_order.append(b)
+                side = getattr(self, "side", None)
+                if side is not None and side.used:   # weight gradients of this bucket may still be running on the side stream
+                    torch.cuda.current_stream().wait_stream(side.stream)
                 self._works.append(dist.all_reduce(self.flat.flat_g[s:e], op=dist.ReduceOp.SUM, group=self.pg, async_op=True))
         return hook
 
@@ -140,6 +143,7 @@ class Trainer:
         self.flat_s = torch.zeros_like(self.flat_p)  # momentum buffer / squared-gradient average
         config.bump_weight_epoch()
         self.exchange = BucketedAllReduce(self.flat, bucket_bytes, process_group) if self.world > 1 else None
+        self._side = dvF.SideWgrad(self.flat_p.device)
         self._install_direct_grads()
         self._flatten_bn_counters()
         self._install_bf16_filters()
@@ -202,7 +206,16 @@ class Trainer:
             self.exchange.reset()
         logits = self.model(images)
         loss = dvF.cross_entropy(logits, labels)
-        loss.backward()
+        side = self._side if config.side_wgrad() else None
+        dvF.set_side_wgrad(side)
+        if self.exchange is not None:
+            self.exchange.side = side
+        try:
+            loss.backward()
+        finally:
+            dvF.set_side_wgrad(None)
+        if side is not None:
+            side.join()
         if self.exchange is not None:
             self.exchange.finish()
         self._optimizer_step()
