@@ -54,8 +54,11 @@ def test_algo_selection_is_host_logic():
     assert lib.lib.dv_conv_algo(C.byref(p), lib.DV_CONV_FPROP) == lib.DV_ALGO_SIMT
     p.C, p.K, p.R, p.S, p.stride, p.pad, p.H, p.W = 64, 128, 3, 3, 2, 1, 56, 56                # ResNet-34 3x3 stride 2
     assert lib.lib.dv_conv_algo(C.byref(p), lib.DV_CONV_FPROP) == lib.DV_ALGO_TC
-    assert lib.lib.dv_conv_algo(C.byref(p), lib.DV_CONV_DGRAD) == lib.DV_ALGO_SIMT
+    assert lib.lib.dv_conv_algo(C.byref(p), lib.DV_CONV_DGRAD) == lib.DV_ALGO_TC      # four parity-class sub-convolutions
     assert lib.lib.dv_conv_algo(C.byref(p), lib.DV_CONV_WGRAD) == lib.DV_ALGO_TC
+    p.R, p.S, p.pad = 5, 5, 2                                                          # any other strided RxS dgrad: CUDA cores
+    assert lib.lib.dv_conv_algo(C.byref(p), lib.DV_CONV_DGRAD) == lib.DV_ALGO_SIMT
+    p.R, p.S, p.pad = 3, 3, 1
     # wgrad scratch is sized by host logic and is a whole number of [K,R,S,C] fp32 slabs
     need = lib.lib.dv_conv_workspace_bytes(C.byref(p), lib.DV_CONV_WGRAD)
     assert need > 0 and need % (128 * 9 * 64 * 4) == 0
