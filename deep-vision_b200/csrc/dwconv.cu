@@ -44,6 +44,25 @@ __device__ __forceinline__ void load_taps(float (*ws)[128 * V], const float* __r
 // accumulators already fill the register budget
 template <int ST> struct StripW { static constexpr int fwd = ST == 1 ? 4 : 2; static constexpr int wgrad = 2; };
 
+// packed fp32 pairs: sm_100's fma.rn.f32x2 does two channels per instruction (ncu on the scalar version: issue slots 67 %
+// busy at 43 % of the HBM roof — the depth-wise kernels are bound by instruction issue before they are bound by memory)
+__device__ __forceinline__ void unpack2(const Vec16<float>& v, float2* f) { f[0] = make_float2(v.raw.x, v.raw.y); f[1] = make_float2(v.raw.z, v.raw.w); }
+__device__ __forceinline__ void unpack2(const Vec16<bf16>& v, float2* f) {
+  const uint32_t w[4] = {v.raw.x, v.raw.y, v.raw.z, v.raw.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) f[i] = make_float2(__uint_as_float(w[i] << 16), __uint_as_float(w[i] & 0xffff0000u));
+}
+__device__ __forceinline__ void pack2(Vec16<float>& v, const float2* f) { v.raw = make_float4(f[0].x, f[0].y, f[1].x, f[1].y); }
+__device__ __forceinline__ void pack2(Vec16<bf16>& v, const float2* f) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(f[i].x, f[i].y);
+    w[i] = *reinterpret_cast<uint32_t*>(&h);
+  }
+  v.raw = make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 template <typename T, int ST>
 __global__ void __launch_bounds__(kThreads, 2)
 dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __restrict__ out, int N, int IH, int IW, int OH, int OW,
@@ -62,19 +81,20 @@ dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __
   const int nstrips = N * OH * strips_w;
   const int s0 = blockIdx.x * strips_per_blk;
   const int s1 = min(nstrips, s0 + strips_per_blk);
-  float bias[V];  // folded-BatchNorm shift (inference) or zero
+  constexpr int H2 = V / 2;
+  float2 bias[H2];  // folded-BatchNorm shift (inference) or zero
 #pragma unroll
-  for (int e = 0; e < V; ++e) bias[e] = ep_shift != nullptr ? ep_shift[c + e] : 0.f;
+  for (int e = 0; e < H2; ++e) bias[e] = ep_shift != nullptr ? make_float2(ep_shift[c + 2 * e], ep_shift[c + 2 * e + 1]) : make_float2(0.f, 0.f);
   for (int sidx = s0 + lane; sidx < s1; sidx += lanes) {
     const int sw = sidx % strips_w;
     const int t = sidx / strips_w;
     const int oh = t % OH, n = t / OH;
     const int ow0 = sw * TW;
-    float acc[TW][V];
+    float2 acc[TW][H2];
 #pragma unroll
     for (int j = 0; j < TW; ++j)
 #pragma unroll
-      for (int e = 0; e < V; ++e) acc[j][e] = bias[e];
+      for (int e = 0; e < H2; ++e) acc[j][e] = bias[e];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
       const int ih = oh * ST + r - 1;
@@ -86,30 +106,30 @@ dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __
         const int iw = ow0 * ST - 1 + k;
         if ((unsigned)iw < (unsigned)IW) raw[k].load(row + (size_t)iw * C);
       }
-      float xv[NCOL][V];
+      float2 xv[NCOL][H2];
 #pragma unroll
       for (int k = 0; k < NCOL; ++k) {
         const int iw = ow0 * ST - 1 + k;
-        if ((unsigned)iw < (unsigned)IW) raw[k].unpack(xv[k]);
+        if ((unsigned)iw < (unsigned)IW) unpack2(raw[k], xv[k]);
         else {
 #pragma unroll
-          for (int e = 0; e < V; ++e) xv[k][e] = 0.f;
+          for (int e = 0; e < H2; ++e) xv[k][e] = make_float2(0.f, 0.f);
         }
       }
       // one shared-memory read of each tap's weights per strip (not per output): the taps are the outer loop
 #pragma unroll
       for (int s = 0; s < 3; ++s) {
-        float wv[V];
+        float2 wv[H2];
         const float* wt = &ws[r * 3 + s][tcg * V];
 #pragma unroll
         for (int e = 0; e < V; e += 4) {
           const float4 q4 = *reinterpret_cast<const float4*>(wt + e);
-          wv[e] = q4.x; wv[e + 1] = q4.y; wv[e + 2] = q4.z; wv[e + 3] = q4.w;
+          wv[e / 2] = make_float2(q4.x, q4.y); wv[e / 2 + 1] = make_float2(q4.z, q4.w);
         }
 #pragma unroll
         for (int j = 0; j < TW; ++j) {
 #pragma unroll
-          for (int e = 0; e < V; ++e) acc[j][e] = fmaf(xv[j * ST + s][e], wv[e], acc[j][e]);
+          for (int e = 0; e < H2; ++e) acc[j][e] = __ffma2_rn(xv[j * ST + s][e], wv[e], acc[j][e]);
         }
       }
     }
@@ -118,11 +138,11 @@ dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __
 #pragma unroll
       for (int j = 0; j < TW; ++j)
 #pragma unroll
-        for (int e = 0; e < V; ++e) acc[j][e] = fmaxf(acc[j][e], 0.f);
+        for (int e = 0; e < H2; ++e) acc[j][e] = make_float2(fmaxf(acc[j][e].x, 0.f), fmaxf(acc[j][e].y, 0.f));
     }
 #pragma unroll
     for (int j = 0; j < TW; ++j) {
-      if (ow0 + j < OW) { Vec16<T> o; o.pack(acc[j]); o.store(orow + (size_t)j * C); }
+      if (ow0 + j < OW) { Vec16<T> o; pack2(o, acc[j]); o.store(orow + (size_t)j * C); }
     }
   }
 }
