@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdv_b200.so")
+LIB_PATH = os.environ.get("DV_B200_LIB") or os.path.join(_HERE, "libdv_b200.so")   # override: A/B builds of the same ABI
 
 DV_F32, DV_BF16 = 0, 1
 DV_ALGO_AUTO, DV_ALGO_SIMT, DV_ALGO_TC = 0, 1, 2
