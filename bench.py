@@ -153,11 +153,44 @@ def kernel_roofline(torch, dv, pk):
     ms = sum(times) / len(times)
     flops = 2.0 * N * H * H * K * Cc * R * R
     achieved = flops / (ms * 1e-3) / 1e12
-    return {"bound": "tensor", "kernel": "conv_tc_gemm_persistent_kernel<256,4> fprop 3x3 256->256 @14x14 B256", "achieved": round(achieved, 1),
+    return {"bound": "tensor", "kernel": "conv_tc_gemm_pair_kernel<6> (cta_group::2) fprop 3x3 256->256 @14x14 B256", "achieved": round(achieved, 1),
             "peak": pk["tf_burst"], "unit": "TFLOP/s", "frac": round(achieved / pk["tf_burst"], 4),
-            # dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` (profiles/r01_ncu_full_gemm.csv);
+            # dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` (profiles/r01_ncu_full_v9_pair_wgrad.csv);
             # the algorithmic minimum is 52.6 MB (x 25.7 + y 25.7 + w 1.2): the output was still in L2 when the capture ended
             "traffic": 26.9e6, "algorithmic_flops": flops,
+            "ms_per_launch": round(ms, 4), "peak_source": pk["source"]}
+
+
+def hbm_roofline(torch, pk):
+    """The dominant HBM-bound kernel class of the step (BatchNorm passes = 45 % of it): dv_bn_bwd_apply on a 256-channel
+    56x56 tensor at batch 256 (no residual: reads x and dy, writes dx = 6 bytes per element), CUDA events, L2 flushed."""
+    import ctypes as C
+    from deep_vision_b200.lib import BnBwdParams, DV_BF16, check, lib
+    M, Cc = 256 * 56 * 56, 256
+    x, dy, dx = (torch.randn(M, Cc, device="cuda").to(torch.bfloat16) for _ in range(3))
+    g, b, sm, si, dg, db = (torch.ones(Cc, device="cuda") for _ in range(6))
+    q = BnBwdParams()
+    q.x, q.dy, q.dx, q.gamma, q.beta = x.data_ptr(), dy.data_ptr(), dx.data_ptr(), g.data_ptr(), b.data_ptr()
+    q.save_mean, q.save_invstd, q.dgamma, q.dbeta = sm.data_ptr(), si.data_ptr(), dg.data_ptr(), db.data_ptr()
+    q.M, q.C, q.dtype, q.relu = M, Cc, DV_BF16, 1
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for _ in range(3):
+        check(lib.dv_bn_bwd_apply(C.byref(q), st), "dv_bn_bwd_apply")
+    times = []
+    for _ in range(10):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        check(lib.dv_bn_bwd_apply(C.byref(q), st), "dv_bn_bwd_apply")
+        e1.record()
+        e1.synchronize()
+        times.append(e0.elapsed_time(e1))
+    ms = sum(times) / len(times)
+    nbytes = 6.0 * M * Cc
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": "bn_bwd_apply_kernel<bf16> C=256 @56x56 B256 (ReLU mask recomputed)", "achieved": round(gbs, 1),
+            "peak": pk["hbm"], "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4), "traffic": None, "algorithmic_bytes": nbytes,
             "ms_per_launch": round(ms, 4), "peak_source": pk["source"]}
 
 
@@ -282,6 +315,7 @@ def run_ours(args):
         if world == 1 and not args.no_roofline:
             try:
                 line["roofline"] = kernel_roofline(torch, dv, pk)
+                line["roofline_hbm"] = hbm_roofline(torch, pk)
             except Exception as e:  # the headline number stands on its own
                 line["roofline"] = {"error": str(e)[:200]}
         if world == 1 and not args.no_cpu_baseline:

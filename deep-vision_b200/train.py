@@ -104,11 +104,18 @@ class BucketedAllReduce:
 
     def reset(self):
         self._pending = list(self._need)
+        self._fired = [False] * len(self.flat.params)
         self._works = []
         self.launch_order = []
 
     def _make_hook(self, j):
         def hook(_param):
+            # A parameter whose gradient is written directly by a kernel reports here itself (functional.grad_sink), and
+            # torch may run the post-accumulate hook for it as well (it does so even when backward returned None for the
+            # parameter): count each parameter once per step.
+            if self._fired[j]:
+                return
+            self._fired[j] = True
             b = self._bucket_of[j]
             self._pending[b] -= 1
             if self._pending[b] == 0:

@@ -97,3 +97,45 @@ def test_bucketed_allreduce_world2_equals_global_batch_gradient():
         expect = g if expect is None else expect + g
     expect = expect / 2
     assert torch.allclose(g0, expect, rtol=1e-5, atol=1e-7)
+
+
+def test_hooks_count_each_parameter_once_per_step():
+    """A parameter whose gradient a kernel writes directly reports to the exchange itself, and torch runs the
+    post-accumulate hook for it too (even when backward returned None for it).  The second report must not count: it used to
+    release a bucket's all-reduce after HALF of its gradients (found on 2 GPUs with tools/dp_check.py)."""
+    m = _tiny()
+    flat = FlatParams(m)
+    ex = BucketedAllReduce.__new__(BucketedAllReduce)      # host logic only: no process group, collectives stubbed
+    ex.flat, ex.pg = flat, None
+    ex.buckets = plan_buckets(flat.offsets, flat.total, 64)
+    ex._bucket_of, ex._need = {}, []
+    for b, (s, e) in enumerate(ex.buckets):
+        members = [j for j, o in enumerate(flat.offsets) if s <= o < e]
+        ex._need.append(len(members))
+        for j in members:
+            ex._bucket_of[j] = b
+    launched = []
+    import deep_vision_b200.train as tr
+
+    class _Work:
+        def wait(self):
+            pass
+
+    orig = tr.dist.all_reduce
+    tr.dist.all_reduce = lambda t, **kw: (launched.append((t.data_ptr(), t.numel())), _Work())[1]
+    try:
+        ex.reset()
+        hooks = [ex._make_hook(j) for j in range(len(flat.params))]
+        order = list(reversed(range(len(hooks))))           # backward visits parameters last to first
+        for n, j in enumerate(order):
+            hooks[j](flat.params[j])
+            hooks[j](flat.params[j])                         # the duplicate report
+            done = {ex._bucket_of[k] for k in order[:n + 1]}
+            # a bucket is out only when ALL of its members have reported once
+            for b in ex.launch_order:
+                assert all(k in order[:n + 1] for k, bb in ex._bucket_of.items() if bb == b)
+            assert set(ex.launch_order) <= done
+        assert sorted(ex.launch_order) == list(range(len(ex.buckets))) and ex._pending == [0] * len(ex.buckets)
+        assert len(launched) == len(ex.buckets)
+    finally:
+        tr.dist.all_reduce = orig
