@@ -206,6 +206,8 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # NCCL announces its version on stdout when NCCL_DEBUG is VERSION or higher; stdout carries exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     if lib.dv_device_check() != 0:
         raise RuntimeError(lib.dv_last_error().decode())
