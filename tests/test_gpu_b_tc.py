@@ -27,6 +27,9 @@ TC_CASES = [
     (2, 32, 8, 8, 64, 1, 1, 0),       # C=32: MobileNet's first point-wise conv; TMA zero-fills the half-empty K block
     (3, 96, 5, 5, 32, 1, 1, 0),       # C=96 (1.5 K blocks), K=32 (tile wider than the tensor)
     (2, 192, 6, 6, 64, 1, 1, 0),      # patch-matrix shape class of the 7x7 stem (Kp=192)
+    (151, 64, 16, 8, 256, 1, 1, 0),   # CTA-pair kernel (M >= 18944, K = 256): 151 M tiles = an odd, half-empty last pair
+    (149, 64, 13, 10, 256, 1, 1, 0),  # CTA-pair kernel, ragged last tile (M = 19370)
+    (38, 64, 24, 24, 256, 3, 1, 1),   # CTA-pair kernel with im2col loads (M = 21888 = 171 tiles)
 ]
 
 

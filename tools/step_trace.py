@@ -58,4 +58,11 @@ with open(args.out, "w") as f:
     f.write("| kernel | launches/step | us/step | share |\n|---|---|---|---|\n")
     for k, (n, t) in rows:
         f.write(f"| `{k}` | {n / STEPS:.0f} | {t / STEPS:.1f} | {100 * t / STEPS / span:.1f}% |\n")
+big = sorted(((g, ev[i].name[:60], ev[i + 1].name[:60]) for i, g in enumerate(gaps)), reverse=True)[:12 * STEPS]
+with open(args.out, "a") as f:
+    f.write("\nLargest gaps (us, after kernel -> before kernel), all %d steps:\n\n" % STEPS)
+    for g, a, b in big:
+        f.write(f"* {g:.1f}  `{a}` -> `{b}`\n")
+    hist = collections.Counter(min(int(g), 10) for g in gaps)
+    f.write("\nGap histogram (us, 10 = 10 or more): " + ", ".join(f"{k}: {v // STEPS}" for k, v in sorted(hist.items())) + "\n")
 print(open(args.out).read()[:3000])
