@@ -223,47 +223,82 @@ __global__ void filter_prep_kernel(const float* __restrict__ w, T* __restrict__ 
 }
 
 // ---- explicit patch matrix for the C=3 stems ---------------------------------------------------------------------------
-// One CTA per output row (n,p): the R input rows it touches are staged in shared memory WITH their zero margins
-// (coalesced 2-byte-element rows, whole-row reads), so every filter row of a patch is S*C CONTIGUOUS staged elements
-// and needs no bounds test; a k -> smem-offset table removes all divisions from the inner loop.  Patch rows leave as
-// 16-byte stores.
+// One CTA per output row (n,p): the R input rows it touches are staged in shared memory WITH their zero margins, so every
+// filter row of a patch is S*C CONTIGUOUS staged elements and needs no bounds test.  ncu on the first version (7x7 stem, batch
+// 256): issue slots 82 % busy, math-pipe throttled, 0.52 ms for a 1.2 GB write — bound by instruction count (a division per
+// staged element, a table look-up per gathered element).  Now: rows are staged with 16-byte loads (the slot is laid out so the
+// image row starts on a 16-byte boundary), a lane keeps one 16-byte group of patch columns for the whole row so its eight source
+// offsets live in registers, and a warp takes 4 pixels x 8 groups per step (conflict-free gathers, whole-line stores).
 template <typename T>
 __global__ void __launch_bounds__(256)
 im2col_kernel(const T* __restrict__ x, T* __restrict__ out, int N, int H, int W, int C, int R, int S, int stride, int pad, int P,
-              int Q, int Kp) {
+              int Q, int Kp, int lead, int Lp) {
   extern __shared__ __align__(16) unsigned char im2col_smem[];
-  const int Lp = (W + 2 * pad) * C;                    // staged row length incl. margins
-  T* rows = reinterpret_cast<T*>(im2col_smem);        // [R][Lp]
-  int* koff = reinterpret_cast<int*>(im2col_smem + (((size_t)R * Lp * sizeof(T) + 15) & ~(size_t)15));  // [Kp]
+  constexpr int V = 16 / (int)sizeof(T);
+  T* rows = reinterpret_cast<T*>(im2col_smem);        // [R][Lp]: `lead` elements of slack, pad*C zeros, the row, zeros
   const int n = blockIdx.x / P, p = blockIdx.x % P;
-  const int rsc = R * S * C, sc = S * C;
-  for (int k = threadIdx.x; k < Kp; k += blockDim.x) koff[k] = k < rsc ? (k / sc) * Lp + (k % sc) : -1;
-  for (int i = threadIdx.x; i < R * Lp; i += blockDim.x) {
-    const int r = i / Lp, e = i - r * Lp;
+  const int rsc = R * S * C, sc = S * C, wc = W * C;
+  const int data0 = lead + pad * C;                    // element index of the image row inside a slot (multiple of V)
+  for (int r = 0; r < R; ++r) {
     const int h = p * stride + r - pad;
-    const int we = e - pad * C;                        // element index inside the real row
-    T v = from_f32<T>(0.f);
-    if ((unsigned)h < (unsigned)H && (unsigned)we < (unsigned)(W * C)) v = x[((size_t)n * H + h) * W * C + we];
-    rows[i] = v;
+    T* slot = rows + (size_t)r * Lp;
+    const bool live = (unsigned)h < (unsigned)H;
+    const T* src = x + ((size_t)n * H + (live ? h : 0)) * wc;
+    if (live && (wc % V) == 0) {
+      for (int i = threadIdx.x; i < wc / V; i += blockDim.x)
+        *reinterpret_cast<uint4*>(slot + data0 + i * V) = *reinterpret_cast<const uint4*>(src + i * V);
+      for (int e = threadIdx.x; e < data0; e += blockDim.x) slot[e] = from_f32<T>(0.f);
+      for (int e = data0 + wc + threadIdx.x; e < Lp; e += blockDim.x) slot[e] = from_f32<T>(0.f);
+    } else {
+      for (int e = threadIdx.x; e < Lp; e += blockDim.x) {
+        const int we = e - data0;
+        slot[e] = (live && (unsigned)we < (unsigned)wc) ? src[we] : from_f32<T>(0.f);
+      }
+    }
   }
+  // columns past R*S*C read from a zero region behind the slots (long enough for any pixel's offset), so the gathers are
+  // unconditional; shared addresses are formed once as 32-bit shared-window offsets (the generic-address form cost an
+  // S2R + LEA per predicated load)
+  const int zero0 = R * Lp;
+  for (int e = threadIdx.x; e < Q * stride * C + 8; e += blockDim.x) rows[zero0 + e] = from_f32<T>(0.f);
   __syncthreads();
-  const int groups = Kp / 8;
+  const int groups = Kp / 8, gtiles = (groups + 7) / 8, qtiles = (Q + 3) / 4;
   T* orow = out + ((size_t)n * P + p) * Q * Kp;
-  for (int v = threadIdx.x; v < Q * groups; v += blockDim.x) {
-    const int q = v / groups, g = v - q * groups;
-    const int base = q * stride * C;
-    T vals[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(rows);
+  for (int gt = 0; gt < gtiles; ++gt) {
+    const int g = gt * 8 + (lane & 7);
+    uint32_t off[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int o = koff[g * 8 + j];
-      vals[j] = o >= 0 ? rows[o + base] : from_f32<T>(0.f);
+      const int k = g * 8 + j;
+      off[j] = sbase + (uint32_t)sizeof(T) * (uint32_t)((g < groups && k < rsc) ? (k / sc) * Lp + lead + (k % sc) : zero0);
     }
-    T* dst = orow + (size_t)q * Kp + g * 8;
-    if (sizeof(T) == 2) {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(vals);
-    } else {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(vals);
-      *reinterpret_cast<uint4*>(dst + 4) = *reinterpret_cast<const uint4*>(vals + 4);
+    if (g >= groups) continue;
+    for (int qt = warp; qt < qtiles; qt += nwarps) {
+      const int q = qt * 4 + (lane >> 3);
+      if (q >= Q) continue;
+      const uint32_t base = (uint32_t)sizeof(T) * (uint32_t)(q * stride * C);
+      T vals[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (sizeof(T) == 2) {
+          unsigned short u;
+          asm volatile("ld.shared.u16 %0, [%1];" : "=h"(u) : "r"(off[j] + base));
+          reinterpret_cast<unsigned short*>(vals)[j] = u;
+        } else {
+          uint32_t u;
+          asm volatile("ld.shared.u32 %0, [%1];" : "=r"(u) : "r"(off[j] + base));
+          reinterpret_cast<uint32_t*>(vals)[j] = u;
+        }
+      }
+      T* dst = orow + (size_t)q * Kp + g * 8;
+      if (sizeof(T) == 2) {
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(vals);
+      } else {
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(vals);
+        *reinterpret_cast<uint4*>(dst + 4) = *reinterpret_cast<const uint4*>(vals + 4);
+      }
     }
   }
 }
@@ -461,11 +496,16 @@ extern "C" int dv_im2col(const void* x, void* patches, int N, int H, int W, int 
   const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
   cudaStream_t st = (cudaStream_t)stream;
   const size_t esz = dtype == DV_BF16 ? 2 : 4;
-  const size_t smem = (((size_t)R * (W + 2 * pad) * C * esz + 15) & ~(size_t)15) + (size_t)Kp * sizeof(int);
+  const int vec = (int)(16 / esz);
+  const int lead = (vec - (pad * C) % vec) % vec;                       // slack so that the image row starts on a 16-byte boundary
+  const int Lp = ceil_div(lead + (W + 2 * pad) * C, vec) * vec;         // slot length, a whole number of 16-byte vectors
+  const size_t smem = ((size_t)R * Lp + (size_t)Q * stride * C + 8) * esz;   // R staged rows + the zero region
   DV_REQUIRE(smem <= 48 * 1024, DV_ERR_UNSUPPORTED, "dv_im2col: %zu bytes of staging exceed 48 KB (R*(W+2*pad)*C too large)", smem);
   DV_REQUIRE((int64_t)N * P <= 0x7fffffff, DV_ERR_UNSUPPORTED, "dv_im2col: too many output rows");
-  DV_DISPATCH_T(dtype, (im2col_kernel<bf16><<<(unsigned)(N * P), 256, smem, st>>>((const bf16*)x, (bf16*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)),
-                (im2col_kernel<float><<<(unsigned)(N * P), 256, smem, st>>>((const float*)x, (float*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp)));
+  DV_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(patches) & 15) == 0, DV_ERR_ARG,
+             "dv_im2col: pointers must be 16-byte aligned");
+  DV_DISPATCH_T(dtype, (im2col_kernel<bf16><<<(unsigned)(N * P), 256, smem, st>>>((const bf16*)x, (bf16*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp, lead, Lp)),
+                (im2col_kernel<float><<<(unsigned)(N * P), 256, smem, st>>>((const float*)x, (float*)patches, N, H, W, C, R, S, stride, pad, P, Q, Kp, lead, Lp)));
   DV_LAUNCH_OK("im2col_kernel");
   return DV_OK;
 }
