@@ -279,6 +279,9 @@ class Trainer:
         self._static_labels.copy_(labels, non_blocking=True)
         self._graph.replay()
         self.steps_done += 1
+        # the replayed kernels rewrote parameters and running statistics through raw pointers: nothing moved a Tensor._version,
+        # so caches keyed on versions (padded stem filters, folded BatchNorm scale/shift of the inference path) must be told
+        config.bump_weight_epoch()
         return self._static_loss
 
     def _capture(self, images, labels):

@@ -141,3 +141,32 @@ def test_run_epochs_schedules_checkpoints_and_resumes(tmp_path):
     assert loggers2["val_loss"]["epochs"] == [0, 1, 2, 0, 3]
     assert abs(trainer2.lr - 0.045 * 0.125) < 1e-12
     assert trainer2.steps_done > 0 and float(trainer2.flat_s.abs().sum()) > 0
+
+
+def test_inference_after_graph_training_sees_the_new_statistics():
+    """Training steps replayed from the CUDA graph rewrite weights and BN running statistics through raw pointers; the folded
+    inference path caches scale/shift per BatchNorm2d and must not serve the values from before the steps."""
+    torch.manual_seed(0)
+    dv.set_compute_dtype(torch.bfloat16)
+    net = dv.models.ResNet34().cuda()
+    cfg = dict(TRAINING_CONFIG["resnet34"])
+    cfg.pop("batch_size")
+    tr = Trainer(net, use_cuda_graph=True, **cfg)
+    x, y = _batch(8, 64)
+
+    def eval_logits(fold):
+        dv.set_fold_bn(fold)
+        try:
+            net.eval()
+            with torch.no_grad():
+                return net(x).float().cpu().numpy()
+        finally:
+            dv.set_fold_bn(True)
+
+    before = eval_logits(True)                 # fills the per-BN caches
+    for _ in range(4):
+        tr.step(x, y)
+    torch.cuda.synchronize()
+    folded, plain = eval_logits(True), eval_logits(False)
+    assert rel_l2(folded, plain) < 3e-2        # same statistics on both paths
+    assert rel_l2(folded, before) > 1e-2       # and they are the new ones
