@@ -9,13 +9,37 @@
 //   bwd_apply  : dx = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M);  dres = dz
 // Partials are reduced in a fixed order, so every result is bit-reproducible run to run.
 #include "common.cuh"
+#include <map>
+#include <mutex>
 #include <mutex>
 
 namespace dv {
 namespace {
 
+static int env_or(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && atoi(v) > 0 ? atoi(v) : dflt;
+}
+
 constexpr int kThreads = 256;
-constexpr int kMaxBlocks = 1184;  // 8 x 148 SMs: every SM fully occupied (2048 threads)
+constexpr int kMaxBlocks = 1184;
+
+// CTAs of `kernel` one SM holds at kThreads threads (register-limited: 2 for the backward kernels, 3-4 for the forward ones).
+// Grids are sized to ONE wave of resident CTAs: with the 8-per-SM grids these kernels started with, three quarters of the
+// CTAs of bn_bwd_apply began only after an earlier CTA had finished (measured in the captured step: 18.87 -> 18.40 ms).
+template <typename K>
+static int resident_ctas(K kernel) {
+  static std::mutex mu;   // keyed on the pointer: K is a function-pointer TYPE shared by instantiations of equal signature
+  static std::map<const void*, int> table;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = table.find((const void*)kernel);
+  if (it != table.end()) return it->second;
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) n = 2;
+  if (n > 8) n = 8;
+  table[(const void*)kernel] = n;
+  return n;
+}  // 8 x 148 SMs: every SM fully occupied (2048 threads)
 
 struct Plan {
   int cg;        // channel groups (C / V)
@@ -39,6 +63,16 @@ static Plan make_plan(int64_t M, int C, int V) {
   p.rows_per_blk = ceil_div64(M, nb);
   p.nblk = (int)ceil_div64(M, p.rows_per_blk);
   return p;
+}
+
+// fewer, longer row ranges so that the grid is one wave of resident CTAs (workspace sized for the uncapped plan still fits)
+static void cap_plan(Plan& p, int64_t M, int max_blocks) {
+  static const int forced = env_or("DV_BN_RED_BLOCKS", 0);
+  if (forced) max_blocks = forced;
+  if (p.nblk > max_blocks && max_blocks > 0) {
+    p.rows_per_blk = ceil_div64(M, max_blocks);
+    p.nblk = (int)ceil_div64(M, p.rows_per_blk);
+  }
 }
 
 // MODE 0: forward statistics of x.  MODE 1: backward sums (dz, dz*xhat).
@@ -294,7 +328,10 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
   }
 }
 
-template <typename T, bool FIXED>
+// U = vectors per thread per iteration.  The residual variant has 3 loads per vector in flight and streams at 0.97 of the HBM
+// roof with U = 2; the variant without identity (2 loads, 1 store) sat at 0.77 with U = 2 (ncu: 16 warps/SM at 114 registers,
+// 8 warps per issue slot waiting on loads) and gets U = 4.
+template <typename T, bool FIXED, int U>
 __global__ void __launch_bounds__(kThreads)
 bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
                     T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -322,7 +359,6 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
     }
   };
   if (FIXED) load_consts((int)(i0 % cg) * V);
-  constexpr int U = 2;
   for (int64_t i = i0; i < nvec; i += stride * U) {
     Vec16<T> vx[U], vg[U], vy[U];
     uint32_t mb[U];
@@ -388,9 +424,11 @@ __global__ void relu_bwd_kernel(const T* __restrict__ y, const T* __restrict__ d
   }
 }
 
-static unsigned stream_grid(int64_t nvec) {
+// grid of a streaming kernel: `per_sm` CTAs per SM (what the kernel's register count lets be resident: one wave, no tail of
+// late-starting CTAs), fewer when the tensor is small
+static unsigned stream_grid(int64_t nvec, int per_sm) {
   int64_t b = ceil_div64(nvec, kThreads);
-  const int64_t cap = (int64_t)num_sms() * 8;
+  const int64_t cap = (int64_t)num_sms() * per_sm;
   return (unsigned)(b < cap ? (b < 1 ? 1 : b) : cap);
 }
 
@@ -399,6 +437,7 @@ static int stats_t(const dv_bn_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
   Plan pl = make_plan(p->M, p->C, V);
+  cap_plan(pl, p->M, resident_ctas(bn_reduce_kernel<T, 0>) * num_sms());
   const size_t need = (size_t)pl.nblk * 2 * p->C * sizeof(float);
   DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "bn_stats: workspace %zu bytes required, %zu given", need,
              p->workspace_bytes);
@@ -420,15 +459,18 @@ static int apply_t(const dv_bn_params* p, cudaStream_t st) {
   const float* mean = p->eval_mode ? p->running_mean : p->save_mean;
   const float* is = p->eval_mode ? p->running_var : p->save_invstd;
   DV_REQUIRE(mean && is, DV_ERR_ARG, "bn_apply: statistics pointers are null");
-  const unsigned grid = stream_grid(ceil_div64(nvec, kUnroll));
+  static const int apply_forced = env_or("DV_BN_APPLY_CTAS", 0);
   DV_REQUIRE(p->relu_mask == nullptr || (V == 8 && p->relu), DV_ERR_UNSUPPORTED, "bn_apply: relu_mask needs bf16 and relu == 1");
   uint8_t* mask = (uint8_t*)p->relu_mask;
-  if (kThreads % (p->C / V) == 0)
+  if (kThreads % (p->C / V) == 0) {
+    const unsigned grid = stream_grid(ceil_div64(nvec, kUnroll), apply_forced ? apply_forced : resident_ctas(bn_apply_kernel<T, true>));
     bn_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
                                                        p->C, p->relu, p->eval_mode, p->eps, mask);
-  else
+  } else {
+    const unsigned grid = stream_grid(ceil_div64(nvec, kUnroll), apply_forced ? apply_forced : resident_ctas(bn_apply_kernel<T, false>));
     bn_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
                                                         p->C, p->relu, p->eval_mode, p->eps, mask);
+  }
   DV_LAUNCH_OK("bn_apply_kernel");
   return DV_OK;
 }
@@ -438,6 +480,7 @@ static int bwd_reduce_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
   Plan pl = make_plan(p->M, p->C, V);
+  cap_plan(pl, p->M, resident_ctas(bn_reduce_kernel<T, 1>) * num_sms());
   const size_t need = p->atomic_sums ? 0 : (size_t)pl.nblk * 2 * p->C * sizeof(float);
   DV_REQUIRE(need == 0 || (p->workspace && p->workspace_bytes >= need), DV_ERR_WORKSPACE,
              "bn_bwd_reduce: workspace %zu bytes required, %zu given", need, p->workspace_bytes);
@@ -463,15 +506,21 @@ static int bwd_apply_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   DV_REQUIRE(p->relu_mask == nullptr || V == 8, DV_ERR_UNSUPPORTED, "bn_bwd_apply: relu_mask needs bf16");
   const int relu_mode = !p->relu ? 0 : (p->relu_mask ? 3 : (p->y ? 1 : 2));
   const int64_t nvec = p->M * p->C / V;
-  const unsigned grid = stream_grid(ceil_div64(nvec, 2));
-  if (kThreads % (p->C / V) == 0)
-    bn_bwd_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
-                                                           p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
-                                                           relu_mode, 1.0f / (float)p->M, (const uint8_t*)p->relu_mask);
-  else
-    bn_bwd_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, p->gamma,
-                                                            p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, p->C,
-                                                            relu_mode, 1.0f / (float)p->M, (const uint8_t*)p->relu_mask);
+  const bool wide = (relu_mode != 1 && p->dres == nullptr);   // two loads per vector only: keep four vectors in flight
+  static const int bwd_forced = env_or("DV_BN_BWD_CTAS", 0);
+#define DV_BWD_APPLY(FIXED_, U_)                                                                                                     \
+  do {                                                                                                                               \
+    const unsigned grid = stream_grid(ceil_div64(nvec, U_), bwd_forced ? bwd_forced : resident_ctas(bn_bwd_apply_kernel<T, FIXED_, U_>)); \
+    bn_bwd_apply_kernel<T, FIXED_, U_><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, \
+                                                                 p->gamma, p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, \
+                                                                 p->C, relu_mode, 1.0f / (float)p->M, (const uint8_t*)p->relu_mask);  \
+  } while (0)
+  if (kThreads % (p->C / V) == 0) {
+    if (wide) DV_BWD_APPLY(true, 4); else DV_BWD_APPLY(true, 2);
+  } else {
+    if (wide) DV_BWD_APPLY(false, 4); else DV_BWD_APPLY(false, 2);
+  }
+#undef DV_BWD_APPLY
   DV_LAUNCH_OK("bn_bwd_apply_kernel");
   return DV_OK;
 }
@@ -583,10 +632,10 @@ extern "C" int dv_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* s
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == DV_BF16) {
     DV_REQUIRE(n % 8 == 0, DV_ERR_UNSUPPORTED, "dv_relu_fwd: n must be a multiple of 8");
-    relu_fwd_kernel<bf16><<<stream_grid(n / 8), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, n / 8);
+    relu_fwd_kernel<bf16><<<stream_grid(n / 8, 8), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, n / 8);
   } else {
     DV_REQUIRE(n % 4 == 0, DV_ERR_UNSUPPORTED, "dv_relu_fwd: n must be a multiple of 4");
-    relu_fwd_kernel<float><<<stream_grid(n / 4), kThreads, 0, st>>>((const float*)x, (float*)y, n / 4);
+    relu_fwd_kernel<float><<<stream_grid(n / 4, 8), kThreads, 0, st>>>((const float*)x, (float*)y, n / 4);
   }
   DV_LAUNCH_OK("relu_fwd_kernel");
   return DV_OK;
@@ -596,10 +645,10 @@ extern "C" int dv_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, i
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == DV_BF16) {
     DV_REQUIRE(n % 8 == 0, DV_ERR_UNSUPPORTED, "dv_relu_bwd: n must be a multiple of 8");
-    relu_bwd_kernel<bf16><<<stream_grid(n / 8), kThreads, 0, st>>>((const bf16*)y, (const bf16*)dy, (bf16*)dx, n / 8);
+    relu_bwd_kernel<bf16><<<stream_grid(n / 8, 8), kThreads, 0, st>>>((const bf16*)y, (const bf16*)dy, (bf16*)dx, n / 8);
   } else {
     DV_REQUIRE(n % 4 == 0, DV_ERR_UNSUPPORTED, "dv_relu_bwd: n must be a multiple of 4");
-    relu_bwd_kernel<float><<<stream_grid(n / 4), kThreads, 0, st>>>((const float*)y, (const float*)dy, (float*)dx, n / 4);
+    relu_bwd_kernel<float><<<stream_grid(n / 4, 8), kThreads, 0, st>>>((const float*)y, (const float*)dy, (float*)dx, n / 4);
   }
   DV_LAUNCH_OK("relu_bwd_kernel");
   return DV_OK;

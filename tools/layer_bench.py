@@ -117,8 +117,18 @@ def bn_rows(batch):
         q.gamma, q.save_mean, q.save_invstd, q.dgamma, q.dbeta = g.data_ptr(), sm.data_ptr(), si.data_ptr(), dg.data_ptr(), db.data_ptr()
         q.workspace, q.workspace_bytes, q.M, q.C, q.dtype, q.relu = ws.data_ptr(), wsz, M, Cc, DV_BF16, 1
         E = M * Cc
+        # the non-residual layers (two of three BatchNorms in a bottleneck): no identity, ReLU mask recomputed from x
+        p2 = BnParams()
+        C.memmove(C.byref(p2), C.byref(p), C.sizeof(p))
+        p2.residual = None
+        q2 = BnBwdParams()
+        C.memmove(C.byref(q2), C.byref(q), C.sizeof(q))
+        q2.y, q2.dres, q2.beta = None, None, b.data_ptr()
         for name, fn, arg, nbytes in (("stats", lib.dv_bn_stats, p, 2 * E), ("apply+res+relu", lib.dv_bn_apply, p, 6 * E),
-                                      ("bwd_reduce", lib.dv_bn_bwd_reduce, q, 6 * E), ("bwd_apply+dres", lib.dv_bn_bwd_apply, q, 10 * E)):
+                                      ("bwd_reduce", lib.dv_bn_bwd_reduce, q, 6 * E), ("bwd_apply+dres", lib.dv_bn_bwd_apply, q, 10 * E),
+                                      ("apply+relu (no residual)", lib.dv_bn_apply, p2, 4 * E),
+                                      ("bwd_reduce (mask recomputed)", lib.dv_bn_bwd_reduce, q2, 4 * E),
+                                      ("bwd_apply (mask recomputed)", lib.dv_bn_bwd_apply, q2, 6 * E)):
             ms = timed(lambda: check(fn(C.byref(arg), stream()), name))
             gb = nbytes / ms / 1e6
             rows.append(dict(layer=f"BN C={Cc} @{H}", passname=name, ms=round(ms, 4), gbs=round(gb, 1), frac=round(gb / PEAK_GB, 3),

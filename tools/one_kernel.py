@@ -9,7 +9,7 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from deep_vision_b200.lib import BnParams, ConvParams, DwConvParams, DV_ALGO_TC, DV_BF16, DV_CONV_WGRAD, check, lib  # noqa: E402
+from deep_vision_b200.lib import BnBwdParams, BnParams, ConvParams, DwConvParams, DV_ALGO_TC, DV_BF16, DV_CONV_WGRAD, check, lib  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--which", default="fprop")
@@ -68,7 +68,16 @@ def run_job(which, shape, iters):
         wsz = lib.dv_bn_workspace_bytes(M, Cb)
         ws = torch.empty(wsz, dtype=torch.uint8, device="cuda")
         q.workspace, q.workspace_bytes, q.M, q.C, q.dtype, q.relu, q.eps, q.momentum = ws.data_ptr(), wsz, M, Cb, DV_BF16, 1, 1e-5, 0.1
-        fn = (lambda: check(lib.dv_bn_apply(C.byref(q), st), "apply")) if which == "bn_apply" else (lambda: check(lib.dv_bn_stats(C.byref(q), st), "stats"))
+        if which == "bn_bwd_apply":     # the shape and variant bench.py's roofline_hbm times: no residual, mask recomputed
+            dyb, dxb = torch.randn_like(xb), torch.empty_like(xb)
+            b = BnBwdParams()
+            b.x, b.dy, b.dx, b.gamma, b.beta = xb.data_ptr(), dyb.data_ptr(), dxb.data_ptr(), v[0].data_ptr(), v[1].data_ptr()
+            b.save_mean, b.save_invstd, b.dgamma, b.dbeta = v[2].data_ptr(), v[3].data_ptr(), v[4].data_ptr(), v[5].data_ptr()
+            b.M, b.C, b.dtype, b.relu = M, Cb, DV_BF16, 1
+            keep = (dyb, dxb)
+            fn = lambda: check(lib.dv_bn_bwd_apply(C.byref(b), st), "bwd_apply")
+        else:
+            fn = (lambda: check(lib.dv_bn_apply(C.byref(q), st), "apply")) if which == "bn_apply" else (lambda: check(lib.dv_bn_stats(C.byref(q), st), "stats"))
     for _ in range(iters):
         fn()
     torch.cuda.synchronize()
