@@ -376,7 +376,9 @@ static int run_fprop(const dv_dwconv_params* p, cudaStream_t st) {
   const int64_t strips = (int64_t)d.N * d.P * ceil_div(d.Q, d.stride == 1 ? StripW<1>::fwd : StripW<2>::fwd);
   DV_REQUIRE(strips < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
   int nb, per;
-  split_units(strips, pl.lanes, 4, 16, &nb, &per);
+  // one wave of resident CTAs (2 per SM for stride 1, 3 for stride 2): every CTA loads the tap table once and streams
+  static const int fwd_cap = getenv("DV_DW_FWD_CAP") ? atoi(getenv("DV_DW_FWD_CAP")) : 0;
+  split_units(strips, pl.lanes, 4, fwd_cap > 0 ? fwd_cap : (d.stride == 1 ? 2 : 3), &nb, &per);
   dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
   if (d.stride == 1)
     dwconv_strip_kernel<T, 1><<<grid, kThreads, 0, st>>>((const T*)p->x, (const float*)p->w, (T*)p->y, d.N, d.H, d.W, d.P, d.Q, d.C, pl.cgb,
@@ -399,14 +401,16 @@ static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
     // dx = "fprop" of dy with the taps flipped (pad 1 both ways)
     const int64_t strips = (int64_t)d.N * d.H * ceil_div(d.W, StripW<1>::fwd);
     DV_REQUIRE(strips < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
-    split_units(strips, pl.lanes, 4, 16, &nb, &per);
+    static const int dg_cap = getenv("DV_DW_FWD_CAP") ? atoi(getenv("DV_DW_FWD_CAP")) : 0;
+    split_units(strips, pl.lanes, 4, dg_cap > 0 ? dg_cap : 2, &nb, &per);
     dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
     dwconv_strip_kernel<T, 1><<<grid, kThreads, 0, st>>>((const T*)p->y, (const float*)p->w, (T*)p->x, d.N, d.P, d.Q, d.H, d.W, d.C, pl.cgb,
                                                        pl.lanes, per, 1);
   } else {
     const int64_t cells = (int64_t)d.N * ((d.H + 1) / 2) * ((d.W + 1) / 2);
     DV_REQUIRE(cells < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
-    split_units(cells, pl.lanes, 8, 16, &nb, &per);
+    static const int s2_cap = getenv("DV_DW_S2_CAP") ? atoi(getenv("DV_DW_S2_CAP")) : 16;
+    split_units(cells, pl.lanes, 8, s2_cap, &nb, &per);
     dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
     dwconv_dgrad_s2_kernel<T><<<grid, kThreads, 0, st>>>((const T*)p->y, (const float*)p->w, (T*)p->x, d.N, d.H, d.W, d.P, d.Q, d.C, pl.cgb,
                                                        pl.lanes, per);

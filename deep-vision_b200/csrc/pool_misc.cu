@@ -9,9 +9,14 @@ namespace {
 
 constexpr int kThreads = 256;
 
-static unsigned grid_for(int64_t n) {
+static int pool_cap() {
+  static const int v = getenv("DV_POOL_CAP") ? atoi(getenv("DV_POOL_CAP")) : 8;
+  return v > 0 ? v : 8;
+}
+
+static unsigned grid_for(int64_t n, int per_sm = 8) {
   int64_t b = ceil_div64(n, kThreads);
-  const int64_t cap = (int64_t)num_sms() * 8;
+  const int64_t cap = (int64_t)num_sms() * per_sm;
   return (unsigned)(b < cap ? (b < 1 ? 1 : b) : cap);
 }
 
@@ -407,7 +412,7 @@ extern "C" int dv_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H
   const int64_t total = (int64_t)N * P * ((Q + 1) / 2) * (C / (dtype == DV_BF16 ? 8 : 4));  // two outputs per thread
   DV_REQUIRE((int64_t)N * H * W * C < (1LL << 31), DV_ERR_UNSUPPORTED, "dv_maxpool_fwd: tensor exceeds 2^31 elements");
   cudaStream_t st = (cudaStream_t)stream;
-  DV_DISPATCH_T(dtype, (maxpool_fwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, idx, N, H, W, C, P, Q)),
+  DV_DISPATCH_T(dtype, (maxpool_fwd_kernel<bf16><<<grid_for(total, pool_cap()), kThreads, 0, st>>>((const bf16*)x, (bf16*)y, idx, N, H, W, C, P, Q)),
                 (maxpool_fwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)x, (float*)y, idx, N, H, W, C, P, Q)));
   DV_LAUNCH_OK("maxpool_fwd_kernel");
   return DV_OK;
@@ -420,7 +425,7 @@ extern "C" int dv_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int 
   const int64_t total = (int64_t)N * ((H + 1) / 2) * ((W + 1) / 2) * (C / (dtype == DV_BF16 ? 8 : 4));  // a 2x2 cell per thread
   DV_REQUIRE((int64_t)N * H * W * C < (1LL << 31), DV_ERR_UNSUPPORTED, "dv_maxpool_bwd: tensor exceeds 2^31 elements");
   cudaStream_t st = (cudaStream_t)stream;
-  DV_DISPATCH_T(dtype, (maxpool_bwd_kernel<bf16><<<grid_for(total), kThreads, 0, st>>>((const bf16*)dy, idx, (bf16*)dx, N, H, W, C, P, Q)),
+  DV_DISPATCH_T(dtype, (maxpool_bwd_kernel<bf16><<<grid_for(total, pool_cap()), kThreads, 0, st>>>((const bf16*)dy, idx, (bf16*)dx, N, H, W, C, P, Q)),
                 (maxpool_bwd_kernel<float><<<grid_for(total), kThreads, 0, st>>>((const float*)dy, idx, (float*)dx, N, H, W, C, P, Q)));
   DV_LAUNCH_OK("maxpool_bwd_kernel");
   return DV_OK;
