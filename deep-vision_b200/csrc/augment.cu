@@ -103,10 +103,76 @@ __global__ void __launch_bounds__(256) augment_apply_kernel(AugArgs a, T* __rest
   }
 }
 
+// ---- Rescale: cv2.resize(image, (new_w, new_h)) with INTER_LINEAR on uint8 (data_load.py:72-99), bit for bit ----------------
+// OpenCV's 8-bit path is fixed point: per axis two taps with weights cvRound(w * 2048) from a float32 fraction of the aligned
+// pixel centre; a horizontal pass into 32-bit sums, then (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2.
+// Along x the fraction is zeroed where the window leaves the image, along y the row indices are clamped instead.
+struct RescaleArgs {
+  const uint8_t* src;
+  const int64_t* src_off;
+  const int32_t* src_hw;
+  const int32_t* dst_hw;
+  uint8_t* dst;
+  int B, Hs, Ws;
+};
+
+__device__ __forceinline__ void resize_tap(int d, int dsize, int ssize, bool vertical, int& i0, int& i1, int& w0, int& w1) {
+  const double scale = 1.0 / ((double)dsize / (double)ssize);
+  float f = (float)(((double)d + 0.5) * scale - 0.5);
+  int s0 = (int)floorf(f);
+  float fr = f - (float)s0;
+  if (!vertical) {
+    if (s0 < 0) { fr = 0.f; s0 = 0; }
+    if (s0 >= ssize - 1) { fr = 0.f; s0 = ssize - 1; }
+  }
+  w1 = __float2int_rn(__fmul_rn(fr, 2048.f));
+  w0 = __float2int_rn(__fmul_rn(__fsub_rn(1.f, fr), 2048.f));
+  i0 = min(max(s0, 0), ssize - 1);
+  i1 = min(max(s0 + 1, 0), ssize - 1);
+}
+
+__global__ void __launch_bounds__(256) rescale_kernel(RescaleArgs a) {
+  const int b = blockIdx.y;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.Hs * a.Ws) return;
+  const int y = i / a.Ws, x = i - y * a.Ws;
+  const int sh = a.src_hw[2 * b], sw = a.src_hw[2 * b + 1], dh = a.dst_hw[2 * b], dw = a.dst_hw[2 * b + 1];
+  uint8_t* out = a.dst + (((size_t)b * a.Hs + y) * a.Ws + x) * 3;
+  if (y >= dh || x >= dw) {  // the rest of the slot: defined, never read by dv_augment
+    out[0] = out[1] = out[2] = 0;
+    return;
+  }
+  int x0, x1, ax0, ax1, y0, y1, ay0, ay1;
+  resize_tap(x, dw, sw, false, x0, x1, ax0, ax1);
+  resize_tap(y, dh, sh, true, y0, y1, ay0, ay1);
+  const uint8_t* img = a.src + a.src_off[b];
+  const uint8_t* r0 = img + (size_t)y0 * sw * 3;
+  const uint8_t* r1 = img + (size_t)y1 * sw * 3;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const int h0 = r0[x0 * 3 + c] * ax0 + r0[x1 * 3 + c] * ax1;
+    const int h1 = r1[x0 * 3 + c] * ax0 + r1[x1 * 3 + c] * ax1;
+    out[c] = (uint8_t)((((ay0 * (h0 >> 4)) >> 16) + ((ay1 * (h1 >> 4)) >> 16) + 2) >> 2);
+  }
+}
+
 }  // namespace
 }  // namespace dv
 
 using namespace dv;
+
+extern "C" int dv_rescale(const dv_rescale_params* p, void* stream) {
+  DV_REQUIRE(p && p->src && p->src_off && p->src_hw && p->dst && p->dst_hw, DV_ERR_ARG, "dv_rescale: null pointer");
+  DV_REQUIRE(p->B > 0 && p->B <= 65535 && p->Hs > 0 && p->Ws > 0 && (int64_t)p->Hs * p->Ws < (1LL << 31), DV_ERR_ARG,
+             "dv_rescale: bad sizes B=%d Hs=%d Ws=%d", p->B, p->Hs, p->Ws);
+  RescaleArgs a;
+  a.src = p->src; a.src_off = p->src_off; a.src_hw = p->src_hw; a.dst_hw = p->dst_hw; a.dst = p->dst;
+  a.B = p->B; a.Hs = p->Hs; a.Ws = p->Ws;
+  dim3 grid((unsigned)ceil_div(p->Hs * p->Ws, 256), (unsigned)p->B);
+  rescale_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+  DV_LAUNCH_OK("rescale_kernel");
+  return DV_OK;
+}
 
 extern "C" int dv_augment(const dv_augment_params* p, void* stream) {
   DV_REQUIRE(p && p->src && p->dst && p->geom && p->factors && p->gray_sums, DV_ERR_ARG, "dv_augment: null pointer");

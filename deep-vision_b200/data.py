@@ -16,7 +16,7 @@ import torch
 
 from . import config
 from .functional import _CL, _dv_dtype, _require_cuda, _stream
-from .lib import AugmentParams, check, lib
+from .lib import AugmentParams, RescaleParams, check, lib
 
 ORDERS = [(0, 1, 2), (0, 2, 1), (1, 0, 2), (1, 2, 0), (2, 0, 1), (2, 1, 0)]   # 0 brightness, 1 contrast, 2 saturation
 IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)   # train.py:324
@@ -91,3 +91,47 @@ class GpuTransform:
         p.std = (C.c_float * 3)(*self.std)
         check(lib.dv_augment(C.byref(p), _stream()), "dv_augment")
         return out
+
+
+class GpuRescale:
+    """Rescale(output_size) of data_load.py:72-99 for a batch of decoded images of different sizes: the host hands over the
+    uint8 HWC arrays as decoded (numpy or torch, any mix of sizes), `dv_rescale` resizes them all in one launch with OpenCV's
+    INTER_LINEAR arithmetic bit for bit, and the result is the slot tensor + size list that `GpuTransform` consumes."""
+
+    def __init__(self, output_size=256):
+        self.output_size = int(output_size)
+
+    def sizes(self, h, w):
+        s = self.output_size                      # data_load.py:88-95, float arithmetic and int() as there
+        if h > w:
+            new_h, new_w = s * h / w, s
+        else:
+            new_h, new_w = s, s * w / h
+        return int(new_h), int(new_w)
+
+    def __call__(self, images, device="cuda"):
+        imgs = [torch.as_tensor(im) for im in images]
+        for im in imgs:
+            if im.dtype != torch.uint8 or im.dim() != 3 or im.shape[2] != 3:
+                raise TypeError("GpuRescale: expected uint8 [H,W,3] images")
+        src_hw = [(int(im.shape[0]), int(im.shape[1])) for im in imgs]
+        dst_hw = [self.sizes(h, w) for h, w in src_hw]
+        offs, total = [], 0
+        for h, w in src_hw:
+            offs.append(total)
+            total += (h * w * 3 + 15) // 16 * 16
+        staged = torch.empty(total, dtype=torch.uint8).pin_memory() if torch.cuda.is_available() else torch.empty(total, dtype=torch.uint8)
+        for im, o, (h, w) in zip(imgs, offs, src_hw):
+            staged[o:o + h * w * 3] = im.contiguous().reshape(-1)
+        src = staged.to(device, non_blocking=True)
+        B = len(imgs)
+        Hs, Ws = max(h for h, _ in dst_hw), max(w for _, w in dst_hw)
+        out = torch.empty((B, Hs, Ws, 3), dtype=torch.uint8, device=device)
+        off_d = torch.tensor(offs, dtype=torch.int64).to(device, non_blocking=True)
+        shw_d = torch.tensor(src_hw, dtype=torch.int32).to(device, non_blocking=True)
+        dhw_d = torch.tensor(dst_hw, dtype=torch.int32).to(device, non_blocking=True)
+        p = RescaleParams()
+        p.src, p.src_off, p.src_hw, p.dst, p.dst_hw = src.data_ptr(), off_d.data_ptr(), shw_d.data_ptr(), out.data_ptr(), dhw_d.data_ptr()
+        p.B, p.Hs, p.Ws = B, Hs, Ws
+        check(lib.dv_rescale(C.byref(p), _stream()), "dv_rescale")
+        return out, dst_hw

@@ -45,6 +45,13 @@ class AugmentParams(C.Structure):
     ]
 
 
+class RescaleParams(C.Structure):
+    _fields_ = [
+        ("src", C.c_void_p), ("src_off", C.c_void_p), ("src_hw", C.c_void_p), ("dst", C.c_void_p), ("dst_hw", C.c_void_p),
+        ("B", C.c_int32), ("Hs", C.c_int32), ("Ws", C.c_int32),
+    ]
+
+
 class BnParams(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("y", C.c_void_p), ("residual", C.c_void_p),
@@ -85,6 +92,7 @@ _SIG = {
     "dv_dwconv_wgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_workspace_bytes": (C.c_size_t, [C.POINTER(DwConvParams)]),
     "dv_augment": (C.c_int, [C.POINTER(AugmentParams), _P]),
+    "dv_rescale": (C.c_int, [C.POINTER(RescaleParams), _P]),
     "dv_bn_fold": (C.c_int, [_P, _P, _P, _P, C.c_float, _P, _P, C.c_int, _P, _P, _P]),
     "dv_bn_stats": (C.c_int, [C.POINTER(BnParams), _P]),
     "dv_bn_apply": (C.c_int, [C.POINTER(BnParams), _P]),

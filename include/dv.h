@@ -279,6 +279,19 @@ typedef struct dv_augment_params {
 } dv_augment_params;
 int dv_augment(const dv_augment_params* p, void* stream);
 
+/* Rescale(256) (data_load.py:72-99): cv2.resize with INTER_LINEAR on uint8, bit for bit (OpenCV's 11-bit fixed-point
+ * two-tap filter), for a ragged batch of decoded images in one launch, written into the slots dv_augment reads.
+ * The sizes come from the caller (Rescale's own int() arithmetic); a slot's unused remainder is zeroed. */
+typedef struct dv_rescale_params {
+  const uint8_t* src;      /* device: decoded RGB images, HWC uint8, stored back to back */
+  const int64_t* src_off;  /* device [B]: byte offset of image b inside src */
+  const int32_t* src_hw;   /* device [B][2]: height, width of image b */
+  uint8_t* dst;            /* device [B][Hs][Ws][3] */
+  const int32_t* dst_hw;   /* device [B][2]: rescaled height, width (<= Hs, Ws) */
+  int32_t B, Hs, Ws;
+} dv_rescale_params;
+int dv_rescale(const dv_rescale_params* p, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Stem / tail ops.
  * ------------------------------------------------------------------------------------------ */

@@ -58,9 +58,24 @@ def main():
         vals.append(vf({"image": img, "annotation": i})["image"].numpy())
         params.append([h, w, top, left, flip, order, bf, cf, sf])
     rec.update(images=np.stack(imgs), train_out=np.stack(outs), val_out=np.stack(vals), params=np.asarray(params, np.float64))
+    # Rescale (data_load.py:72-99, cv2.resize): down- and up-scaling, both orientations, a degenerate 1-pixel-high image
+    rs_in, rs_out, rs_hw = [], [], []
+    target = 40
+    for j, (h, w) in enumerate([(75, 100), (100, 66), (40, 40), (30, 55), (17, 23), (1, 7), (90, 41), (64, 200)]):
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        out = dl.Rescale(target)({"image": img, "annotation": j})["image"]
+        pi = np.zeros((100, 200, 3), np.uint8)
+        pi[:h, :w] = img
+        po = np.zeros((300, 300, 3), np.uint8)
+        po[:out.shape[0], :out.shape[1]] = out
+        rs_in.append(pi)
+        rs_out.append(po)
+        rs_hw.append([h, w, out.shape[0], out.shape[1]])
+    rec.update(rescale_target=target, rescale_in=np.stack(rs_in), rescale_out=np.stack(rs_out), rescale_hw=np.asarray(rs_hw, np.int64))
     import PIL
     import torchvision
-    rec["versions"] = np.asarray([PIL.__version__, torchvision.__version__])
+    import cv2
+    rec["versions"] = np.asarray([PIL.__version__, torchvision.__version__, cv2.__version__])
     np.savez_compressed(OUT, **rec)
     print("wrote", OUT, os.path.getsize(OUT), "bytes")
 

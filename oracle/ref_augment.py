@@ -1,5 +1,5 @@
-"""CPU restatement (test infrastructure only) of the reference's training / validation image transforms AFTER decoding
-and rescaling — ResNet/pytorch/data_load.py: RandomHorizontalFlip :102-112, RandomCrop :115-143, CenterCrop :146-172,
+"""CPU restatement (test infrastructure only) of the reference's training / validation image transforms after decoding
+— ResNet/pytorch/data_load.py: Rescale :72-99 (cv2.resize, INTER_LINEAR), RandomHorizontalFlip :102-112, RandomCrop :115-143, CenterCrop :146-172,
 ColorJitter :213-297 (torchvision's PIL path: brightness, contrast, saturation in a shuffled order; hue = 0),
 ToTensor :175-193 (float, NOT divided by 255), Normalize :196-210 — as composed at ResNet/pytorch/train.py:315-331.
 
@@ -13,6 +13,55 @@ pins this file against the reference's own transform classes (tests/golden/augme
     brightness: deg = 0        contrast: deg = int(mean(L) + 0.5)        saturation: deg = L
 """
 import numpy as np
+
+
+def _resize_coefs(d, s, vertical):
+    """Source indices and 11-bit fixed-point weights of OpenCV's INTER_LINEAR for uint8 (resize.cpp, the HResizeLinear /
+    VResizeLinear pair): pixel centres aligned, the fraction taken in float32, weights = cvRound(w * 2048).  Along x the
+    fraction is zeroed where the window leaves the image; along y it is kept and the ROW INDICES are clamped instead."""
+    scale = 1.0 / (np.float64(d) / np.float64(s))
+    f = ((np.arange(d) + 0.5) * scale - 0.5).astype(np.float32)
+    s0 = np.floor(f).astype(np.int64)
+    fr = (f - s0.astype(np.float32)).astype(np.float32)
+    if not vertical:
+        lo = s0 < 0
+        fr[lo] = 0
+        s0[lo] = 0
+        hi = s0 >= s - 1
+        fr[hi] = 0
+        s0[hi] = s - 1
+    w1 = np.rint(fr * np.float32(2048)).astype(np.int64)
+    w0 = np.rint((np.float32(1) - fr) * np.float32(2048)).astype(np.int64)
+    return np.clip(s0, 0, s - 1), np.clip(s0 + 1, 0, s - 1), w0, w1
+
+
+def resize_bilinear_u8(img, new_h, new_w):
+    """cv2.resize(img, (new_w, new_h)) for a uint8 HWC image, bit for bit (third-party dependency: opencv-python, installed
+    4.13.0; pinned against cv2 itself and against the reference's Rescale in tests/test_augment_oracle_cpu.py)."""
+    h, w = img.shape[:2]
+    x0, x1, ax0, ax1 = _resize_coefs(new_w, w, False)
+    y0, y1, ay0, ay1 = _resize_coefs(new_h, h, True)
+    src = img.astype(np.int64)
+    rows = src[:, x0] * ax0[None, :, None] + src[:, x1] * ax1[None, :, None]
+    r0, r1 = rows[y0], rows[y1]
+    out = (((ay0[:, None, None] * (r0 >> 4)) >> 16) + ((ay1[:, None, None] * (r1 >> 4)) >> 16) + 2) >> 2
+    return out.astype(np.uint8)
+
+
+def rescale_size(h, w, output_size):
+    """Rescale.__call__ (data_load.py:86-97): the smaller edge becomes output_size, the other keeps the aspect ratio (int())."""
+    if h > w:
+        new_h, new_w = output_size * h / w, output_size
+    else:
+        new_h, new_w = output_size, output_size * w / h
+    return int(new_h), int(new_w)
+
+
+def rescale(img, output_size):
+    """data_load.py:72-99 for an int output_size."""
+    nh, nw = rescale_size(img.shape[0], img.shape[1], output_size)
+    return resize_bilinear_u8(img, nh, nw)
+
 
 ORDERS = [(0, 1, 2), (0, 2, 1), (1, 0, 2), (1, 2, 0), (2, 0, 1), (2, 1, 0)]   # 0 brightness, 1 contrast, 2 saturation
 

@@ -26,3 +26,13 @@ def test_blend_branches():
     assert ref_augment._blend(np.zeros_like(img), img, 1.2).tolist() == [[[0, 153, 255]]]       # extrapolation clips
     g = ref_augment._gray(np.array([[[255, 255, 255], [255, 0, 0]]], np.uint8))
     assert g.tolist() == [[255, 76]]
+
+
+def test_rescale_oracle_equals_reference_rescale():
+    """oracle.ref_augment.rescale == the reference's Rescale (cv2.resize) on frozen outputs: exact, up- and down-scaling."""
+    d = np.load(os.path.join(os.path.dirname(__file__), "golden", "augment_ref.npz"))
+    target = int(d["rescale_target"])
+    for img, out, (h, w, nh, nw) in zip(d["rescale_in"], d["rescale_out"], d["rescale_hw"]):
+        assert ref_augment.rescale_size(int(h), int(w), target) == (int(nh), int(nw))
+        got = ref_augment.rescale(img[:h, :w], target)
+        assert got.shape == (nh, nw, 3) and np.array_equal(got, out[:nh, :nw])

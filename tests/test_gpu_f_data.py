@@ -79,3 +79,28 @@ def test_augmented_batch_feeds_the_model_without_a_layout_pass():
     with torch.no_grad():
         y = net(x * 0.02)   # the reference's un-scaled 0..255 normalisation gives inputs of magnitude ~500
     assert tuple(y.shape) == (4, 1000) and torch.isfinite(y).all()
+
+
+def test_rescale_matches_reference_rescale_bit_for_bit():
+    """dv_rescale on a ragged batch == outputs of the reference's Rescale (cv2.resize) frozen in the fixture, and the composed
+    pipeline decode -> GpuRescale -> GpuTransform(validation) == the oracle's rescale + centre crop + normalise."""
+    from deep_vision_b200.data import GpuRescale
+    d = _golden()
+    target = int(d["rescale_target"])
+    imgs = [img[:h, :w].copy() for img, (h, w, _, _) in zip(d["rescale_in"], d["rescale_hw"])]
+    slots, sizes = GpuRescale(target)(imgs)
+    torch.cuda.synchronize()
+    got = slots.cpu().numpy()
+    for b, (out, (h, w, nh, nw)) in enumerate(zip(d["rescale_out"], d["rescale_hw"])):
+        assert sizes[b] == (int(nh), int(nw))
+        assert np.array_equal(got[b, :nh, :nw], out[:nh, :nw]), b
+        assert not got[b, nh:].any() and not got[b, :, nw:].any()
+    # full-size: 375x500 and 500x333 photographs -> 256 on the short side -> centre crop 224
+    rng = np.random.default_rng(9)
+    big = [rng.integers(0, 256, (375, 500, 3), dtype=np.uint8), rng.integers(0, 256, (500, 333, 3), dtype=np.uint8),
+           rng.integers(0, 256, (120, 90, 3), dtype=np.uint8)]
+    slots, sizes = GpuRescale(256)(big)
+    val = GpuTransform(224, train=False, dtype=torch.float32, nchw=True)(slots, sizes).cpu().numpy()
+    for b, im in enumerate(big):
+        ref = ref_augment.val_transform(ref_augment.rescale(im, 256), 224)
+        assert np.array_equal(val[b], ref), b
