@@ -9,6 +9,9 @@
 //   bwd_apply  : dx = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M);  dres = dz
 // Partials are reduced in a fixed order, so every result is bit-reproducible run to run.
 #include "common.cuh"
+#ifndef DV_BN_RED_U
+#define DV_BN_RED_U 6
+#endif
 #include <map>
 #include <mutex>
 #include <mutex>
@@ -75,17 +78,19 @@ static void cap_plan(Plan& p, int64_t M, int max_blocks) {
   }
 }
 
-// MODE 0: forward statistics of x.  MODE 1: backward sums (dz, dz*xhat).
-template <typename T, int MODE>
+// MODE 0: forward statistics of x.  MODE 1: backward sums (dz, dz*xhat).  RELU (compile time, so that the registers of the
+// variants not taken are not reserved): see below.
+template <typename T, int MODE, int RELU>
 __global__ void __launch_bounds__(kThreads)
 bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, const float* __restrict__ mean,
                  const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta,
-                 float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par, int64_t rows_per_blk, int relu,
+                 float* __restrict__ partial, int64_t M, int C, int cgb, int rows_par, int64_t rows_per_blk,
                  float* __restrict__ atomic_s1 = nullptr, float* __restrict__ atomic_s2 = nullptr,
                  const uint8_t* __restrict__ mask = nullptr) {
   // relu: 0 = no activation, 1 = mask from the stored output y, 2 = mask recomputed from x exactly as bn_apply computed it,
   //       3 = mask from the bit mask bn_apply wrote (one byte per 16-byte bf16 vector)
   constexpr int V = Vec16<T>::N;
+  constexpr int relu = RELU;
   __shared__ float red[2][kThreads * V];
   const int tcg = threadIdx.x % cgb, trow = threadIdx.x / cgb;
   const bool active = trow < rows_par;
@@ -112,7 +117,7 @@ bn_reduce_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __re
         }
       }
       // U independent 16-byte loads per stream in flight per thread (memory-level parallelism), then the arithmetic
-      constexpr int U = 4;
+      constexpr int U = (MODE == 1 && RELU != 1) ? DV_BN_RED_U : 4;
       for (int64_t r = r0 + trow; r < r1; r += (int64_t)rows_par * U) {
         Vec16<T> vx[U], vg[U], vy[U];
         uint32_t mb[U];
@@ -437,12 +442,12 @@ static int stats_t(const dv_bn_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
   Plan pl = make_plan(p->M, p->C, V);
-  cap_plan(pl, p->M, resident_ctas(bn_reduce_kernel<T, 0>) * num_sms());
+  cap_plan(pl, p->M, resident_ctas(bn_reduce_kernel<T, 0, 0>) * num_sms());
   const size_t need = (size_t)pl.nblk * 2 * p->C * sizeof(float);
   DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "bn_stats: workspace %zu bytes required, %zu given", need,
              p->workspace_bytes);
-  bn_reduce_kernel<T, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
-                                                      (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, 0);
+  bn_reduce_kernel<T, 0, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                                         (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par, pl.rows_per_blk);
   DV_LAUNCH_OK("bn_reduce_kernel<stats>");
   bn_stats_finalize_kernel<T><<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const T*)p->x, (const float*)p->workspace, pl.nblk, p->C, p->M, p->eps,
                                                                   p->momentum, p->save_mean, p->save_invstd, p->running_mean,
@@ -479,18 +484,33 @@ template <typename T>
 static int bwd_reduce_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "bn: C=%d must be a multiple of %d", p->C, V);
-  Plan pl = make_plan(p->M, p->C, V);
-  cap_plan(pl, p->M, resident_ctas(bn_reduce_kernel<T, 1>) * num_sms());
-  const size_t need = p->atomic_sums ? 0 : (size_t)pl.nblk * 2 * p->C * sizeof(float);
-  DV_REQUIRE(need == 0 || (p->workspace && p->workspace_bytes >= need), DV_ERR_WORKSPACE,
-             "bn_bwd_reduce: workspace %zu bytes required, %zu given", need, p->workspace_bytes);
   DV_REQUIRE(!p->relu || p->y || p->beta || p->relu_mask, DV_ERR_ARG, "bn_bwd_reduce: relu needs relu_mask, y (stored mask) or beta (recomputed mask)");
   DV_REQUIRE(p->relu_mask == nullptr || V == 8, DV_ERR_UNSUPPORTED, "bn_bwd_reduce: relu_mask needs bf16");
   const int relu_mode = !p->relu ? 0 : (p->relu_mask ? 3 : (p->y ? 1 : 2));
-  bn_reduce_kernel<T, 1><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, p->save_mean, p->save_invstd,
-                                                      p->gamma, p->beta, (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par,
-                                                      pl.rows_per_blk, relu_mode, p->atomic_sums ? p->dbeta : nullptr,
-                                                      p->atomic_sums ? p->dgamma : nullptr, (const uint8_t*)p->relu_mask);
+  Plan pl = make_plan(p->M, p->C, V);
+  int resident = 2;
+  switch (relu_mode) {
+    case 0: resident = resident_ctas(bn_reduce_kernel<T, 1, 0>); break;
+    case 1: resident = resident_ctas(bn_reduce_kernel<T, 1, 1>); break;
+    case 2: resident = resident_ctas(bn_reduce_kernel<T, 1, 2>); break;
+    default: resident = resident_ctas(bn_reduce_kernel<T, 1, 3>); break;
+  }
+  cap_plan(pl, p->M, resident * num_sms());
+  const size_t need = p->atomic_sums ? 0 : (size_t)pl.nblk * 2 * p->C * sizeof(float);
+  DV_REQUIRE(need == 0 || (p->workspace && p->workspace_bytes >= need), DV_ERR_WORKSPACE,
+             "bn_bwd_reduce: workspace %zu bytes required, %zu given", need, p->workspace_bytes);
+#define DV_BWD_REDUCE(R_)                                                                                                          \
+  bn_reduce_kernel<T, 1, R_><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, p->save_mean, p->save_invstd, \
+                                                          p->gamma, p->beta, (float*)p->workspace, p->M, p->C, pl.cgb, pl.rows_par,     \
+                                                          pl.rows_per_blk, p->atomic_sums ? p->dbeta : nullptr,                          \
+                                                          p->atomic_sums ? p->dgamma : nullptr, (const uint8_t*)p->relu_mask)
+  switch (relu_mode) {
+    case 0: DV_BWD_REDUCE(0); break;
+    case 1: DV_BWD_REDUCE(1); break;
+    case 2: DV_BWD_REDUCE(2); break;
+    default: DV_BWD_REDUCE(3); break;
+  }
+#undef DV_BWD_REDUCE
   DV_LAUNCH_OK("bn_reduce_kernel<bwd>");
   if (p->atomic_sums) return DV_OK;  // dbeta += sum(dz), dgamma += sum(dz*xhat) were accumulated in place
   bn_bwd_finalize_kernel<<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const float*)p->workspace, pl.nblk, p->C, p->dgamma, p->dbeta);
@@ -575,8 +595,8 @@ static int stats_static_t(const dv_bn_params* p, cudaStream_t st) {
   if (rc) return rc;
   // Every partial the finalize pass reads is overwritten by the reduce pass of the same call, so nothing in the shared
   // array has to be cleared between calls.
-  bn_reduce_kernel<T, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, scratch, p->M,
-                                                      p->C, pl.cgb, pl.rows_par, pl.rows_per_blk, 0);
+  bn_reduce_kernel<T, 0, 0><<<pl.nblk, kThreads, 0, st>>>((const T*)p->x, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, scratch,
+                                                         p->M, p->C, pl.cgb, pl.rows_par, pl.rows_per_blk);
   DV_LAUNCH_OK("bn_reduce_kernel<stats,static>");
   bn_stats_finalize_kernel<T><<<ceil_div(p->C, 32), 32 * kFinLanes, 0, st>>>((const T*)p->x, scratch, pl.nblk, p->C, p->M, p->eps,
                                                                             p->momentum, p->save_mean, p->save_invstd, p->running_mean,
