@@ -44,7 +44,7 @@ def set_conv_algo(algo):
 
 
 def fuse_bn_stats():
-    return _state["fuse_bn_stats"]
+    return _state["fuse_bn_stats"] and not _state["deterministic"]
 
 
 def set_fuse_bn_stats(flag):
@@ -61,9 +61,7 @@ def set_deterministic(flag):
     """False (default): split reductions (wgrad tiles, BN backward sums, fused BN statistics) are combined with fp32
     atomics — fewer launches and less traffic, summation order varies run to run.  True: fixed-order second-stage
     reductions, bit-reproducible results."""
-    _state["deterministic"] = bool(flag)
-    if flag:
-        _state["fuse_bn_stats"] = False
+    _state["deterministic"] = bool(flag)   # fuse_bn_stats() answers False while this is set (the fused sums use atomics)
 
 
 def atomic_wgrad():
