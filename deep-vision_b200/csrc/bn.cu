@@ -7,7 +7,9 @@
 //   apply      : y = relu((x-mean)*invstd*gamma + beta [+ residual])
 //   bwd_reduce : dbeta = sum(dz), dgamma = sum(dz*xhat), dz = dy * (y > 0)
 //   bwd_apply  : dx = gamma*invstd*(dz - dbeta/M - xhat*dgamma/M);  dres = dz
-// Partials are reduced in a fixed order, so every result is bit-reproducible run to run.
+// Partials are reduced in a fixed order, so every result is bit-reproducible run to run.  The ReLU mask of the backward passes is
+// recomputed from x (no identity), read from the 1-bit mask the apply pass wrote (identity added), or taken from a stored y.
+// Grids are one wave of resident CTAs (occupancy query per kernel): the backward kernels hold 114-128 registers.
 #include "common.cuh"
 #ifndef DV_BN_RED_U
 #define DV_BN_RED_U 6

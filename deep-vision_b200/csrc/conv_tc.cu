@@ -2,15 +2,20 @@
 // 128B-swizzled shared memory by TMA (tiled 2-D maps for filters and 1x1 activations, im2col maps for 3x3 /
 // strided activations), tcgen05.mma with the fp32 accumulator in TMEM, tcgen05.ld epilogue.
 //
-//   gemm kernel (fprop, and dgrad as "fprop of dy with flipped/transposed filters"):
-//       D[128 pixels x BN channels] += A[128 px x 64 ch] (K-major) * B[BN x 64 ch] (K-major), K = taps * C/64 blocks
+//   gemm kernels (fprop; dgrad as "fprop of dy" with the KRSC filters read MN-major and the taps flipped by index; 1x1 stride-s
+//   dgrad = GEMM + strided row scatter; 3x3 stride-2 dgrad = four parity-class stride-1 sub-convolutions):
+//       D[128 pixels x BN channels] += A[128 px x 64 ch] (K-major) * B[BN x 64 ch], K = taps * C/64 blocks
+//       persistent, accumulator double-buffered in TMEM; a CTA-pair variant (cta_group::2) takes the 256-wide layers.
+//       Epilogue: TMEM -> bf16 -> swizzled shared tile -> TMA store / TMA reduce-add, optional BatchNorm sums, optional folded
+//       BatchNorm (scale, shift, identity by TMA, ReLU) for inference.
 //   wgrad kernel:
-//       D[128 k x BNC c] += dY[64 px x 128 k]^T (MN-major) * Xtap[64 px x BNC c] (MN-major), reduction over pixels,
-//       split across CTAs, fp32 partials to scratch, deterministic second-stage reduce.
+//       D[128 k x BNC c] += dY[64 px x 128 k]^T (MN-major) * Xtap[64 px x BNC c] (MN-major), reduction over pixels split
+//       across one wave of CTAs; tiles added into dW with fp32 vector reductions, or written as partials and reduced in a
+//       fixed order (deterministic mode).
 //
-// Warp roles per CTA (192 threads): warp 0 = TMA producer (one lane), warp 1 = TMEM owner + MMA issuer (one lane),
-// warps 2..5 = epilogue (each owns the 32 TMEM lanes of its warp_id%4 quarter).  smem ring of STAGES stages,
-// full/empty mbarriers, tcgen05.commit releases a stage and finally signals the epilogue.
+// Warp roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer (both run warp-uniform loops and
+// issue from the lane elect.sync picks), warps 2..5 = epilogue (each owns the 32 TMEM lanes of its warp_id%4 quarter).  smem
+// ring of STAGES stages, full/empty mbarriers, tcgen05.commit releases a stage and finally signals the epilogue.
 #include "common.cuh"
 #include <cuda.h>  // CUtensorMap + enums only; the two encode entry points are resolved at run time (no -lcuda)
 #include <mutex>

@@ -3,7 +3,9 @@
 // the HBM roof: NHWC, one 16-byte channel vector per thread, consecutive threads on consecutive channels (coalesced
 // 128 B lines), the 9 taps of a channel slab cached in shared memory.  Each thread produces a STRIP of 4 neighbouring
 // outputs along W and keeps the input columns they share in registers (18 loads instead of 36 for stride 1), all index
-// arithmetic is 32-bit and the stride is a template constant.
+// arithmetic is 32-bit, the stride is a template constant, the FMAs are packed (fma.rn.f32x2) and grids are one wave of
+// resident CTAs.  Measured 0.1-0.6 of the HBM roof (profiles/r01_layer_bench_v10_depthwise.md): the kernels are bound by
+// instruction issue and load latency at 16-24 warps per SM, see DESIGN.md section 3.2 for what was tried.
 //   fprop : y[n,p,q,c]  = sum_{r,s} x[n, p*st+r-1, q*st+s-1, c] * w[c,r,s]
 //   dgrad : stride 1: the same kernel on dy with the taps flipped;
 //           stride 2: one thread per 2x2 block of dx, which depends on exactly dy[i..i+1][j..j+1]
