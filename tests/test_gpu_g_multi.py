@@ -12,15 +12,28 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_two_rank_step_equals_averaged_shard_gradients():
+def _run_dp_check(port, **env):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-           "--master-port", "29533", os.path.join(root, "tools", "dp_check.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=root)
+           "--master-port", str(port), os.path.join(root, "tools", "dp_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=root, env=dict(os.environ, **env))
     lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
     assert r.returncode == 0 and lines, r.stderr[-2000:]
-    out = json.loads(lines[-1])
+    return json.loads(lines[-1])
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_rank_default_mode_keeps_replicas_identical():
+    """The default configuration (fp32 atomics, weight gradients on the side stream): every bucket is exchanged once, after all of
+    its gradients — the reduced buffers and the updated parameters are bit-identical on both ranks, eager and captured."""
+    out = _run_dp_check(29534, DP_CHECK_ATOMICS="1")
+    assert out["ranks_identical_graph0"] and out["ranks_identical_graph1"] and out["debug"]["flat_g_identical"]
+    assert out["debug"]["pending_after"] == [0] * out["debug"]["buckets"]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_rank_step_equals_averaged_shard_gradients():
+    out = _run_dp_check(29533)
     assert out["ranks_identical_graph0"] and out["ranks_identical_graph1"]
     assert out["debug"]["pending_after"] == [0] * out["debug"]["buckets"]
     assert out["plain_autograd_twice_rel_diff"] == 0.0          # fixed-order mode is bit-reproducible
