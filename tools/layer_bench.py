@@ -67,7 +67,7 @@ def conv_rows(batch):
         y = torch.empty(batch, P, P, K, device="cuda", dtype=torch.bfloat16)
         dy = torch.randn(batch, P, P, K, device="cuda").to(torch.bfloat16)
         dx = torch.empty_like(x)
-        dw = torch.empty(K, R, R, Cc, device="cuda")
+        dw = torch.zeros(K, R, R, Cc, device="cuda")
         flops = 2.0 * batch * P * P * K * Cc * R * R
         min_bytes = 2.0 * (x.numel() + y.numel()) + 2.0 * w.numel()
         for name, pass_id, fn in (("fprop", DV_CONV_FPROP, lib.dv_conv_fprop), ("dgrad", DV_CONV_DGRAD, lib.dv_conv_dgrad),
@@ -80,9 +80,12 @@ def conv_rows(batch):
                     sums = torch.zeros(2 * K, device="cuda")
                     p.stat_sums = sums.data_ptr()
             elif pass_id == DV_CONV_DGRAD:
-                p.x, p.w, p.y, p.w_t = dx.data_ptr(), w.data_ptr(), dy.data_ptr(), wt.data_ptr()
+                p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), dy.data_ptr()      # as in training: KRSC filters read MN-major
+                if os.environ.get("LB_WT"):
+                    p.w_t = wt.data_ptr()
             else:
                 p.x, p.w, p.y = x.data_ptr(), dw.data_ptr(), dy.data_ptr()
+                p.accumulate = 0 if os.environ.get("LB_WGRAD_PARTIALS") else 1   # as in training: tiles added into dW
             need = lib.dv_conv_workspace_bytes(C.byref(p), pass_id)
             ws = torch.empty(max(need, 16), dtype=torch.uint8, device="cuda")
             p.workspace, p.workspace_bytes = ws.data_ptr(), need
