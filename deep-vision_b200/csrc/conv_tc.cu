@@ -95,6 +95,14 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, uint32_
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
+// fp32 tile ADDED to a 3-D tensor (wgrad: dW [K][taps][C]); elements outside the tensor are clipped
+__device__ __forceinline__ void tma_reduce_add_3d(const CUtensorMap* tm, uint32_t smem_addr, int c0, int c1, int c2) {
+  asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_addr), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* tm) {
@@ -889,6 +897,7 @@ struct WgradArgs {
   int kb_per_split; // 64-pixel blocks per split
   int kb_total;
   int c_tiles;
+  int tma_reduce;   // accumulate mode: 1 = fp32 tiles go to dW through TMA reduce-add, 0 = per-lane red.global.add
 };
 
 // MH = number of 128-row halves of the output tile (1 or 2).  With MH == 2 a CTA owns 256 output channels: two
@@ -896,7 +905,8 @@ struct WgradArgs {
 // 256 (not 128) output channels.
 template <int BNC, int STAGES, int MH>
 __global__ void __launch_bounds__(kThreads)
-conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const WgradArgs g) {
+conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+                     const __grid_constant__ CUtensorMap tmDW, const WgradArgs g) {
   constexpr int kPix = 64;                       // pixels per stage (= 4 MMAs of K=16)
   constexpr int kChunk = kPix * 128;             // one [64 px][64 ch] box = 8 KB
   constexpr int kABytesW = MH * 2 * kChunk;      // 128*MH output channels of dY
@@ -1000,6 +1010,34 @@ conv_tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_cons
     const int quarter = warp & 3;
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
+    if (g.dw_atomic != nullptr && g.tma_reduce) {
+      // Every MMA has completed, so the operand ring is free: each warp stages its [32 filters][32 channels] fp32 chunks there
+      // (row = lane, 128 B, 16-byte pieces XOR-swizzled by row) and hands them to the TMA unit, which ADDS whole 128-byte lines
+      // into dW at the L2 (cp.reduce.async.bulk) and clips what lies outside [K][taps][C].  The per-lane red.global.add.v4.f32 it
+      // replaces touched 32 different lines per instruction, half a sector each.
+      uint8_t* tiles = smem + (size_t)quarter * (MH * (BNC / 32)) * 4096;
+#pragma unroll 1
+      for (int h = 0; h < MH; ++h) {
+#pragma unroll 1
+        for (int c = 0; c < BNC / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(h * BNC + c * 32), v);
+          tmem_ld_wait();
+          const uint32_t tile = smem_u32(tiles + (size_t)(h * (BNC / 32) + c) * 4096);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(tile + lane * 128 + ((j ^ (lane & 7)) * 16)), "r"(v[4 * j]),
+                         "r"(v[4 * j + 1]), "r"(v[4 * j + 2]), "r"(v[4 * j + 3])
+                         : "memory");
+          fence_proxy_async_smem();
+          __syncwarp();
+          const int c0 = c_tile * BNC + c * 32, k0 = k_tile * (128 * MH) + h * 128 + quarter * 32;
+          if (lane == 0 && c0 < g.C && k0 < g.K) tma_reduce_add_3d(&tmDW, tile, c0, tap, k0);
+        }
+      }
+      if (lane == 0) tma_store_wait_read();   // the bulk reductions have read their tiles before shared memory goes away
+      __syncwarp();
+    } else
 #pragma unroll 1
     for (int h = 0; h < MH; ++h) {
       const int k = k_tile * (128 * MH) + h * 128 + quarter * 32 + lane;
@@ -1102,6 +1140,20 @@ static int make_map_2d(CUtensorMap* tm, const void* ptr, uint64_t rows, uint64_t
 // NHWC activation, im2col traversal of a R x S window with the given stride / padding; one load = `pixels` output
 // positions (walking q, then p, then n) x 64 channels.  Coordinates passed to the load are the input coordinate of
 // the window's top-left tap for the first output position: (c, q*stride - pad, p*stride - pad, n), offsets = (s, r).
+// dW as a 3-D fp32 tensor {C, taps, K} with a box of 32 channels x 1 tap x 32 filters (one epilogue warp's chunk)
+static int make_map_dw(CUtensorMap* tm, float* dw, int K, int taps, int C) {
+  DriverApi& api = driver_api();
+  DV_REQUIRE(api.ok, DV_ERR_CUDA, "conv_tc: cuTensorMapEncode* entry points not available from the driver");
+  cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)taps, (cuuint64_t)K};
+  cuuint64_t strides[2] = {(cuuint64_t)C * 4, (cuuint64_t)taps * C * 4};
+  cuuint32_t box[3] = {32, 1, 32};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = api.tiled(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, dw, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DV_REQUIRE(r == CUDA_SUCCESS, DV_ERR_CUDA, "cuTensorMapEncodeTiled(dW) failed (%d) K=%d taps=%d C=%d", (int)r, K, taps, C);
+  return DV_OK;
+}
+
 // corners != nullptr: {lower_w, lower_h, upper_w, upper_h} given explicitly (window origins run over [lower, dim - 1 + upper])
 static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W, int C, int R, int S, int stride, int pad,
                            uint32_t pixels, const int* corners = nullptr) {
@@ -1199,7 +1251,7 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
 }
 
 template <int BNC, int STAGES, int MH>
-static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const WgradArgs& g, int tiles, int splits,
+static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const CUtensorMap& tmDW, const WgradArgs& g, int tiles, int splits,
                         cudaStream_t st) {
   constexpr int smem = STAGES * (2 * MH + BNC / 64) * 8192 + 1024 + 256;
   static_assert(smem <= 227 * 1024, "wgrad ring exceeds shared memory");
@@ -1207,7 +1259,8 @@ static int launch_wgrad(const CUtensorMap& tmDY, const CUtensorMap& tmX, const W
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_wgrad_kernel<BNC, STAGES, MH>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                   cudaSharedmemCarveoutMaxShared));
   dim3 grid((unsigned)tiles, (unsigned)splits);
-  conv_tc_wgrad_kernel<BNC, STAGES, MH><<<grid, kThreads, smem, st>>>(tmDY, tmX, g);
+  static_assert(MH == 2 || 4 * (BNC / 32) * 4096 <= STAGES * (2 * MH + BNC / 64) * 8192, "epilogue tiles must fit the operand ring");
+  conv_tc_wgrad_kernel<BNC, STAGES, MH><<<grid, kThreads, smem, st>>>(tmDY, tmX, tmDW, g);
   DV_LAUNCH_OK("conv_tc_wgrad_kernel");
   return DV_OK;
 }
@@ -1474,19 +1527,26 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
   if (g.x_im2col) rc = make_map_im2col(&tmB, p->x, p->N, p->H, p->W, p->C, p->R, p->S, p->stride, p->pad, 64);
   else rc = make_map_2d(&tmB, p->x, (uint64_t)g.Mpix, (uint64_t)p->C, 64);
   if (rc) return rc;
+  alignas(64) CUtensorMap tmW = tmA;   // only read by the kernel when g.tma_reduce is set
+  static const int tma_reduce_enabled = env_int("DV_TC_WGRAD_TMA", 1);
+  if (p->accumulate && tma_reduce_enabled && w.mh == 1 && aligned16(p->w) && (p->C % 4) == 0) {
+    rc = make_map_dw(&tmW, (float*)p->w, p->K, p->R * p->S, p->C);
+    if (rc) return rc;
+    g.tma_reduce = 1;
+  }
   if (w.mh == 1) {
     switch (w.bnc) {
-      case 64: rc = launch_wgrad<64, 4, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
-      case 128: rc = launch_wgrad<128, 3, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
-      case 192: rc = launch_wgrad<192, 4, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
-      default: rc = launch_wgrad<256, 4, 1>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      case 64: rc = launch_wgrad<64, 4, 1>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
+      case 128: rc = launch_wgrad<128, 3, 1>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
+      case 192: rc = launch_wgrad<192, 4, 1>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
+      default: rc = launch_wgrad<256, 4, 1>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
     }
   } else {
     switch (w.bnc) {
-      case 64: rc = launch_wgrad<64, 5, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
-      case 128: rc = launch_wgrad<128, 4, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
-      case 192: rc = launch_wgrad<192, 3, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
-      default: rc = launch_wgrad<256, 3, 2>(tmA, tmB, g, w.tiles, w.splits, st); break;
+      case 64: rc = launch_wgrad<64, 5, 2>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
+      case 128: rc = launch_wgrad<128, 4, 2>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
+      case 192: rc = launch_wgrad<192, 3, 2>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
+      default: rc = launch_wgrad<256, 3, 2>(tmA, tmB, tmW, g, w.tiles, w.splits, st); break;
     }
   }
   if (rc) return rc;

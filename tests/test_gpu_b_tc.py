@@ -89,6 +89,38 @@ def test_tc_wgrad_matches_oracle(case):
     assert np.array_equal(dw, dw2)         # fixed-order split reduction: bit-reproducible
 
 
+@pytest.mark.parametrize("case", WGRAD_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_wgrad_accumulate_adds_into_dw(case):
+    """dv_conv_params.accumulate = 1 (what the trainer uses): the tiles are ADDED into dW — through TMA reduce-add of fp32 tiles,
+    clipped at the tensor's K / C edges — on top of what is already there; twice in a row adds twice."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, Cc, H, W, K, R, stride, pad = case
+    x = _rand((N, Cc, H, W), 1, BF)
+    w = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+    P, Q = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - R) // stride + 1
+    dy = _rand((N, K, P, Q), 3, BF)
+    _, dw_ref = ref_ops.conv2d_backward(x, w, dy, stride, pad)
+    prior = np.random.default_rng(4).standard_normal((K, R, R, Cc)).astype(np.float32)
+    xd = torch.from_numpy(np.ascontiguousarray(x.transpose(0, 2, 3, 1))).cuda().to(BF)
+    dyd = torch.from_numpy(np.ascontiguousarray(dy.transpose(0, 2, 3, 1))).cuda().to(BF)
+    guard = torch.full((K * R * R * Cc + 64,), 7.0, device="cuda")          # dW sits inside a larger buffer: nothing outside may change
+    dwd = guard[32:32 + K * R * R * Cc].view(K, R, R, Cc)
+    dwd.copy_(torch.from_numpy(prior))
+    p = lib.ConvParams()
+    p.x, p.w, p.y = xd.data_ptr(), dwd.data_ptr(), dyd.data_ptr()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo, p.accumulate = N, H, W, Cc, K, R, R, stride, pad, lib.DV_BF16, lib.DV_ALGO_TC, 1
+    for times in (1, 2):
+        lib.check(lib.lib.dv_conv_wgrad(C.byref(p), stream_ptr()), "wgrad accumulate")
+        torch.cuda.synchronize()
+        got = dwd.double().cpu().numpy().transpose(0, 3, 1, 2)
+        want = prior.astype(np.float64).transpose(0, 3, 1, 2) + times * dw_ref
+        assert rel_l2(got, want) < 1e-4, times
+    assert float(guard[:32].min()) == 7.0 and float(guard[:32].max()) == 7.0
+    assert float(guard[32 + K * R * R * Cc:].min()) == 7.0 and float(guard[32 + K * R * R * Cc:].max()) == 7.0
+
+
 def _gpu_conv(pass_id, xd, wd, dyd, stride, pad, algo, wt=None):
     """device tensors in (NHWC / KRSC, bf16) -> device tensor out; for the full-size checks (no host round trip)."""
     import ctypes as C
