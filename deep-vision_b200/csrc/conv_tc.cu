@@ -10,8 +10,8 @@
 //       BatchNorm (scale, shift, identity by TMA, ReLU) for inference.
 //   wgrad kernel:
 //       D[128 k x BNC c] += dY[64 px x 128 k]^T (MN-major) * Xtap[64 px x BNC c] (MN-major), reduction over pixels split
-//       across one wave of CTAs; tiles added into dW with fp32 vector reductions, or written as partials and reduced in a
-//       fixed order (deterministic mode).
+//       across one wave of CTAs; tiles added into dW by TMA reduce-add (fp32, staged in the idle operand ring), or written as
+//       partials and reduced in a fixed order (deterministic mode).
 //
 // Warp roles per CTA (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer (both run warp-uniform loops and
 // issue from the lane elect.sync picks), warps 2..5 = epilogue (each owns the 32 TMEM lanes of its warp_id%4 quarter).  smem

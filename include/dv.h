@@ -80,7 +80,7 @@ typedef struct dv_conv_params {
   int32_t y_f32;      /* fprop only: 1 = write y as fp32 even when dtype is bf16 (the logits of nn.Linear) */
   int32_t accumulate; /* dgrad: 1 = dx += result instead of dx = result (the second gradient of a tensor that feeds two
                          consumers, e.g. a residual block's input: resnet50.py:147-163).
-                         wgrad: 1 = dw += result, added straight into dw with fp32 vector reductions — no workspace, no
+                         wgrad: 1 = dw += result, added straight into dw (fp32 tiles through TMA reduce-add) — no workspace, no
                          second pass; the caller provides a zeroed (or to-be-accumulated) dw and accepts a summation order
                          that varies run to run.  0 = split partials in the workspace + fixed-order reduce (bit-reproducible) */
   /* fprop on the tensor-core path only, optional — inference with the BatchNorm that follows the convolution folded into
