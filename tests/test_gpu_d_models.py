@@ -2,7 +2,7 @@
 
 fp32: eval-mode logits <= 1e-4 of the reference's fp64 logits; train-mode logits are gated at the larger of 1e-4 and
 10x the reference's own fp32-vs-fp64 distance on that fixture (random-init BN networks amplify rounding; SURVEY.md
-App. B).  bf16: eval-mode logits <= 2e-2 with identical top-1 (north_star); train-mode is reported against torch
+App. B).  bf16: eval-mode logits <= 2e-2 with identical top-1 (north_star) for all four models; train-mode is reported against torch
 autocast's own distance on the same fixture (stored in it) and gated at max(3e-1, 2x that).
 """
 import numpy as np
@@ -74,10 +74,67 @@ def test_model_bf16_logits(name):
     else:
         floor = float(rec["torch_bf16_autocast_rel"])
         print(f"{name}: ours {err:.3e}  torch bf16 autocast {floor:.3e}")
-        # north_star bar: 2e-2 and identical top-1.  The 152-layer stack keeps its residual stream in bf16 through 50
-        # blocks (torch's CPU autocast keeps it in fp32) and lands at ~3e-2; it is gated at 5e-2 and reported.
-        assert err < (5e-2 if "resnet152" in name else 2e-2), (err, floor)
+        # north_star bar for every model, ResNet-152 included: 2e-2 and identical top-1.  (The default eval path folds
+        # BatchNorm into the convolution's epilogue: one bf16 rounding per conv->BN(+identity)(+ReLU) group; measured
+        # 5.6e-3 on the 152-layer stack, 5.8e-3 on ResNet-50.)
+        assert err < 2e-2, (err, floor)
         assert np.array_equal(y.argmax(1), rec["logits_fp64"].argmax(1))
+
+
+UNFUSED_EVAL = ["model_resnet34_b4_224_eval", "model_resnet50_b2_64_eval", "model_mobilenet1_b2_64_eval",
+                pytest.param("model_resnet152_b2_64_eval", marks=pytest.mark.xfail(
+                    strict=True, reason="set_fold_bn(False) rounds the conv output to bf16 BEFORE the eval-mode BN (two roundings per "
+                                        "group): 3.08e-2 on the 152-layer stack; a CPU emulation of exactly that arithmetic on the "
+                                        "reference weights gives 3.08e-2 as well (tools/diag_eval_stream.py).  Not the default path."))]
+
+
+@pytest.mark.parametrize("name", UNFUSED_EVAL)
+def test_model_bf16_logits_unfused_eval_path(name):
+    """The debugging switch set_fold_bn(False): eval-mode BN as its own pass after a bf16 convolution output.  Held to the
+    same 2e-2 bar; the one case that misses it is marked, not hidden behind a wider gate."""
+    dv.set_fold_bn(False)
+    try:
+        y, rec = _logits(name, torch.bfloat16)
+    finally:
+        dv.set_fold_bn(True)
+    err = rel_l2(y, rec["logits_fp64"])
+    print(f"{name}: unfused eval path {err:.3e}")
+    assert err < 2e-2, err
+
+
+@pytest.mark.parametrize("dtype,bar", [(torch.float32, 1e-4), (torch.bfloat16, 2e-2)], ids=["fp32", "bf16"])
+def test_resnet50_eval_logits_at_the_bench_configuration(dtype, bar):
+    """BASELINE.json configs[1]'s shape — 256 x 3 x 224 x 224 — through the whole ResNet-50 in eval mode, so every kernel runs
+    with the grid, tile walk and tensor maps of the benchmarked configuration.  Eval-mode images are independent, so the oracle
+    port (oracle.ref_models, fp64 on the host) is evaluated on twelve of the 256 images: the first, middle and last four.
+    Measured: fp32 2.0e-6, bf16 4.7e-3."""
+    from oracle import ref_models
+    torch.manual_seed(0)
+    m = dv.models.ResNet50()
+    sd = ref_models.clone_state(m.state_dict(), dtype=torch.float64)
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(256, 3, 224, 224, generator=g)
+    sel = [0, 1, 2, 3, 126, 127, 128, 129, 252, 253, 254, 255]
+    xs = x[sel]
+    if dtype == torch.bfloat16:
+        xs = xs.to(torch.bfloat16).float()      # the product rounds the image once at the entrance; not a model error
+    with torch.no_grad():
+        ref = ref_models.model_forward("resnet50", xs.double(), sd, bn_train=False).numpy()
+    dv.set_compute_dtype(dtype)
+    m = m.cuda().eval()
+    with torch.no_grad():
+        y = m(x.cuda())
+    torch.cuda.synchronize()
+    y = y.cpu().numpy()
+    assert y.shape == (256, 1000) and np.isfinite(y).all()
+    err = rel_l2(y[sel], ref)
+    print(f"resnet50 eval B=256 224x224 {dtype}: {err:.3e}")
+    assert err < bar, err
+    # identical top-1 (north_star) wherever the reference's own decision is not a near-tie of its two best logits
+    top = np.sort(ref, axis=1)
+    decided = (top[:, -1] - top[:, -2]) > 4 * np.abs(y[sel] - ref).max()
+    print(f"top-1 decided on {int(decided.sum())} of {len(sel)} images")
+    assert np.array_equal(y[sel].argmax(1)[decided], ref.argmax(1)[decided])
 
 
 def test_resnet50_train_step_fp32_matches_oracle_gradients():
