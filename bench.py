@@ -1,14 +1,21 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark of the hot path: ResNet-50 V1 bf16 training step, batch 256/GPU, synthetic 224x224
-(BASELINE.json configs[1]; configs[2] under torchrun with --gpus N).
+(BASELINE.json configs[1]; configs[2] under torchrun with --gpus N; configs[3]/[4] with --model mobilenet1 / resnet152).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--model resnet50|resnet34|resnet152|mobilenet1] [--batch B]
+                    [--deterministic]
     python bench.py --impl reference ...     # the reference's PyTorch CPU path (oracle port) on the host cores
 
-Prints ONE JSON line (rank 0).  `value` = images/s of the whole job, inputs resident in HBM; `e2e` = the same step fed
-from pinned host memory with the loss read back every step (the reference's train.py:444-470 behaviour);
-`roofline` = the dominant kernel class timed with CUDA events in this process; `cpu_baseline` = the oracle port of the
-reference step on the host cores (bounded sample).
+Prints ONE JSON line (rank 0).
+  value            images/s of the whole job, inputs resident in HBM (CUDA events, max over ranks)
+  e2e              the same step fed from pinned host memory (fp32 NCHW batches, what train.py:444-446 moves) with the loss
+                   read back every step (train.py:470); e2e_uint8 = the same with uint8 batches normalised on the device
+                   (deep_vision_b200.data.GpuTransform)
+  roofline         best-shape tensor-bound kernel, timed live;  roofline_hbm: an HBM-bound BatchNorm pass, timed live
+  conv_time_weighted   all 52 non-stem convolutions x 3 passes timed one by one: total FLOPs / total time vs the burst peak
+  step_top_kernel  the kernel class with the largest share of the captured step (CUPTI) and its in-step roofline fraction
+  cpu_baseline     the oracle port of the reference step on the host cores (bounded sample), plus BASELINE configs[0]
+The reference arm imports nothing from the product package: its process never maps libdv_b200.so.
 """
 import argparse
 import json
@@ -27,6 +34,14 @@ MODELS = {
     "resnet152": dict(ctor="ResNet152", batch=128, gflop_per_img=67.45),
     "mobilenet1": dict(ctor="MobileNetV1", batch=256, gflop_per_img=3.28),
 }
+# ResNet/pytorch/train.py:166-214 — the reference's optimiser settings (kept here too so that the reference arm needs
+# nothing from the product package)
+OPTIM = {
+    "resnet34": dict(optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4),
+    "resnet50": dict(optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4),
+    "resnet152": dict(optimizer="sgd", lr=0.1, momentum=0.9, weight_decay=1e-4),
+    "mobilenet1": dict(optimizer="rmsprop", lr=0.045, alpha=0.9, eps=1.0, weight_decay=0.0),
+}
 
 
 def peaks():
@@ -36,6 +51,16 @@ def peaks():
         return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
                     source="measured")
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback")
+
+
+def ncu_traffic(key):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of a kernel, from the committed summary of an `ncu --set full`
+    capture (profiles/ncu_traffic.json, written by tools/ncu_traffic.py from the raw CSV).  None when no capture is on file."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(key)
+        return None if rec is None else float(rec["dram_bytes"])
+    except (OSError, ValueError, KeyError):
+        return None
 
 
 class ClockSampler:
@@ -77,32 +102,60 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_reference_step(model, batch, steps, warmup):
-    """The reference's training step on the host cores: oracle/ref_models.py (a torch-functional port of the model
-    files; /root/reference does not exist on the GPU box), fp32, all host threads, same synthetic distribution."""
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.lower().startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+def cpu_reference_step(model, batch, reps=3, warmup=1):
+    """The reference's training step on the host cores: oracle/ref_models.py (a torch-functional port of the model files;
+    /root/reference does not exist on the GPU box) driven by a state_dict from oracle/ref_init.py, fp32, all host threads,
+    same synthetic distribution.  Best of `reps` single steps after `warmup`.  Returns (images/s, s/step, cores)."""
     import torch
-    from oracle import ref_models
-    import deep_vision_b200 as dv
-    from deep_vision_b200.train import TRAINING_CONFIG
+    from oracle import ref_init, ref_models
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    torch.manual_seed(0)
-    net = getattr(dv.models, MODELS[model]["ctor"])()
-    sd = ref_models.clone_state(net.state_dict(), dtype=torch.float32, requires_grad=True)
-    cfg = TRAINING_CONFIG[model]
+    sd = ref_models.clone_state(ref_init.init_state(model, seed=0), dtype=torch.float32, requires_grad=True)
     g = torch.Generator().manual_seed(1234)
     images = torch.randn(batch, 3, 224, 224, generator=g)
     labels = torch.randint(0, 1000, (batch,), generator=g)
     opt_state = {}
+    cfg = OPTIM[model]
     kw = dict(optimizer=cfg["optimizer"], lr=cfg["lr"], momentum=cfg.get("momentum", 0.0), weight_decay=cfg["weight_decay"],
               alpha=cfg.get("alpha", 0.9), eps=cfg.get("eps", 1.0))
     for _ in range(warmup):
         ref_models.train_step(model, sd, images, labels, opt_state, **kw)
-    t0 = time.perf_counter()
-    for _ in range(steps):
+    best = float("inf")
+    for _ in range(reps):
+        t0 = time.perf_counter()
         ref_models.train_step(model, sd, images, labels, opt_state, **kw)
-    dt = time.perf_counter() - t0
-    return batch * steps / dt, dt / steps, cores
+        best = min(best, time.perf_counter() - t0)
+    return batch / best, best, cores
+
+
+def cpu_config0(reps=3):
+    """BASELINE.json configs[0]: ResNet-34 fp32 forward, batch 4 of 3x224x224 synthetic, on the CPU (model in eval mode under
+    no_grad, as the reference's notebooks and validate() run it).  Best of `reps` after one warm-up."""
+    import torch
+    from oracle import ref_init, ref_models
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = ref_models.clone_state(ref_init.init_state("resnet34", seed=0), dtype=torch.float32)
+    x = torch.randn(4, 3, 224, 224, generator=torch.Generator().manual_seed(1234))
+    best = float("inf")
+    with torch.no_grad():
+        ref_models.model_forward("resnet34", x, sd, bn_train=False)
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            ref_models.model_forward("resnet34", x, sd, bn_train=False)
+            best = min(best, time.perf_counter() - t0)
+    return {"workload": "ResNet-34 fp32 forward, batch 4, 3x224x224 synthetic, CPU (BASELINE configs[0])", "value": round(4 / best, 2),
+            "unit": "images/s", "ms": round(best * 1e3, 2), "cores": cores, "sample": f"best of {reps} after 1 warm-up"}
 
 
 def run_reference(args):
@@ -110,24 +163,42 @@ def run_reference(args):
     if rank != 0:
         return
     batch = args.cpu_batch
-    ips, sec, cores = cpu_reference_step(args.model, batch, max(1, min(args.steps, 3)), 1)
+    reps = max(1, min(args.steps, 3))
+    ips, sec, cores = cpu_reference_step(args.model, batch, reps, 1)
+    assert "deep_vision_b200" not in sys.modules and not any("libdv_b200" in l for l in open("/proc/self/maps")), \
+        "the reference arm must not load the product"
     line = {
         "impl": "reference", "metric": "train images/sec", "value": round(ips, 3), "unit": "images/s", "n_gpus": args.gpus,
-        "steps": max(1, min(args.steps, 3)), "warmup": 1, "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True,
+        "steps": reps, "warmup": 1, "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.model} V1 training step (fwd+CE+bwd+optimizer), 224x224 synthetic, CPU batch {batch} "
                                f"(bounded sample of the batch-{MODELS[args.model]['batch']}/GPU workload)"},
-        "cpu_baseline": {"value": round(ips, 3), "unit": "images/s", "cores": cores, "kind": "port",
-                         "sample": f"{max(1, min(args.steps, 3))} steps of batch {batch} after 1 warm-up"},
+        "cpu_baseline": {"value": round(ips, 3), "unit": "images/s", "cores": cores, "kind": "port", "cpu": cpu_model(),
+                         "sample": f"best of {reps} steps of batch {batch} (fp32, oracle/ref_models.py) after 1 warm-up"},
         "e2e": {"value": round(ips, 3), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
 
 
-def kernel_roofline(torch, dv, pk):
-    """Dominant kernel class = the tcgen05 implicit-GEMM convolution.  Timed here on its heaviest ResNet-50 layer shape
-    (3x3, 256->256 at 14x14, batch 256: M=50176, N=256, K=2304, 59.2 GFLOP) with CUDA events on the launching stream,
-    L2 flushed between launches."""
+def _event_times(torch, fn, flush, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    times = []
+    for _ in range(iters):
+        flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        e1.synchronize()
+        times.append(e0.elapsed_time(e1))
+    return sum(times) / len(times)
+
+
+def kernel_roofline(torch, pk):
+    """Best-shape tensor-bound kernel = the tcgen05 implicit-GEMM convolution on its heaviest ResNet-50 layer shape (3x3,
+    256->256 at 14x14, batch 256: M=50176, N=256, K=2304, 59.2 GFLOP), CUDA events on the launching stream, L2 flushed between
+    launches.  The whole-step view of the convolutions is `conv_time_weighted`."""
     import ctypes as C
     from deep_vision_b200.lib import ConvParams, DV_ALGO_TC, DV_BF16, check, lib
     N, H, Cc, K, R = 256, 14, 256, 256, 3
@@ -139,31 +210,18 @@ def kernel_roofline(torch, dv, pk):
     p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, H, Cc, K, R, R, 1, 1, DV_BF16, DV_ALGO_TC
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    for _ in range(3):
-        check(lib.dv_conv_fprop(C.byref(p), st), "dv_conv_fprop")
-    times = []
-    for _ in range(10):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        check(lib.dv_conv_fprop(C.byref(p), st), "dv_conv_fprop")
-        e1.record()
-        e1.synchronize()
-        times.append(e0.elapsed_time(e1))
-    ms = sum(times) / len(times)
+    ms = _event_times(torch, lambda: check(lib.dv_conv_fprop(C.byref(p), st), "dv_conv_fprop"), flush)
     flops = 2.0 * N * H * H * K * Cc * R * R
     achieved = flops / (ms * 1e-3) / 1e12
     return {"bound": "tensor", "kernel": "conv_tc_gemm_pair_kernel<6> (cta_group::2) fprop 3x3 256->256 @14x14 B256", "achieved": round(achieved, 1),
             "peak": pk["tf_burst"], "unit": "TFLOP/s", "frac": round(achieved / pk["tf_burst"], 4),
-            # dram__bytes_read.sum + dram__bytes_write.sum per launch from `ncu --set full` (profiles/r01_ncu_full_v9_pair_wgrad.csv);
-            # the algorithmic minimum is 52.6 MB (x 25.7 + y 25.7 + w 1.2): the output was still in L2 when the capture ended
-            "traffic": 26.9e6, "algorithmic_flops": flops,
+            "traffic": ncu_traffic("conv_fprop_3x3_256_14"), "algorithmic_flops": flops, "algorithmic_bytes": 2.0 * (x.numel() + y.numel() + w.numel()),
             "ms_per_launch": round(ms, 4), "peak_source": pk["source"]}
 
 
 def hbm_roofline(torch, pk):
-    """The dominant HBM-bound kernel class of the step (BatchNorm passes = 45 % of it): dv_bn_bwd_apply on a 256-channel
-    56x56 tensor at batch 256 (no residual: reads x and dy, writes dx = 6 bytes per element), CUDA events, L2 flushed."""
+    """An HBM-bound pass of the step's largest kernel family (BatchNorm): dv_bn_bwd_apply on a 256-channel 56x56 tensor at
+    batch 256 (no residual: reads x and dy, writes dx = 6 bytes per element), CUDA events, L2 flushed."""
     import ctypes as C
     from deep_vision_b200.lib import BnBwdParams, DV_BF16, check, lib
     M, Cc = 256 * 56 * 56, 256
@@ -175,31 +233,113 @@ def hbm_roofline(torch, pk):
     q.M, q.C, q.dtype, q.relu = M, Cc, DV_BF16, 1
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    for _ in range(3):
-        check(lib.dv_bn_bwd_apply(C.byref(q), st), "dv_bn_bwd_apply")
-    times = []
-    for _ in range(10):
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        check(lib.dv_bn_bwd_apply(C.byref(q), st), "dv_bn_bwd_apply")
-        e1.record()
-        e1.synchronize()
-        times.append(e0.elapsed_time(e1))
-    ms = sum(times) / len(times)
+    ms = _event_times(torch, lambda: check(lib.dv_bn_bwd_apply(C.byref(q), st), "dv_bn_bwd_apply"), flush)
     nbytes = 6.0 * M * Cc
     gbs = nbytes / (ms * 1e-3) / 1e9
     return {"bound": "hbm", "kernel": "bn_bwd_apply_kernel<bf16> C=256 @56x56 B256 (ReLU mask recomputed)", "achieved": round(gbs, 1),
-            "peak": pk["hbm"], "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4), "traffic": None, "algorithmic_bytes": nbytes,
-            "ms_per_launch": round(ms, 4), "peak_source": pk["source"]}
+            "peak": pk["hbm"], "unit": "GB/s", "frac": round(gbs / pk["hbm"], 4), "traffic": ncu_traffic("bn_bwd_apply_256_56"),
+            "algorithmic_bytes": nbytes, "ms_per_launch": round(ms, 4), "peak_source": pk["source"]}
+
+
+def conv_time_weighted(torch, pk):
+    """All 19 distinct ResNet-50 convolution shapes x {fprop, dgrad, wgrad} at batch 256, each timed alone with the L2 flushed
+    (tools/layer_bench.py), weighted by how often the shape occurs: 5.74 TFLOP of tensor work over the sum of the times."""
+    from tools import layer_bench
+    rows = layer_bench.conv_rows(256, iters=5)
+    tw = layer_bench.time_weighted(rows)
+    worst = min((r for r in rows if r["bound"] == "tensor"), key=lambda r: r["frac"])
+    return {"tflop_per_step": tw["tflop"], "ms_sum": tw["ms"], "achieved": tw["tflops"], "unit": "TFLOP/s", "peak": pk["tf_burst"],
+            "frac": round(tw["tflops"] / pk["tf_burst"], 4),
+            "worst_tensor_bound": {"layer": worst["layer"], "pass": worst["passname"], "frac": worst["frac"], "ms": worst["ms"]}}
+
+
+class BnInventory:
+    """Element counts of every BatchNorm2d call of one training step (forward pre-hooks), for the algorithmic bytes of the
+    BatchNorm kernel classes: E elements, residual yes/no, ReLU yes/no, and whether the backward sums came fused out of the
+    dgrad epilogue (no bn_reduce launch for that layer)."""
+
+    def __init__(self, model, dvnn):
+        self.rows, self.handles = [], []
+        for m in model.modules():
+            if isinstance(m, dvnn.BatchNorm2d):
+                self.handles.append(m.register_forward_pre_hook(self._hook, with_kwargs=True))
+
+    def _hook(self, mod, args, kwargs):
+        x = args[0]
+        numel = x.x.shape[0] * mod.num_features if hasattr(x, "conv") else x.numel()   # (a PendingConv only in inference)
+        res = kwargs.get("residual", args[1] if len(args) > 1 else None) is not None
+        relu = kwargs.get("act", args[2] if len(args) > 2 else None) is not None
+        self.rows.append(dict(mod=mod, E=int(numel), res=res, relu=relu))
+
+    def close(self):
+        for h in self.handles:
+            h.remove()
+
+    def bytes_of(self, cls):
+        tot = 0.0
+        for r in self.rows:
+            E, res, mask = r["E"], r["res"], r["res"] and r["relu"]
+            fused = bool(getattr(r["mod"], "_dv_bwd_sums_fused", False))
+            if cls == "bn_apply":
+                tot += 4 * E + (2 * E if res else 0) + (E / 8 if mask else 0)
+            elif cls == "bn_bwd_reduce":
+                tot += 0 if fused else 4 * E + (E / 8 if mask else 0)
+            elif cls == "bn_bwd_apply":
+                tot += 6 * E + ((2 * E + E / 8) if res else 0)
+        return tot
+
+
+def kernel_class(name):
+    """CUPTI kernel name -> class: templates dropped, except that bn_reduce_kernel<T, MODE, RELU> is split into the forward
+    statistics pass (MODE 0) and the backward sums (MODE 1)."""
+    n = name.replace("(anonymous namespace)::", "").replace("void ", "").replace("dv::", "")
+    base = n.split("<")[0].split("(")[0]
+    if base == "bn_reduce_kernel" and "<" in n:
+        targs = [a.strip() for a in n.split("<", 1)[1].split(">")[0].split(",")]
+        return "bn_bwd_reduce" if len(targs) > 1 and targs[1] == "1" else "bn_stats"
+    return {"bn_apply_kernel": "bn_apply", "bn_bwd_apply_kernel": "bn_bwd_apply"}.get(base, base)
+
+
+def step_top_kernel(torch, trainer, images, labels, inventory, pk, steps=3):
+    """CUPTI timeline (torch.profiler) of `steps` replays of the captured step: share of every kernel class; for the top class,
+    when it is one of the BatchNorm passes, its in-step HBM roofline (algorithmic bytes of all its launches / its busy time)."""
+    import collections
+    from torch.profiler import ProfilerActivity, profile
+    trainer.step(images, labels)   # (re-)records the captured step for this input if needed
+    torch.cuda.synchronize()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        for _ in range(steps):
+            trainer.step(images, labels)
+        torch.cuda.synchronize()
+    ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and e.time_range.end > e.time_range.start]
+    if not ev:
+        return None
+    span = (max(e.time_range.end for e in ev) - min(e.time_range.start for e in ev)) / steps
+    agg = collections.defaultdict(lambda: [0, 0.0])
+    for e in ev:
+        k = kernel_class(e.name)
+        agg[k][0] += 1
+        agg[k][1] += e.time_range.end - e.time_range.start
+    rows = sorted(((k, n / steps, t / steps) for k, (n, t) in agg.items()), key=lambda r: -r[2])
+    k, n, us = rows[0]
+    out = {"kernel": k, "launches_per_step": round(n, 1), "us_per_step": round(us, 1), "share_of_step": round(us / span, 4),
+           "span_us": round(span, 1), "busy_us": round(sum(r[2] for r in rows), 1),
+           "classes": [{"kernel": r[0], "launches": round(r[1], 1), "us": round(r[2], 1)} for r in rows[:8]]}
+    nbytes = inventory.bytes_of(k)
+    if nbytes > 0:
+        gbs = nbytes / (us * 1e-6) / 1e9
+        out.update({"bound": "hbm", "algorithmic_bytes": nbytes, "achieved": round(gbs, 1), "unit": "GB/s", "peak": pk["hbm"],
+                    "frac": round(gbs / pk["hbm"], 4)})
+    return out
 
 
 def run_ours(args):
     import torch
     import torch.distributed as dist
     import deep_vision_b200 as dv
+    from deep_vision_b200 import nn as dvnn
     from deep_vision_b200.lib import lib
-    from deep_vision_b200.train import TRAINING_CONFIG, Trainer
+    from deep_vision_b200.train import TRAINING_CONFIG, HostFeeder, Trainer
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -214,6 +354,8 @@ def run_ours(args):
     spec = MODELS[args.model]
     batch = args.batch or spec["batch"]
     dv.set_compute_dtype(torch.bfloat16)
+    if args.deterministic:
+        dv.set_deterministic(True)   # fixed-order reductions everywhere: the mode whose gradients are proved bit-reproducible
     torch.manual_seed(0)  # identical replicas on every rank
     net = getattr(dv.models, spec["ctor"])().cuda()
     cfg = dict(TRAINING_CONFIG[args.model])
@@ -229,12 +371,14 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # launches per step (the CUDA graph replays them without passing through the library's counter)
+    inventory = BnInventory(net, dvnn)
     c0 = lib.dv_launch_count()
     trainer.use_graph, keep = False, trainer.use_graph
     trainer.step(images, labels)
     torch.cuda.synchronize()
     launches_per_step = int(lib.dv_launch_count() - c0)
     trainer.use_graph = keep
+    inventory.close()
 
     for _ in range(max(args.warmup, 3)):
         trainer.step(images, labels)
@@ -265,35 +409,64 @@ def run_ours(args):
 
     # end to end: every step's batch starts in pinned host memory and the loss is read back to the host every step
     # (train.py:444-446,470).  HostFeeder copies batch i+1 on a side stream while step i computes.
-    from deep_vision_b200.train import HostFeeder
-    himg = [torch.randn(batch, 3, 224, 224).pin_memory() for _ in range(2)]
-    hlab = [torch.randint(0, 1000, (batch,)).pin_memory() for _ in range(2)]
-    feeder = HostFeeder(trainer)
     k2 = max(3, min(args.steps, 20))
 
-    def e2e_loop(n):
-        feeder.prefetch(himg[0], hlab[0])
-        last = 0.0
-        for i in range(n):
-            dimg, dlab = feeder.take()
-            if i + 1 < n:
-                feeder.prefetch(himg[(i + 1) & 1], hlab[(i + 1) & 1])
-            loss_t = trainer.step(dimg, dlab)
-            feeder.release()
-            last = loss_t.item()                     # device -> host read of the step's result, every step
-        return last
+    def e2e_run(himg, hlab, transform=None):
+        feeder = HostFeeder(trainer)
+        sizes = [tuple(himg[0].shape[1:3])] * batch if transform is not None else None
 
-    e2e_loop(2)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    e2e_loop(k2)
-    e1.record()
-    barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_e2e = float(t.item())
+        def loop(n):
+            feeder.prefetch(himg[0], hlab[0])
+            draws = transform.draw(sizes) if transform is not None else None
+            last = 0.0
+            for i in range(n):
+                dimg, dlab = feeder.take()
+                if i + 1 < n:
+                    feeder.prefetch(himg[(i + 1) & 1], hlab[(i + 1) & 1])
+                if transform is not None:
+                    dimg = transform(dimg, sizes, draws)
+                loss_t = trainer.step(dimg, dlab)
+                feeder.release()
+                if transform is not None and i + 1 < n:
+                    draws = transform.draw(sizes)        # host-side random draws of the NEXT batch, while this step runs on the GPU
+                last = loss_t.item()                     # device -> host read of the step's result, every step
+            return last
+
+        loop(2)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        loop(k2)
+        e1.record()
+        barrier()
+        t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    himg = [torch.randn(batch, 3, 224, 224).pin_memory() for _ in range(2)]
+    hlab = [torch.randint(0, 1000, (batch,)).pin_memory() for _ in range(2)]
+    ms_e2e = e2e_run(himg, hlab)
+    h2d = int(himg[0].numel() * 4 + hlab[0].numel() * 8)
+    del himg
+
+    # the same loop fed the way the repo's own input pipeline feeds it: uint8 256x256 images over PCIe, random
+    # crop / flip / colour jitter / normalise on the device, NHWC bf16 straight into the model
+    e2e_u8 = None
+    if not args.no_uint8:
+        try:
+            from deep_vision_b200.data import GpuTransform
+            tf = GpuTransform(crop=224, train=True)
+            hu8 = [torch.randint(0, 256, (batch, 256, 256, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+            trainer._graph = None      # the captured step is re-recorded for an NHWC bf16 input (no layout kernel)
+            ms_u8 = e2e_run(hu8, hlab, transform=tf)
+            e2e_u8 = {"value": round(batch * world * k2 / (ms_u8 * 1e-3), 1), "unit": "images/s",
+                      "h2d_bytes_per_step": int(hu8[0].numel() + hlab[0].numel() * 8), "d2h_bytes_per_step": 4, "steps": k2,
+                      "input": "uint8 [B,256,256,3] -> dv_augment on the device (crop 224, flip, colour jitter, normalise)"}
+            del hu8
+            trainer._graph = None
+        except Exception as e:  # the fp32 figure stands on its own
+            e2e_u8 = {"error": str(e)[:200]}
 
     if rank == 0:
         pk = peaks()
@@ -306,25 +479,34 @@ def run_ours(args):
             "config": {"workload": f"{args.model} V1 bf16 training step (fwd+CE+bwd+grad allreduce+{cfg['optimizer']}), batch {batch}/GPU, "
                                    f"3x224x224 synthetic, random-init weights", "global_batch": batch * world,
                        "parallelism": f"dp{world}", "cuda_graph": not args.no_graph,
+                       "reductions": "fixed-order (deterministic)" if args.deterministic else "fp32 atomics / TMA reduce-add (default)",
                        "l2": "per-step working set (>10 GB of activations) exceeds the 126 MB L2; no explicit flush"},
-            "e2e": {"value": round(ips_e2e, 1), "unit": "images/s", "h2d_bytes_per_step": int(himg[0].numel() * 4 + hlab[0].numel() * 8),
-                    "d2h_bytes_per_step": 4, "steps": k2},
+            "e2e": {"value": round(ips_e2e, 1), "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4, "steps": k2},
             "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
             "clocks": clk.summary(), "loss": round(loss_val, 4),
             "conv_tflops": round(spec["gflop_per_img"] * ips / 1e3, 1),
             "conv_frac_of_peak": round(spec["gflop_per_img"] * ips / world / 1e3 / pk["tf_sustained"], 4),
         }
+        if e2e_u8 is not None:
+            line["e2e_uint8"] = e2e_u8
         if world == 1 and not args.no_roofline:
             try:
-                line["roofline"] = kernel_roofline(torch, dv, pk)
+                line["step_top_kernel"] = step_top_kernel(torch, trainer, images, labels, inventory, pk)
+            except Exception as e:
+                line["step_top_kernel"] = {"error": str(e)[:200]}
+            del trainer, net
+            torch.cuda.empty_cache()
+            try:
+                line["roofline"] = kernel_roofline(torch, pk)
                 line["roofline_hbm"] = hbm_roofline(torch, pk)
+                line["conv_time_weighted"] = conv_time_weighted(torch, pk)
             except Exception as e:  # the headline number stands on its own
-                line["roofline"] = {"error": str(e)[:200]}
+                line.setdefault("roofline", {"error": str(e)[:200]})
         if world == 1 and not args.no_cpu_baseline:
-            nsteps = 2
-            ips_cpu, sec, cores = cpu_reference_step(args.model, args.cpu_batch, nsteps, 1)
-            line["cpu_baseline"] = {"value": round(ips_cpu, 3), "unit": "images/s", "cores": cores, "kind": "port",
-                                    "sample": f"{nsteps} steps of batch {args.cpu_batch} (fp32, oracle/ref_models.py) after 1 warm-up"}
+            ips_cpu, sec, cores = cpu_reference_step(args.model, args.cpu_batch, 3, 1)
+            line["cpu_baseline"] = {"value": round(ips_cpu, 3), "unit": "images/s", "cores": cores, "kind": "port", "cpu": cpu_model(),
+                                    "sample": f"best of 3 steps of batch {args.cpu_batch} (fp32, oracle/ref_models.py) after 1 warm-up",
+                                    "config0": cpu_config0()}
         print(json.dumps(line), flush=True)
     if world > 1:
         # Tearing down a process group whose collectives were captured in a CUDA graph can block for minutes; the numbers
@@ -344,10 +526,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--model", default="resnet50", choices=sorted(MODELS))
     ap.add_argument("--batch", type=int, default=0)
-    ap.add_argument("--cpu-batch", type=int, default=16)
+    ap.add_argument("--cpu-batch", type=int, default=32)
+    ap.add_argument("--deterministic", action="store_true", help="fixed-order reductions (set_deterministic(True)): the cost of the bit-reproducible mode")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-uint8", action="store_true", help="skip the second end-to-end figure (uint8 input through GpuTransform)")
     ap.add_argument("--profile", action="store_true", help="warm up, run --steps eager steps, print a short line, exit (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":
