@@ -88,7 +88,12 @@ def make_trainer(net, config, **trainer_kwargs):
     kind = {optim.SGD: "sgd", optim.RMSprop: "rmsprop"}.get(opt, opt)
     if kind not in ("sgd", "rmsprop"):
         raise NotImplementedError(f"optimizer {opt!r}: the hot path has fused SGD (train.py:166-184) and RMSprop (train.py:199-205)")
-    return Trainer(net, optimizer=kind, **dict(config.get("optimizer_params", {})), **trainer_kwargs)
+    # What the config leaves out takes TORCH's default for that optimiser class, as it does in the reference (train.py:361-365):
+    # the mobilenet1 entry names no weight_decay, so RMSprop runs with none ("very little or no weight decay", train.py:199-205).
+    defaults = {"sgd": dict(momentum=0.0, weight_decay=0.0), "rmsprop": dict(lr=0.01, alpha=0.99, eps=1e-8, weight_decay=0.0)}[kind]
+    params = dict(defaults)
+    params.update(config.get("optimizer_params", {}))
+    return Trainer(net, optimizer=kind, **params, **trainer_kwargs)
 
 
 def _unpack(batch, device):

@@ -9,18 +9,13 @@ from . import functional as F
 
 
 def accuracy(output, target, topk=(1,)):
-    """train.py:524-538 — precision@k in percent for each k of `topk`.  output: [B,classes] logits, target: [B]."""
+    """Precision@k in percent for each k of `topk` (train.py:524-538, same signature and return type: a list of 1-element
+    tensors).  output: [B,classes] logits, target: [B].  A sample counts for k when its label is among its k largest logits."""
     with torch.no_grad():
-        maxk = max(topk)
-        batch_size = target.size(0)
-        _, pred = output.topk(maxk, 1, True, True)
-        pred = pred.t()
-        correct = pred.eq(target.view(1, -1).expand_as(pred))
-        res = []
-        for k in topk:
-            correct_k = correct[:k].reshape(-1).float().sum(0, keepdim=True)
-            res.append(correct_k.mul_(100.0 / batch_size))
-        return res
+        ranked = output.topk(max(topk), dim=1).indices                 # [B, maxk], best first
+        hit_rank = (ranked == target.view(-1, 1)).float().cumsum(dim=1)  # [B, maxk]: 1 from the column where the label sits
+        scale = 100.0 / target.size(0)
+        return [hit_rank[:, k - 1].sum().reshape(1) * scale for k in topk]
 
 
 def validate(net, loader, device="cuda"):

@@ -54,6 +54,19 @@ def plan_buckets(offsets, total, cap_elems):
     return buckets
 
 
+def flat_view(flat, off, shape):
+    """The slice of a flat buffer that belongs to a parameter of logical `shape`, shaped like the parameter.  4-D filters
+    are stored KRSC (channels_last), so their view is a permutation of the [K,R,S,C] block — NOT `.view(K,C,R,S)`.
+    Every place that pairs a parameter with flat optimiser state or gradients goes through this (checkpoint.py too)."""
+    n = 1
+    for d in shape:
+        n *= int(d)
+    if len(shape) == 4:
+        K, Cc, R, S = (int(d) for d in shape)
+        return flat[off:off + n].view(K, R, S, Cc).permute(0, 3, 1, 2)
+    return flat[off:off + n].view(tuple(shape))
+
+
 class FlatParams:
     """All trainable parameters of a module as views into ONE flat fp32 buffer (and their gradients into another).
     4-D filters are laid out KRSC (channels_last) so the convolution kernels read the master copy in place."""
@@ -68,13 +81,8 @@ class FlatParams:
         off = 0
         for p in self.params:
             n = p.numel()
-            if p.dim() == 4:
-                K, Cc, R, S = p.shape
-                pv = self.flat_p[off:off + n].view(K, R, S, Cc).permute(0, 3, 1, 2)
-                gv = self.flat_g[off:off + n].view(K, R, S, Cc).permute(0, 3, 1, 2)
-            else:
-                pv = self.flat_p[off:off + n].view(p.shape)
-                gv = self.flat_g[off:off + n].view(p.shape)
+            pv = flat_view(self.flat_p, off, p.shape)
+            gv = flat_view(self.flat_g, off, p.shape)
             pv.copy_(p.data)
             p.data = pv
             p.grad = gv
@@ -272,9 +280,13 @@ class Trainer:
             return loss
         if self._graph is None:
             self._capture(images, labels)
-        if images.shape != self._static_images.shape:
-            raise RuntimeError(f"Trainer(use_cuda_graph=True): batch shape changed from {tuple(self._static_images.shape)} to "
-                               f"{tuple(images.shape)}; feed full batches (drop_last) or use use_cuda_graph=False")
+        if images.shape != self._static_images.shape or images.dtype != self._static_images.dtype:
+            # A batch of another shape — the ragged last batch of an epoch: the reference's DataLoader has no drop_last
+            # (train.py:229-234; 1,281,167 % 256 = 143) and trains it.  It runs eagerly through the same kernels; the optimiser
+            # takes lr by value and the flat state is shared with the captured step, so nothing is re-recorded.
+            loss = self._step_body(images, labels)
+            self.steps_done += 1
+            return loss
         self._static_images.copy_(images, non_blocking=True)
         self._static_labels.copy_(labels, non_blocking=True)
         self._graph.replay()
@@ -286,17 +298,26 @@ class Trainer:
 
     def _capture(self, images, labels):
         """Warm up eagerly on a side stream (allocator, filter caches, NCCL), then record fwd+bwd+exchange+optimiser
-        into one CUDA graph.  The momentum buffer's first-step special case (buf = g) is met by the eager warm-up
-        steps, which are real training steps."""
+        into one CUDA graph.  The two warm-up steps are NOT training steps: parameters, optimiser state, BN running
+        statistics and counters are put back afterwards, so the first replay is the one update this batch gets (the
+        reference updates once per batch, train.py:457-467).  With the state buffer at zero the recorded update
+        buf = momentum*buf + g equals torch's first-step special case buf = g."""
         self._static_images = images.clone()
         self._static_labels = labels.clone()
-        if not self._warmed:   # a re-capture (set_lr) records straight away: nothing is executed, no batch is trained twice
+        if not self._warmed:   # a re-capture (set_lr) records straight away: nothing is executed
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):
+                keep = [self.flat_p.clone(), self.flat_s.clone()] + [b.detach().clone() for b in self.model.buffers()]
                 for _ in range(2):
                     self._step_body(self._static_images, self._static_labels)
-                    self.steps_done += 1
+                self.flat_p.copy_(keep[0])
+                self.flat_s.copy_(keep[1])
+                for b, saved in zip(self.model.buffers(), keep[2:]):
+                    b.detach().copy_(saved)
+                if self.flat_p16 is not None:
+                    self.flat_p16.copy_(self.flat_p)
+                config.bump_weight_epoch()
             torch.cuda.current_stream().wait_stream(s)
             self._warmed = True
         torch.cuda.synchronize()
@@ -315,7 +336,27 @@ class Trainer:
         config.bump_weight_epoch()
 
     def state_dict(self):
-        return {"optimizer": self.kind, "steps": self.steps_done, "lr": self.lr, "state": self.flat_s.clone()}
+        """The optimiser state in torch.optim's own layout, so that the reference's `optimizer.load_state_dict(
+        checkpoint['optimizer'])` (train.py:295) accepts a file written here: per parameter index (net.parameters() order)
+        the momentum buffer (SGD) or squared-gradient average (RMSprop) as an OIHW fp32 tensor, plus one param_group with the
+        hyper-parameters.  `load_checkpoint` reads the same layout back, whoever wrote it."""
+        key = {"sgd": "momentum_buffer", "rmsprop": "square_avg"}[self.kind]
+        state = {}
+        if self.steps_done > 0:
+            for idx, (p, off) in enumerate(zip(self.flat.params, self.flat.offsets)):
+                entry = {key: flat_view(self.flat_s, off, p.shape).detach().contiguous().cpu().clone()}
+                if self.kind == "rmsprop":
+                    entry["step"] = torch.tensor(float(self.steps_done))
+                state[idx] = entry
+        if self.kind == "sgd":
+            group = dict(lr=self.lr, momentum=self.momentum, dampening=0, weight_decay=self.weight_decay, nesterov=False,
+                         maximize=False, foreach=None, differentiable=False, fused=None)
+        else:
+            group = dict(lr=self.lr, momentum=0, alpha=self.alpha, eps=self.eps, centered=False, weight_decay=self.weight_decay,
+                         capturable=False, foreach=None, maximize=False, differentiable=False)
+        group["params"] = list(range(len(self.flat.params)))
+        group["dv_steps"] = int(self.steps_done)   # torch carries unknown group keys along untouched
+        return {"state": state, "param_groups": [group]}
 
 
 class HostFeeder:

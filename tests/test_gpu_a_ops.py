@@ -112,10 +112,6 @@ def test_conv_simt_matches_oracle(case, dtype):
     assert rel_l2(run_conv(lib.DV_CONV_WGRAD, x, w, dy, stride, pad, dtype, lib.DV_ALGO_SIMT), dw_ref) < 1e-4  # fp32 output
 
 
-def _bn_call(fn_name, x, dtype, **kw):
-    pass
-
-
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
 @pytest.mark.parametrize("shape,residual,relu", [((4, 64, 7, 7), False, True), ((2, 32, 9, 5), True, True),
                                                  ((3, 256, 4, 4), True, False), ((2, 2048, 2, 2), False, False),

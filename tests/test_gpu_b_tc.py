@@ -208,6 +208,18 @@ def test_tc_full_size_against_cuda_core_kernel_and_properties(case):
     err = float((dw_tc - dw_si).norm() / dw_si.norm())
     assert err < 1e-4, f"wgrad TC vs SIMT {err}"
 
+    # dgrad and wgrad of the FULL-SIZE launch against the oracle.  dgrad is per image: the first and the last image of the
+    # batch (both ends of the tile walk) are checked.  wgrad sums over the batch: with dy zeroed outside those two images the
+    # same full-size launch computes exactly their partial sum, which numpy finishes in seconds.
+    sel = [0, N - 1]
+    nchw = lambda t: t.double().cpu().numpy().transpose(0, 3, 1, 2)
+    dx_or, dw_or = ref_ops.conv2d_backward(nchw(xd[sel]), nchw(wd), nchw(dyd[sel]), stride, pad)
+    assert rel_l2(nchw(dx_tc[sel]), dx_or) < 2e-2, "full-size dgrad vs oracle"
+    dy2 = torch.zeros_like(dyd)
+    dy2[sel] = dyd[sel]
+    dw2 = _gpu_conv(lib.DV_CONV_WGRAD, xd, wd, dy2, stride, pad, lib.DV_ALGO_TC)
+    assert rel_l2(nchw(dw2), dw_or) < 1e-4, "full-size wgrad (two-image partial) vs oracle"
+
 
 @pytest.mark.parametrize("geom", [(7, 2, 3, 64), (3, 2, 1, 32)], ids=["resnet_stem_7x7", "mobilenet_stem_3x3"])
 def test_stem_conv_module_matches_oracle(geom):

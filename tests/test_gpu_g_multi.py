@@ -1,6 +1,7 @@
-"""Two-GPU test of the data-parallel step (needs >= 2 GPUs; the 1-GPU round-end run skips it): tools/dp_check.py under
-torchrun — replicas identical after a step (eager and CUDA graph), reduced gradient == sum of per-shard plain-autograd
-gradients, update == SGD on their average (reference semantics train.py:353-355)."""
+"""Tests of the data-parallel step on real GPUs: tools/dp_check.py under torchrun — replicas identical after a step, reduced
+gradient == sum of per-shard plain-autograd gradients, update == SGD on their average (reference
+semantics train.py:353-355).  Two ranks over NCCL when the box has two GPUs (eager and CUDA graph); on a single GPU the same
+two-rank run goes through gloo with both ranks on device 0, so the exchange logic is exercised in every round-end run."""
 import json
 import os
 import subprocess
@@ -10,6 +11,25 @@ import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
+
+
+def test_two_ranks_on_one_gpu_through_gloo_equal_averaged_shard_gradients():
+    """(e) on a 1-GPU box: fixed-order mode, so the reduced gradient must equal the sum of the two per-shard plain-autograd
+    gradients to rounding, the update must be SGD on their average, and both replicas must end bit-identical."""
+    out = _run_dp_check(29535, DP_CHECK_BACKEND="gloo")
+    assert out["ranks_identical_graph0"] and out["debug"]["flat_g_identical"] and out["debug"]["p0_identical"]
+    assert out["debug"]["world"] == 2 and out["debug"]["pending_after"] == [0] * out["debug"]["buckets"]
+    assert out["plain_autograd_twice_rel_diff"] == 0.0
+    assert out["grad_sum_rel_err"] < 1e-6 and out["update_rel_err"] < 1e-5
+
+
+def test_two_ranks_on_one_gpu_default_mode_keeps_replicas_identical():
+    """The benchmarked mode (fp32 atomics / TMA reduce-add, weight gradients on the side stream) through the same two-rank run:
+    every bucket is exchanged exactly once and after all of its gradients, so both ranks hold bit-identical reduced buffers and
+    parameters (each rank's own summation order differs, the all-reduce output does not)."""
+    out = _run_dp_check(29536, DP_CHECK_BACKEND="gloo", DP_CHECK_ATOMICS="1")
+    assert out["ranks_identical_graph0"] and out["debug"]["flat_g_identical"]
+    assert out["debug"]["pending_after"] == [0] * out["debug"]["buckets"]
 
 
 def _run_dp_check(port, **env):

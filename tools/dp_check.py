@@ -1,7 +1,11 @@
 #!/usr/bin/env python
 """Data-parallel equivalence on real GPUs: after one Trainer step on W ranks with different batches,
 every rank holds the same parameters, and they equal SGD applied to the AVERAGE of the per-shard gradients computed by plain
-autograd (per-shard BatchNorm statistics, as nn.DataParallel).  Run under torchrun; rank 0 prints one JSON line."""
+autograd (per-shard BatchNorm statistics, as nn.DataParallel).  Run under torchrun; rank 0 prints one JSON line.
+
+DP_CHECK_BACKEND=gloo puts every rank on GPU 0 and exchanges through gloo (NCCL refuses two ranks on one device): the same
+Trainer / BucketedAllReduce code path — bucket hooks, side-stream weight gradients, 1/world in the optimiser — on a box with
+a single GPU.  gloo collectives cannot be captured in a CUDA graph, so only the eager step is checked there."""
 import json
 import os
 import sys
@@ -14,15 +18,21 @@ import deep_vision_b200 as dv  # noqa: E402
 from deep_vision_b200.train import Trainer  # noqa: E402
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-torch.cuda.set_device(local)
-dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+backend = os.environ.get("DP_CHECK_BACKEND", "nccl")
+if backend == "gloo":
+    local = 0
+    torch.cuda.set_device(0)
+    dist.init_process_group("gloo")
+else:
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 dv.set_compute_dtype(torch.bfloat16)
 # fixed-order reductions: a random-init ResNet-50 on a tiny batch amplifies the run-to-run rounding of fp32 atomics to O(1)
 # gradient differences (measured: the SAME plain-autograd gradient computed twice differed by 1.09 relative), which would
 # drown what this script checks
 dv.set_deterministic(os.environ.get("DP_CHECK_ATOMICS", "0") != "1")
 out = {}
-for graph in (False, True):
+for graph in ((False,) if backend == "gloo" else (False, True)):
     torch.manual_seed(0)
     net = dv.models.ResNet50().cuda()
     ref = dv.models.ResNet50().cuda()
@@ -34,7 +44,6 @@ for graph in (False, True):
         g = torch.Generator().manual_seed(100 + r)   # CPU generator: the same values on every rank
         batches.append((torch.randn(8, 3, 96, 96, generator=g).cuda(), torch.randint(0, 1000, (8,), generator=g).cuda()))
     p0 = tr.flat_p.clone()
-    steps = 3 if graph else 1     # graph mode: 2 eager warm-up steps + 1 replay, all on the same batch
     tr.step(*batches[rank])
     torch.cuda.synchronize()
     if not graph:
