@@ -33,6 +33,26 @@ class GpuTransform:
         self.mean, self.std = tuple(mean), tuple(std)
         self.dtype, self.nchw = dtype, bool(nchw)
 
+    def _to_device(self, arr, dev):
+        """Small per-batch tables go through a ring of PINNED staging buffers: a copy from pageable memory makes the host wait
+        for everything already queued on the stream (the previous training step), which serialises host and GPU."""
+        ring = self.__dict__.setdefault("_ring", {})
+        key = (arr.shape, arr.dtype.str)
+        slots = ring.setdefault(key, {"i": 0, "bufs": [], "events": []})
+        if len(slots["bufs"]) < 4:
+            slots["bufs"].append(torch.from_numpy(np.empty_like(arr)).pin_memory())
+            slots["events"].append(None)
+        i = slots["i"] % len(slots["bufs"])
+        slots["i"] += 1
+        if slots["events"][i] is not None:
+            slots["events"][i].synchronize()       # the copy that last used this slot has run
+        slots["bufs"][i].numpy()[...] = arr
+        out = slots["bufs"][i].to(dev, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(dev))
+        slots["events"][i] = ev
+        return out
+
     def draw(self, sizes):
         """sizes: [(h, w)] of the rescaled images.  Returns (geom int32 [B,4], factors float32 [B,3]) — one image after the
         other, each consuming the generators in the order flip, crop top/left, brightness, contrast, saturation, shuffle
@@ -74,9 +94,9 @@ class GpuTransform:
             sizes = [(Hs, Ws)] * B
         geom, fac = params if params is not None else self.draw(sizes)
         dev = images_u8.device
-        geom_d = torch.from_numpy(np.ascontiguousarray(geom, np.int32)).to(dev, non_blocking=True)
-        fac_d = torch.from_numpy(np.ascontiguousarray(fac, np.float32)).to(dev, non_blocking=True)
-        widths_d = torch.tensor([w for _, w in sizes], dtype=torch.int32).to(dev, non_blocking=True)
+        geom_d = self._to_device(np.ascontiguousarray(geom, np.int32), dev)
+        fac_d = self._to_device(np.ascontiguousarray(fac, np.float32), dev)
+        widths_d = self._to_device(np.asarray([w for _, w in sizes], np.int32), dev)
         sums = torch.empty(B, dtype=torch.int32, device=dev)
         dtype = self.dtype or config.compute_dtype()
         if self.nchw:
