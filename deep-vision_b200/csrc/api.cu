@@ -56,6 +56,8 @@ static int run_conv(const dv_conv_params* p, int pass, void* stream, const char*
   const bool folded = p->ep_scale || p->ep_shift || p->ep_residual || p->ep_relu;
   DV_REQUIRE(!folded || (pass == DV_CONV_FPROP && algo == DV_ALGO_TC), DV_ERR_UNSUPPORTED,
              "%s: the folded-BatchNorm epilogue (ep_*) exists on the tensor-core fprop path only", who);
+  DV_REQUIRE(p->bnb_x == nullptr || (pass == DV_CONV_DGRAD && algo == DV_ALGO_TC), DV_ERR_UNSUPPORTED,
+             "%s: the BatchNorm-backward sums (bnb_*) exist on the tensor-core dgrad path only", who);
   return algo == DV_ALGO_TC ? conv_tc(p, pass, st) : conv_simt(p, pass, st);
 }
 

@@ -281,7 +281,35 @@ struct GemmArgs {
   const float* ep_shift;
   const bf16* ep_res;
   int ep_relu;
+  // dgrad, optional (EPI == 2): the output dx is the gradient w.r.t. a = relu(bn(x0)).  While a dx tile is still on chip the
+  // epilogue fetches the matching x0 tile (tensor map tmR), recomputes the ReLU mask exactly as bn_apply computed it and adds
+  //   dbeta[c] += sum_m dz,   dgamma[c] += invstd[c] * sum_m dz * (x0 - mean[c]),   dz = dx * (relu'(bn(x0)))
+  // which is all that BatchNorm's backward reduce pass (4 bytes per element of HBM traffic) would have produced.
+  const float* bnb_gamma;
+  const float* bnb_beta;
+  const float* bnb_mean;
+  const float* bnb_invstd;
+  float* bnb_dgamma;
+  float* bnb_dbeta;
 };
+
+// BatchNorm-backward sums over one staged [32 rows][64 columns] tile (EPI == 2).  The lane owns columns 2*lane, 2*lane+1 of the
+// group: `xw` holds its two x0 values of every row (read from the staging buffer before dy overwrote it), dy is read back from
+// the staging buffer as it was rounded to bf16 — the values bn_bwd_apply will read.  Sums are returned through a/b.
+__device__ __forceinline__ void bnb_tile_sums(const uint8_t* my_stage, const uint32_t* xw, int lane, float sc0, float sh0, float mu0, float sc1,
+                                              float sh1, float mu1, float& a0, float& a1, float& b0, float& b1) {
+  const int wch = lane >> 2, wof = (lane & 3) * 4;
+#pragma unroll   // fully: xw[] must stay in registers (constant indices)
+  for (int r = 0; r < 32; ++r) {
+    const uint32_t word = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+    const float d0 = __uint_as_float(word << 16), d1 = __uint_as_float(word & 0xffff0000u);
+    const float x0 = __uint_as_float(xw[r] << 16), x1 = __uint_as_float(xw[r] & 0xffff0000u);
+    const float z0 = fmaf(x0, sc0, sh0) > 0.f ? d0 : 0.f;   // the expressions of bn_apply_kernel / bn_reduce_kernel<.,1,2>
+    const float z1 = fmaf(x1, sc1, sh1) > 0.f ? d1 : 0.f;
+    a0 += z0; a1 += z1;
+    b0 = fmaf(z0, x0 - mu0, b0); b1 = fmaf(z1, x1 - mu1, b1);
+  }
+}
 
 // Folded-BatchNorm epilogue on the 32 accumulator columns [col0, col0+32) of the output row held by one lane.  The identity
 // tile was brought into the warp's staging buffer by TMA in the layout the result is written back in ([32 rows][128 B],
@@ -328,10 +356,13 @@ __device__ __forceinline__ void apply_folded_epilogue(uint32_t* v, const GemmArg
 // B_MN: the B operand is taken as [64 reduction rows][64 output columns] boxes straight from KRSC filters and consumed
 // MN-major — the dgrad case, where the reduction runs over K (filter rows) and the output over C (contiguous), with the
 // tap flipped by index.  No transposed copy of the filters is needed.
-template <int BN, int STAGES, bool STATS, bool B_MN, bool FOLD>
+// EPI: 0 = plain, 1 = folded BatchNorm (inference fprop), 2 = BatchNorm-backward sums of the producing layer (dgrad)
+template <int BN, int STAGES, bool STATS, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kThreads)
 conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
+  constexpr bool FOLD = EPI == 1, BNB = EPI == 2;
+  static_assert(!BNB || STATS, "the BatchNorm-backward sums ride on the staged (TMA store) epilogue");
   constexpr int ACC = 2;
   constexpr int kBBytes = BN * kBlockK * 2;
   constexpr int kStageBytes = kABytes + kBBytes;
@@ -473,15 +504,20 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 #pragma unroll
     for (int i = 0; i < BN / 64; ++i) { s1[i][0] = s1[i][1] = s2[i][0] = s2[i][1] = 0.f; }
     auto flush_stats = [&]() {
-      if (g.stat_sums == nullptr || stat_n_tile < 0) return;
+      if ((BNB ? (const void*)g.bnb_dgamma : (const void*)g.stat_sums) == nullptr || stat_n_tile < 0) return;
 #pragma unroll
       for (int i = 0; i < BN / 64; ++i) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int col = stat_n_tile * BN + i * 64 + 2 * lane + e;
           if (col < g.Nout) {
-            atomicAdd(g.stat_sums + col, s1[i][e]);
-            atomicAdd(g.stat_sums + g.Nout + col, s2[i][e]);
+            if (BNB) {
+              atomicAdd(g.bnb_dbeta + col, s1[i][e]);
+              atomicAdd(g.bnb_dgamma + col, s2[i][e] * __ldg(g.bnb_invstd + col));
+            } else {
+              atomicAdd(g.stat_sums + col, s1[i][e]);
+              atomicAdd(g.stat_sums + g.Nout + col, s2[i][e]);
+            }
           }
           s1[i][e] = 0.f;
           s2[i][e] = 0.f;
@@ -581,9 +617,21 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           __syncwarp();
           const bool group_live = cgp * 64 < n_left && m_base < g.M;
           const bool with_res = FOLD && g.ep_res != nullptr && group_live;
-          if (with_res && lane == 0) {  // identity tile -> staging buffer (rows / columns past the tensor are zero-filled)
+          const bool with_x0 = BNB && group_live;
+          if ((with_res || with_x0) && lane == 0) {  // identity / x0 tile -> staging buffer (rows / columns past the tensor are zero-filled)
             mbar_expect_tx(&res_bar[quarter], 32 * 128);
             tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
+          }
+          uint32_t xw[BNB ? 32 : 1];
+          if (BNB) {
+            if (with_x0) {   // (warp-uniform) the lane's two columns of x0, all 32 rows, before dy takes the buffer
+              mbar_wait(&res_bar[quarter], res_phase);
+              res_phase ^= 1;
+              const int wch = lane >> 2, wof = (lane & 3) * 4;
+#pragma unroll
+              for (int r = 0; r < 32; ++r) xw[r] = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+            }
+            __syncwarp();
           }
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
@@ -614,7 +662,21 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             if (g.accumulate) tma_reduce_add_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
             else tma_store_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
           }
-          if (g.stat_sums != nullptr) {
+          if (BNB) {
+            if (with_x0) {
+              const int col = n_tile * BN + cgp * 64 + 2 * lane;   // Nout is a multiple of 8: col and col+1 are both in or both out
+              float sc0 = 0.f, sh0 = 0.f, mu0 = 0.f, sc1 = 0.f, sh1 = 0.f, mu1 = 0.f;
+              if (col < g.Nout) {
+                mu0 = __ldg(g.bnb_mean + col); mu1 = __ldg(g.bnb_mean + col + 1);
+                sc0 = __ldg(g.bnb_invstd + col) * __ldg(g.bnb_gamma + col); sc1 = __ldg(g.bnb_invstd + col + 1) * __ldg(g.bnb_gamma + col + 1);
+                sh0 = __ldg(g.bnb_beta + col) - mu0 * sc0; sh1 = __ldg(g.bnb_beta + col + 1) - mu1 * sc1;
+              }
+              float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+              bnb_tile_sums(my_stage, xw, lane, sc0, sh0, mu0, sc1, sh1, mu1, a0, a1, b0, b1);
+              s1[cgp][0] += a0; s1[cgp][1] += a1;
+              s2[cgp][0] += b0; s2[cgp][1] += b1;
+            }
+          } else if (g.stat_sums != nullptr) {
             // column sums over this warp's 32 rows from the bf16-rounded values (what BN will read back)
             const int wch = lane >> 2, wof = (lane & 3) * 4;
             float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
@@ -653,10 +715,11 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 // accumulator-ready barriers are signalled in both CTAs by a multicast commit; the peer's epilogue hands accumulators
 // back by a remote arrive.
 // ------------------------------------------------------------------------------------------------------------
-template <int STAGES, bool B_MN, bool FOLD>
+template <int STAGES, bool B_MN, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads)
 conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
+  constexpr bool FOLD = EPI == 1, BNB = EPI == 2;
   constexpr int BN = 256, ACC = 2;
   constexpr int kBHalfBytes = (BN / 2) * kBlockK * 2;  // 16 KB: this CTA's half of the filter tile
   constexpr int kStageBytes = kABytes + kBHalfBytes;    // 32 KB
@@ -792,15 +855,20 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
     for (int i = 0; i < BN / 64; ++i) { s1[i][0] = s1[i][1] = s2[i][0] = s2[i][1] = 0.f; }
     auto flush_stats = [&]() {
-      if (g.stat_sums == nullptr || stat_n_tile < 0) return;
+      if ((BNB ? (const void*)g.bnb_dgamma : (const void*)g.stat_sums) == nullptr || stat_n_tile < 0) return;
 #pragma unroll
       for (int i = 0; i < BN / 64; ++i) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
           const int col = stat_n_tile * BN + i * 64 + 2 * lane + e;
           if (col < g.Nout) {
-            atomicAdd(g.stat_sums + col, s1[i][e]);
-            atomicAdd(g.stat_sums + g.Nout + col, s2[i][e]);
+            if (BNB) {
+              atomicAdd(g.bnb_dbeta + col, s1[i][e]);
+              atomicAdd(g.bnb_dgamma + col, s2[i][e] * __ldg(g.bnb_invstd + col));
+            } else {
+              atomicAdd(g.stat_sums + col, s1[i][e]);
+              atomicAdd(g.stat_sums + g.Nout + col, s2[i][e]);
+            }
           }
           s1[i][e] = 0.f;
           s2[i][e] = 0.f;
@@ -821,9 +889,21 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         __syncwarp();
         const bool group_live = cgp * 64 < n_left && m_base < g.M;
         const bool with_res = FOLD && g.ep_res != nullptr && group_live;
-        if (with_res && lane == 0) {
+        const bool with_x0 = BNB && group_live;
+        if ((with_res || with_x0) && lane == 0) {
           mbar_expect_tx(&res_bar[quarter], 32 * 128);
           tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
+        }
+        uint32_t xw[BNB ? 32 : 1];
+        if (BNB) {
+          if (with_x0) {
+            mbar_wait(&res_bar[quarter], res_phase);
+            res_phase ^= 1;
+            const int wch = lane >> 2, wof = (lane & 3) * 4;
+#pragma unroll
+            for (int r = 0; r < 32; ++r) xw[r] = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+          }
+          __syncwarp();
         }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
@@ -854,7 +934,21 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           if (g.accumulate) tma_reduce_add_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
           else tma_store_2d(&tmO, my_stage_u32, n_tile * BN + cgp * 64, m_base);
         }
-        if (g.stat_sums != nullptr) {
+        if (BNB) {
+          if (with_x0) {
+            const int col = n_tile * BN + cgp * 64 + 2 * lane;
+            float sc0 = 0.f, sh0 = 0.f, mu0 = 0.f, sc1 = 0.f, sh1 = 0.f, mu1 = 0.f;
+            if (col < g.Nout) {
+              mu0 = __ldg(g.bnb_mean + col); mu1 = __ldg(g.bnb_mean + col + 1);
+              sc0 = __ldg(g.bnb_invstd + col) * __ldg(g.bnb_gamma + col); sc1 = __ldg(g.bnb_invstd + col + 1) * __ldg(g.bnb_gamma + col + 1);
+              sh0 = __ldg(g.bnb_beta + col) - mu0 * sc0; sh1 = __ldg(g.bnb_beta + col + 1) - mu1 * sc1;
+            }
+            float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+            bnb_tile_sums(my_stage, xw, lane, sc0, sh0, mu0, sc1, sh1, mu1, a0, a1, b0, b1);
+            s1[cgp][0] += a0; s1[cgp][1] += a1;
+            s2[cgp][0] += b0; s2[cgp][1] += b1;
+          }
+        } else if (g.stat_sums != nullptr) {
           const int wch = lane >> 2, wof = (lane & 3) * 4;
           float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
 #pragma unroll 8
@@ -1181,18 +1275,18 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int STAGES, bool B_MN, bool FOLD>
+template <int STAGES, bool B_MN, int EPI>
 static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                             cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + kEpiStageBytes + 256;
   static_assert(smem <= 227 * 1024, "pair kernel ring exceeds shared memory");
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int num_n = ceil_div(g.Nout, 256);
   const int pairs = ceil_div(ceil_div(g.M, kBlockM), 2) * num_n;
   int clusters = num_sms() / 2;
   if (clusters > num_n) clusters -= clusters % num_n;
   if (clusters > pairs) clusters = pairs;
-  conv_tc_gemm_pair_kernel<STAGES, B_MN, FOLD><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
+  conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
   DV_LAUNCH_OK("conv_tc_gemm_pair_kernel");
   return DV_OK;
 }
@@ -1202,14 +1296,14 @@ static int env_int(const char* name, int dflt) {
   return v ? atoi(v) : dflt;
 }
 
-template <int BN, int STAGES, bool STATS, bool B_MN, bool FOLD>
+template <int BN, int STAGES, bool STATS, bool B_MN, int EPI>
 static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                                   cudaStream_t st) {
   constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + 256;
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   // ask for the whole L1/shared array as shared memory: otherwise the driver sizes the carve-out for ONE CTA of this
   // kernel and a second CTA never becomes resident (measured: occupancy 1 -> 2 for the 96 KB variants)
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, cudaFuncAttributePreferredSharedMemoryCarveout,
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                   cudaSharedmemCarveoutMaxShared));
   // CTAs per SM the grid is sized for: two when two rings (<= 113 KB each) and two accumulator pairs (2 x 2 x BN <= 512 TMEM
   // columns) fit, else one.  cudaOccupancyMaxActiveBlocksPerMultiprocessor answers 1 for these kernels at ANY shared
@@ -1218,17 +1312,17 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   static int occ_cached = 0;
   if (occ_cached == 0) {
     int occ = 0;
-    DV_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, kThreads, smem));
+    DV_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI>, kThreads, smem));
     occ_cached = (smem <= 115712 && 4 * BN <= 512) ? 2 : 1;
     const int forced = env_int("DV_TC_OCC", 0);  // experiment knob
     if (forced > 0) occ_cached = forced;
     if (env_int("DV_TC_DEBUG", 0)) {
       cudaFuncAttributes fa;
-      cudaFuncGetAttributes(&fa, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>);
+      cudaFuncGetAttributes(&fa, conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI>);
       int sweep[4] = {0, 0, 0, 0};
       const int sizes[4] = {32 << 10, 64 << 10, 96 << 10, 110 << 10};
       for (int i = 0; i < 4; ++i)
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sweep[i], conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD>, kThreads, sizes[i]);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&sweep[i], conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI>, kThreads, sizes[i]);
       int dev = 0, smem_sm = 0, smem_res = 0;
       cudaGetDevice(&dev);
       cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
@@ -1245,7 +1339,7 @@ static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB
   int slots = num_sms() * occ_cached;
   if (slots > num_n) slots -= slots % num_n;  // a CTA then keeps one n-tile for its whole life (running BN sums stay put)
   const int grid = total < slots ? total : slots;
-  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, FOLD><<<grid, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);
+  conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI><<<grid, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);
   DV_LAUNCH_OK("conv_tc_gemm_persistent_kernel");
   return DV_OK;
 }
@@ -1357,7 +1451,8 @@ static bool use_pair(const GemmArgs& g, int bn) {
 }
 
 // STAGED (TMA store / TMA reduce-add epilogue, optional BN sums) whenever the output is a dense bf16 [M][Nout] matrix
-static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, bool b_mn, cudaStream_t st) {
+static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& g, int bn, bool b_mn, cudaStream_t st,
+                         const void* bnb_x0 = nullptr) {
   const bool staged = !g.scatter && !g.out_f32;
   alignas(64) CUtensorMap tmO;
   if (staged) {
@@ -1366,7 +1461,7 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
   } else {
     tmO = tmA;  // unused by the kernel
   }
-  alignas(64) CUtensorMap tmR = tmO;  // identity tensor of a folded-BN epilogue: same geometry as the output
+  alignas(64) CUtensorMap tmR = tmO;  // identity tensor of a folded-BN epilogue / x0 of the BN-backward sums: same geometry as the output
   if (g.ep_res != nullptr) {
     DV_REQUIRE(staged, DV_ERR_UNSUPPORTED, "conv_tc: a residual epilogue needs the TMA-store output path");
     int rc = make_map_2d(&tmR, g.ep_res, (uint64_t)g.M, (uint64_t)g.Nout, 32);
@@ -1375,15 +1470,27 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
   const bool fold = g.ep_scale != nullptr;  // fprop only (conv_tc checks): staged, K-major B
   if (fold) {
     DV_REQUIRE(staged && !b_mn, DV_ERR_UNSUPPORTED, "conv_tc: the folded epilogue exists on the fprop TMA-store path only");
-    if (use_pair(g, bn)) return launch_gemm_pair<6, false, true>(tmA, tmB, tmO, tmR, g, st);
+    if (use_pair(g, bn)) return launch_gemm_pair<6, false, 1>(tmA, tmB, tmO, tmR, g, st);
     switch (bn) {
-      case 64: return launch_gemm_persistent<64, 4, true, false, true>(tmA, tmB, tmO, tmR, g, st);
-      case 128: return launch_gemm_persistent<128, 3, true, false, true>(tmA, tmB, tmO, tmR, g, st);
-      default: return launch_gemm_persistent<256, 4, true, false, true>(tmA, tmB, tmO, tmR, g, st);
+      case 64: return launch_gemm_persistent<64, 4, true, false, 1>(tmA, tmB, tmO, tmR, g, st);
+      case 128: return launch_gemm_persistent<128, 3, true, false, 1>(tmA, tmB, tmO, tmR, g, st);
+      default: return launch_gemm_persistent<256, 4, true, false, 1>(tmA, tmB, tmO, tmR, g, st);
     }
   }
-  if (use_pair(g, bn)) return b_mn ? launch_gemm_pair<6, true, false>(tmA, tmB, tmO, tmR, g, st) : launch_gemm_pair<6, false, false>(tmA, tmB, tmO, tmR, g, st);
-#define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_, false>(tmA, tmB, tmO, tmR, g, st)
+  if (g.bnb_dgamma != nullptr) {   // dgrad with the producing layer's BatchNorm-backward sums (conv_tc checked the preconditions)
+    DV_REQUIRE(staged && b_mn && !g.accumulate && bnb_x0 != nullptr, DV_ERR_UNSUPPORTED,
+               "conv_tc: BatchNorm-backward sums need the plain TMA-store dgrad path (stride 1, no accumulate, KRSC filters)");
+    int rc = make_map_2d(&tmR, bnb_x0, (uint64_t)g.M, (uint64_t)g.Nout, 32);
+    if (rc) return rc;
+    if (use_pair(g, bn)) return launch_gemm_pair<6, true, 2>(tmA, tmB, tmO, tmR, g, st);
+    switch (bn) {
+      case 64: return launch_gemm_persistent<64, 4, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
+      case 128: return launch_gemm_persistent<128, 3, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
+      default: return launch_gemm_persistent<256, 4, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
+    }
+  }
+  if (use_pair(g, bn)) return b_mn ? launch_gemm_pair<6, true, 0>(tmA, tmB, tmO, tmR, g, st) : launch_gemm_pair<6, false, 0>(tmA, tmB, tmO, tmR, g, st);
+#define DV_GEMM_CASE(BN_, ST_, STG_, BMN_) return launch_gemm_persistent<BN_, ST_, STG_, BMN_, 0>(tmA, tmB, tmO, tmR, g, st)
   if (b_mn) {
     if (staged) { switch (bn) { case 64: DV_GEMM_CASE(64, 4, true, true); case 128: DV_GEMM_CASE(128, 3, true, true); default: DV_GEMM_CASE(256, 4, true, true); } }
     switch (bn) { case 64: DV_GEMM_CASE(64, 4, false, true); case 128: DV_GEMM_CASE(128, 3, false, true); default: DV_GEMM_CASE(256, 4, false, true); }
@@ -1440,6 +1547,17 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     g.kb_per_tap = ceil_div(p->K, 64);
     g.Cin = p->K;
     const int bn = pick_bn(p->C);
+    const void* bnb_x0 = nullptr;
+    if (p->bnb_x != nullptr) {
+      DV_REQUIRE(p->stride == 1 && !p->accumulate && b_mn, DV_ERR_UNSUPPORTED,
+                 "conv_tc dgrad: bnb_* (BatchNorm-backward sums) needs stride 1, accumulate == 0 and w_t == NULL");
+      DV_REQUIRE(p->bnb_gamma && p->bnb_beta && p->bnb_mean && p->bnb_invstd && p->bnb_dgamma && p->bnb_dbeta, DV_ERR_ARG,
+                 "conv_tc dgrad: bnb_x given but one of bnb_gamma/beta/mean/invstd/dgamma/dbeta is null");
+      DV_REQUIRE(aligned16(p->bnb_x), DV_ERR_ARG, "conv_tc dgrad: bnb_x must be 16-byte aligned");
+      g.bnb_gamma = p->bnb_gamma; g.bnb_beta = p->bnb_beta; g.bnb_mean = p->bnb_mean; g.bnb_invstd = p->bnb_invstd;
+      g.bnb_dgamma = p->bnb_dgamma; g.bnb_dbeta = p->bnb_dbeta;
+      bnb_x0 = p->bnb_x;
+    }
     if (p->stride == 1) {
       // dx = conv(dy, w_t) with pad' = R-1-pad: an fprop whose "input" is dy [N,P,Q,K] and whose output is [N,H,W,C]
       const int padp = p->R - 1 - p->pad;
@@ -1503,7 +1621,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
     if (b_mn) rc = make_map_2d(&tmB, p->w, (uint64_t)p->K, (uint64_t)p->R * p->S * p->C, 64);
     else rc = make_map_2d(&tmB, p->w_t, (uint64_t)p->C, (uint64_t)p->R * p->S * p->K, use_pair(g, bn) ? 128u : (uint32_t)bn);
     if (rc) return rc;
-    return gemm_dispatch(tmA, tmB, g, bn, b_mn, st);
+    return gemm_dispatch(tmA, tmB, g, bn, b_mn, st, bnb_x0);
   }
 
   // wgrad

@@ -93,6 +93,23 @@ typedef struct dv_conv_params {
   const float* ep_shift;
   const void* ep_residual;
   int32_t ep_relu;
+  /* dgrad on the tensor-core path only, optional — the backward sums of the BatchNorm whose OUTPUT is this convolution's input.
+   * In conv1 -> bn1 -> relu -> conv2 (resnet50.py:152-158) the dgrad of conv2 produces dy of bn1; nn.BatchNorm2d's backward then
+   * needs  dbeta = sum_m dz,  dgamma = sum_m dz * xhat,  dz = dy * (bn1(x0) > 0),  over the M = N*H*W rows of x0 (bn1's input, the
+   * output of conv1).  With bnb_x set, the dgrad epilogue fetches the x0 tile that matches each dx tile while it is still on chip
+   * and ADDS those sums into bnb_dgamma / bnb_dbeta (fp32 [C], zeroed or to-be-accumulated by the caller; run-to-run summation
+   * order), so dv_bn_bwd_reduce need not run for that layer (it would re-read dy and x0 from HBM: 4 bytes per element).
+   *   bnb_x [N,H,W,C] dtype (same geometry as dx); bnb_gamma / bnb_beta / bnb_mean / bnb_invstd: fp32 [C] of that BatchNorm
+   *   (save_mean / save_invstd of its forward).  The ReLU mask is recomputed from x0 with bn_apply's own expressions.
+   * Requires stride == 1, accumulate == 0, w_t == NULL and the tensor-core path (ask dv_conv_algo); anything else is rejected
+   * with DV_ERR_UNSUPPORTED rather than ignored.  All NULL = plain dgrad. */
+  const void* bnb_x;
+  const float* bnb_gamma;
+  const float* bnb_beta;
+  const float* bnb_mean;
+  const float* bnb_invstd;
+  float* bnb_dgamma;
+  float* bnb_dbeta;
 } dv_conv_params;
 
 enum { DV_CONV_FPROP = 0, DV_CONV_DGRAD = 1, DV_CONV_WGRAD = 2 };
