@@ -9,7 +9,8 @@ _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
           "atomic_wgrad": os.environ.get("DV_ATOMIC_WGRAD", "1") == "1",
           "atomic_bn_bwd": os.environ.get("DV_ATOMIC_BN", "0") == "1",
           "fold_bn": os.environ.get("DV_FOLD_BN", "1") != "0",
-          "side_wgrad": os.environ.get("DV_SIDE_WGRAD", "1") == "1"}
+          "side_wgrad": os.environ.get("DV_SIDE_WGRAD", "1") == "1",
+          "fuse_bn_bwd": os.environ.get("DV_FUSE_BN_BWD", "1") == "1"}
 
 
 def compute_dtype():
@@ -88,3 +89,14 @@ def set_fold_bn(flag):
 def side_wgrad():
     """Trainer: launch dense weight-gradient kernels on a second stream beside the dgrad -> BN-backward chain."""
     return _state["side_wgrad"] and not _state["deterministic"]
+
+
+def fuse_bn_bwd():
+    """The dgrad of a dense convolution whose input is relu(bn(x0)) also produces that BatchNorm's backward sums (dgamma, dbeta)
+    in its epilogue (dv_conv_params.bnb_*), so the BatchNorm's own backward reduce pass is not launched.  The sums are combined
+    with fp32 atomics, hence off in the fixed-order mode."""
+    return _state["fuse_bn_bwd"] and not _state["deterministic"]
+
+
+def set_fuse_bn_bwd(flag):
+    _state["fuse_bn_bwd"] = bool(flag)

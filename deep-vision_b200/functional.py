@@ -184,6 +184,23 @@ class GradSlot:
         self.t = None
 
 
+class BnBwdHandoff:
+    """What the dgrad of a dense convolution needs in order to produce, in its epilogue, the backward sums of the BatchNorm
+    whose output is that convolution's input (conv1 -> bn1 -> relu -> conv2, resnet50.py:152-158: conv2's dgrad computes dy of
+    bn1 and can sum dz and dz*xhat while the tile is on chip; dv_conv_params.bnb_*).  Filled by _BatchNormAct.forward for a
+    train-mode bf16 BatchNorm with ReLU and without residual, attached to its output tensor, claimed by the convolution
+    that consumes it.  `claims` counts consumers seen at forward time: with more than one the gradient of the tensor is a
+    sum of several dgrads and nothing is fused.  In backward the convolution leaves (dx, dgamma, dbeta) here; the BatchNorm
+    uses the sums only if the dy it receives IS that dx (autograd summed nothing else onto it)."""
+
+    __slots__ = ("x", "gamma", "beta", "mean", "invstd", "claims", "result", "owner")
+
+    def __init__(self, owner=None):
+        self.x = self.gamma = self.beta = self.mean = self.invstd = self.result = None
+        self.claims = 0
+        self.owner = owner
+
+
 def _run_conv(fn, p, pass_id, device, what):
     need = lib.dv_conv_workspace_bytes(C.byref(p), pass_id)
     if need:
@@ -232,8 +249,11 @@ class _Conv2d(torch.autograd.Function):
     mobilenet_v1.py:30,139-145.  Backward = dgrad + wgrad (autograd of train.py:460)."""
 
     @staticmethod
-    def forward(ctx, x, weight, stride, pad, cache, algo, slot=None, role=None, stats=None):
+    def forward(ctx, x, weight, stride, pad, cache, algo, slot=None, role=None, stats=None, handoff=None):
         ctx.slot, ctx.role = slot, role
+        ctx.handoff = handoff
+        if handoff is not None:
+            handoff.claims += 1
         _require_cuda(x, "conv2d")
         x = _nhwc(x)
         N, Cc, H, W = x.shape
@@ -291,7 +311,7 @@ class _Conv2d(torch.autograd.Function):
                 if sink:
                     sink[1](weight)
                     dw = None
-            return None, dw, None, None, None, None, None, None, None
+            return None, dw, None, None, None, None, None, None, None, None
         N, Cc, H, W = x.shape
         if ctx.needs_input_grad[0]:
             acc = 0
@@ -303,7 +323,21 @@ class _Conv2d(torch.autograd.Function):
                 dx = torch.empty_like(x, memory_format=_CL)
             p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dy.data_ptr(), ctx.w_t.data_ptr() if ctx.w_t is not None else None,
                              N, H, W, Cc, K, R, S, stride, pad, dt, algo, accumulate=acc)
+            h = ctx.handoff
+            fused = None
+            if (h is not None and h.x is not None and h.claims == 1 and acc == 0 and stride == 1 and ctx.w_t is None
+                    and config.fuse_bn_bwd() and lib.dv_conv_algo(C.byref(p), DV_CONV_DGRAD) == DV_ALGO_TC):
+                # this dx is dy of the BatchNorm that produced x: let the epilogue add that layer's dgamma / dbeta
+                sg, sb = grad_sink(h.gamma), grad_sink(h.beta)
+                dgamma = sg[0] if sg else torch.zeros(Cc, dtype=torch.float32, device=x.device)
+                dbeta = sb[0] if sb else torch.zeros(Cc, dtype=torch.float32, device=x.device)
+                p.bnb_x, p.bnb_gamma, p.bnb_beta = h.x.data_ptr(), h.gamma.data_ptr(), h.beta.data_ptr()
+                p.bnb_mean, p.bnb_invstd = h.mean.data_ptr(), h.invstd.data_ptr()
+                p.bnb_dgamma, p.bnb_dbeta = dgamma.data_ptr(), dbeta.data_ptr()
+                fused = (dgamma, dbeta)
             _run_conv(lib.dv_conv_dgrad, p, DV_CONV_DGRAD, x.device, "dv_conv_dgrad")
+            if fused is not None:
+                h.result = (dx, fused[0], fused[1])
             if ctx.role == "deposit":
                 ctx.slot.t, dx = dx, None
         if ctx.needs_input_grad[1]:
@@ -326,7 +360,7 @@ class _Conv2d(torch.autograd.Function):
             if sink:
                 sink[1](weight)
                 dw = None
-        return dx, dw, None, None, None, None, None, None, None
+        return dx, dw, None, None, None, None, None, None, None, None
 
 
 def _attach_stats(p, stats, y, pass_id):
@@ -340,7 +374,8 @@ def _attach_stats(p, stats, y, pass_id):
 
 
 def conv2d(x, weight, stride=1, padding=0, cache=None, algo=DV_ALGO_AUTO, slot=None, role=None, stats=None):
-    y = _Conv2d.apply(x, weight, int(stride), int(padding), cache or FilterCache(), algo, slot, role, stats)
+    y = _Conv2d.apply(x, weight, int(stride), int(padding), cache or FilterCache(), algo, slot, role, stats,
+                      getattr(x, "_dv_bn_handoff", None))
     if stats is not None and stats.pending:
         y._dv_stat_sums = stats  # picked up by the BatchNorm that consumes y
     return y
@@ -412,8 +447,9 @@ class _BatchNormAct(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None,
-                sums=None):
+                sums=None, handoff=None):
         ctx.res_slot = res_slot
+        ctx.handoff = None
         _require_cuda(x, "batch_norm")
         x = _nhwc(x)
         N, Cc, H, W = x.shape
@@ -464,6 +500,9 @@ class _BatchNormAct(torch.autograd.Function):
         ctx.bit_mask = mask is not None
         if use_batch_stats:
             ctx.save_for_backward(x, keep_y, gamma, save_mean, save_invstd, beta)
+            if (handoff is not None and relu and residual is None and x.dtype == torch.bfloat16 and any(ctx.needs_input_grad[:4])):
+                handoff.x, handoff.gamma, handoff.beta, handoff.mean, handoff.invstd = x, gamma, beta, save_mean, save_invstd
+                ctx.handoff = handoff
         else:
             ctx.save_for_backward(x, keep_y, gamma, running_mean, running_var, beta)
             ctx.eps = eps
@@ -497,9 +536,28 @@ class _BatchNormAct(torch.autograd.Function):
         p.gamma, p.beta, p.save_mean, p.save_invstd = gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), second.data_ptr()
         p.dgamma, p.dbeta = dgamma.data_ptr(), dbeta.data_ptr()
         p.M, p.C, p.dtype, p.relu = M, Cc, _dv_dtype(x.dtype), int(ctx.relu)
-        ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
-        p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
-        check(lib.dv_bn_bwd_reduce(C.byref(p), _stream()), "dv_bn_bwd_reduce")
+        # sums that the consumer's dgrad epilogue already produced (BnBwdHandoff) — valid only if this dy IS that dgrad's output
+        h, pre = ctx.handoff, None
+        if h is not None and h.result is not None:
+            pre, h.result = h.result, None
+            if pre[0].data_ptr() == dy.data_ptr() and pre[0].shape == dy.shape:
+                if sg is None:
+                    dgamma = pre[1]
+                if sb is None:
+                    dbeta = pre[2]
+                p.dgamma, p.dbeta = pre[1].data_ptr(), pre[2].data_ptr()
+            else:                       # autograd added other gradients onto it: the partial sums are void
+                if sg:
+                    sg[0].zero_()
+                if sb:
+                    sb[0].zero_()
+                pre = None
+        if h is not None and h.owner is not None:
+            h.owner._dv_bwd_sums_fused = pre is not None
+        if pre is None:
+            ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
+            p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+            check(lib.dv_bn_bwd_reduce(C.byref(p), _stream()), "dv_bn_bwd_reduce")
         check(lib.dv_bn_bwd_apply(C.byref(p), _stream()), "dv_bn_bwd_apply")
         if sg:
             sg[1](gamma)
@@ -509,13 +567,17 @@ class _BatchNormAct(torch.autograd.Function):
             dbeta = None
         if ctx.res_slot is not None and dres is not None:
             ctx.res_slot.t, dres = dres, None   # handed to the main path's dgrad, not to autograd
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None, None
 
 
-def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None):
+def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, res_slot=None, owner=None):
     sums = getattr(x, "_dv_stat_sums", None)
-    return _BatchNormAct.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum), float(eps),
-                               bool(relu), res_slot, sums)
+    handoff = BnBwdHandoff(owner) if (relu and residual is None and torch.is_grad_enabled() and config.fuse_bn_bwd()) else None
+    y = _BatchNormAct.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum), float(eps),
+                            bool(relu), res_slot, sums, handoff)
+    if handoff is not None and handoff.x is not None:
+        y._dv_bn_handoff = handoff      # claimed by the dense convolution that consumes y (functional.conv2d)
+    return y
 
 
 class _ReLU(torch.autograd.Function):

@@ -73,7 +73,7 @@ class BatchNorm2d(nn.BatchNorm2d):
             raise NotImplementedError("deep_vision_b200.nn.BatchNorm2d: affine=False is not on the hot path")
         rm = self.running_mean if (not self.training or self.track_running_stats) else None
         rv = self.running_var if (not self.training or self.track_running_stats) else None
-        return F.batch_norm_act(x, residual, self.weight, self.bias, rm, rv, training, eaf, self.eps, act is not None, res_slot)
+        return F.batch_norm_act(x, residual, self.weight, self.bias, rm, rv, training, eaf, self.eps, act is not None, res_slot, self)
 
 
 class ReLU(nn.ReLU):

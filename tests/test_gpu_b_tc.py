@@ -383,3 +383,98 @@ def test_tc_fprop_folded_batchnorm_epilogue(case):
     assert lib.lib.dv_conv_fprop(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED
     p.algo = lib.DV_ALGO_TC
     assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED
+
+
+BNB_CASES = [
+    # N, C, H, W, K, R, pad        dgrad output = [N,H,W,C]: the tensor whose BatchNorm sums are fused
+    (2, 64, 8, 8, 64, 3, 1),          # 64-wide tile, 3x3, M = 128
+    (3, 128, 7, 7, 256, 1, 0),        # 128-wide tile, ragged M (147)
+    (2, 256, 8, 8, 128, 1, 0),        # 256-wide tile, persistent kernel
+    (5, 64, 6, 5, 192, 3, 1),         # H != W, three reduction blocks
+    (3, 96, 5, 5, 32, 1, 0),          # C = 96: the second 64-column group is half empty
+    (2, 512, 4, 4, 64, 1, 0),         # two 256-wide n tiles per CTA walk
+    (151, 64, 16, 8, 256, 1, 0),      # many M tiles per CTA: running sums across tiles, one flush
+    (38, 256, 24, 24, 64, 1, 0),      # CTA-pair kernel (M = 21888, 256 columns)
+    (37, 256, 24, 23, 128, 3, 1),     # CTA-pair kernel, 3x3, odd number of M tiles (the peer's last tile is empty)
+]
+
+
+@pytest.mark.parametrize("case", BNB_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_dgrad_fused_bn_backward_sums(case):
+    """dv_conv_params.bnb_*: the dgrad epilogue adds dbeta = sum dz and dgamma = sum dz*xhat of the BatchNorm that produced the
+    convolution's input (dz = dx masked by relu(bn(x0)) > 0).  Checked three ways: dx is unchanged by the option (bit for bit);
+    the sums equal fp64 sums over the kernel's own bf16 dx (what a separate reduce pass would read); and they equal
+    dv_bn_bwd_reduce's on the same tensors.  The accumulators are pre-loaded, so the test also shows that the sums are ADDED."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, Cc, H, W, K, R, pad = case
+    g = torch.Generator(device="cuda").manual_seed(11)
+    dy = torch.randn((N, H + 2 * pad - R + 1, W + 2 * pad - R + 1, K), generator=g, device="cuda").to(BF)
+    w = (torch.randn((K, R, R, Cc), generator=g, device="cuda") * 0.1).to(BF)
+    x0 = (torch.randn((N, H, W, Cc), generator=g, device="cuda") * 1.5 + 0.3).to(BF)
+    gamma = torch.rand(Cc, generator=g, device="cuda") + 0.5
+    beta = torch.randn(Cc, generator=g, device="cuda") * 0.3
+    xf = x0.float().reshape(-1, Cc)
+    mean = xf.mean(0)
+    invstd = 1.0 / torch.sqrt(xf.var(0, unbiased=False) + 1e-5)
+
+    def dgrad(with_sums):
+        dx = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=BF)
+        dgamma = torch.full((Cc,), 2.0, device="cuda")
+        dbeta = torch.full((Cc,), -3.0, device="cuda")
+        p = lib.ConvParams()
+        p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), dy.data_ptr()
+        p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, W, Cc, K, R, R, 1, pad, lib.DV_BF16, lib.DV_ALGO_TC
+        if with_sums:
+            p.bnb_x, p.bnb_gamma, p.bnb_beta, p.bnb_mean, p.bnb_invstd = x0.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr()
+            p.bnb_dgamma, p.bnb_dbeta = dgamma.data_ptr(), dbeta.data_ptr()
+        lib.check(lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()), "dgrad")
+        torch.cuda.synchronize()
+        return dx, dgamma, dbeta
+
+    dx_plain, _, _ = dgrad(False)
+    dx, dgamma, dbeta = dgrad(True)
+    assert torch.equal(dx.view(torch.int16), dx_plain.view(torch.int16))
+    # fp64 sums over the kernel's dx; elements whose pre-activation is within rounding of zero may fall on either side
+    sc = (invstd * gamma).double()
+    pre = x0.double().reshape(-1, Cc) * sc + (beta.double() - mean.double() * sc)
+    dz = dx.double().reshape(-1, Cc) * (pre > 0)
+    xhat = (x0.double().reshape(-1, Cc) - mean.double()) * invstd.double()
+    want_b, want_g = dz.sum(0), (dz * xhat).sum(0)
+    scale_b = dz.abs().sum(0) + 1e-6          # the sums cancel heavily: compare against the size of what was summed
+    scale_g = (dz * xhat).abs().sum(0) + 1e-6
+    assert float(((dbeta.double() + 3.0 - want_b).abs() / scale_b).max()) < 1e-4
+    assert float(((dgamma.double() - 2.0 - want_g).abs() / scale_g).max()) < 1e-4
+    # and the stand-alone reduce pass on the same tensors
+    q = lib.BnBwdParams()
+    dg2, db2 = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    M = N * H * W
+    ws = torch.empty(lib.lib.dv_bn_workspace_bytes(M, Cc), dtype=torch.uint8, device="cuda")
+    q.x, q.dy, q.gamma, q.beta, q.save_mean, q.save_invstd = x0.data_ptr(), dx.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr()
+    q.dgamma, q.dbeta, q.workspace, q.workspace_bytes = dg2.data_ptr(), db2.data_ptr(), ws.data_ptr(), ws.numel()
+    q.M, q.C, q.dtype, q.relu = M, Cc, lib.DV_BF16, 1
+    lib.check(lib.lib.dv_bn_bwd_reduce(C.byref(q), stream_ptr()), "bwd_reduce")
+    torch.cuda.synchronize()
+    assert float(((dbeta - (-3.0) - db2).double().abs() / scale_b).max()) < 1e-4
+    assert float(((dgamma - 2.0 - dg2).double().abs() / scale_g).max()) < 1e-4
+
+
+def test_tc_dgrad_bn_sums_rejects_what_it_cannot_fuse():
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    t = torch.zeros(2 * 8 * 8 * 64, device="cuda", dtype=BF)
+    v = torch.zeros(64, device="cuda")
+    p = lib.ConvParams()
+    p.x, p.w, p.y = t.data_ptr(), t.data_ptr(), t.data_ptr()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = 2, 8, 8, 64, 64, 1, 1, 1, 0, lib.DV_BF16, lib.DV_ALGO_TC
+    p.bnb_x, p.bnb_gamma, p.bnb_beta, p.bnb_mean, p.bnb_invstd, p.bnb_dgamma, p.bnb_dbeta = [t.data_ptr()] + [v.data_ptr()] * 6
+    p.accumulate = 1
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED       # accumulate: the final dx never is on chip
+    p.accumulate, p.algo = 0, lib.DV_ALGO_SIMT
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED       # CUDA-core path has no such epilogue
+    p.algo = lib.DV_ALGO_TC
+    assert lib.lib.dv_conv_fprop(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED       # dgrad only
+    p.bnb_dbeta = None
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_ARG

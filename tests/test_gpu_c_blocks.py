@@ -67,3 +67,38 @@ def test_block_bf16_matches_reference(name, algo):
     # running statistics: fp32 arithmetic, but taken over the bf16-rounded conv output (as torch autocast does)
     assert all(v < 2e-2 for k, v in errs.items() if k.startswith("after/")), errs
     assert errs["dx"] < 1.5e-1 and all(v < 1.5e-1 for k, v in errs.items() if k.startswith("grad/")), errs
+
+
+@pytest.mark.parametrize("name,fused_layers", [("block_bottleneck_256_64_256", 2), ("block_bottleneck_128_64_256_s2_proj", 2),
+                                                ("block_basic_64_64", 1), ("block_dwsep_32_64_s1", 1)])
+def test_block_bf16_fused_bn_backward_sums_equal_the_reduce_pass(name, fused_layers):
+    """With set_fuse_bn_bwd(True) (default) the dgrad of conv2 / conv3 / the point-wise conv produces dgamma, dbeta of the
+    BatchNorm in front of it, and that BatchNorm's reduce + finalize launches disappear.  Same gradients as with the separate
+    pass (fixed forward statistics, so the two runs see identical activations), two launches fewer per fused layer."""
+    from deep_vision_b200.lib import lib
+    rec = load_golden(name)
+    dv.set_compute_dtype(torch.bfloat16)
+    dv.set_fuse_bn_stats(False)        # bit-reproducible forward: both runs back-propagate through the same tensors
+    grads, launches = {}, {}
+    try:
+        for fuse in (False, True):
+            dv.set_fuse_bn_bwd(fuse)
+            m = CASES[name]()
+            m.load_state_dict(golden_state(rec))
+            m = m.cuda().train()
+            x = torch.from_numpy(rec["x"]).cuda().requires_grad_(True)
+            n0 = lib.dv_launch_count()
+            y = m(x)
+            y.backward(torch.from_numpy(rec["dy"]).cuda().to(torch.bfloat16))
+            torch.cuda.synchronize()
+            launches[fuse] = lib.dv_launch_count() - n0
+            grads[fuse] = {k: p.grad.detach().double().cpu().numpy() for k, p in m.named_parameters()}
+            grads[fuse]["dx"] = x.grad.double().cpu().numpy()
+            fused = [k for k, mod in m.named_modules() if getattr(mod, "_dv_bwd_sums_fused", False)]
+            assert len(fused) == (fused_layers if fuse else 0), fused
+    finally:
+        dv.set_fuse_bn_bwd(True)
+        dv.set_fuse_bn_stats(True)
+    assert launches[False] - launches[True] == 2 * fused_layers, launches
+    for k in grads[True]:
+        assert rel_l2(grads[True][k], grads[False][k]) < 2e-3, k     # bf16 dx downstream of an fp32 sum that moved in its last bits
