@@ -282,11 +282,15 @@ template <typename T, bool FIXED>
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, const float* __restrict__ gamma,
                 const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ invstd_or_var,
-                int64_t nvec, int C, int relu, int eval_mode, float eps, uint8_t* __restrict__ mask) {
+                int64_t nvec, int C, int relu, int eval_mode, float eps, uint8_t* __restrict__ mask, int reverse) {
+  // reverse: walk the tensor from its END.  The producer of x (a convolution's epilogue, walking tiles upwards) leaves the
+  // LAST bytes it wrote in the L2; a consumer that starts there meets them before they are evicted, and leaves the START of
+  // y in the L2 for the next convolution, which walks upwards again.
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t last = nvec - 1;
   float sc[V], sh[V];
   auto load_consts = [&](int c) {
 #pragma unroll
@@ -296,21 +300,23 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
       sh[j] = beta[c + j] - mean[c + j] * sc[j];
     }
   };
-  if (FIXED) load_consts((int)(i0 % cg) * V);
+  if (FIXED) load_consts((int)((reverse ? last - i0 : i0) % cg) * V);   // nvec is a multiple of cg: the group stays fixed either way
   for (int64_t i = i0; i < nvec; i += stride * kUnroll) {
     Vec16<T> vx[kUnroll], vr[kUnroll];
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
-      const int64_t k = i + u * stride;
-      if (k < nvec) {
+      const int64_t kk = i + u * stride;
+      if (kk < nvec) {
+        const int64_t k = reverse ? last - kk : kk;
         vx[u].load(x + k * V);
         if (res != nullptr) vr[u].load(res + k * V);
       }
     }
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
-      const int64_t k = i + u * stride;
-      if (k >= nvec) break;
+      const int64_t kk = i + u * stride;
+      if (kk >= nvec) break;
+      const int64_t k = reverse ? last - kk : kk;
       if (!FIXED) load_consts((int)(k % cg) * V);
       float xv[V], rv[V], out[V];
       vx[u].unpack(xv);
@@ -344,11 +350,12 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
                     T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ dgamma,
                     const float* __restrict__ dbeta, int64_t nvec, int C, int relu, float inv_m,
-                    const uint8_t* __restrict__ mask) {
+                    const uint8_t* __restrict__ mask, int reverse) {
   constexpr int V = Vec16<T>::N;
   const int cg = C / V;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t last = nvec - 1;   // reverse: walk from the end (see bn_apply_kernel)
   // dx = k1*dz - k2*(x - mean) - k3   with k1 = gamma*invstd, k2 = k1*invstd*dgamma/M, k3 = k1*dbeta/M
   float k1[V], k2[V], k3[V], mu[V], msc[V], msh[V];
   auto load_consts = [&](int c) {
@@ -365,14 +372,15 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
       }
     }
   };
-  if (FIXED) load_consts((int)(i0 % cg) * V);
+  if (FIXED) load_consts((int)((reverse ? last - i0 : i0) % cg) * V);
   for (int64_t i = i0; i < nvec; i += stride * U) {
     Vec16<T> vx[U], vg[U], vy[U];
     uint32_t mb[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int64_t k = i + u * stride;
-      if (k < nvec) {
+      const int64_t kk = i + u * stride;
+      if (kk < nvec) {
+        const int64_t k = reverse ? last - kk : kk;
         vx[u].load(x + k * V);
         vg[u].load(dy + k * V);
         if (relu == 1) vy[u].load(y + k * V);
@@ -381,8 +389,9 @@ bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* _
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int64_t k = i + u * stride;
-      if (k >= nvec) break;
+      const int64_t kk = i + u * stride;
+      if (kk >= nvec) break;
+      const int64_t k = reverse ? last - kk : kk;
       if (!FIXED) load_consts((int)(k % cg) * V);
       float xv[V], gv[V], out[V];
       vx[u].unpack(xv);
@@ -469,14 +478,16 @@ static int apply_t(const dv_bn_params* p, cudaStream_t st) {
   static const int apply_forced = env_or("DV_BN_APPLY_CTAS", 0);
   DV_REQUIRE(p->relu_mask == nullptr || (V == 8 && p->relu), DV_ERR_UNSUPPORTED, "bn_apply: relu_mask needs bf16 and relu == 1");
   uint8_t* mask = (uint8_t*)p->relu_mask;
+  static const int rev_env = env_or("DV_BN_APPLY_REV", 0);   // experiment knob: 1 = always walk downwards, 2 = never
+  const int reverse = rev_env == 1 ? 1 : (rev_env == 2 ? 0 : (p->reverse ? 1 : 0));
   if (kThreads % (p->C / V) == 0) {
     const unsigned grid = stream_grid(ceil_div64(nvec, kUnroll), apply_forced ? apply_forced : resident_ctas(bn_apply_kernel<T, true>));
     bn_apply_kernel<T, true><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
-                                                       p->C, p->relu, p->eval_mode, p->eps, mask);
+                                                       p->C, p->relu, p->eval_mode, p->eps, mask, reverse);
   } else {
     const unsigned grid = stream_grid(ceil_div64(nvec, kUnroll), apply_forced ? apply_forced : resident_ctas(bn_apply_kernel<T, false>));
     bn_apply_kernel<T, false><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->residual, (T*)p->y, p->gamma, p->beta, mean, is, nvec,
-                                                        p->C, p->relu, p->eval_mode, p->eps, mask);
+                                                        p->C, p->relu, p->eval_mode, p->eps, mask, reverse);
   }
   DV_LAUNCH_OK("bn_apply_kernel");
   return DV_OK;
@@ -530,12 +541,14 @@ static int bwd_apply_t(const dv_bn_bwd_params* p, cudaStream_t st) {
   const int64_t nvec = p->M * p->C / V;
   const bool wide = (relu_mode != 1 && p->dres == nullptr);   // two loads per vector only: keep four vectors in flight
   static const int bwd_forced = env_or("DV_BN_BWD_CTAS", 0);
+  static const int rev_env = env_or("DV_BN_BWD_REV", 0);   // experiment knob: 1 = always walk downwards, 2 = never
+  const int reverse = rev_env == 1 ? 1 : (rev_env == 2 ? 0 : (p->reverse ? 1 : 0));
 #define DV_BWD_APPLY(FIXED_, U_)                                                                                                     \
   do {                                                                                                                               \
     const unsigned grid = stream_grid(ceil_div64(nvec, U_), bwd_forced ? bwd_forced : resident_ctas(bn_bwd_apply_kernel<T, FIXED_, U_>)); \
     bn_bwd_apply_kernel<T, FIXED_, U_><<<grid, kThreads, 0, st>>>((const T*)p->x, (const T*)p->y, (const T*)p->dy, (T*)p->dx, (T*)p->dres, \
                                                                  p->gamma, p->beta, p->save_mean, p->save_invstd, p->dgamma, p->dbeta, nvec, \
-                                                                 p->C, relu_mode, 1.0f / (float)p->M, (const uint8_t*)p->relu_mask);  \
+                                                                 p->C, relu_mode, 1.0f / (float)p->M, (const uint8_t*)p->relu_mask, reverse);  \
   } while (0)
   if (kThreads % (p->C / V) == 0) {
     if (wide) DV_BWD_APPLY(true, 4); else DV_BWD_APPLY(true, 2);

@@ -441,6 +441,13 @@ def dwconv3x3(x, weight, stride=1):
 # ----------------------------------------------------------------------------------------------------------------
 # batch norm (+ residual) (+ ReLU)
 # ----------------------------------------------------------------------------------------------------------------
+# Traversal direction of the streaming BatchNorm passes (dv_bn_params.reverse): a pass that starts at the END of a tensor meets
+# the bytes its producer (a convolution walking its tiles upwards) wrote last, while they are still in the L2.
+import os as _os
+_ZIGZAG = {"fwd": _os.environ.get("DV_ZZ_FWD", "1") == "1", "bwd": _os.environ.get("DV_ZZ_BWD", "1") == "1",
+           "bwd_fused": _os.environ.get("DV_ZZ_BWD_FUSED", "1") == "1"}
+
+
 class _BatchNormAct(torch.autograd.Function):
     """y = relu(bn(x) [+ residual]) — nn.BatchNorm2d + nn.ReLU(inplace=True) (+ `x + identity`) at
     resnet50.py:152-164, resnet34.py:135-142, mobilenet_v1.py:129-133,152-156."""
@@ -491,6 +498,7 @@ class _BatchNormAct(torch.autograd.Function):
         if relu and residual is not None and use_batch_stats and x.dtype == torch.bfloat16 and any(ctx.needs_input_grad[:4]):
             mask = torch.empty((M, Cc // 8), dtype=torch.uint8, device=x.device)
             p.relu_mask = mask.data_ptr()
+        p.reverse = int(_ZIGZAG["fwd"] and use_batch_stats)
         check(lib.dv_bn_apply(C.byref(p), _stream()), "dv_bn_apply")
         ctx.batch_stats = use_batch_stats
         ctx.relu = bool(relu)
@@ -554,6 +562,7 @@ class _BatchNormAct(torch.autograd.Function):
                 pre = None
         if h is not None and h.owner is not None:
             h.owner._dv_bwd_sums_fused = pre is not None
+        p.reverse = int(_ZIGZAG["bwd_fused"] if pre is not None else _ZIGZAG["bwd"])
         if pre is None:
             ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
             p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()

@@ -62,7 +62,7 @@ class BnParams(C.Structure):
         ("save_mean", C.c_void_p), ("save_invstd", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("M", C.c_int64), ("C", C.c_int32), ("dtype", C.c_int32), ("relu", C.c_int32), ("eval_mode", C.c_int32),
-        ("eps", C.c_float), ("momentum", C.c_float), ("relu_mask", C.c_void_p),
+        ("eps", C.c_float), ("momentum", C.c_float), ("relu_mask", C.c_void_p), ("reverse", C.c_int32),
     ]
 
 
@@ -73,7 +73,7 @@ class BnBwdParams(C.Structure):
         ("dgamma", C.c_void_p), ("dbeta", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("M", C.c_int64), ("C", C.c_int32), ("dtype", C.c_int32), ("relu", C.c_int32), ("atomic_sums", C.c_int32),
-        ("relu_mask", C.c_void_p),
+        ("relu_mask", C.c_void_p), ("reverse", C.c_int32),
     ]
 
 

@@ -194,6 +194,8 @@ typedef struct dv_bn_params {
   void* relu_mask;      /* optional (bf16 only): uint8 [M][C/8] written by dv_bn_apply when relu == 1; bit j of byte
                            (m, c/8) = (y[m][c+j] > 0).  Lets the backward of a RESIDUAL block read 1 bit instead of 16 per
                            element for the ReLU mask (see dv_bn_bwd_params.relu_mask) */
+  int32_t reverse;      /* dv_bn_apply: 1 = walk the rows from the last to the first (same result).  A pass that starts where
+                           its producer stopped finds those bytes still in the 126 MB L2 */
 } dv_bn_params;
 
 /* batch statistics (mean, biased var -> invstd) + running-stat update */
@@ -252,6 +254,7 @@ typedef struct dv_bn_bwd_params {
                            finalize (bit-reproducible) */
   const void* relu_mask; /* optional (bf16 only): the bit mask dv_bn_apply wrote; when set (and relu == 1) it is used
                            instead of y, which is then not read by either backward pass */
+  int32_t reverse;      /* dv_bn_bwd_apply: 1 = walk the rows from the last to the first (same result); see dv_bn_params.reverse */
 } dv_bn_bwd_params;
 
 /* dgamma, dbeta (with the ReLU mask recomputed from y) */
