@@ -211,3 +211,22 @@ def test_folded_batchnorm_inference_matches_unfused_and_golden(name):
     assert rel_l2(y2, y2_plain) < 2e-2
     if "mobilenet" not in name:   # (a fresh MobileNetV1 in eval mode has logits ~ the classifier bias: nothing to see there)
         assert rel_l2(y2, y_fold) > 1e-3
+
+
+def test_captured_forward_replays_the_eager_inference_pass():
+    """inference.CapturedForward: the eval-mode forward recorded into a CUDA graph gives the eager pass's logits bit for bit,
+    for every new batch copied into its static input, and refuses another shape."""
+    torch.manual_seed(0)
+    dv.set_compute_dtype(torch.bfloat16)
+    net = dv.models.ResNet34().cuda().eval()
+    g = torch.Generator().manual_seed(3)
+    xs = [torch.randn(8, 3, 64, 64, generator=g).cuda() for _ in range(3)]
+    fwd = dv.inference.CapturedForward(net, xs[0])
+    for x in xs:
+        with torch.no_grad():
+            want = net(x).clone()
+        got = fwd(x)
+        torch.cuda.synchronize()
+        assert torch.equal(got, want)
+    with pytest.raises(RuntimeError):
+        fwd(xs[0][:4])
