@@ -50,6 +50,16 @@ def run_job(which, shape, iters):
     if which == "fprop":
         p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
         fn = lambda: check(lib.dv_conv_fprop(C.byref(p), st), "fprop")
+    elif which in ("dgrad", "dgrad_bnb"):
+        dx = torch.empty_like(x)
+        p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), y.normal_().data_ptr()
+        if which == "dgrad_bnb":      # with the BatchNorm-backward sums of the producing layer in the epilogue
+            x0 = torch.randn_like(x)
+            v = [torch.ones(Cc, device="cuda") for _ in range(4)] + [torch.zeros(Cc, device="cuda") for _ in range(2)]
+            p.bnb_x = x0.data_ptr()
+            p.bnb_gamma, p.bnb_beta, p.bnb_mean, p.bnb_invstd, p.bnb_dgamma, p.bnb_dbeta = [t.data_ptr() for t in v]
+            keep = (x0, v)
+        fn = lambda: check(lib.dv_conv_dgrad(C.byref(p), st), "dgrad")
     elif which in ("wgrad", "wgrad_acc"):
         dw = torch.zeros(K, R, R, Cc, device="cuda")
         p.accumulate = 1 if which == "wgrad_acc" else 0
