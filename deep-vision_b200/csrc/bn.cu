@@ -345,7 +345,7 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
 // roof with U = 2; the variant without identity (2 loads, 1 store) sat at 0.77 with U = 2 (ncu: 16 warps/SM at 114 registers,
 // 8 warps per issue slot waiting on loads) and gets U = 4.
 template <typename T, bool FIXED, int U>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)   // two CTAs per SM: 128 registers at most (the U = 4 variant sits right at that line)
 bn_bwd_apply_kernel(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
                     T* __restrict__ dres, const float* __restrict__ gamma, const float* __restrict__ beta,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ dgamma,

@@ -301,16 +301,21 @@ struct GemmArgs {
 __device__ __forceinline__ void bnb_tile_sums(const uint8_t* my_stage, const uint32_t* xw, int lane, float sc0, float sh0, float mu0, float sc1,
                                               float sh1, float mu1, float& a0, float& a1, float& b0, float& b1) {
   const int wch = lane >> 2, wof = (lane & 3) * 4;
+  // two columns per lane = one packed fp32 pair per row: fma.rn.f32x2 / add.rn.f32x2 (IEEE, the same bits as the scalar forms)
+  const float2 sc = make_float2(sc0, sc1), sh = make_float2(sh0, sh1), nmu = make_float2(-mu0, -mu1);
+  float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
 #pragma unroll   // fully: xw[] must stay in registers (constant indices)
   for (int r = 0; r < 32; ++r) {
     const uint32_t word = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
-    const float d0 = __uint_as_float(word << 16), d1 = __uint_as_float(word & 0xffff0000u);
-    const float x0 = __uint_as_float(xw[r] << 16), x1 = __uint_as_float(xw[r] & 0xffff0000u);
-    const float z0 = fmaf(x0, sc0, sh0) > 0.f ? d0 : 0.f;   // the expressions of bn_apply_kernel / bn_reduce_kernel<.,1,2>
-    const float z1 = fmaf(x1, sc1, sh1) > 0.f ? d1 : 0.f;
-    a0 += z0; a1 += z1;
-    b0 = fmaf(z0, x0 - mu0, b0); b1 = fmaf(z1, x1 - mu1, b1);
+    const float2 d = make_float2(__uint_as_float(word << 16), __uint_as_float(word & 0xffff0000u));
+    const float2 x = make_float2(__uint_as_float(xw[r] << 16), __uint_as_float(xw[r] & 0xffff0000u));
+    const float2 pre = __ffma2_rn(x, sc, sh);   // the expression of bn_apply_kernel / bn_reduce_kernel<.,1,2>: fmaf(x, sc, sh) > 0
+    const float2 z = make_float2(pre.x > 0.f ? d.x : 0.f, pre.y > 0.f ? d.y : 0.f);
+    a = __fadd2_rn(a, z);
+    b = __ffma2_rn(z, __fadd2_rn(x, nmu), b);
   }
+  a0 += a.x; a1 += a.y;
+  b0 += b.x; b1 += b.y;
 }
 
 // Folded-BatchNorm epilogue on the 32 accumulator columns [col0, col0+32) of the output row held by one lane.  The identity
