@@ -39,9 +39,12 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
-def plan_buckets(offsets, total, cap_elems):
+def plan_buckets(offsets, total, cap_elems, tail_elems=0):
     """Cut [0,total) into contiguous ranges of >= cap_elems elements (the last may be smaller), walking parameters
     from the END of the flat buffer: backward produces the last layers' gradients first, so bucket 0 is ready first.
+    tail_elems > 0: the range that holds the FIRST parameters — whose all-reduce can only start after the very last weight
+    gradient of the step (the stem's) and is therefore the one transfer nothing overlaps — is cut once more so that this
+    exposed piece carries at most about tail_elems elements; the rest of it goes out as soon as its own gradients are in.
     Returns [(start, end)] in launch order."""
     buckets, end, i = [], total, len(offsets) - 1
     while i >= 0:
@@ -51,6 +54,12 @@ def plan_buckets(offsets, total, cap_elems):
             i -= 1
         buckets.append((start, end))
         end = start
+    if tail_elems > 0 and buckets:
+        s, e = buckets[-1]
+        inner = [o for o in offsets if s < o < e and o - s <= tail_elems]
+        if inner:
+            cut = max(inner)
+            buckets[-1:] = [(cut, e), (s, cut)]
     return buckets
 
 
@@ -96,9 +105,9 @@ class BucketedAllReduce:
     flat gradient buffer, each launched asynchronously from the autograd hook of the bucket's last-arriving
     parameter; `finish()` makes the current stream wait for all of them."""
 
-    def __init__(self, flat, bucket_bytes=25 << 20, process_group=None):
+    def __init__(self, flat, bucket_bytes=25 << 20, process_group=None, tail_bytes=1 << 20):
         self.flat, self.pg = flat, process_group
-        self.buckets = plan_buckets(flat.offsets, flat.total, max(1, bucket_bytes // 4))
+        self.buckets = plan_buckets(flat.offsets, flat.total, max(1, bucket_bytes // 4), tail_bytes // 4)
         self._bucket_of, self._need = {}, []
         for b, (s, e) in enumerate(self.buckets):
             members = [j for j, o in enumerate(flat.offsets) if s <= o < e]

@@ -23,6 +23,10 @@ def test_plan_buckets_covers_everything_back_to_front():
     assert all((e - s) >= 300 for s, e in b[:-1])
     assert plan_buckets([0], 10, 1 << 30) == [(0, 10)]
     assert plan_buckets([0, 5], 10, 1) == [(5, 10), (0, 5)]
+    # the exposed tail: the range with the first parameters is cut so that what waits for the last gradient is small
+    assert plan_buckets(offsets, total, 600) == [(400, 1200), (0, 400)]
+    assert plan_buckets(offsets, total, 600, tail_elems=160) == [(400, 1200), (150, 400), (0, 150)]
+    assert plan_buckets(offsets, total, 600, tail_elems=50) == [(400, 1200), (0, 400)]   # no parameter boundary within reach
 
 
 def _tiny():
