@@ -62,7 +62,7 @@ def _worker(rank, world, port, q):
     try:
         m = _tiny()
         flat = FlatParams(m)
-        ex = BucketedAllReduce(flat, bucket_bytes=256)   # tiny buckets -> several collectives
+        ex = BucketedAllReduce(flat, bucket_bytes=256, tail_bytes=0)   # tiny buckets -> several collectives (no tail cut: a 1-parameter bucket may overtake)
         x, y = _shard(rank)
         flat.flat_g.zero_()
         ex.reset()
