@@ -18,7 +18,12 @@ ap.add_argument("--model", default="resnet50")
 ap.add_argument("--batch", type=int, default=256)
 ap.add_argument("--out", default="gpurun_out/step_trace.md")
 args = ap.parse_args()
-torch.cuda.set_device(0)
+import torch.distributed as dist  # noqa: E402
+rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+if world > 1:      # under torchrun: every rank trains, rank 0 writes the timeline (NCCL kernels included)
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 dv.set_compute_dtype(torch.bfloat16)
 torch.manual_seed(0)
 ctor = {"resnet50": "ResNet50", "resnet34": "ResNet34", "resnet152": "ResNet152", "mobilenet1": "MobileNetV1"}[args.model]
@@ -38,6 +43,11 @@ with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for _ in range(STEPS):
         trainer.step(x, y)
     torch.cuda.synchronize()
+if world > 1:
+    dist.barrier()
+    torch.cuda.synchronize()
+    if rank != 0:
+        os._exit(0)
 ev = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA and e.time_range.end > e.time_range.start]
 ev.sort(key=lambda e: e.time_range.start)
 span = (ev[-1].time_range.end - ev[0].time_range.start) / STEPS
@@ -52,7 +62,7 @@ for e in ev:
     agg[k][1] += e.time_range.end - e.time_range.start
 rows = sorted(agg.items(), key=lambda kv: -kv[1][1])
 with open(args.out, "w") as f:
-    f.write(f"# In-step kernel timeline, {args.model} batch {args.batch} bf16, CUDA graph, {STEPS} steps averaged (CUPTI)\n\n")
+    f.write(f"# In-step kernel timeline, {args.model} batch {args.batch} bf16, CUDA graph, {STEPS} steps averaged (CUPTI), rank 0 of {world}\n\n")
     f.write(f"span per step {span / 1e3:.3f} ms, kernels busy {busy / 1e3:.3f} ms, idle between kernels {(span - busy) / 1e3:.3f} ms "
             f"({len(ev) // STEPS} launches per step, median gap {sorted(gaps)[len(gaps) // 2]:.2f} us)\n\n")
     f.write("| kernel | launches/step | us/step | share |\n|---|---|---|---|\n")
@@ -66,3 +76,6 @@ with open(args.out, "a") as f:
     hist = collections.Counter(min(int(g), 10) for g in gaps)
     f.write("\nGap histogram (us, 10 = 10 or more): " + ", ".join(f"{k}: {v // STEPS}" for k, v in sorted(hist.items())) + "\n")
 print(open(args.out).read()[:3000])
+if world > 1:
+    sys.stdout.flush()
+    os._exit(0)
