@@ -177,7 +177,7 @@ def run_reference(args):
                          "sample": f"best of {reps} steps of batch {batch} (fp32, oracle/ref_models.py) after 1 warm-up"},
         "e2e": {"value": round(ips, 3), "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 def _event_times(torch, fn, flush, iters=10, warm=3):
@@ -388,7 +388,7 @@ def run_ours(args):
             trainer.step(images, labels)
         barrier()
         if rank == 0:
-            print(json.dumps({"profile": True, "launches_per_step": launches_per_step, "steps": args.steps}), flush=True)
+            print(json.dumps({"profile": True, "launches_per_step": launches_per_step, "steps": args.steps}), file=_OUT, flush=True)
         if world > 1:
             sys.stdout.flush()
             os._exit(0)
@@ -507,7 +507,7 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": round(ips_cpu, 3), "unit": "images/s", "cores": cores, "kind": "port", "cpu": cpu_model(),
                                     "sample": f"best of 3 steps of batch {args.cpu_batch} (fp32, oracle/ref_models.py) after 1 warm-up",
                                     "config0": cpu_config0()}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_OUT, flush=True)
     if world > 1:
         # Tearing down a process group whose collectives were captured in a CUDA graph can block for minutes; the numbers
         # are out, every rank is past the barrier, so leave without the teardown.
@@ -516,6 +516,9 @@ def run_ours(args):
         dist.barrier()
         torch.cuda.synchronize()
         os._exit(0)
+
+
+_OUT = sys.stdout
 
 
 def main():
@@ -534,6 +537,12 @@ def main():
     ap.add_argument("--no-uint8", action="store_true", help="skip the second end-to-end figure (uint8 input through GpuTransform)")
     ap.add_argument("--profile", action="store_true", help="warm up, run --steps eager steps, print a short line, exit (for ncu)")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: whatever a library prints there (NCCL announces its version on stdout under
+    # NCCL_DEBUG=VERSION, whatever NCCL_DEBUG_FILE says) goes to stderr; the line itself is written to the saved descriptor.
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
