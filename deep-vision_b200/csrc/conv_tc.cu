@@ -1731,3 +1731,518 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
 }
 
 }  // namespace dv
+
+// ============================================================================================================
+// C <= 4 stems (resnet50.py:20-28 7x7/2, mobilenet_v1.py:30 3x3/2) without a patch matrix
+// ============================================================================================================
+// The image is kept as NHWC4 bf16 with its zero border written out ([N][Hp][Wp][4], 8 bytes per pixel, `pad` pixels on the
+// left / top).  With stride 2 the window of output column q starts at padded pixel 2q = byte 16q of the row, so ONE tiled
+// tensor map with OVERLAPPING strides describes every patch row:
+//     dim0 = 32 elements (8 pixels x 4 channels: the S <= 7 taps of one filter row, the rest meets zero weights),
+//     dim1 = Q window origins, 16 bytes apart,   dim2 = image rows,   dim3 = images.
+// A box {32, Q, 1, 1} is the A operand of one filter row for one whole output row: [Q pixels][64 bytes], SWIZZLE_64B, K-major —
+// no im2col buffer in HBM, no index arithmetic on the SM.  K = R blocks of 32.
+//   fprop : D[128 px (Q used) x 64 k] += A_r [px x 32] * W_r [64 k x 32]      (filters resident in shared memory for the CTA's life)
+//   wgrad : D[128 (64 k used) x R*32] += dY^T [k x 16 px] * [X_0 | ... | X_{R-1}] [16 px x R*32]    (one MMA, N = R*32, per 16 pixels)
+namespace dv {
+namespace {
+
+constexpr int kStemWin = 32;                       // elements per filter row in the packed K layout (8 pixels x 4 channels)
+constexpr int kStemABytes = kBlockM * kStemWin * 2;  // 8 KB: 128 rows x 64 B
+constexpr int kStemMaxR = 7;
+
+__device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+          smem_u32(smem)),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* tm, uint32_t smem_addr, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_addr), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// SWIZZLE_64B descriptors: 8-row groups are 512 B apart (SBO); layout type 4
+constexpr uint32_t kDescHi64 = (512u >> 4) | (1u << 14) | (4u << 29);
+__device__ __forceinline__ uint64_t desc_pack_hi(uint32_t lo, uint32_t hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+  return d;
+}
+
+struct StemArgs {
+  int tiles;       // N * P output rows
+  int P, Q, R;
+  int Nout;        // output channels (<= 64)
+  float* stat_sums;
+  float* dw;       // wgrad, accumulate mode: packed fp32 [64][R*32], tiles are ADDED with red.global
+  float* ws;       // wgrad, fixed-order mode: [grid][64][R*32] partials
+};
+
+template <int STAGES>
+__global__ void __launch_bounds__(kThreads)
+conv_stem_fprop_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+                       const StemArgs g) {
+  constexpr int BN = 64, ACC = 2;
+  constexpr int kBRow = BN * kStemWin * 2;   // 4 KB: one filter row of all 64 output channels
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("dv conv_stem: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  uint8_t* sB = smem + STAGES * kStemABytes;
+  uint8_t* stage_out = sB + kStemMaxR * kBRow;           // 28 KB of filters, then 4 x [32 rows][128 B]
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + kEpiStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + ACC;
+  uint64_t* bfull_bar = tempty_bar + ACC;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bfull_bar + 1);
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+
+  // rows Q..127 of every A stage are never written by TMA: zero them once, so that those accumulator rows (clipped by the store,
+  // but summed into the BatchNorm statistics) are exactly zero
+  for (int i = threadIdx.x * 16; i < STAGES * kStemABytes; i += kThreads * 16) {
+    if ((i % kStemABytes) >= g.Q * 64) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0, 0, 0, 0);
+  }
+  fence_proxy_async_smem();
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmO);
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    for (int i = 0; i < ACC; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 4); }
+    mbar_init(bfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, ACC * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (elect_one()) {   // the filters: R boxes of [64 k][32], once
+      mbar_expect_tx(bfull_bar, (uint32_t)(g.R * kBRow));
+      for (int r = 0; r < g.R; ++r) tma_load_2d(sB + r * kBRow, &tmB, bfull_bar, r * kStemWin, 0);
+    }
+    __syncwarp();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < g.tiles; tile += gridDim.x) {
+      const int n = tile / g.P, p = tile - n * g.P;
+      for (int r = 0; r < g.R; ++r) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        if (elect_one()) {
+          mbar_expect_tx(&full_bar[stage], (uint32_t)(g.Q * 64));
+          tma_load_4d(smem + stage * kStemABytes, &tmA, &full_bar[stage], 0, 0, 2 * p + r, n);
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, 0);
+    const uint32_t a_lo0 = desc_lo_kmajor(smem_u32(smem));
+    const uint32_t b_lo0 = desc_lo_kmajor(smem_u32(sB));
+    mbar_wait(bfull_bar, 0);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < g.tiles; tile += gridDim.x) {
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+      for (int r = 0; r < g.R; ++r) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_lo = a_lo0 + (uint32_t)stage * (kStemABytes >> 4);
+          const uint32_t b_lo = b_lo0 + (uint32_t)r * (kBRow >> 4);
+          umma_f16(d_tmem, desc_pack_hi(a_lo, kDescHi64), desc_pack_hi(b_lo, kDescHi64), idesc, r ? 1u : 0u);
+          umma_f16(d_tmem, desc_pack_hi(a_lo + 2u, kDescHi64), desc_pack_hi(b_lo + 2u, kDescHi64), idesc, 1u);   // +32 B: the second 16 of K
+          umma_commit(&empty_bar[stage]);
+          if (r == g.R - 1) umma_commit(&tfull_bar[acc]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
+    }
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    uint8_t* my_stage = stage_out + quarter * (32 * 128);
+    const uint32_t my_stage_u32 = smem_u32(my_stage);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    float s1[2] = {0.f, 0.f}, s2[2] = {0.f, 0.f};
+    for (int tile = blockIdx.x; tile < g.tiles; tile += gridDim.x) {
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+      if (lane == 0) tma_store_wait_read();
+      __syncwarp();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_addr + (uint32_t)(half * 32), v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t w[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
+            w[e] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          const int ch = (half * 4 + j) ^ (lane & 7);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_stage_u32 + lane * 128 + ch * 16), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                       "r"(w[3])
+                       : "memory");
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&tempty_bar[acc]);                                   // every TMEM read of this warp is complete
+        if (quarter * 32 < g.Q) tma_store_3d(&tmO, my_stage_u32, 0, quarter * 32, tile);   // rows past Q are clipped by the map
+      }
+      if (g.stat_sums != nullptr) {
+        const int wch = lane >> 2, wof = (lane & 3) * 4;
+        float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+#pragma unroll 8
+        for (int r = 0; r < 32; ++r) {
+          const uint32_t word = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+          const float x0 = __uint_as_float(word << 16), x1 = __uint_as_float(word & 0xffff0000u);
+          a0 += x0; a1 += x1;
+          b0 = fmaf(x0, x0, b0); b1 = fmaf(x1, x1, b1);
+        }
+        s1[0] += a0; s1[1] += a1; s2[0] += b0; s2[1] += b1;
+      }
+      if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
+    }
+    if (g.stat_sums != nullptr) {
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int col = 2 * lane + e;
+        if (col < g.Nout) {
+          atomicAdd(g.stat_sums + col, s1[e]);
+          atomicAdd(g.stat_sums + g.Nout + col, s2[e]);
+        }
+      }
+    }
+    if (lane == 0) tma_store_wait_read();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, ACC * BN);
+}
+
+
+// Stem wgrad.  One stage = one output row (n, p): dY [Q px][64 k] (MN-major, 128 B per pixel) and the R patch rows [Q px][32]
+// (64 B per pixel, SWIZZLE_64B).  Per 16 pixels ONE MMA: D[128 x R*32] += dY^T * [X_0 | ... | X_{R-1}]; the R blocks are 8 KB
+// apart, which is the descriptor's stride between 32-column atoms.  Only 64 of the 128 accumulator rows carry filters: the
+// second 64-channel chunk of the A operand is a zero buffer shared by all stages (reached through the descriptor's chunk
+// stride), not a TMA fill.  A CTA accumulates all of its rows in TMEM and adds (or stores) its [64][R*32] tile once.
+template <int STAGES>
+__global__ void __launch_bounds__(kThreads)
+conv_stem_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const StemArgs g) {
+  constexpr int kDyBytes = 16384;                         // [<=128 px][128 B]
+  constexpr int kStageBytes = kDyBytes + kStemMaxR * kStemABytes;   // 72 KB
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("dv conv_stem: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  uint8_t* zero_chunk = smem + STAGES * kStageBytes;      // 16 KB of zeros: channels 64..127 of dY
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(zero_chunk + kDyBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  const int ncols = g.R * kStemWin;                        // 224 for the 7x7 stem
+  for (int i = threadIdx.x * 16; i < kDyBytes; i += kThreads * 16) *reinterpret_cast<uint4*>(zero_chunk + i) = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmDY);
+    prefetch_tmap(&tmX);
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const int my_tiles = (g.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;   // >= 1: the grid never exceeds the tile count
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < g.tiles; tile += gridDim.x) {
+      const int n = tile / g.P, p = tile - n * g.P;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (elect_one()) {
+        uint8_t* sDY = smem + stage * kStageBytes;
+        mbar_expect_tx(&full_bar[stage], (uint32_t)(g.Q * 128 + g.R * g.Q * 64));
+        tma_load_2d(sDY, &tmDY, &full_bar[stage], 0, tile * g.Q);
+        for (int r = 0; r < g.R; ++r) tma_load_4d(sDY + kDyBytes + r * kStemABytes, &tmX, &full_bar[stage], 0, 0, 2 * p + r, n);
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = make_idesc(128, ncols, 1, 1);
+    constexpr uint32_t kHiA = (1024u >> 4) | (1u << 14) | (2u << 29);   // dY: SWIZZLE_128B, 8-pixel groups 1 KB apart
+    constexpr uint32_t kHiB = (512u >> 4) | (1u << 14) | (4u << 29);    // X:  SWIZZLE_64B, 8-pixel groups 512 B apart
+    const int ksteps = g.Q / 16;
+    int stage = 0, it = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < g.tiles; tile += gridDim.x, ++it) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t sDY = smem_u32(smem + stage * kStageBytes);
+        const uint32_t lbo_a = (smem_u32(zero_chunk) - sDY) >> 4;       // "next 64 channels" = the zero chunk
+        const uint32_t a_lo0 = ((sDY & 0x3FFFFu) >> 4) | (lbo_a << 16);
+        const uint32_t b_lo0 = (((sDY + kDyBytes) & 0x3FFFFu) >> 4) | ((uint32_t)(kStemABytes >> 4) << 16);   // 32-column atoms 8 KB apart
+        for (int k = 0; k < ksteps; ++k)
+          umma_f16(tmem_base, desc_pack_hi(a_lo0 + (uint32_t)k * (2048u >> 4), kHiA), desc_pack_hi(b_lo0 + (uint32_t)k * (1024u >> 4), kHiB), idesc,
+                   (it == 0 && k == 0) ? 0u : 1u);
+        umma_commit(&empty_bar[stage]);
+        if (it == my_tiles - 1) umma_commit(tmem_full_bar);
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    const int quarter = warp & 3;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    if (quarter < 2) {   // accumulator rows 0..63 = the 64 filters
+      const int k = quarter * 32 + lane;
+      float* orow = (g.dw != nullptr ? g.dw : g.ws + (size_t)blockIdx.x * 64 * ncols) + (size_t)k * ncols;
+      for (int c = 0; c < ncols / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(c * 32), v);
+        tmem_ld_wait();
+        if (k < g.Nout) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (g.dw != nullptr)
+              asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(orow + c * 32 + j * 4), "f"(__uint_as_float(v[4 * j])),
+                           "f"(__uint_as_float(v[4 * j + 1])), "f"(__uint_as_float(v[4 * j + 2])), "f"(__uint_as_float(v[4 * j + 3]))
+                           : "memory");
+            else
+              *reinterpret_cast<uint4*>(orow + c * 32 + j * 4) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 256);
+}
+
+// x [N][H][W][C<=4] bf16 -> xp [N][Hp][Wp][4] bf16 with `pad` zero pixels on the left / top, zeros to the right / bottom and in
+// the unused channels.  One thread per padded pixel (8-byte store).
+__global__ void stem_pad_kernel(const bf16* __restrict__ x, bf16* __restrict__ xp, int N, int H, int W, int C, int Hp, int Wp, int pad) {
+  const int64_t total = (int64_t)N * Hp * Wp;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int wp = (int)(i % Wp);
+    const int64_t t = i / Wp;
+    const int hp = (int)(t % Hp), n = (int)(t / Hp);
+    const int h = hp - pad, w = wp - pad;
+    uint16_t v[4] = {0, 0, 0, 0};
+    if ((unsigned)h < (unsigned)H && (unsigned)w < (unsigned)W) {
+      const uint16_t* src = reinterpret_cast<const uint16_t*>(x) + (((size_t)n * H + h) * W + w) * C;
+      for (int c = 0; c < C; ++c) v[c] = src[c];
+    }
+    reinterpret_cast<uint2*>(xp)[i] = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
+  }
+}
+// fp32 KRSC filters -> bf16 [64][R][32]: wp[k][r][s*4 + c] = w[k][r][s][c], zero elsewhere (rows k >= K, taps s >= S, channels c >= C)
+__global__ void stem_pack_w_kernel(const float* __restrict__ w, bf16* __restrict__ wp, int K, int R, int S, int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 64 * R * kStemWin) return;
+  const int e = i % kStemWin, r = (i / kStemWin) % R, k = i / (kStemWin * R);
+  const int s = e >> 2, c = e & 3;
+  const float v = (k < K && s < S && c < C) ? w[(((size_t)k * R + r) * S + s) * C + c] : 0.f;
+  wp[i] = __float2bfloat16_rn(v);
+}
+// packed fp32 [splits][64][R*32] -> dW [K][R][S][C] (KRSC): sum over splits in a fixed order, drop the padding columns
+__global__ void stem_unpack_dw_kernel(const float* __restrict__ packed, float* __restrict__ dw, int splits, int K, int R, int S, int C) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= K * R * S * C) return;
+  const int c = i % C, s = (i / C) % S, r = (i / (C * S)) % R, k = i / (C * S * R);
+  const size_t col = (size_t)k * R * kStemWin + r * kStemWin + s * 4 + c, stride = (size_t)64 * R * kStemWin;
+  float acc = 0.f;
+  for (int j = 0; j < splits; ++j) acc += packed[(size_t)j * stride + col];
+  dw[i] = acc;
+}
+
+struct StemGeom {
+  int P, Q, Hp, Wp;
+};
+static bool stem_geometry(const dv_stem_params* p, StemGeom* gm, const char** why) {
+  *why = "";
+  if (p->C < 1 || p->C > 4) { *why = "C must be 1..4"; return false; }
+  if (p->stride != 2) { *why = "stride must be 2 (the window origin advances by 16 bytes)"; return false; }
+  if (p->R < 1 || p->R > kStemMaxR || p->S < 1 || p->S > 7) { *why = "filter larger than 7x7"; return false; }
+  if (p->K < 8 || p->K > 64 || p->K % 8) { *why = "K must be a multiple of 8, at most 64"; return false; }
+  if (p->pad < 0 || p->pad > 7) { *why = "bad pad"; return false; }
+  gm->P = (p->H + 2 * p->pad - p->R) / 2 + 1;
+  gm->Q = (p->W + 2 * p->pad - p->S) / 2 + 1;
+  if (gm->Q < 16 || gm->Q > 128 || gm->Q % 16) { *why = "output width must be a multiple of 16, at most 128"; return false; }
+  gm->Wp = p->pad + p->W;
+  if (gm->Wp < 2 * (gm->Q - 1) + 8) gm->Wp = 2 * (gm->Q - 1) + 8;
+  gm->Wp += gm->Wp & 1;                                      // row pitch a multiple of 16 bytes
+  gm->Hp = p->pad + p->H;
+  if (gm->Hp < 2 * (gm->P - 1) + p->R) gm->Hp = 2 * (gm->P - 1) + p->R;
+  if ((int64_t)p->N * gm->P >= (1LL << 31) / 128) { *why = "too many output rows"; return false; }
+  return true;
+}
+// the sliding-window map over the padded image (see the section header)
+static int make_map_stem_x(CUtensorMap* tm, const void* xp, int N, const StemGeom& gm) {
+  const MapKey key{{4, (uint64_t)(uintptr_t)xp, (uint64_t)N, (uint64_t)gm.Hp, (uint64_t)gm.Wp, (uint64_t)gm.Q}};
+  if (map_cache_get(key, tm)) return DV_OK;
+  DriverApi& api = driver_api();
+  DV_REQUIRE(api.ok, DV_ERR_CUDA, "conv_stem: cuTensorMapEncode* entry points not available from the driver");
+  cuuint64_t dims[4] = {(cuuint64_t)kStemWin, (cuuint64_t)gm.Q, (cuuint64_t)gm.Hp, (cuuint64_t)N};
+  cuuint64_t strides[3] = {16, (cuuint64_t)gm.Wp * 8, (cuuint64_t)gm.Hp * gm.Wp * 8};
+  cuuint32_t box[4] = {(cuuint32_t)kStemWin, (cuuint32_t)gm.Q, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = api.tiled(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(xp), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DV_REQUIRE(r == CUDA_SUCCESS, DV_ERR_CUDA, "cuTensorMapEncodeTiled(stem image) failed (%d) N=%d Hp=%d Wp=%d Q=%d", (int)r, N, gm.Hp, gm.Wp, gm.Q);
+  map_cache_put(key, *tm);
+  return DV_OK;
+}
+
+}  // namespace
+}  // namespace dv
+
+using namespace dv;
+
+extern "C" int dv_stem_supported(const dv_stem_params* p, int* Hp, int* Wp) {
+  if (!p) return 0;
+  StemGeom gm;
+  const char* why;
+  if (!stem_geometry(p, &gm, &why)) return 0;
+  if (Hp) *Hp = gm.Hp;
+  if (Wp) *Wp = gm.Wp;
+  return 1;
+}
+
+extern "C" int dv_stem_pad_input(const dv_stem_params* p, const void* x_nhwc, void* stream) {
+  DV_REQUIRE(p && x_nhwc && p->x, DV_ERR_ARG, "dv_stem_pad_input: null pointer");
+  StemGeom gm;
+  const char* why;
+  DV_REQUIRE(stem_geometry(p, &gm, &why), DV_ERR_UNSUPPORTED, "dv_stem_pad_input: %s", why);
+  DV_REQUIRE(aligned16(p->x), DV_ERR_ARG, "dv_stem_pad_input: the padded image must be 16-byte aligned");
+  const int64_t total = (int64_t)p->N * gm.Hp * gm.Wp;
+  const unsigned grid = (unsigned)(ceil_div64(total, 256) < (int64_t)num_sms() * 16 ? ceil_div64(total, 256) : (int64_t)num_sms() * 16);
+  stem_pad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x_nhwc, (bf16*)p->x, p->N, p->H, p->W, p->C, gm.Hp, gm.Wp, p->pad);
+  DV_LAUNCH_OK("stem_pad_kernel");
+  return DV_OK;
+}
+
+extern "C" int dv_stem_pack_filters(const dv_stem_params* p, const float* w_krsc, void* stream) {
+  DV_REQUIRE(p && w_krsc && p->w, DV_ERR_ARG, "dv_stem_pack_filters: null pointer");
+  StemGeom gm;
+  const char* why;
+  DV_REQUIRE(stem_geometry(p, &gm, &why), DV_ERR_UNSUPPORTED, "dv_stem_pack_filters: %s", why);
+  const int n = 64 * p->R * kStemWin;
+  stem_pack_w_kernel<<<ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(w_krsc, (bf16*)p->w, p->K, p->R, p->S, p->C);
+  DV_LAUNCH_OK("stem_pack_w_kernel");
+  return DV_OK;
+}
+
+extern "C" int dv_stem_fprop(const dv_stem_params* p, void* stream) {
+  DV_REQUIRE(p && p->x && p->w && p->y, DV_ERR_ARG, "dv_stem_fprop: null pointer");
+  StemGeom gm;
+  const char* why;
+  DV_REQUIRE(stem_geometry(p, &gm, &why), DV_ERR_UNSUPPORTED, "dv_stem_fprop: %s", why);
+  DV_REQUIRE(aligned16(p->x) && aligned16(p->w) && aligned16(p->y), DV_ERR_ARG, "dv_stem_fprop: pointers must be 16-byte aligned");
+  alignas(64) CUtensorMap tmA, tmB, tmO;
+  int rc = make_map_stem_x(&tmA, p->x, p->N, gm);
+  if (rc) return rc;
+  DriverApi& api = driver_api();
+  {  // filters [64][R*32] bf16, box {32, 64}, SWIZZLE_64B
+    cuuint64_t dims[2] = {(cuuint64_t)p->R * kStemWin, 64};
+    cuuint64_t strides[1] = {(cuuint64_t)p->R * kStemWin * 2};
+    cuuint32_t box[2] = {(cuuint32_t)kStemWin, 64}, estr[2] = {1, 1};
+    CUresult r = api.tiled(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p->w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DV_REQUIRE(r == CUDA_SUCCESS, DV_ERR_CUDA, "cuTensorMapEncodeTiled(stem filters) failed (%d)", (int)r);
+  }
+  {  // output [N*P][Q][K] bf16, box {64, 32, 1}: a warp's 32 pixels of one output row; pixels past Q and channels past K are clipped
+    cuuint64_t dims[3] = {(cuuint64_t)p->K, (cuuint64_t)gm.Q, (cuuint64_t)p->N * gm.P};
+    cuuint64_t strides[2] = {(cuuint64_t)p->K * 2, (cuuint64_t)gm.Q * p->K * 2};
+    cuuint32_t box[3] = {64, 32, 1}, estr[3] = {1, 1, 1};
+    CUresult r = api.tiled(&tmO, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, p->y, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DV_REQUIRE(r == CUDA_SUCCESS, DV_ERR_CUDA, "cuTensorMapEncodeTiled(stem output) failed (%d) K=%d Q=%d", (int)r, p->K, gm.Q);
+  }
+  StemArgs g{};
+  g.tiles = p->N * gm.P; g.P = gm.P; g.Q = gm.Q; g.R = p->R; g.Nout = p->K; g.stat_sums = p->stat_sums;
+  constexpr int STAGES = 8;
+  constexpr int smem = STAGES * kStemABytes + kStemMaxR * 64 * kStemWin * 2 + kEpiStageBytes + 256;
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_stem_fprop_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_stem_fprop_kernel<STAGES>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  const int slots = 2 * num_sms();
+  conv_stem_fprop_kernel<STAGES><<<g.tiles < slots ? g.tiles : slots, kThreads, smem, (cudaStream_t)stream>>>(tmA, tmB, tmO, g);
+  DV_LAUNCH_OK("conv_stem_fprop_kernel");
+  return DV_OK;
+}
+
+extern "C" size_t dv_stem_workspace_bytes(const dv_stem_params* p) {
+  StemGeom gm;
+  const char* why;
+  if (!p || !stem_geometry(p, &gm, &why)) return 0;
+  const int tiles = p->N * gm.P;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  return (size_t)(p->accumulate ? 1 : grid) * 64 * p->R * kStemWin * sizeof(float);
+}
+
+extern "C" int dv_stem_wgrad(const dv_stem_params* p, void* stream) {
+  DV_REQUIRE(p && p->x && p->y && p->dw, DV_ERR_ARG, "dv_stem_wgrad: null pointer");
+  StemGeom gm;
+  const char* why;
+  DV_REQUIRE(stem_geometry(p, &gm, &why), DV_ERR_UNSUPPORTED, "dv_stem_wgrad: %s", why);
+  const size_t need = dv_stem_workspace_bytes(p);
+  DV_REQUIRE(p->workspace && p->workspace_bytes >= need && aligned16(p->workspace), DV_ERR_WORKSPACE,
+             "dv_stem_wgrad: workspace of %zu bytes required, %zu given", need, p->workspace_bytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  alignas(64) CUtensorMap tmDY, tmX;
+  int rc = make_map_2d(&tmDY, p->y, (uint64_t)p->N * gm.P * gm.Q, (uint64_t)p->K, (uint32_t)gm.Q);
+  if (rc) return rc;
+  rc = make_map_stem_x(&tmX, p->x, p->N, gm);
+  if (rc) return rc;
+  StemArgs g{};
+  g.tiles = p->N * gm.P; g.P = gm.P; g.Q = gm.Q; g.R = p->R; g.Nout = p->K;
+  const int grid = g.tiles < num_sms() ? g.tiles : num_sms();
+  const int splits = p->accumulate ? 1 : grid;
+  if (p->accumulate) {   // one packed tile that every CTA adds into; the caller's dw is then updated by the unpack pass below
+    DV_CUDA_OK(cudaMemsetAsync(p->workspace, 0, (size_t)64 * p->R * kStemWin * sizeof(float), st));
+    g.dw = (float*)p->workspace;
+  } else {
+    g.ws = (float*)p->workspace;
+  }
+  constexpr int STAGES = 2;
+  constexpr int smem = STAGES * (16384 + kStemMaxR * kStemABytes) + 16384 + 256;
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_stem_wgrad_kernel<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  conv_stem_wgrad_kernel<STAGES><<<grid, kThreads, smem, st>>>(tmDY, tmX, g);
+  DV_LAUNCH_OK("conv_stem_wgrad_kernel");
+  const int n = p->K * p->R * p->S * p->C;
+  stem_unpack_dw_kernel<<<ceil_div(n, 256), 256, 0, st>>>((const float*)p->workspace, p->dw, splits, p->K, p->R, p->S, p->C);
+  DV_LAUNCH_OK("stem_unpack_dw_kernel");
+  return DV_OK;
+}

@@ -29,6 +29,15 @@ class ConvParams(C.Structure):
     ]
 
 
+class StemParams(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p), ("dw", C.c_void_p), ("stat_sums", C.c_void_p),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("K", C.c_int32),
+        ("R", C.c_int32), ("S", C.c_int32), ("stride", C.c_int32), ("pad", C.c_int32), ("accumulate", C.c_int32),
+    ]
+
+
 class DwConvParams(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p),
@@ -89,6 +98,12 @@ _SIG = {
     "dv_im2col": (C.c_int, [_P, _P] + [C.c_int] * 10 + [_P]),
     "dv_pad_rows": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "dv_unpad_rows": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
+    "dv_stem_supported": (C.c_int, [C.POINTER(StemParams), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "dv_stem_pad_input": (C.c_int, [C.POINTER(StemParams), _P, _P]),
+    "dv_stem_pack_filters": (C.c_int, [C.POINTER(StemParams), _P, _P]),
+    "dv_stem_fprop": (C.c_int, [C.POINTER(StemParams), _P]),
+    "dv_stem_wgrad": (C.c_int, [C.POINTER(StemParams), _P]),
+    "dv_stem_workspace_bytes": (C.c_size_t, [C.POINTER(StemParams)]),
     "dv_dwconv_fprop": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_dgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_wgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),

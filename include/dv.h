@@ -139,6 +139,31 @@ int dv_pad_rows(const float* src, void* dst, int rows, int cols, int dst_pitch, 
 /* dst[r, 0:cols] = src[r, 0:cols] with src row pitch src_pitch (fp32 -> fp32) */
 int dv_unpad_rows(const float* src, float* dst, int rows, int cols, int src_pitch, void* stream);
 
+/* The same stems WITHOUT a patch matrix (tensor-core path, bf16): the image is kept as NHWC4 with its zero border written out
+ * (dv_stem_pad_input: [N][Hp][Wp][4] bf16, 8 bytes per pixel) and every patch row is one TMA box of a tensor map with
+ * overlapping strides (window origins 16 bytes = one stride-2 step apart), so fprop and wgrad read the 100 MB image where the
+ * patch-matrix path writes and re-reads 1.2 GB.  Requirements: C <= 4, stride 2, R,S <= 7, K a multiple of 8 and <= 64, output
+ * width Q a multiple of 16 and <= 128 (dv_stem_supported answers 1 and the padded extents).  wgrad writes dw = the gradient
+ * (never accumulates into dw itself); `accumulate` only picks how CTA tiles are combined: 1 = fp32 atomics (run-to-run order),
+ * 0 = per-CTA partials in the workspace + fixed-order sum.  Replaces nn.Conv2d at resnet50.py:20-28, mobilenet_v1.py:30. */
+typedef struct dv_stem_params {
+  void* x;            /* padded image [N][Hp][Wp][4] bf16: out of dv_stem_pad_input, in of fprop / wgrad */
+  void* w;            /* packed filters [64][R][32] bf16: out of dv_stem_pack_filters, in of fprop */
+  void* y;            /* fprop: out [N,P,Q,K] bf16; wgrad: dy in */
+  float* dw;          /* wgrad: out, fp32 KRSC [K][R][S][C] */
+  float* stat_sums;   /* fprop, optional: as dv_conv_params.stat_sums */
+  void* workspace;    /* wgrad: dv_stem_workspace_bytes() */
+  size_t workspace_bytes;
+  int32_t N, H, W, C, K, R, S, stride, pad;
+  int32_t accumulate;
+} dv_stem_params;
+int dv_stem_supported(const dv_stem_params* p, int* Hp, int* Wp);
+int dv_stem_pad_input(const dv_stem_params* p, const void* x_nhwc, void* stream);   /* x_nhwc: [N,H,W,C] bf16 */
+int dv_stem_pack_filters(const dv_stem_params* p, const float* w_krsc, void* stream);
+int dv_stem_fprop(const dv_stem_params* p, void* stream);
+int dv_stem_wgrad(const dv_stem_params* p, void* stream);
+size_t dv_stem_workspace_bytes(const dv_stem_params* p);
+
 /* ------------------------------------------------------------------------------------------
  * Depth-wise 3x3 convolution, pad 1, stride 1 or 2, groups == C.
  * Replaces nn.Conv2d(C, C, 3, padding=1, stride, groups=C, bias=False) at mobilenet_v1.py:112-122.

@@ -478,3 +478,73 @@ def test_tc_dgrad_bn_sums_rejects_what_it_cannot_fuse():
     assert lib.lib.dv_conv_fprop(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED       # dgrad only
     p.bnb_dbeta = None
     assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_ARG
+
+
+STEM_CASES = [
+    # N, H, W, C, K, R, pad          stride 2
+    (2, 64, 64, 3, 64, 7, 3),       # ResNet stem geometry, Q = 32
+    (3, 96, 64, 3, 64, 7, 3),       # H != W (P = 48, Q = 32)
+    (2, 64, 96, 3, 32, 3, 1),       # MobileNet stem: 3x3, K = 32, Q = 48
+    (1, 32, 224, 4, 64, 7, 3),      # full output width Q = 112, C = 4
+    (5, 20, 32, 3, 16, 5, 2),       # Q = 16, odd-sized everything else
+]
+
+
+@pytest.mark.parametrize("case", STEM_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_stem_direct_convolution_matches_oracle(case):
+    """dv_stem_*: the C <= 4 stride-2 stems on the tensor cores straight from the padded NHWC4 image (sliding-window tensor map),
+    fprop with fused BatchNorm sums and wgrad in both reduction modes, against the numpy oracle."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, H, W, Cc, K, R, pad = case
+    x = _rand((N, Cc, H, W), 1, BF)
+    w = _rand((K, Cc, R, R), 2, BF, scale=0.1)
+    y_ref = ref_ops.conv2d(x, w, 2, pad)
+    dy = _rand(y_ref.shape, 3, BF)
+    _, dw_ref = ref_ops.conv2d_backward(x, w, dy, 2, pad)
+    P, Q = y_ref.shape[2], y_ref.shape[3]
+    xd = torch.from_numpy(x.transpose(0, 2, 3, 1).copy()).cuda().to(BF)
+    wd = torch.from_numpy(w.transpose(0, 2, 3, 1).copy()).cuda().float().contiguous()        # fp32 KRSC master filters
+    dyd = torch.from_numpy(dy.transpose(0, 2, 3, 1).copy()).cuda().to(BF)
+    p = lib.StemParams()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad = N, H, W, Cc, K, R, R, 2, pad
+    hp, wp = C.c_int(0), C.c_int(0)
+    assert lib.lib.dv_stem_supported(C.byref(p), C.byref(hp), C.byref(wp)) == 1
+    xp = torch.full((N, hp.value, wp.value, 4), float("nan"), device="cuda", dtype=BF)
+    wpk = torch.full((64, R, 32), float("nan"), device="cuda", dtype=BF)
+    y = torch.full((N, P, Q, K), float("nan"), device="cuda", dtype=BF)
+    sums = torch.zeros(2 * K, device="cuda")
+    p.x, p.w, p.y, p.stat_sums = xp.data_ptr(), wpk.data_ptr(), y.data_ptr(), sums.data_ptr()
+    lib.check(lib.lib.dv_stem_pad_input(C.byref(p), xd.data_ptr(), stream_ptr()), "pad")
+    lib.check(lib.lib.dv_stem_pack_filters(C.byref(p), wd.data_ptr(), stream_ptr()), "pack")
+    lib.check(lib.lib.dv_stem_fprop(C.byref(p), stream_ptr()), "stem fprop")
+    torch.cuda.synchronize()
+    got = y.double().cpu().numpy().transpose(0, 3, 1, 2)
+    assert np.isfinite(got).all()
+    assert rel_l2(got, y_ref) < 2e-2
+    assert np.max(np.abs(got - y_ref) / (np.abs(y_ref) + 1e-2)) < 2e-2
+    yb = y.double().reshape(-1, K)
+    assert rel_l2(sums[:K].double().cpu().numpy(), yb.sum(0).cpu().numpy()) < 1e-4
+    assert rel_l2(sums[K:].double().cpu().numpy(), (yb * yb).sum(0).cpu().numpy()) < 1e-4
+    for accumulate in (0, 1):
+        dw = torch.full((K, R, R, Cc), float("nan"), device="cuda")
+        p.y, p.dw, p.accumulate = dyd.data_ptr(), dw.data_ptr(), accumulate
+        ws = torch.empty(max(lib.lib.dv_stem_workspace_bytes(C.byref(p)), 16), dtype=torch.uint8, device="cuda")
+        p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+        for _ in range(2):      # twice: the result replaces dw, it is not added to it
+            lib.check(lib.lib.dv_stem_wgrad(C.byref(p), stream_ptr()), "stem wgrad")
+        torch.cuda.synchronize()
+        assert rel_l2(dw.double().cpu().numpy().transpose(0, 3, 1, 2), dw_ref) < 1e-4, accumulate
+
+
+def test_stem_direct_rejects_other_geometries():
+    import ctypes as C
+    lib = _lib()
+    p = lib.StemParams()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad = 2, 64, 64, 3, 64, 7, 7, 2, 3
+    assert lib.lib.dv_stem_supported(C.byref(p), None, None) == 1
+    for field, bad in (("stride", 1), ("C", 8), ("K", 128), ("R", 9), ("W", 60)):     # W = 60 -> Q = 30, not a multiple of 16
+        q = lib.StemParams.from_buffer_copy(p)
+        setattr(q, field, bad)
+        assert lib.lib.dv_stem_supported(C.byref(q), None, None) == 0, field
