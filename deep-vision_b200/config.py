@@ -10,7 +10,8 @@ _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
           "atomic_bn_bwd": os.environ.get("DV_ATOMIC_BN", "0") == "1",
           "fold_bn": os.environ.get("DV_FOLD_BN", "1") != "0",
           "side_wgrad": os.environ.get("DV_SIDE_WGRAD", "1") == "1",
-          "fuse_bn_bwd": os.environ.get("DV_FUSE_BN_BWD", "1") == "1"}
+          "fuse_bn_bwd": os.environ.get("DV_FUSE_BN_BWD", "1") == "1",
+          "stem_direct": os.environ.get("DV_STEM_DIRECT", "1") == "1"}
 
 
 def compute_dtype():
@@ -100,3 +101,12 @@ def fuse_bn_bwd():
 
 def set_fuse_bn_bwd(flag):
     _state["fuse_bn_bwd"] = bool(flag)
+
+
+def stem_direct():
+    """C <= 4 stride-2 stems run straight from a padded NHWC4 image (dv_stem_*) instead of through a patch matrix."""
+    return _state["stem_direct"]
+
+
+def set_stem_direct(flag):
+    _state["stem_direct"] = bool(flag)

@@ -11,7 +11,7 @@ import torch
 
 from . import config
 from .lib import (DV_ALGO_AUTO, DV_ALGO_SIMT, DV_ALGO_TC, DV_BF16, DV_CONV_DGRAD, DV_CONV_FPROP, DV_CONV_WGRAD, DV_F32,
-                  BnBwdParams, BnParams, ConvParams, DwConvParams, check, lib)
+                  BnBwdParams, BnParams, ConvParams, DwConvParams, StemParams, check, lib)
 
 _CL = torch.channels_last
 
@@ -106,6 +106,22 @@ class FilterCache:
         self.pad_key = None
         self.w_pad = None
         self.external = None   # (dtype, tensor): a copy some other kernel keeps current (the trainer's fused optimiser)
+        self.stem_key = None
+        self.w_stem = None
+
+    def get_stem(self, weight, sp):
+        """[64][R][32] bf16 filters in the packed K layout of the direct stem kernels (dv_stem_pack_filters)."""
+        key = (weight.data_ptr(), weight._version, config.weight_epoch(), weight.device)
+        if key != self.stem_key:
+            wm = weight.detach()
+            if not wm.is_contiguous(memory_format=_CL):
+                wm = wm.contiguous(memory_format=_CL)
+            if self.w_stem is None or self.w_stem.device != weight.device:
+                self.w_stem = torch.empty((64, weight.shape[2], 32), dtype=torch.bfloat16, device=weight.device)
+            sp.w = self.w_stem.data_ptr()
+            check(lib.dv_stem_pack_filters(C.byref(sp), wm.data_ptr(), _stream()), "dv_stem_pack_filters")
+            self.stem_key = key
+        return self.w_stem
 
     def get_padded(self, weight, dtype, kp):
         """[K][Kp] compute-dtype filters (rows zero-padded from R*S*C to Kp) for the patch-matrix path of the stems."""
@@ -264,8 +280,30 @@ class _Conv2d(torch.autograd.Function):
         Q = (W + 2 * pad - S) // stride + 1
         dt = _dv_dtype(x.dtype)
         y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
-        # C=3 stems (resnet50.py:20-28, mobilenet_v1.py:30): explicit patch matrix + the tensor-core 1x1 path
+        # C=3 stems (resnet50.py:20-28, mobilenet_v1.py:30).  Direct path: padded NHWC4 image + sliding-window tensor map
+        # (dv_stem_*); the 100 MB image is also what the backward pass keeps.
         ctx.patches = None
+        ctx.stem = None
+        if (x.dtype == torch.bfloat16 and algo != DV_ALGO_SIMT and Cc <= 4 and config.stem_direct() and not ctx.needs_input_grad[0]):
+            sp = StemParams()
+            sp.N, sp.H, sp.W, sp.C, sp.K, sp.R, sp.S, sp.stride, sp.pad = N, H, W, Cc, K, R, S, stride, pad
+            hp, wp = C.c_int(0), C.c_int(0)
+            if lib.dv_stem_supported(C.byref(sp), C.byref(hp), C.byref(wp)) == 1:
+                xp = torch.empty((N, hp.value, wp.value, 4), dtype=x.dtype, device=x.device)
+                sp.x = xp.data_ptr()
+                check(lib.dv_stem_pad_input(C.byref(sp), x.data_ptr(), _stream()), "dv_stem_pad_input")
+                w_stem = cache.get_stem(weight, sp)
+                sp.w, sp.y = w_stem.data_ptr(), y.data_ptr()
+                if stats is not None:
+                    if stats.pending:
+                        stats.t.zero_()
+                    sp.stat_sums = stats.t.data_ptr()
+                    stats.pending = True
+                check(lib.dv_stem_fprop(C.byref(sp), _stream()), "dv_stem_fprop")
+                ctx.save_for_backward(xp, weight)
+                ctx.stem = (N, H, W, Cc, stride, pad)
+                ctx.geom = (stride, pad, algo)
+                return y
         if (x.dtype == torch.bfloat16 and algo != DV_ALGO_SIMT and Cc < 16 and R * S * Cc <= 256 and K % 8 == 0
                 and not ctx.needs_input_grad[0]):
             kp = -(-(R * S * Cc) // 64) * 64
@@ -299,6 +337,31 @@ class _Conv2d(torch.autograd.Function):
         K, _, R, S = weight.shape
         dt = _dv_dtype(x.dtype)
         dx = dw = None
+        if ctx.stem is not None:
+            if ctx.needs_input_grad[1]:
+                N, H, W, Cc, _, _ = ctx.stem
+                sink = grad_sink(weight)
+                dw = sink[0] if sink else torch.empty((K, Cc, R, S), dtype=torch.float32, device=x.device, memory_format=_CL)
+                sp = StemParams()
+                sp.N, sp.H, sp.W, sp.C, sp.K, sp.R, sp.S, sp.stride, sp.pad = N, H, W, Cc, K, R, S, stride, pad
+                sp.x, sp.y, sp.dw = x.data_ptr(), dy.data_ptr(), dw.data_ptr()
+                sp.accumulate = 1 if config.atomic_wgrad() else 0
+
+                def launch():
+                    ws = _workspace(lib.dv_stem_workspace_bytes(C.byref(sp)), x.device)
+                    sp.workspace, sp.workspace_bytes = ws.data_ptr(), ws.numel()
+                    check(lib.dv_stem_wgrad(C.byref(sp), _stream()), "dv_stem_wgrad")
+
+                side = _side_wgrad["obj"] if (sink and sp.accumulate) else None
+                if side is not None:
+                    with torch.cuda.stream(side.fork(x, dy)):
+                        launch()
+                else:
+                    launch()
+                if sink:
+                    sink[1](weight)
+                    dw = None
+            return None, dw, None, None, None, None, None, None, None, None
         if ctx.patches is not None:
             M, kp, N, Cc, H, W = ctx.patches
             if ctx.needs_input_grad[1]:

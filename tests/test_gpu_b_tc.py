@@ -221,15 +221,18 @@ def test_tc_full_size_against_cuda_core_kernel_and_properties(case):
     assert rel_l2(nchw(dw2), dw_or) < 1e-4, "full-size wgrad (two-image partial) vs oracle"
 
 
+@pytest.mark.parametrize("size", [30, 64], ids=["patch_matrix_path", "direct_path"])
 @pytest.mark.parametrize("geom", [(7, 2, 3, 64), (3, 2, 1, 32)], ids=["resnet_stem_7x7", "mobilenet_stem_3x3"])
-def test_stem_conv_module_matches_oracle(geom):
-    """The C=3 stems through the product's nn.Conv2d (patch matrix + tcgen05 GEMM, wgrad through the tensor cores)."""
+def test_stem_conv_module_matches_oracle(geom, size):
+    """The C=3 stems through the product's nn.Conv2d: 64x64 images take the direct path (dv_stem_*, output width a multiple of
+    16), 30x30 ones the patch matrix + tcgen05 GEMM; wgrad through the tensor cores either way."""
     import deep_vision_b200 as dv
+    from deep_vision_b200.lib import lib as _l
     R, stride, pad, K = geom
     dv.set_compute_dtype(torch.bfloat16)
     torch.manual_seed(3)
     conv = dv.nn.Conv2d(3, K, R, stride=stride, padding=pad, bias=False).cuda()
-    x = torch.randn(4, 3, 30, 30)
+    x = torch.randn(4, 3, size, size)
     xr = bf16_round(x.numpy())
     wr = bf16_round(conv.weight.detach().cpu().numpy())
     y_ref = ref_ops.conv2d(xr, wr, stride, pad)
