@@ -189,6 +189,7 @@ def test_folded_batchnorm_inference_matches_unfused_and_golden(name):
     y_fold, n_fold = run()
     dv.set_fold_bn(False)
     try:
+        run()                               # (first unfused call packs the stem's filters once)
         y_plain, n_plain = run()
     finally:
         dv.set_fold_bn(True)

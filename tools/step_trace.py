@@ -61,6 +61,7 @@ for e in ev:
     agg[k][0] += 1
     agg[k][1] += e.time_range.end - e.time_range.start
 rows = sorted(agg.items(), key=lambda kv: -kv[1][1])
+os.makedirs(os.path.dirname(args.out) or ".", exist_ok=True)
 with open(args.out, "w") as f:
     f.write(f"# In-step kernel timeline, {args.model} batch {args.batch} bf16, CUDA graph, {STEPS} steps averaged (CUPTI), rank 0 of {world}\n\n")
     f.write(f"span per step {span / 1e3:.3f} ms, kernels busy {busy / 1e3:.3f} ms, idle between kernels {(span - busy) / 1e3:.3f} ms "
