@@ -287,7 +287,6 @@ struct GemmArgs {
   // epilogue fetches the matching x0 tile (tensor map tmR), recomputes the ReLU mask exactly as bn_apply computed it and adds
   //   dbeta[c] += sum_m dz,   dgamma[c] += invstd[c] * sum_m dz * (x0 - mean[c]),   dz = dx * (relu'(bn(x0)))
   // which is all that BatchNorm's backward reduce pass (4 bytes per element of HBM traffic) would have produced.
-  int b_resident;   // pair kernel: the CTA keeps its half of the filter tile (all K blocks, <= 64 KB) in shared memory for its whole life
   const float* bnb_gamma;
   const float* bnb_beta;
   const float* bnb_mean;
@@ -744,14 +743,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
   uint64_t* res_bar = tempty_bar + ACC;  // one per epilogue warp: the identity tile of a folded-BN epilogue has landed
-  uint64_t* bres_bar = res_bar + 4;      // the resident filter half-tiles of both CTAs have landed (CTA 0's copy is the one waited on)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bres_bar + 1);
-  // Resident filters (g.b_resident): short-K layers (1x1, C <= 256) spend their L2->SM bandwidth re-fetching the SAME 128 x K filter
-  // half-tile for every 256-pixel tile (ncu: 206 MB of L2->SM traffic for 70 MB of DRAM traffic on 256->1024 @14).  A cluster keeps
-  // one n tile for its whole life, so the half-tile is loaded once behind the A ring (stages then hold activations only).
-  const bool bres = g.b_resident != 0;
-  const uint32_t stage_stride = bres ? (uint32_t)kABytes : (uint32_t)kStageBytes;
-  uint8_t* sBres = smem + STAGES * kABytes;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 4);
 
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -774,7 +766,6 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps of each CTA (used in CTA 0 only)
     }
     for (int i = 0; i < 4; ++i) mbar_init(&res_bar[i], 1);
-    mbar_init(bres_bar, 2);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc_pair(tmem_ptr, kTmemCols);
@@ -784,26 +775,6 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   const uint32_t tmem_base = *tmem_ptr;
 
   if (warp == 0) {
-    if (bres) {
-      if (elect_one()) {
-        const int n_tile = cluster_id % num_n;   // fixed: the host sizes the grid so that num_clusters % num_n == 0
-        if (rank == 0) mbar_expect_tx(bres_bar, (uint32_t)(2 * num_kb * kBHalfBytes));
-        int tap = 0, cb = 0;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          uint8_t* sB = sBres + kb * kBHalfBytes;
-          if (B_MN) {
-#pragma unroll
-            for (int j = 0; j < 2; ++j)
-              tma_load_2d_pair(sB + j * 8192, &tmB, bres_bar, (g.taps - 1 - tap) * g.Nout + n_tile * BN + (int)rank * 128 + j * 64, cb * kBlockK);
-          } else {
-            tma_load_2d_pair(sB, &tmB, bres_bar, tap * g.Cin + cb * kBlockK, n_tile * BN + (int)rank * 128);
-          }
-          if (++cb == g.kb_per_tap) { cb = 0; ++tap; }
-        }
-        if (rank != 0) mbar_arrive_remote(bres_bar, 0);
-      }
-      __syncwarp();
-    }
     int stage = 0;
     uint32_t phase = 0;
     for (int pair = cluster_id; pair < total_pairs; pair += num_clusters) {
@@ -822,18 +793,16 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         if (elect_one()) {
-          uint8_t* sA = smem + stage * stage_stride;
+          uint8_t* sA = smem + stage * kStageBytes;
           uint8_t* sB = sA + kABytes;
-          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * stage_stride);
+          if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);
           if (g.a_im2col) {
             const int r = tap / g.S, s = tap - r * g.S;
             tma_load_im2col_pair(sA, &tmA, &full_bar[stage], cb * kBlockK, w0, h0, n_img, (uint16_t)s, (uint16_t)r);
           } else {
             tma_load_2d_pair(sA, &tmA, &full_bar[stage], cb * kBlockK, m0);
           }
-          if (bres) {
-            // filters are resident
-          } else if (B_MN) {
+          if (B_MN) {
             // this CTA's 128 output columns = two [64 k][64 c] boxes of the KRSC filters (flipped tap)
 #pragma unroll
             for (int j = 0; j < 2; ++j)
@@ -855,10 +824,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       constexpr uint32_t kStageStep = kStageBytes >> 4;
       constexpr uint32_t kBStep = B_MN ? (2048u >> 4) : 2u;
       const uint32_t a_lo0 = desc_lo_kmajor(smem_u32(smem));
-      const uint32_t b_base = bres ? smem_u32(sBres) : smem_u32(smem) + kABytes;
-      const uint32_t b_lo0 = B_MN ? desc_lo_mnmajor(b_base) : desc_lo_kmajor(b_base);
-      const uint32_t a_step = stage_stride >> 4;
-      if (bres) mbar_wait(bres_bar, 0);
+      const uint32_t b_lo0 = B_MN ? desc_lo_mnmajor(smem_u32(smem) + kABytes) : desc_lo_kmajor(smem_u32(smem) + kABytes);
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
       for (int pair = cluster_id; pair < total_pairs; pair += num_clusters) {
@@ -869,8 +835,8 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           if (elect_one()) {
-            const uint32_t a_lo = a_lo0 + (uint32_t)stage * a_step;
-            const uint32_t b_lo = b_lo0 + (bres ? (uint32_t)kb * (uint32_t)(kBHalfBytes >> 4) : (uint32_t)stage * kStageStep);
+            const uint32_t a_lo = a_lo0 + (uint32_t)stage * kStageStep;
+            const uint32_t b_lo = b_lo0 + (uint32_t)stage * kStageStep;
             umma_f16_pair(d_tmem, desc_pack(a_lo), desc_pack(b_lo), idesc, kb ? 1u : 0u);
 #pragma unroll
             for (int k = 1; k < kBlockK / 16; ++k)
@@ -1375,11 +1341,7 @@ static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
   int clusters = num_sms() / 2;
   if (clusters > num_n) clusters -= clusters % num_n;
   if (clusters > pairs) clusters = pairs;
-  GemmArgs ga = g;
-  static const int bres_enabled = getenv("DV_TC_BRES") ? atoi(getenv("DV_TC_BRES")) : 1;
-  // resident filters: every K block of the CTA's half-tile fits behind the (then 16 KB) stages, and a cluster never changes its n tile
-  ga.b_resident = (bres_enabled && STAGES >= 6 && g.taps * g.kb_per_tap <= 4 && clusters % num_n == 0) ? 1 : 0;   // 6 x 16 KB of A + 4 x 16 KB of B inside the ring's 192 KB
-  conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, ga);  // __cluster_dims__(2,1,1)
+  conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
   DV_LAUNCH_OK("conv_tc_gemm_pair_kernel");
   return DV_OK;
 }
