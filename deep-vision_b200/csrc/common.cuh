@@ -101,5 +101,10 @@ int conv_simt(const dv_conv_params* p, int pass, cudaStream_t st);
 int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st);
 bool conv_tc_supported(const dv_conv_params* p, int pass, const char** why);
 size_t conv_tc_workspace(const dv_conv_params* p, int pass);
+// bf16 tiled tensor map (encoded through the driver entry point conv_tc.cu resolves): `tm` points at a 64-byte aligned CUtensorMap,
+// dims in elements (innermost first), strides in bytes for dims 1..rank-1, swizzle 0 = none, 1 = 32 B, 2 = 64 B, 3 = 128 B.
+// Out-of-range box elements read as zero.
+int make_tiled_map_bf16(void* tm, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
+                        int swizzle);
 
 }  // namespace dv

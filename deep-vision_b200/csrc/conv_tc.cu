@@ -1443,6 +1443,31 @@ static WgradPlan plan_wgrad(const dv_conv_params* p) {
 
 }  // namespace
 
+int make_tiled_map_bf16(void* tm, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
+                        int swizzle) {
+  DriverApi& api = driver_api();
+  DV_REQUIRE(api.ok, DV_ERR_CUDA, "cuTensorMapEncode* entry points not available from the driver");
+  DV_REQUIRE(rank >= 2 && rank <= 5, DV_ERR_ARG, "make_tiled_map_bf16: rank %d", rank);
+  MapKey key{};
+  key.v[0] = 16 + (uint64_t)rank * 8 + (uint64_t)swizzle;
+  key.v[1] = (uint64_t)(uintptr_t)ptr;
+  for (int i = 0; i < rank; ++i) key.v[2 + i] = dims[i] | ((uint64_t)box[i] << 40);
+  for (int i = 0; i + 1 < rank; ++i) key.v[7 + i] = strides_bytes[i];
+  if (map_cache_get(key, (CUtensorMap*)tm)) return DV_OK;
+  cuuint64_t d[5], st[4];
+  cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
+  const CUtensorMapSwizzle sw = swizzle == 3 ? CU_TENSOR_MAP_SWIZZLE_128B : swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_64B
+                              : swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+  CUresult r = api.tiled((CUtensorMap*)tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, b, e,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DV_REQUIRE(r == CUDA_SUCCESS, DV_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) rank=%d dims0=%llu box0=%u", (int)r, rank,
+             (unsigned long long)dims[0], box[0]);
+  map_cache_put(key, *(CUtensorMap*)tm);
+  return DV_OK;
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // dispatch
 // ------------------------------------------------------------------------------------------------------------

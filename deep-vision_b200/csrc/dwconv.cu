@@ -11,6 +11,7 @@
 //           stride 2: one thread per 2x2 block of dx, which depends on exactly dy[i..i+1][j..j+1]
 //   wgrad : dw[c,r,s]   = sum_{n,p,q} dy[n,p,q,c] * x[n, p*st+r-1, q*st+s-1, c]      (block partials -> fixed-order reduce)
 #include "common.cuh"
+#include <cuda.h>  // CUtensorMap (type only)
 
 namespace dv {
 namespace {
@@ -158,6 +159,158 @@ dwconv_strip_kernel(const T* __restrict__ in, const float* __restrict__ w, T* __
 #pragma unroll
     for (int j = 0; j < TW; ++j) {
       if (ow0 + j < OW) { Vec16<T> o; pack2(o, acc[j]); o.store(orow + (size_t)j * C); }
+    }
+  }
+}
+
+// ---- TMA-staged variant (bf16, stride 1) -----------------------------------------------------------------------------
+// The strip kernel above keeps its 18 input vectors per strip in REGISTERS while they are in flight: at 128 registers only 16
+// warps are resident and ncu shows them waiting on global loads with the HBM half idle.  Here the input halo tile of a
+// (TH x 16 pixel, CB channel) output tile is brought into shared memory by one TMA box load per tile — a 4-D tiled map over
+// [N][H][W][C] whose out-of-range rows / columns read as zero, so padding costs nothing — through a ring of STAGES tiles:
+// the bytes in flight live in shared memory, not in registers, and the arithmetic reads 16-byte vectors from the tile
+// (a quarter-warp reads one pixel's 128 contiguous bytes: conflict-free).  One thread per strip of 4 outputs x 8 channels.
+__device__ __forceinline__ uint32_t dw_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void dw_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dw_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void dw_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dw_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void dw_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(dw_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void dw_mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = dw_smem_u32(bar);
+  uint32_t done = 0;
+  long long t0 = 0;
+  for (uint32_t spin = 0;; ++spin) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    if (done) return;
+    if ((spin & 0x3ff) == 0x3ff) {   // a protocol bug must trap, not hang the GPU
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000LL) { printf("dv dwconv: mbarrier wait timed out (block %d,%d)\n", blockIdx.x, blockIdx.y); __trap(); }
+    }
+  }
+}
+__device__ __forceinline__ void dw_tma_load_4d(void* smem, const void* tm, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+                   dw_smem_u32(smem)),
+               "l"(reinterpret_cast<uint64_t>(tm)), "r"(dw_smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
+struct DwTmaArgs {
+  int N, OH, OW, C;        // output extents (== input extents for stride 1)
+  int tiles_h, tiles_w;
+  int flip, ep_relu;
+  const float* ep_shift;
+};
+
+template <int CB>
+struct DwTile {
+  static constexpr int GROUPS = CB / 8;            // 16-byte channel groups per pixel
+  static constexpr int NSTRIP = kThreads / GROUPS;  // strips of 4 outputs per tile
+  static constexpr int TW = 16, TH = NSTRIP / 4;    // output tile
+  static constexpr int IW = TW + 2, IH = TH + 2;    // input halo tile
+  static constexpr int STAGE_BYTES = IH * IW * CB * 2;
+};
+
+template <int CB, int STAGES>
+__global__ void __launch_bounds__(kThreads, 2)
+dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restrict__ w, bf16* __restrict__ out, const DwTmaArgs g) {
+  using TL = DwTile<CB>;
+  constexpr int V = 8, H2 = 4;
+  extern __shared__ __align__(128) uint8_t dw_smem[];
+  uint8_t* tiles = dw_smem;
+  float* ws = reinterpret_cast<float*>(dw_smem + STAGES * TL::STAGE_BYTES);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ws + 9 * CB);
+  uint64_t* empty_bar = full_bar + STAGES;
+  const int c0 = blockIdx.y * CB;
+  load_taps_split<V>(ws, w, c0, CB, g.flip != 0, TL::GROUPS);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { dw_mbar_init(&full_bar[i], 1); dw_mbar_init(&empty_bar[i], kThreads / 32); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int per_img = g.tiles_h * g.tiles_w;
+  const int ntiles = g.N * per_img;
+  const int my_tiles = blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  auto issue = [&](int it) {   // thread 0: tile `it` of this CTA into stage it % STAGES
+    const int tile = blockIdx.x + it * gridDim.x;
+    const int n = tile / per_img, rem = tile - n * per_img;
+    const int th = rem / g.tiles_w, tw = rem - th * g.tiles_w;
+    const int s = it % STAGES;
+    dw_mbar_expect_tx(&full_bar[s], TL::STAGE_BYTES);
+    dw_tma_load_4d(tiles + s * TL::STAGE_BYTES, &tmX, &full_bar[s], c0, tw * TL::TW - 1, th * TL::TH - 1, n);
+  };
+  if (threadIdx.x == 0)
+    for (int it = 0; it < STAGES && it < my_tiles; ++it) issue(it);
+
+  const int tcg = threadIdx.x % TL::GROUPS, strip = threadIdx.x / TL::GROUPS;
+  const int row = strip >> 2, col0 = (strip & 3) * 4;
+  const int c = c0 + tcg * V;
+  float2 bias[H2];
+#pragma unroll
+  for (int e = 0; e < H2; ++e) bias[e] = g.ep_shift != nullptr ? make_float2(g.ep_shift[c + 2 * e], g.ep_shift[c + 2 * e + 1]) : make_float2(0.f, 0.f);
+
+  for (int it = 0; it < my_tiles; ++it) {
+    const int s = it % STAGES;
+    const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+    dw_mbar_wait(&full_bar[s], ph);
+    const uint8_t* tile_in = tiles + s * TL::STAGE_BYTES;
+    float2 acc[4][H2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < H2; ++e) acc[j][e] = bias[e];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      float2 xv[6][H2];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        Vec16<bf16> raw;
+        raw.raw = *reinterpret_cast<const uint4*>(tile_in + (((row + r) * TL::IW + col0 + k) * CB + tcg * V) * 2);
+        unpack2(raw, xv[k]);
+      }
+#pragma unroll
+      for (int sx = 0; sx < 3; ++sx) {
+        float2 wv[H2];
+#pragma unroll
+        for (int e = 0; e < V; e += 4) {
+          const float4 q4 = *reinterpret_cast<const float4*>(ws + (((r * 3 + sx) * (V / 4) + e / 4) * TL::GROUPS + tcg) * 4);
+          wv[e / 2] = make_float2(q4.x, q4.y); wv[e / 2 + 1] = make_float2(q4.z, q4.w);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int e = 0; e < H2; ++e) acc[j][e] = __ffma2_rn(xv[j + sx][e], wv[e], acc[j][e]);
+      }
+    }
+    // this warp has read everything it needs from the stage: hand it back, and let thread 0 refill it for tile it + STAGES
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) dw_mbar_arrive(&empty_bar[s]);
+    if (threadIdx.x == 0 && it + STAGES < my_tiles) {
+      dw_mbar_wait(&empty_bar[s], ph);
+      issue(it + STAGES);
+    }
+    const int tile = blockIdx.x + it * gridDim.x;
+    const int n = tile / per_img, rem = tile - n * per_img;
+    const int th = rem / g.tiles_w, tw = rem - th * g.tiles_w;
+    const int oh = th * TL::TH + row, ow0 = tw * TL::TW + col0;
+    if (oh < g.OH && c < g.C) {
+      if (g.ep_relu) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int e = 0; e < H2; ++e) acc[j][e] = make_float2(fmaxf(acc[j][e].x, 0.f), fmaxf(acc[j][e].y, 0.f));
+      }
+      bf16* orow = out + (((size_t)n * g.OH + oh) * g.OW + ow0) * g.C + c;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (ow0 + j < g.OW) { Vec16<bf16> o; pack2(o, acc[j]); o.store(orow + (size_t)j * g.C); }
     }
   }
 }
@@ -369,11 +522,48 @@ static int wgrad_blocks(const DwDims& d, int lanes, int* per_blk) {
   return nb;
 }
 
+// TMA-staged stride-1 kernel: `in` and `out` are [N][H][W][C] bf16 (fprop: x -> y; dgrad: dy -> dx with flipped taps)
+template <int CB>
+static int launch_dw_tma_s1(const void* in, const float* w, void* out, int N, int H, int W, int C, int flip, const float* ep_shift, int ep_relu,
+                            cudaStream_t st) {
+  using TL = DwTile<CB>;
+  constexpr int STAGES = 3;
+  alignas(64) CUtensorMap tm;
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  const uint64_t strides[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
+  const uint32_t box[4] = {(uint32_t)CB, (uint32_t)TL::IW, (uint32_t)TL::IH, 1};
+  int rc = make_tiled_map_bf16(&tm, in, 4, dims, strides, box, 0);
+  if (rc) return rc;
+  DwTmaArgs g{};
+  g.N = N; g.OH = H; g.OW = W; g.C = C;
+  g.tiles_h = ceil_div(H, TL::TH); g.tiles_w = ceil_div(W, TL::TW);
+  g.flip = flip; g.ep_relu = ep_relu; g.ep_shift = ep_shift;
+  constexpr int smem = STAGES * TL::STAGE_BYTES + 9 * CB * 4 + 2 * STAGES * 8;
+  DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_s1_kernel<CB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int cblocks = C / CB;
+  const int64_t ntiles = (int64_t)N * g.tiles_h * g.tiles_w;
+  DV_REQUIRE(ntiles < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
+  int gx = 2 * num_sms() / cblocks;
+  if (gx < 1) gx = 1;
+  if (gx > ntiles) gx = (int)ntiles;
+  dwconv_tma_s1_kernel<CB, STAGES><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, w, (bf16*)out, g);
+  DV_LAUNCH_OK("dwconv_tma_s1_kernel");
+  return DV_OK;
+}
+static bool dw_tma_ok(const dv_dwconv_params* p) {
+  static const int enabled = getenv("DV_DW_TMA") ? atoi(getenv("DV_DW_TMA")) : 1;
+  return enabled && p->dtype == DV_BF16 && p->C % 32 == 0 && p->W >= 14 && p->H >= 8 &&
+         ((reinterpret_cast<uintptr_t>(p->x) | reinterpret_cast<uintptr_t>(p->y)) & 15) == 0;
+}
+
 template <typename T>
 static int run_fprop(const dv_dwconv_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
+  if (sizeof(T) == 2 && d.stride == 1 && dw_tma_ok(p))
+    return p->C % 64 == 0 ? launch_dw_tma_s1<64>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st)
+                          : launch_dw_tma_s1<32>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st);
   DwPlan pl = dw_plan(p->C, V);
   const int64_t strips = (int64_t)d.N * d.P * ceil_div(d.Q, d.stride == 1 ? StripW<1>::fwd : StripW<2>::fwd);
   DV_REQUIRE(strips < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
@@ -397,6 +587,9 @@ static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
+  if (sizeof(T) == 2 && d.stride == 1 && dw_tma_ok(p))
+    return p->C % 64 == 0 ? launch_dw_tma_s1<64>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.C, 1, nullptr, 0, st)
+                          : launch_dw_tma_s1<32>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.C, 1, nullptr, 0, st);
   DwPlan pl = dw_plan(p->C, V);
   int nb, per;
   if (d.stride == 1) {

@@ -221,7 +221,10 @@ def test_bn_forward_backward_matches_oracle(shape, residual, relu, dtype):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
-@pytest.mark.parametrize("case", [(2, 32, 10, 10, 1), (2, 64, 9, 11, 2), (1, 1024, 7, 7, 1), (3, 128, 8, 8, 2), (2, 2048, 4, 4, 1)],
+@pytest.mark.parametrize("case", [(2, 32, 10, 10, 1), (2, 64, 9, 11, 2), (1, 1024, 7, 7, 1), (3, 128, 8, 8, 2), (2, 2048, 4, 4, 1),
+                                  # W >= 14: the TMA-staged kernels (halo tiles through shared memory); ragged tiles in both directions
+                                  (2, 64, 20, 30, 1), (2, 32, 17, 14, 1), (1, 128, 33, 16, 1), (2, 96, 12, 20, 1), (3, 256, 28, 28, 1),
+                                  (2, 64, 20, 30, 2), (2, 32, 17, 15, 2), (1, 128, 28, 28, 2)],
                          ids=lambda c: "x".join(map(str, c)))
 def test_dwconv_matches_oracle(case, dtype):
     lib = _lib()
@@ -403,12 +406,13 @@ def test_cross_entropy_matches_oracle():
     assert rel_l2(d.cpu().numpy(), 0.25 * d_ref) < 1e-5
 
 
+@pytest.mark.parametrize("hw", [(9, 10), (18, 21)], ids=["strip_kernel", "tma_kernel"])
 @pytest.mark.parametrize("stride", [1, 2])
-def test_dwconv_folded_batchnorm_epilogue(stride):
+def test_dwconv_folded_batchnorm_epilogue(stride, hw):
     """dv_dwconv_params.ep_shift / ep_relu with taps scaled by dv_bn_fold == oracle dwconv -> eval BN -> ReLU."""
     lib = _lib()
     dtype = torch.bfloat16
-    N, Cc, H, W = 3, 64, 9, 10
+    N, Cc, (H, W) = 3, 64, hw
     x = _rand((N, Cc, H, W), 51, dtype)
     w = _rand((Cc, 1, 3, 3), 52, torch.float32, scale=0.3)
     rng = np.random.default_rng(53)
