@@ -315,6 +315,114 @@ dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __res
   }
 }
 
+// TMA-staged wgrad (bf16, stride 1 or 2): per output tile the x halo tile AND the dy tile come in by TMA (out-of-range dy reads
+// as zero, so ragged edges need no tests); a thread keeps the 9 x 8 fp32 sums of its channel group over all of its CTA's tiles,
+// the CTA reduces its strips once at the end and writes one partial row per tap.
+template <int CB, int ST>
+struct DwWgTile {
+  static constexpr int GROUPS = CB / 8, NSTRIP = kThreads / GROUPS, TW = 16, TH = NSTRIP / 4;
+  static constexpr int IW = (TW - 1) * ST + 3, IH = (TH - 1) * ST + 3;
+  static constexpr int X_BYTES = ((IH * IW * CB * 2 + 127) / 128) * 128, DY_BYTES = TH * TW * CB * 2;
+  static constexpr int STAGE_BYTES = X_BYTES + DY_BYTES;
+};
+
+template <int CB, int ST, int STAGES>
+__global__ void __launch_bounds__(kThreads, 1)
+dwconv_tma_wgrad_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, float* __restrict__ partial,
+                        int N, int tiles_h, int tiles_w, int C) {
+  using TL = DwWgTile<CB, ST>;
+  constexpr int V = 8, H2 = 4, NCOL = 3 * ST + 3;   // input columns a strip of 4 outputs touches: 6 (stride 1) or 9 (stride 2)
+  extern __shared__ __align__(128) uint8_t dw_smem[];
+  uint8_t* tiles = dw_smem;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(dw_smem + STAGES * TL::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  const int c0 = blockIdx.y * CB;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { dw_mbar_init(&full_bar[i], 1); dw_mbar_init(&empty_bar[i], kThreads / 32); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int per_img = tiles_h * tiles_w;
+  const int ntiles = N * per_img;
+  const int my_tiles = blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  auto issue = [&](int it) {
+    const int tile = blockIdx.x + it * gridDim.x;
+    const int n = tile / per_img, rem = tile - n * per_img;
+    const int th = rem / tiles_w, tw = rem - th * tiles_w;
+    const int s = it % STAGES;
+    uint8_t* dst = tiles + s * TL::STAGE_BYTES;
+    dw_mbar_expect_tx(&full_bar[s], TL::IH * TL::IW * CB * 2 + TL::DY_BYTES);
+    dw_tma_load_4d(dst, &tmX, &full_bar[s], c0, tw * TL::TW * ST - 1, th * TL::TH * ST - 1, n);
+    dw_tma_load_4d(dst + TL::X_BYTES, &tmDY, &full_bar[s], c0, tw * TL::TW, th * TL::TH, n);
+  };
+  if (threadIdx.x == 0)
+    for (int it = 0; it < STAGES && it < my_tiles; ++it) issue(it);
+  const int tcg = threadIdx.x % TL::GROUPS, strip = threadIdx.x / TL::GROUPS;
+  const int row = strip >> 2, col0 = (strip & 3) * 4;
+  float2 acc[9][H2];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int e = 0; e < H2; ++e) acc[t][e] = make_float2(0.f, 0.f);
+  for (int it = 0; it < my_tiles; ++it) {
+    const int s = it % STAGES;
+    const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+    dw_mbar_wait(&full_bar[s], ph);
+    const uint8_t* tx = tiles + s * TL::STAGE_BYTES;
+    const uint8_t* tdy = tx + TL::X_BYTES;
+    float2 gv[4][H2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      Vec16<bf16> raw;
+      raw.raw = *reinterpret_cast<const uint4*>(tdy + ((row * TL::TW + col0 + j) * CB + tcg * V) * 2);
+      unpack2(raw, gv[j]);
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      float2 xv[NCOL][H2];
+#pragma unroll
+      for (int k = 0; k < NCOL; ++k) {
+        Vec16<bf16> raw;
+        raw.raw = *reinterpret_cast<const uint4*>(tx + (((row * ST + r) * TL::IW + col0 * ST + k) * CB + tcg * V) * 2);
+        unpack2(raw, xv[k]);
+      }
+#pragma unroll
+      for (int sx = 0; sx < 3; ++sx)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int e = 0; e < H2; ++e) acc[r * 3 + sx][e] = __ffma2_rn(xv[j * ST + sx][e], gv[j][e], acc[r * 3 + sx][e]);
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) dw_mbar_arrive(&empty_bar[s]);
+    if (threadIdx.x == 0 && it + STAGES < my_tiles) {
+      dw_mbar_wait(&empty_bar[s], ph);
+      issue(it + STAGES);
+    }
+  }
+  // reduce the CTA's strips (fixed order), one tap at a time, through the (now idle) tile ring
+  __syncthreads();
+  float* red = reinterpret_cast<float*>(dw_smem);
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+#pragma unroll
+    for (int e = 0; e < H2; ++e) { red[threadIdx.x * V + 2 * e] = acc[t][e].x; red[threadIdx.x * V + 2 * e + 1] = acc[t][e].y; }
+    __syncthreads();
+    if (strip == 0 && c0 + tcg * V < C) {
+      float sum[V];
+#pragma unroll
+      for (int e = 0; e < V; ++e) sum[e] = 0.f;
+      for (int l = 0; l < TL::NSTRIP; ++l)
+#pragma unroll
+        for (int e = 0; e < V; ++e) sum[e] += red[(l * TL::GROUPS + tcg) * V + e];
+      float* dst = partial + ((size_t)blockIdx.x * 9 + t) * C + c0 + tcg * V;
+#pragma unroll
+      for (int e = 0; e < V; ++e) dst[e] = sum[e];
+    }
+    __syncthreads();
+  }
+}
+
 // stride-2 dgrad: dx[2i+a, 2j+b] for a,b in {0,1} from dy[i..i+1][j..j+1]
 //   (2i  ,2j  ) = dy[i,j]*w11
 //   (2i  ,2j+1) = dy[i,j]*w12 + dy[i,j+1]*w10
@@ -614,11 +722,58 @@ static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
   return DV_OK;
 }
 
+static int dw_tma_wgrad_blocks(const DwDims& d, int CB, int TH) {   // CTAs along x (one per SM over all channel blocks)
+  const int64_t ntiles = (int64_t)d.N * ceil_div(d.P, TH) * ceil_div(d.Q, 16);
+  int gx = num_sms() / (d.C / CB);
+  if (gx < 1) gx = 1;
+  if (gx > ntiles) gx = (int)ntiles;
+  return gx;
+}
+void dwconv_wgrad_finalize_launch(const float* partial, float* dw, int nblk, int C, cudaStream_t st);
+
+template <int CB, int ST>
+static int launch_dw_tma_wgrad(const dv_dwconv_params* p, const DwDims& d, cudaStream_t st) {
+  using TL = DwWgTile<CB, ST>;
+  constexpr int STAGES = ST == 1 ? 3 : 2;
+  const int gx = dw_tma_wgrad_blocks(d, CB, TL::TH);
+  const size_t need = (size_t)gx * 9 * d.C * sizeof(float);
+  DV_REQUIRE(p->workspace && p->workspace_bytes >= need, DV_ERR_WORKSPACE, "dwconv_wgrad: workspace %zu bytes required, %zu given", need,
+             p->workspace_bytes);
+  alignas(64) CUtensorMap tmX, tmDY;
+  {
+    const uint64_t dims[4] = {(uint64_t)d.C, (uint64_t)d.W, (uint64_t)d.H, (uint64_t)d.N};
+    const uint64_t strides[3] = {(uint64_t)d.C * 2, (uint64_t)d.W * d.C * 2, (uint64_t)d.H * d.W * d.C * 2};
+    const uint32_t box[4] = {(uint32_t)CB, (uint32_t)TL::IW, (uint32_t)TL::IH, 1};
+    int rc = make_tiled_map_bf16(&tmX, p->x, 4, dims, strides, box, 0);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[4] = {(uint64_t)d.C, (uint64_t)d.Q, (uint64_t)d.P, (uint64_t)d.N};
+    const uint64_t strides[3] = {(uint64_t)d.C * 2, (uint64_t)d.Q * d.C * 2, (uint64_t)d.P * d.Q * d.C * 2};
+    const uint32_t box[4] = {(uint32_t)CB, (uint32_t)TL::TW, (uint32_t)TL::TH, 1};
+    int rc = make_tiled_map_bf16(&tmDY, p->y, 4, dims, strides, box, 0);
+    if (rc) return rc;
+  }
+  constexpr int smem = STAGES * TL::STAGE_BYTES + 2 * STAGES * 8 + 128;
+  static_assert(smem <= 227 * 1024, "depth-wise wgrad ring exceeds shared memory");
+  DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_wgrad_kernel<CB, ST, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  dwconv_tma_wgrad_kernel<CB, ST, STAGES><<<dim3((unsigned)gx, (unsigned)(d.C / CB)), kThreads, smem, st>>>(
+      tmX, tmDY, (float*)p->workspace, d.N, ceil_div(d.P, TL::TH), ceil_div(d.Q, TL::TW), d.C);
+  DV_LAUNCH_OK("dwconv_tma_wgrad_kernel");
+  dwconv_wgrad_finalize_launch((const float*)p->workspace, (float*)p->w, gx, d.C, st);
+  DV_LAUNCH_OK("dwconv_wgrad_finalize_kernel");
+  return DV_OK;
+}
+
 template <typename T>
 static int run_wgrad(const dv_dwconv_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
+  if (sizeof(T) == 2 && dw_tma_ok(p) && d.Q >= 8) {
+    if (d.stride == 1) return p->C % 64 == 0 ? launch_dw_tma_wgrad<64, 1>(p, d, st) : launch_dw_tma_wgrad<32, 1>(p, d, st);
+    return p->C % 64 == 0 ? launch_dw_tma_wgrad<64, 2>(p, d, st) : launch_dw_tma_wgrad<32, 2>(p, d, st);
+  }
   DwPlan pl = dw_plan(p->C, V);
   int per;
   const int nb = wgrad_blocks(d, pl.lanes, &per);
@@ -636,6 +791,10 @@ static int run_wgrad(const dv_dwconv_params* p, cudaStream_t st) {
   dwconv_wgrad_finalize_kernel<<<ceil_div(9 * p->C, 32), 256, 0, st>>>((const float*)p->workspace, (float*)p->w, nb, p->C);
   DV_LAUNCH_OK("dwconv_wgrad_finalize_kernel");
   return DV_OK;
+}
+
+void dwconv_wgrad_finalize_launch(const float* partial, float* dw, int nblk, int C, cudaStream_t st) {
+  dwconv_wgrad_finalize_kernel<<<ceil_div(9 * C, 32), 256, 0, st>>>(partial, dw, nblk, C);
 }
 
 static int check(const dv_dwconv_params* p, const char* who) {
@@ -661,6 +820,11 @@ extern "C" size_t dv_dwconv_workspace_bytes(const dv_dwconv_params* p) {
     int per;
     const size_t nb = (size_t)wgrad_blocks(d, pl.lanes, &per);
     const size_t need = nb * 9 * p->C * sizeof(float);
+    if (need > best) best = need;
+  }
+  if (p->C % 32 == 0) {   // the TMA-staged kernels: one partial row per CTA along x
+    const int CB = p->C % 64 == 0 ? 64 : 32;
+    const size_t need = (size_t)dw_tma_wgrad_blocks(d, CB, 256 / (CB / 8) / 4) * 9 * p->C * sizeof(float);
     if (need > best) best = need;
   }
   return best;
