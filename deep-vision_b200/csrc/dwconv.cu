@@ -207,6 +207,7 @@ struct DwTmaArgs {
   int tiles_h, tiles_w;
   int flip, ep_relu;
   const float* ep_shift;
+  float* stat_sums;        // fprop, optional: [2][C] += per-channel sum and sum of squares of the bf16-rounded outputs (BatchNorm statistics)
 };
 
 template <int CB>
@@ -255,6 +256,9 @@ dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __res
   float2 bias[H2];
 #pragma unroll
   for (int e = 0; e < H2; ++e) bias[e] = g.ep_shift != nullptr ? make_float2(g.ep_shift[c + 2 * e], g.ep_shift[c + 2 * e + 1]) : make_float2(0.f, 0.f);
+  float2 st1[H2], st2[H2];   // running sum / sum of squares of what this thread stored
+#pragma unroll
+  for (int e = 0; e < H2; ++e) { st1[e] = make_float2(0.f, 0.f); st2[e] = make_float2(0.f, 0.f); }
 
   for (int it = 0; it < my_tiles; ++it) {
     const int s = it % STAGES;
@@ -310,7 +314,34 @@ dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __res
       bf16* orow = out + (((size_t)n * g.OH + oh) * g.OW + ow0) * g.C + c;
 #pragma unroll
       for (int j = 0; j < 4; ++j)
-        if (ow0 + j < g.OW) { Vec16<bf16> o; pack2(o, acc[j]); o.store(orow + (size_t)j * g.C); }
+        if (ow0 + j < g.OW) {
+          Vec16<bf16> o;
+          pack2(o, acc[j]);
+          o.store(orow + (size_t)j * g.C);
+          if (g.stat_sums != nullptr) {   // from the rounded values: what the BatchNorm will read back
+            float2 rv[H2];
+            unpack2(o, rv);
+#pragma unroll
+            for (int e = 0; e < H2; ++e) { st1[e] = __fadd2_rn(st1[e], rv[e]); st2[e] = __ffma2_rn(rv[e], rv[e], st2[e]); }
+          }
+        }
+    }
+  }
+  if (g.stat_sums != nullptr) {   // CTA-wide: strips of one channel group -> one pair of atomics per channel
+    __syncthreads();
+    float* red = reinterpret_cast<float*>(dw_smem);
+#pragma unroll
+    for (int e = 0; e < H2; ++e) {
+      red[threadIdx.x * 16 + 2 * e] = st1[e].x; red[threadIdx.x * 16 + 2 * e + 1] = st1[e].y;
+      red[threadIdx.x * 16 + 8 + 2 * e] = st2[e].x; red[threadIdx.x * 16 + 8 + 2 * e + 1] = st2[e].y;
+    }
+    __syncthreads();
+    if (threadIdx.x < TL::GROUPS * 16) {
+      const int grp = threadIdx.x / 16, k = threadIdx.x % 16;   // k < 8: sum of channel k, else sum of squares of channel k - 8
+      float sum = 0.f;
+      for (int l = 0; l < TL::NSTRIP; ++l) sum += red[(l * TL::GROUPS + grp) * 16 + k];
+      const int ch = c0 + grp * V + (k & 7);
+      if (ch < g.C) atomicAdd(g.stat_sums + (k < 8 ? 0 : g.C) + ch, sum);
     }
   }
 }
@@ -633,7 +664,7 @@ static int wgrad_blocks(const DwDims& d, int lanes, int* per_blk) {
 // TMA-staged stride-1 kernel: `in` and `out` are [N][H][W][C] bf16 (fprop: x -> y; dgrad: dy -> dx with flipped taps)
 template <int CB>
 static int launch_dw_tma_s1(const void* in, const float* w, void* out, int N, int H, int W, int C, int flip, const float* ep_shift, int ep_relu,
-                            cudaStream_t st) {
+                            cudaStream_t st, float* stat_sums = nullptr) {
   using TL = DwTile<CB>;
   constexpr int STAGES = 3;
   alignas(64) CUtensorMap tm;
@@ -645,7 +676,7 @@ static int launch_dw_tma_s1(const void* in, const float* w, void* out, int N, in
   DwTmaArgs g{};
   g.N = N; g.OH = H; g.OW = W; g.C = C;
   g.tiles_h = ceil_div(H, TL::TH); g.tiles_w = ceil_div(W, TL::TW);
-  g.flip = flip; g.ep_relu = ep_relu; g.ep_shift = ep_shift;
+  g.flip = flip; g.ep_relu = ep_relu; g.ep_shift = ep_shift; g.stat_sums = stat_sums;
   constexpr int smem = STAGES * TL::STAGE_BYTES + 9 * CB * 4 + 2 * STAGES * 8;
   DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_s1_kernel<CB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int cblocks = C / CB;
@@ -670,8 +701,9 @@ static int run_fprop(const dv_dwconv_params* p, cudaStream_t st) {
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
   if (sizeof(T) == 2 && d.stride == 1 && dw_tma_ok(p))
-    return p->C % 64 == 0 ? launch_dw_tma_s1<64>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st)
-                          : launch_dw_tma_s1<32>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st);
+    return p->C % 64 == 0 ? launch_dw_tma_s1<64>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums)
+                          : launch_dw_tma_s1<32>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums);
+  DV_REQUIRE(p->stat_sums == nullptr, DV_ERR_UNSUPPORTED, "dwconv fprop: stat_sums is honoured by the TMA-staged stride-1 kernel only (ask dv_dwconv_fuses_stats)");
   DwPlan pl = dw_plan(p->C, V);
   const int64_t strips = (int64_t)d.N * d.P * ceil_div(d.Q, d.stride == 1 ? StripW<1>::fwd : StripW<2>::fwd);
   DV_REQUIRE(strips < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
@@ -828,6 +860,9 @@ extern "C" size_t dv_dwconv_workspace_bytes(const dv_dwconv_params* p) {
     if (need > best) best = need;
   }
   return best;
+}
+extern "C" int dv_dwconv_fuses_stats(const dv_dwconv_params* p) {
+  return (p && p->stride == 1 && p->dtype == DV_BF16 && dw_tma_ok(p)) ? 1 : 0;
 }
 extern "C" int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_fprop");

@@ -458,7 +458,7 @@ class _DwConv3x3(torch.autograd.Function):
     """nn.Conv2d(C, C, 3, padding=1, stride, groups=C, bias=False) — mobilenet_v1.py:112-122."""
 
     @staticmethod
-    def forward(ctx, x, weight, stride):
+    def forward(ctx, x, weight, stride, stats=None):
         _require_cuda(x, "dwconv3x3")
         x = _nhwc(x)
         N, Cc, H, W = x.shape
@@ -467,6 +467,11 @@ class _DwConv3x3(torch.autograd.Function):
         w = weight.detach().contiguous()  # [C,1,3,3] fp32 == [C][3][3]
         y = torch.empty((N, Cc, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
         p = _dw_params(x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cc, stride, _dv_dtype(x.dtype))
+        if stats is not None and lib.dv_dwconv_fuses_stats(C.byref(p)) == 1:
+            if stats.pending:
+                stats.t.zero_()
+            p.stat_sums = stats.t.data_ptr()
+            stats.pending = True
         check(lib.dv_dwconv_fprop(C.byref(p), _stream()), "dv_dwconv_fprop")
         ctx.save_for_backward(x, weight)
         ctx.stride = stride
@@ -494,11 +499,14 @@ class _DwConv3x3(torch.autograd.Function):
             ws = _workspace(need, x.device)
             p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
             check(lib.dv_dwconv_wgrad(C.byref(p), _stream()), "dv_dwconv_wgrad")
-        return dx, dw, None
+        return dx, dw, None, None
 
 
-def dwconv3x3(x, weight, stride=1):
-    return _DwConv3x3.apply(x, weight, int(stride))
+def dwconv3x3(x, weight, stride=1, stats=None):
+    y = _DwConv3x3.apply(x, weight, int(stride), stats)
+    if stats is not None and stats.pending:
+        y._dv_stat_sums = stats   # picked up by the BatchNorm that consumes y
+    return y
 
 
 # ----------------------------------------------------------------------------------------------------------------

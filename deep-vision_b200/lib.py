@@ -43,7 +43,7 @@ class DwConvParams(C.Structure):
         ("x", C.c_void_p), ("w", C.c_void_p), ("y", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("stride", C.c_int32),
-        ("dtype", C.c_int32), ("ep_shift", C.c_void_p), ("ep_relu", C.c_int32),
+        ("dtype", C.c_int32), ("ep_shift", C.c_void_p), ("ep_relu", C.c_int32), ("stat_sums", C.c_void_p),
     ]
 
 
@@ -104,6 +104,7 @@ _SIG = {
     "dv_stem_fprop": (C.c_int, [C.POINTER(StemParams), _P]),
     "dv_stem_wgrad": (C.c_int, [C.POINTER(StemParams), _P]),
     "dv_stem_workspace_bytes": (C.c_size_t, [C.POINTER(StemParams)]),
+    "dv_dwconv_fuses_stats": (C.c_int, [C.POINTER(DwConvParams)]),
     "dv_dwconv_fprop": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_dgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_wgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),

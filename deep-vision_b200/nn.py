@@ -36,13 +36,13 @@ class Conv2d(nn.Conv2d):
         x = F.to_compute_layout(x)
         if defer and inference.wanted(self, x):
             return inference.PendingConv(x, self)
-        if self._dv_depthwise:
-            return F.dwconv3x3(x, self.weight, self.stride[0])
         stats = None
         if self.training and config.fuse_bn_stats() and x.dtype == torch.bfloat16 and config.conv_algo() != 1:
             if self._dv_stats is None or self._dv_stats.t.device != x.device:
                 self._dv_stats = F.StatSums(self.out_channels, x.device)
             stats = self._dv_stats
+        if self._dv_depthwise:
+            return F.dwconv3x3(x, self.weight, self.stride[0], stats)
         return F.conv2d(x, self.weight, self.stride[0], self.padding[0], self._dv_cache, config.conv_algo(), grad_slot, role, stats)
 
 

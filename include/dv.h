@@ -183,7 +183,12 @@ typedef struct dv_dwconv_params {
    * channel, so the caller passes w[c,:,:] * scale[c].  dgrad / wgrad reject a non-NULL ep_shift. */
   const float* ep_shift;
   int32_t ep_relu;
+  float* stat_sums;   /* fprop only, optional: [2][C] fp32 that the kernel ADDS the per-channel sum and sum of squares of the (bf16-rounded)
+                         output to — the statistics pass of the BatchNorm that follows (mobilenet_v1.py:126), see dv_bn_stats_from_sums.
+                         Honoured by the TMA-staged stride-1 kernel only: dv_dwconv_fuses_stats() answers 1 for such parameters, any
+                         other path rejects a non-NULL stat_sums */
 } dv_dwconv_params;
+int dv_dwconv_fuses_stats(const dv_dwconv_params* p);
 
 int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream);
 int dv_dwconv_dgrad(const dv_dwconv_params* p, void* stream);

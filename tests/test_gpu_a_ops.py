@@ -240,10 +240,22 @@ def test_dwconv_matches_oracle(case, dtype):
     yd = torch.full((N, P, Q, Cc), float("nan"), device="cuda", dtype=dtype)
     p = lib.DwConvParams()
     p.x, p.w, p.y, p.N, p.H, p.W, p.C, p.stride, p.dtype = xd.data_ptr(), wd.data_ptr(), yd.data_ptr(), N, H, W, Cc, stride, _dv(dtype)
+    fused = lib.lib.dv_dwconv_fuses_stats(C.byref(p)) == 1      # TMA-staged stride-1 kernel: BatchNorm sums from its registers
+    sums = torch.full((2 * Cc,), 1.5, device="cuda")
+    if fused:
+        p.stat_sums = sums.data_ptr()
     lib.check(lib.lib.dv_dwconv_fprop(C.byref(p), stream_ptr()), "dv_dwconv_fprop")
     torch.cuda.synchronize()
     tol = TOL[dtype]
     assert rel_l2(np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2)), y_ref) < tol
+    if fused:
+        yb = yd.double().reshape(-1, Cc)
+        assert rel_l2((sums[:Cc].double() - 1.5).cpu().numpy(), yb.sum(0).cpu().numpy()) < 1e-4       # ADDED to what was there
+        assert rel_l2((sums[Cc:].double() - 1.5).cpu().numpy(), (yb * yb).sum(0).cpu().numpy()) < 1e-4
+    else:
+        p.stat_sums = sums.data_ptr()
+        assert lib.lib.dv_dwconv_fprop(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED                 # never silently ignored
+    p.stat_sums = None
     dyd = _dev(np.transpose(dy, (0, 2, 3, 1)), dtype)
     dxd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
     p.x, p.y = dxd.data_ptr(), dyd.data_ptr()
