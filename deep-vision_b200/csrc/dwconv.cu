@@ -210,20 +210,21 @@ struct DwTmaArgs {
   float* stat_sums;        // fprop, optional: [2][C] += per-channel sum and sum of squares of the bf16-rounded outputs (BatchNorm statistics)
 };
 
-template <int CB>
+template <int CB, int ST = 1>
 struct DwTile {
   static constexpr int GROUPS = CB / 8;            // 16-byte channel groups per pixel
   static constexpr int NSTRIP = kThreads / GROUPS;  // strips of 4 outputs per tile
   static constexpr int TW = 16, TH = NSTRIP / 4;    // output tile
-  static constexpr int IW = TW + 2, IH = TH + 2;    // input halo tile
-  static constexpr int STAGE_BYTES = IH * IW * CB * 2;
+  static constexpr int IW = (TW - 1) * ST + 3, IH = (TH - 1) * ST + 3;    // input halo tile
+  static constexpr int STAGE_BYTES = ((IH * IW * CB * 2 + 127) / 128) * 128;
+  static constexpr int LOAD_BYTES = IH * IW * CB * 2;
 };
 
-template <int CB, int STAGES>
-__global__ void __launch_bounds__(kThreads, 2)
-dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restrict__ w, bf16* __restrict__ out, const DwTmaArgs g) {
-  using TL = DwTile<CB>;
-  constexpr int V = 8, H2 = 4;
+template <int CB, int ST, int STAGES>
+__global__ void __launch_bounds__(kThreads, ST == 1 ? 2 : 1)
+dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restrict__ w, bf16* __restrict__ out, const DwTmaArgs g) {
+  using TL = DwTile<CB, ST>;
+  constexpr int V = 8, H2 = 4, NCOL = 3 * ST + 3;   // input columns under a strip of 4 outputs
   extern __shared__ __align__(128) uint8_t dw_smem[];
   uint8_t* tiles = dw_smem;
   float* ws = reinterpret_cast<float*>(dw_smem + STAGES * TL::STAGE_BYTES);
@@ -244,8 +245,8 @@ dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __res
     const int n = tile / per_img, rem = tile - n * per_img;
     const int th = rem / g.tiles_w, tw = rem - th * g.tiles_w;
     const int s = it % STAGES;
-    dw_mbar_expect_tx(&full_bar[s], TL::STAGE_BYTES);
-    dw_tma_load_4d(tiles + s * TL::STAGE_BYTES, &tmX, &full_bar[s], c0, tw * TL::TW - 1, th * TL::TH - 1, n);
+    dw_mbar_expect_tx(&full_bar[s], TL::LOAD_BYTES);
+    dw_tma_load_4d(tiles + s * TL::STAGE_BYTES, &tmX, &full_bar[s], c0, tw * TL::TW * ST - 1, th * TL::TH * ST - 1, n);
   };
   if (threadIdx.x == 0)
     for (int it = 0; it < STAGES && it < my_tiles; ++it) issue(it);
@@ -272,11 +273,11 @@ dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __res
       for (int e = 0; e < H2; ++e) acc[j][e] = bias[e];
 #pragma unroll
     for (int r = 0; r < 3; ++r) {
-      float2 xv[6][H2];
+      float2 xv[NCOL][H2];
 #pragma unroll
-      for (int k = 0; k < 6; ++k) {
+      for (int k = 0; k < NCOL; ++k) {
         Vec16<bf16> raw;
-        raw.raw = *reinterpret_cast<const uint4*>(tile_in + (((row + r) * TL::IW + col0 + k) * CB + tcg * V) * 2);
+        raw.raw = *reinterpret_cast<const uint4*>(tile_in + (((row * ST + r) * TL::IW + col0 * ST + k) * CB + tcg * V) * 2);
         unpack2(raw, xv[k]);
       }
 #pragma unroll
@@ -290,7 +291,7 @@ dwconv_tma_s1_kernel(const __grid_constant__ CUtensorMap tmX, const float* __res
 #pragma unroll
         for (int j = 0; j < 4; ++j)
 #pragma unroll
-          for (int e = 0; e < H2; ++e) acc[j][e] = __ffma2_rn(xv[j + sx][e], wv[e], acc[j][e]);
+          for (int e = 0; e < H2; ++e) acc[j][e] = __ffma2_rn(xv[j * ST + sx][e], wv[e], acc[j][e]);
       }
     }
     // this warp has read everything it needs from the stage: hand it back, and let thread 0 refill it for tile it + STAGES
@@ -661,12 +662,13 @@ static int wgrad_blocks(const DwDims& d, int lanes, int* per_blk) {
   return nb;
 }
 
-// TMA-staged stride-1 kernel: `in` and `out` are [N][H][W][C] bf16 (fprop: x -> y; dgrad: dy -> dx with flipped taps)
-template <int CB>
-static int launch_dw_tma_s1(const void* in, const float* w, void* out, int N, int H, int W, int C, int flip, const float* ep_shift, int ep_relu,
-                            cudaStream_t st, float* stat_sums = nullptr) {
-  using TL = DwTile<CB>;
-  constexpr int STAGES = 3;
+// TMA-staged forward-shaped kernel: `in` [N][H][W][C] -> `out` [N][OH][OW][C], bf16 (fprop: x -> y, stride 1 or 2; stride-1 dgrad:
+// dy -> dx with flipped taps)
+template <int CB, int ST>
+static int launch_dw_tma_fwd(const void* in, const float* w, void* out, int N, int H, int W, int OH, int OW, int C, int flip,
+                             const float* ep_shift, int ep_relu, cudaStream_t st, float* stat_sums = nullptr) {
+  using TL = DwTile<CB, ST>;
+  constexpr int STAGES = ST == 1 ? 3 : 2;
   alignas(64) CUtensorMap tm;
   const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
   const uint64_t strides[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
@@ -674,19 +676,20 @@ static int launch_dw_tma_s1(const void* in, const float* w, void* out, int N, in
   int rc = make_tiled_map_bf16(&tm, in, 4, dims, strides, box, 0);
   if (rc) return rc;
   DwTmaArgs g{};
-  g.N = N; g.OH = H; g.OW = W; g.C = C;
-  g.tiles_h = ceil_div(H, TL::TH); g.tiles_w = ceil_div(W, TL::TW);
+  g.N = N; g.OH = OH; g.OW = OW; g.C = C;
+  g.tiles_h = ceil_div(OH, TL::TH); g.tiles_w = ceil_div(OW, TL::TW);
   g.flip = flip; g.ep_relu = ep_relu; g.ep_shift = ep_shift; g.stat_sums = stat_sums;
   constexpr int smem = STAGES * TL::STAGE_BYTES + 9 * CB * 4 + 2 * STAGES * 8;
-  DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_s1_kernel<CB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  static_assert(smem <= 227 * 1024, "depth-wise tile ring exceeds shared memory");
+  DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_fwd_kernel<CB, ST, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int cblocks = C / CB;
   const int64_t ntiles = (int64_t)N * g.tiles_h * g.tiles_w;
   DV_REQUIRE(ntiles < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
-  int gx = 2 * num_sms() / cblocks;
+  int gx = (ST == 1 ? 2 : 1) * num_sms() / cblocks;
   if (gx < 1) gx = 1;
   if (gx > ntiles) gx = (int)ntiles;
-  dwconv_tma_s1_kernel<CB, STAGES><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, w, (bf16*)out, g);
-  DV_LAUNCH_OK("dwconv_tma_s1_kernel");
+  dwconv_tma_fwd_kernel<CB, ST, STAGES><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, w, (bf16*)out, g);
+  DV_LAUNCH_OK("dwconv_tma_fwd_kernel");
   return DV_OK;
 }
 static bool dw_tma_ok(const dv_dwconv_params* p) {
@@ -700,10 +703,15 @@ static int run_fprop(const dv_dwconv_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
-  if (sizeof(T) == 2 && d.stride == 1 && dw_tma_ok(p))
-    return p->C % 64 == 0 ? launch_dw_tma_s1<64>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums)
-                          : launch_dw_tma_s1<32>(p->x, (const float*)p->w, p->y, d.N, d.H, d.W, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums);
-  DV_REQUIRE(p->stat_sums == nullptr, DV_ERR_UNSUPPORTED, "dwconv fprop: stat_sums is honoured by the TMA-staged stride-1 kernel only (ask dv_dwconv_fuses_stats)");
+  if (sizeof(T) == 2 && dw_tma_ok(p) && d.Q >= 8) {
+    const float* w = (const float*)p->w;
+    if (d.stride == 1)
+      return p->C % 64 == 0 ? launch_dw_tma_fwd<64, 1>(p->x, w, p->y, d.N, d.H, d.W, d.P, d.Q, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums)
+                            : launch_dw_tma_fwd<32, 1>(p->x, w, p->y, d.N, d.H, d.W, d.P, d.Q, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums);
+    return p->C % 64 == 0 ? launch_dw_tma_fwd<64, 2>(p->x, w, p->y, d.N, d.H, d.W, d.P, d.Q, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums)
+                          : launch_dw_tma_fwd<32, 2>(p->x, w, p->y, d.N, d.H, d.W, d.P, d.Q, d.C, 0, p->ep_shift, p->ep_relu, st, p->stat_sums);
+  }
+  DV_REQUIRE(p->stat_sums == nullptr, DV_ERR_UNSUPPORTED, "dwconv fprop: stat_sums is honoured by the TMA-staged kernels only (ask dv_dwconv_fuses_stats)");
   DwPlan pl = dw_plan(p->C, V);
   const int64_t strips = (int64_t)d.N * d.P * ceil_div(d.Q, d.stride == 1 ? StripW<1>::fwd : StripW<2>::fwd);
   DV_REQUIRE(strips < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
@@ -728,8 +736,8 @@ static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
   if (sizeof(T) == 2 && d.stride == 1 && dw_tma_ok(p))
-    return p->C % 64 == 0 ? launch_dw_tma_s1<64>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.C, 1, nullptr, 0, st)
-                          : launch_dw_tma_s1<32>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.C, 1, nullptr, 0, st);
+    return p->C % 64 == 0 ? launch_dw_tma_fwd<64, 1>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.H, d.W, d.C, 1, nullptr, 0, st)
+                          : launch_dw_tma_fwd<32, 1>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.H, d.W, d.C, 1, nullptr, 0, st);
   DwPlan pl = dw_plan(p->C, V);
   int nb, per;
   if (d.stride == 1) {
@@ -862,7 +870,8 @@ extern "C" size_t dv_dwconv_workspace_bytes(const dv_dwconv_params* p) {
   return best;
 }
 extern "C" int dv_dwconv_fuses_stats(const dv_dwconv_params* p) {
-  return (p && p->stride == 1 && p->dtype == DV_BF16 && dw_tma_ok(p)) ? 1 : 0;
+  if (!p || (p->stride != 1 && p->stride != 2) || p->dtype != DV_BF16 || !dw_tma_ok(p)) return 0;
+  return dims_of(p).Q >= 8 ? 1 : 0;
 }
 extern "C" int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_fprop");
