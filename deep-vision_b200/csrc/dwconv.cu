@@ -12,6 +12,9 @@
 //   wgrad : dw[c,r,s]   = sum_{n,p,q} dy[n,p,q,c] * x[n, p*st+r-1, q*st+s-1, c]      (block partials -> fixed-order reduce)
 #include "common.cuh"
 #include <cuda.h>  // CUtensorMap (type only)
+#ifndef DV_DW_RW
+#define DV_DW_RW 2   // output rows per thread of the TMA-staged stride-1 kernel
+#endif
 
 namespace dv {
 namespace {
@@ -210,20 +213,23 @@ struct DwTmaArgs {
   float* stat_sums;        // fprop, optional: [2][C] += per-channel sum and sum of squares of the bf16-rounded outputs (BatchNorm statistics)
 };
 
-template <int CB, int ST = 1>
+template <int CB, int ST = 1, int RW = 1>
 struct DwTile {
   static constexpr int GROUPS = CB / 8;            // 16-byte channel groups per pixel
-  static constexpr int NSTRIP = kThreads / GROUPS;  // strips of 4 outputs per tile
-  static constexpr int TW = 16, TH = NSTRIP / 4;    // output tile
+  static constexpr int NSTRIP = kThreads / GROUPS;  // strips (4 outputs wide, RW rows high) per tile
+  static constexpr int TW = 16, TH = RW * NSTRIP / 4;    // output tile
   static constexpr int IW = (TW - 1) * ST + 3, IH = (TH - 1) * ST + 3;    // input halo tile
   static constexpr int STAGE_BYTES = ((IH * IW * CB * 2 + 127) / 128) * 128;
   static constexpr int LOAD_BYTES = IH * IW * CB * 2;
 };
 
-template <int CB, int ST, int STAGES>
-__global__ void __launch_bounds__(kThreads, ST == 1 ? 2 : 1)
+// RW = output rows per thread (stride 1 only): with two rows a thread reads 4 input rows for 8 outputs instead of 6, and the strip
+// kernel's instruction count per output, which is what bounds the stride-1 case, drops by a third.
+template <int CB, int ST, int RW, int STAGES>
+__global__ void __launch_bounds__(kThreads, (ST == 1 && RW == 1) ? 2 : 1)
 dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restrict__ w, bf16* __restrict__ out, const DwTmaArgs g) {
-  using TL = DwTile<CB, ST>;
+  static_assert(RW == 1 || ST == 1, "two rows per thread exist for stride 1 only");
+  using TL = DwTile<CB, ST, RW>;
   constexpr int V = 8, H2 = 4, NCOL = 3 * ST + 3;   // input columns under a strip of 4 outputs
   extern __shared__ __align__(128) uint8_t dw_smem[];
   uint8_t* tiles = dw_smem;
@@ -266,32 +272,39 @@ dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __re
     const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
     dw_mbar_wait(&full_bar[s], ph);
     const uint8_t* tile_in = tiles + s * TL::STAGE_BYTES;
-    float2 acc[4][H2];
+    float2 acc[RW][4][H2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int o = 0; o < RW; ++o)
 #pragma unroll
-      for (int e = 0; e < H2; ++e) acc[j][e] = bias[e];
+      for (int j = 0; j < 4; ++j)
 #pragma unroll
-    for (int r = 0; r < 3; ++r) {
+        for (int e = 0; e < H2; ++e) acc[o][j][e] = bias[e];
+#pragma unroll
+    for (int ir = 0; ir < 2 + RW; ++ir) {   // input rows under this thread's RW output rows
       float2 xv[NCOL][H2];
 #pragma unroll
       for (int k = 0; k < NCOL; ++k) {
         Vec16<bf16> raw;
-        raw.raw = *reinterpret_cast<const uint4*>(tile_in + (((row * ST + r) * TL::IW + col0 * ST + k) * CB + tcg * V) * 2);
+        raw.raw = *reinterpret_cast<const uint4*>(tile_in + (((row * RW * ST + ir) * TL::IW + col0 * ST + k) * CB + tcg * V) * 2);
         unpack2(raw, xv[k]);
       }
 #pragma unroll
-      for (int sx = 0; sx < 3; ++sx) {
-        float2 wv[H2];
+      for (int o = 0; o < RW; ++o) {
+        const int r = ir - o;                // filter row this input row meets for output row o
+        if (r < 0 || r > 2) continue;
 #pragma unroll
-        for (int e = 0; e < V; e += 4) {
-          const float4 q4 = *reinterpret_cast<const float4*>(ws + (((r * 3 + sx) * (V / 4) + e / 4) * TL::GROUPS + tcg) * 4);
-          wv[e / 2] = make_float2(q4.x, q4.y); wv[e / 2 + 1] = make_float2(q4.z, q4.w);
+        for (int sx = 0; sx < 3; ++sx) {
+          float2 wv[H2];
+#pragma unroll
+          for (int e = 0; e < V; e += 4) {
+            const float4 q4 = *reinterpret_cast<const float4*>(ws + (((r * 3 + sx) * (V / 4) + e / 4) * TL::GROUPS + tcg) * 4);
+            wv[e / 2] = make_float2(q4.x, q4.y); wv[e / 2 + 1] = make_float2(q4.z, q4.w);
+          }
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < H2; ++e) acc[o][j][e] = __ffma2_rn(xv[j * ST + sx][e], wv[e], acc[o][j][e]);
         }
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-#pragma unroll
-          for (int e = 0; e < H2; ++e) acc[j][e] = __ffma2_rn(xv[j * ST + sx][e], wv[e], acc[j][e]);
       }
     }
     // this warp has read everything it needs from the stage: hand it back, and let thread 0 refill it for tile it + STAGES
@@ -304,28 +317,32 @@ dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __re
     const int tile = blockIdx.x + it * gridDim.x;
     const int n = tile / per_img, rem = tile - n * per_img;
     const int th = rem / g.tiles_w, tw = rem - th * g.tiles_w;
-    const int oh = th * TL::TH + row, ow0 = tw * TL::TW + col0;
-    if (oh < g.OH && c < g.C) {
-      if (g.ep_relu) {
+    const int ow0 = tw * TL::TW + col0;
+#pragma unroll
+    for (int o = 0; o < RW; ++o) {
+      const int oh = th * TL::TH + row * RW + o;
+      if (oh < g.OH && c < g.C) {
+        if (g.ep_relu) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < H2; ++e) acc[o][j][e] = make_float2(fmaxf(acc[o][j][e].x, 0.f), fmaxf(acc[o][j][e].y, 0.f));
+        }
+        bf16* orow = out + (((size_t)n * g.OH + oh) * g.OW + ow0) * g.C + c;
 #pragma unroll
         for (int j = 0; j < 4; ++j)
+          if (ow0 + j < g.OW) {
+            Vec16<bf16> ov;
+            pack2(ov, acc[o][j]);
+            ov.store(orow + (size_t)j * g.C);
+            if (g.stat_sums != nullptr) {   // from the rounded values: what the BatchNorm will read back
+              float2 rv[H2];
+              unpack2(ov, rv);
 #pragma unroll
-          for (int e = 0; e < H2; ++e) acc[j][e] = make_float2(fmaxf(acc[j][e].x, 0.f), fmaxf(acc[j][e].y, 0.f));
-      }
-      bf16* orow = out + (((size_t)n * g.OH + oh) * g.OW + ow0) * g.C + c;
-#pragma unroll
-      for (int j = 0; j < 4; ++j)
-        if (ow0 + j < g.OW) {
-          Vec16<bf16> o;
-          pack2(o, acc[j]);
-          o.store(orow + (size_t)j * g.C);
-          if (g.stat_sums != nullptr) {   // from the rounded values: what the BatchNorm will read back
-            float2 rv[H2];
-            unpack2(o, rv);
-#pragma unroll
-            for (int e = 0; e < H2; ++e) { st1[e] = __fadd2_rn(st1[e], rv[e]); st2[e] = __ffma2_rn(rv[e], rv[e], st2[e]); }
+              for (int e = 0; e < H2; ++e) { st1[e] = __fadd2_rn(st1[e], rv[e]); st2[e] = __ffma2_rn(rv[e], rv[e], st2[e]); }
+            }
           }
-        }
+      }
     }
   }
   if (g.stat_sums != nullptr) {   // CTA-wide: strips of one channel group -> one pair of atomics per channel
@@ -343,6 +360,107 @@ dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __re
       for (int l = 0; l < TL::NSTRIP; ++l) sum += red[(l * TL::GROUPS + grp) * 16 + k];
       const int ch = c0 + grp * V + (k & 7);
       if (ch < g.C) atomicAdd(g.stat_sums + (k < 8 ? 0 : g.C) + ch, sum);
+    }
+  }
+}
+
+// TMA-staged stride-2 dgrad: the dy tile of an (8 x 8 cell) block — a cell (i, j) is the 2x2 block dx[2i..2i+1][2j..2j+1], which
+// depends on dy[i..i+1][j..j+1] exactly (see dwconv_dgrad_s2_kernel below) — comes in by one TMA box (9 x 9 pixels, rows / columns
+// past the tensor read as zero); a thread owns two neighbouring cells of one channel group: 6 shared-memory vectors in, 8 stores out.
+template <int CB>
+struct DwS2Tile {
+  static constexpr int GROUPS = CB / 8, NSTRIP = kThreads / GROUPS;   // a strip = 2 cells
+  static constexpr int CW = 8, CH = NSTRIP / 4;                        // cells per tile (4 strips per cell row)
+  static constexpr int IW = CW + 1, IH = CH + 1;
+  static constexpr int LOAD_BYTES = IH * IW * CB * 2, STAGE_BYTES = ((LOAD_BYTES + 127) / 128) * 128;
+};
+
+template <int CB, int STAGES>
+__global__ void __launch_bounds__(kThreads, 2)
+dwconv_tma_dgrad_s2_kernel(const __grid_constant__ CUtensorMap tmDY, const float* __restrict__ w, bf16* __restrict__ dx, int N, int H, int W,
+                           int C, int tiles_h, int tiles_w) {
+  using TL = DwS2Tile<CB>;
+  constexpr int V = 8;
+  extern __shared__ __align__(128) uint8_t dw_smem[];
+  uint8_t* tiles = dw_smem;
+  float* ws = reinterpret_cast<float*>(dw_smem + STAGES * TL::STAGE_BYTES);   // [9][CB] taps, tap-major
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ws + 9 * CB);
+  uint64_t* empty_bar = full_bar + STAGES;
+  const int c0 = blockIdx.y * CB;
+  for (int i = threadIdx.x; i < 9 * CB; i += kThreads) {
+    const int ch = i / 9, tap = i - ch * 9;
+    ws[tap * CB + ch] = w[(size_t)(c0 + ch) * 9 + tap];
+  }
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STAGES; ++i) { dw_mbar_init(&full_bar[i], 1); dw_mbar_init(&empty_bar[i], kThreads / 32); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int per_img = tiles_h * tiles_w;
+  const int ntiles = N * per_img;
+  const int my_tiles = blockIdx.x < ntiles ? (ntiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  auto issue = [&](int it) {
+    const int tile = blockIdx.x + it * gridDim.x;
+    const int n = tile / per_img, rem = tile - n * per_img;
+    const int th = rem / tiles_w, tw = rem - th * tiles_w;
+    const int s = it % STAGES;
+    dw_mbar_expect_tx(&full_bar[s], TL::LOAD_BYTES);
+    dw_tma_load_4d(tiles + s * TL::STAGE_BYTES, &tmDY, &full_bar[s], c0, tw * TL::CW, th * TL::CH, n);
+  };
+  if (threadIdx.x == 0)
+    for (int it = 0; it < STAGES && it < my_tiles; ++it) issue(it);
+  const int tcg = threadIdx.x % TL::GROUPS, strip = threadIdx.x / TL::GROUPS;
+  const int crow = strip >> 2, ccol0 = (strip & 3) * 2;
+  const int c = c0 + tcg * V;
+  const float* wt = ws + tcg * V;
+  for (int it = 0; it < my_tiles; ++it) {
+    const int s = it % STAGES;
+    const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+    dw_mbar_wait(&full_bar[s], ph);
+    const uint8_t* t_in = tiles + s * TL::STAGE_BYTES;
+    float g[2][3][V];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 3; ++b) {
+        Vec16<bf16> raw;
+        raw.raw = *reinterpret_cast<const uint4*>(t_in + (((crow + a) * TL::IW + ccol0 + b) * CB + tcg * V) * 2);
+        raw.unpack(g[a][b]);
+      }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) dw_mbar_arrive(&empty_bar[s]);
+    if (threadIdx.x == 0 && it + STAGES < my_tiles) {
+      dw_mbar_wait(&empty_bar[s], ph);
+      issue(it + STAGES);
+    }
+    const int tile = blockIdx.x + it * gridDim.x;
+    const int n = tile / per_img, rem = tile - n * per_img;
+    const int th = rem / tiles_w, tw = rem - th * tiles_w;
+    const int h = 2 * (th * TL::CH + crow);
+#pragma unroll
+    for (int cell = 0; cell < 2; ++cell) {
+      const int x = 2 * (tw * TL::CW + ccol0 + cell);
+      if (h >= H || x >= W || c >= C) continue;
+      float o00[V], o01[V], o10[V], o11[V];
+#pragma unroll
+      for (int e = 0; e < V; ++e) {
+        const float w00 = wt[0 * CB + e], w01 = wt[1 * CB + e], w02 = wt[2 * CB + e];
+        const float w10 = wt[3 * CB + e], w11 = wt[4 * CB + e], w12 = wt[5 * CB + e];
+        const float w20 = wt[6 * CB + e], w21 = wt[7 * CB + e], w22 = wt[8 * CB + e];
+        const float g00 = g[0][cell][e], g01 = g[0][cell + 1][e], g10 = g[1][cell][e], g11 = g[1][cell + 1][e];
+        o00[e] = g00 * w11;
+        o01[e] = fmaf(g00, w12, g01 * w10);
+        o10[e] = fmaf(g00, w21, g10 * w01);
+        o11[e] = fmaf(g00, w22, fmaf(g01, w20, fmaf(g10, w02, g11 * w00)));
+      }
+      bf16* base = dx + (((size_t)n * H + h) * W + x) * C + c;
+      Vec16<bf16> o;
+      o.pack(o00); o.store(base);
+      if (x + 1 < W) { o.pack(o01); o.store(base + C); }
+      if (h + 1 < H) {
+        o.pack(o10); o.store(base + (size_t)W * C);
+        if (x + 1 < W) { o.pack(o11); o.store(base + (size_t)W * C + C); }
+      }
     }
   }
 }
@@ -667,8 +785,9 @@ static int wgrad_blocks(const DwDims& d, int lanes, int* per_blk) {
 template <int CB, int ST>
 static int launch_dw_tma_fwd(const void* in, const float* w, void* out, int N, int H, int W, int OH, int OW, int C, int flip,
                              const float* ep_shift, int ep_relu, cudaStream_t st, float* stat_sums = nullptr) {
-  using TL = DwTile<CB, ST>;
-  constexpr int STAGES = ST == 1 ? 3 : 2;
+  constexpr int RW = ST == 1 ? DV_DW_RW : 1;
+  using TL = DwTile<CB, ST, RW>;
+  constexpr int STAGES = (ST == 1 && RW == 1) ? 3 : (ST == 1 ? 3 : 2);
   alignas(64) CUtensorMap tm;
   const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
   const uint64_t strides[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
@@ -681,14 +800,14 @@ static int launch_dw_tma_fwd(const void* in, const float* w, void* out, int N, i
   g.flip = flip; g.ep_relu = ep_relu; g.ep_shift = ep_shift; g.stat_sums = stat_sums;
   constexpr int smem = STAGES * TL::STAGE_BYTES + 9 * CB * 4 + 2 * STAGES * 8;
   static_assert(smem <= 227 * 1024, "depth-wise tile ring exceeds shared memory");
-  DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_fwd_kernel<CB, ST, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_fwd_kernel<CB, ST, RW, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int cblocks = C / CB;
   const int64_t ntiles = (int64_t)N * g.tiles_h * g.tiles_w;
   DV_REQUIRE(ntiles < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
-  int gx = (ST == 1 ? 2 : 1) * num_sms() / cblocks;
+  int gx = ((ST == 1 && RW == 1) ? 2 : 1) * num_sms() / cblocks;
   if (gx < 1) gx = 1;
   if (gx > ntiles) gx = (int)ntiles;
-  dwconv_tma_fwd_kernel<CB, ST, STAGES><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, w, (bf16*)out, g);
+  dwconv_tma_fwd_kernel<CB, ST, RW, STAGES><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, w, (bf16*)out, g);
   DV_LAUNCH_OK("dwconv_tma_fwd_kernel");
   return DV_OK;
 }
@@ -730,6 +849,31 @@ static int run_fprop(const dv_dwconv_params* p, cudaStream_t st) {
   return DV_OK;
 }
 
+template <int CB>
+static int launch_dw_tma_dgrad_s2(const dv_dwconv_params* p, const DwDims& d, cudaStream_t st) {
+  using TL = DwS2Tile<CB>;
+  constexpr int STAGES = 4;
+  alignas(64) CUtensorMap tm;
+  const uint64_t dims[4] = {(uint64_t)d.C, (uint64_t)d.Q, (uint64_t)d.P, (uint64_t)d.N};
+  const uint64_t strides[3] = {(uint64_t)d.C * 2, (uint64_t)d.Q * d.C * 2, (uint64_t)d.P * d.Q * d.C * 2};
+  const uint32_t box[4] = {(uint32_t)CB, (uint32_t)TL::IW, (uint32_t)TL::IH, 1};
+  int rc = make_tiled_map_bf16(&tm, p->y, 4, dims, strides, box, 0);
+  if (rc) return rc;
+  const int tiles_h = ceil_div((d.H + 1) / 2, TL::CH), tiles_w = ceil_div((d.W + 1) / 2, TL::CW);
+  const int64_t ntiles = (int64_t)d.N * tiles_h * tiles_w;
+  DV_REQUIRE(ntiles < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
+  constexpr int smem = STAGES * TL::STAGE_BYTES + 9 * CB * 4 + 2 * STAGES * 8;
+  DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_dgrad_s2_kernel<CB, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int cblocks = d.C / CB;
+  int gx = 2 * num_sms() / cblocks;
+  if (gx < 1) gx = 1;
+  if (gx > ntiles) gx = (int)ntiles;
+  dwconv_tma_dgrad_s2_kernel<CB, STAGES><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, (const float*)p->w, (bf16*)p->x, d.N,
+                                                                                                    d.H, d.W, d.C, tiles_h, tiles_w);
+  DV_LAUNCH_OK("dwconv_tma_dgrad_s2_kernel");
+  return DV_OK;
+}
+
 template <typename T>
 static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
@@ -749,6 +893,8 @@ static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
     dim3 grid((unsigned)nb, (unsigned)pl.cchunks);
     dwconv_strip_kernel<T, 1><<<grid, kThreads, 0, st>>>((const T*)p->y, (const float*)p->w, (T*)p->x, d.N, d.P, d.Q, d.H, d.W, d.C, pl.cgb,
                                                        pl.lanes, per, 1);
+  } else if (sizeof(T) == 2 && dw_tma_ok(p) && d.Q >= 8) {
+    return p->C % 64 == 0 ? launch_dw_tma_dgrad_s2<64>(p, d, st) : launch_dw_tma_dgrad_s2<32>(p, d, st);
   } else {
     const int64_t cells = (int64_t)d.N * ((d.H + 1) / 2) * ((d.W + 1) / 2);
     DV_REQUIRE(cells < (1LL << 31), DV_ERR_UNSUPPORTED, "dwconv: tensor too large");
