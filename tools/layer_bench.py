@@ -116,9 +116,13 @@ def time_weighted(rows):
     return dict(ms=round(ms, 3), tflop=round(tflop, 3), tflops=round(tf, 1), frac_of_burst=round(tf / PEAK_TF, 4))
 
 
-def bn_rows(batch):
+BN_SHAPES = {"resnet50": [(64, 112), (64, 56), (256, 56), (128, 28), (512, 28), (256, 14), (1024, 14), (512, 7), (2048, 7)],
+             "mobilenet1": [(32, 112), (64, 112), (64, 56), (128, 56), (128, 28), (256, 28), (256, 14), (512, 14), (512, 7), (1024, 7)]}
+
+
+def bn_rows(batch, model="resnet50"):
     rows = []
-    for (Cc, H) in [(64, 112), (64, 56), (256, 56), (128, 28), (512, 28), (256, 14), (1024, 14), (512, 7), (2048, 7)]:
+    for (Cc, H) in BN_SHAPES[model]:
         M = batch * H * H
         x = torch.randn(M, Cc, device="cuda").to(torch.bfloat16)
         y, dy, dx, res, dres = (torch.randn(M, Cc, device="cuda").to(torch.bfloat16) for _ in range(5))
@@ -179,6 +183,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--out", default="gpurun_out/layer_bench")
     ap.add_argument("--what", default="conv,bn,dw")
+    ap.add_argument("--bn-model", default="resnet50", choices=sorted(BN_SHAPES), help="whose BatchNorm tensor shapes the bn table uses")
     args = ap.parse_args()
     out = {}
     md = [f"# Per-layer roofline, batch {args.batch}, bf16 (peaks: {PEAK_TF} TFLOP/s burst, {PEAK_GB} GB/s measured)", ""]
@@ -195,7 +200,7 @@ def main():
         md += ["", f"Sum over the 52 non-stem convs x 3 passes: **{tot:.2f} ms** per step = {tw['tflops']} TFLOP/s time-weighted = "
                    f"**{tw['frac_of_burst']} of the burst peak** ({tw['tflop']} TFLOP).", ""]
     if "bn" in args.what:
-        rows = bn_rows(args.batch)
+        rows = bn_rows(args.batch, args.bn_model)
         out["bn"] = rows
         md += ["## Batch norm passes", "", "| tensor | pass | ms | GB/s | frac of HBM roof |", "|---|---|---|---|---|"]
         md += [f"| {r['layer']} | {r['passname']} | {r['ms']} | {r['gbs']} | {r['frac']} |" for r in rows]
