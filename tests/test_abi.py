@@ -71,3 +71,18 @@ def test_no_cpu_path():
     m = dv.models.MobileNetV1()
     with pytest.raises(RuntimeError, match="CUDA"):
         m(torch.zeros(1, 3, 32, 32))
+
+
+def test_stem_geometry_is_host_logic():
+    """dv_stem_supported: which C <= 4 convolutions the direct (no patch matrix) path takes, and the padded image extents."""
+    from deep_vision_b200 import lib
+    p = lib.StemParams()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad = 256, 224, 224, 3, 64, 7, 7, 2, 3      # resnet50.py:20-28
+    hp, wp = C.c_int(0), C.c_int(0)
+    assert lib.lib.dv_stem_supported(C.byref(p), C.byref(hp), C.byref(wp)) == 1
+    assert (hp.value, wp.value) == (229, 230)          # 3 + 224 rows (+2 for the last window), row pitch 230 * 8 B = a multiple of 16
+    p.K, p.R, p.S, p.pad = 32, 3, 3, 1                 # mobilenet_v1.py:30
+    assert lib.lib.dv_stem_supported(C.byref(p), C.byref(hp), C.byref(wp)) == 1 and wp.value % 2 == 0
+    p.stride = 1
+    assert lib.lib.dv_stem_supported(C.byref(p), None, None) == 0
+    assert lib.lib.dv_stem_fprop(None, None) == 1 and b"null" in lib.lib.dv_last_error()
