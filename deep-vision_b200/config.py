@@ -11,7 +11,8 @@ _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
           "fold_bn": os.environ.get("DV_FOLD_BN", "1") != "0",
           "side_wgrad": os.environ.get("DV_SIDE_WGRAD", "1") == "1",
           "fuse_bn_bwd": os.environ.get("DV_FUSE_BN_BWD", "1") == "1",
-          "stem_direct": os.environ.get("DV_STEM_DIRECT", "1") == "1"}
+          "stem_direct": os.environ.get("DV_STEM_DIRECT", "1") == "1",
+          "fuse_stem_pool": os.environ.get("DV_FUSE_STEM_POOL", "1") == "1"}
 
 
 def compute_dtype():
@@ -110,3 +111,12 @@ def stem_direct():
 
 def set_stem_direct(flag):
     _state["stem_direct"] = bool(flag)
+
+
+def fuse_stem_pool():
+    """Train-mode bn1 -> relu -> maxpool of the ResNet stem as one forward pass and two backward passes (dv_bn_relu_maxpool_*)."""
+    return _state["fuse_stem_pool"]
+
+
+def set_fuse_stem_pool(flag):
+    _state["fuse_stem_pool"] = bool(flag)

@@ -11,7 +11,7 @@ import torch
 
 from . import config
 from .lib import (DV_ALGO_AUTO, DV_ALGO_SIMT, DV_ALGO_TC, DV_BF16, DV_CONV_DGRAD, DV_CONV_FPROP, DV_CONV_WGRAD, DV_F32,
-                  BnBwdParams, BnParams, ConvParams, DwConvParams, StemParams, check, lib)
+                  BnBwdParams, BnParams, BnPoolParams, ConvParams, DwConvParams, StemParams, check, lib)
 
 _CL = torch.channels_last
 
@@ -658,6 +658,75 @@ def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training
     if handoff is not None and handoff.x is not None:
         y._dv_bn_handoff = handoff      # claimed by the dense convolution that consumes y (functional.conv2d)
     return y
+
+
+class _BnReluMaxPool(torch.autograd.Function):
+    """maxpool3x3s2(relu(bn(x))) in train mode — bn1 / relu / maxpool of the ResNet stem (resnet50.py:49-52) — without ever
+    writing the normalised tensor or the pool's input gradient (dv_bn_relu_maxpool_*)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, momentum, eps, sums):
+        _require_cuda(x, "bn_relu_maxpool")
+        x = _nhwc(x)
+        N, Cc, H, W = x.shape
+        M = N * H * W
+        save_mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        save_invstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        p = BnParams()
+        p.x, p.gamma, p.beta = x.data_ptr(), gamma.data_ptr(), beta.data_ptr()
+        p.running_mean = running_mean.data_ptr() if running_mean is not None else None
+        p.running_var = running_var.data_ptr() if running_var is not None else None
+        p.save_mean, p.save_invstd = save_mean.data_ptr(), save_invstd.data_ptr()
+        p.M, p.C, p.dtype, p.relu, p.eps, p.momentum = M, Cc, _dv_dtype(x.dtype), 1, eps, momentum
+        if sums is not None and sums.pending and sums.t.numel() == 2 * Cc:
+            check(lib.dv_bn_stats_from_sums(C.byref(p), sums.t.data_ptr(), _stream()), "dv_bn_stats_from_sums")
+            sums.pending = False
+        else:
+            ws = _workspace(lib.dv_bn_workspace_bytes(M, Cc), x.device)
+            p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+            check(lib.dv_bn_stats(C.byref(p), _stream()), "dv_bn_stats")
+        P, Q = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+        y = torch.empty((N, Cc, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        idx = torch.empty((N, Cc, P, Q), dtype=torch.uint8, device=x.device, memory_format=_CL)
+        q = BnPoolParams()
+        q.x, q.y, q.idx = x.data_ptr(), y.data_ptr(), idx.data_ptr()
+        q.gamma, q.beta, q.save_mean, q.save_invstd = gamma.data_ptr(), beta.data_ptr(), save_mean.data_ptr(), save_invstd.data_ptr()
+        q.N, q.H, q.W, q.C, q.dtype = N, H, W, Cc, _dv_dtype(x.dtype)
+        check(lib.dv_bn_relu_maxpool_fwd(C.byref(q), _stream()), "dv_bn_relu_maxpool_fwd")
+        ctx.save_for_backward(x, idx, gamma, beta, save_mean, save_invstd)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, idx, gamma, beta, mean, invstd = ctx.saved_tensors
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        N, Cc, H, W = x.shape
+        dx = torch.empty_like(x, memory_format=_CL)
+        sg, sb = grad_sink(gamma), grad_sink(beta)
+        dgamma = sg[0] if sg else torch.empty(Cc, dtype=torch.float32, device=x.device)
+        dbeta = sb[0] if sb else torch.empty(Cc, dtype=torch.float32, device=x.device)
+        q = BnPoolParams()
+        q.x, q.idx, q.dy, q.dx = x.data_ptr(), idx.data_ptr(), dy.data_ptr(), dx.data_ptr()
+        q.gamma, q.beta, q.save_mean, q.save_invstd = gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr()
+        q.dgamma, q.dbeta = dgamma.data_ptr(), dbeta.data_ptr()
+        q.N, q.H, q.W, q.C, q.dtype = N, H, W, Cc, _dv_dtype(x.dtype)
+        ws = _workspace(lib.dv_bn_pool_workspace_bytes(C.byref(q)), x.device)
+        q.workspace, q.workspace_bytes = ws.data_ptr(), ws.numel()
+        check(lib.dv_bn_relu_maxpool_bwd(C.byref(q), _stream()), "dv_bn_relu_maxpool_bwd")
+        if sg:
+            sg[1](gamma)
+            dgamma = None
+        if sb:
+            sb[1](beta)
+            dbeta = None
+        return (dx if ctx.needs_input_grad[0] else None), dgamma, dbeta, None, None, None, None, None
+
+
+def bn_relu_maxpool(x, gamma, beta, running_mean, running_var, momentum, eps):
+    sums = getattr(x, "_dv_stat_sums", None)
+    return _BnReluMaxPool.apply(x, gamma, beta, running_mean, running_var, float(momentum), float(eps), sums)
 
 
 class _ReLU(torch.autograd.Function):

@@ -75,6 +75,15 @@ class BnParams(C.Structure):
     ]
 
 
+class BnPoolParams(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p), ("y", C.c_void_p), ("idx", C.c_void_p), ("dy", C.c_void_p), ("dx", C.c_void_p),
+        ("gamma", C.c_void_p), ("beta", C.c_void_p), ("save_mean", C.c_void_p), ("save_invstd", C.c_void_p),
+        ("dgamma", C.c_void_p), ("dbeta", C.c_void_p), ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
+        ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("dtype", C.c_int32),
+    ]
+
+
 class BnBwdParams(C.Structure):
     _fields_ = [
         ("x", C.c_void_p), ("y", C.c_void_p), ("dy", C.c_void_p), ("dx", C.c_void_p), ("dres", C.c_void_p),
@@ -119,6 +128,9 @@ _SIG = {
     "dv_bn_bwd_reduce": (C.c_int, [C.POINTER(BnBwdParams), _P]),
     "dv_bn_bwd_apply": (C.c_int, [C.POINTER(BnBwdParams), _P]),
     "dv_bn_workspace_bytes": (C.c_size_t, [C.c_int64, C.c_int]),
+    "dv_bn_relu_maxpool_fwd": (C.c_int, [C.POINTER(BnPoolParams), _P]),
+    "dv_bn_relu_maxpool_bwd": (C.c_int, [C.POINTER(BnPoolParams), _P]),
+    "dv_bn_pool_workspace_bytes": (C.c_size_t, [C.POINTER(BnPoolParams)]),
     "dv_relu_fwd": (C.c_int, [_P, _P, C.c_int64, C.c_int, _P]),
     "dv_relu_bwd": (C.c_int, [_P, _P, _P, C.c_int64, C.c_int, _P]),
     "dv_maxpool_fwd": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P]),

@@ -34,8 +34,7 @@ class ResNetScaffold(tnn.Module):
         self._initialize_weights()
 
     def forward(self, x):
-        x = self.bn1(self.conv1(x, defer=True), act=self.relu)
-        x = self.maxpool(x)
+        x = self.bn1.forward_relu_maxpool(self.conv1(x, defer=True), self.relu, self.maxpool)   # bn1 -> relu -> maxpool
         for stage in (self.conv2x, self.conv3x, self.conv4x, self.conv5x):
             x = stage(x)
         x = self.avgpool(x)

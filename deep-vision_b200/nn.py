@@ -59,6 +59,11 @@ class BatchNorm2d(nn.BatchNorm2d):
                 return y
             x = x.materialize()
         x = F.to_compute_layout(x)
+        eaf, training, rm, rv = self._bookkeeping()
+        return F.batch_norm_act(x, residual, self.weight, self.bias, rm, rv, training, eaf, self.eps, act is not None, res_slot, self)
+
+    def _bookkeeping(self):
+        """nn.BatchNorm2d.forward's own bookkeeping: the counter, the averaging factor, which statistics are used and updated."""
         if self.momentum is None:
             eaf = 0.0
         else:
@@ -73,7 +78,22 @@ class BatchNorm2d(nn.BatchNorm2d):
             raise NotImplementedError("deep_vision_b200.nn.BatchNorm2d: affine=False is not on the hot path")
         rm = self.running_mean if (not self.training or self.track_running_stats) else None
         rv = self.running_var if (not self.training or self.track_running_stats) else None
-        return F.batch_norm_act(x, residual, self.weight, self.bias, rm, rv, training, eaf, self.eps, act is not None, res_slot, self)
+        return eaf, training, rm, rv
+
+    def forward_relu_maxpool(self, x, act, pool):
+        """``pool(act(self(x)))`` for the ResNet stem (bn1 -> relu -> maxpool, resnet50.py:49-52).  In train mode the three run as
+        one fused pass (functional.bn_relu_maxpool); otherwise — eval mode, folded inference, another pooling geometry, a channel
+        count the fused kernels do not take — exactly the separate modules."""
+        c = self.num_features
+        v = 8 if config.compute_dtype() == torch.bfloat16 else 4
+        fusable = (self.training and config.fuse_stem_pool() and self.affine and isinstance(act, nn.ReLU) and isinstance(pool, MaxPool2d)
+                   and not isinstance(x, inference.PendingConv) and pool.kernel_size in (3, (3, 3)) and pool.stride in (2, (2, 2))
+                   and pool.padding in (1, (1, 1)) and not pool.ceil_mode and not pool.return_indices and c % v == 0 and 256 % (c // v) == 0 and (c // v) <= 256)
+        if not fusable:
+            return pool(self(x, act=act))
+        x = F.to_compute_layout(x)
+        eaf, _, rm, rv = self._bookkeeping()
+        return F.bn_relu_maxpool(x, self.weight, self.bias, rm, rv, eaf, self.eps)
 
 
 class ReLU(nn.ReLU):

@@ -300,6 +300,32 @@ size_t dv_bn_workspace_bytes(int64_t M, int C);
 int dv_bn_fold(const float* gamma, const float* beta, const float* running_mean, const float* running_var, float eps,
                float* scale, float* shift, int C, const float* dw_w, float* dw_w_scaled, void* stream);
 
+/* nn.BatchNorm2d + nn.ReLU + nn.MaxPool2d(3, 2, 1) of the ResNet stem (resnet50.py:30-34, 49-52; resnet34.py likewise) as ONE pass
+ * forward and two passes backward over conv1's output, the largest activation of the network: the normalised tensor and the
+ * pool's input gradient (411 MB each at batch 256) never exist.  Bit for bit what dv_bn_apply(relu) -> dv_maxpool_fwd and
+ * dv_maxpool_bwd -> dv_bn_bwd_reduce -> dv_bn_bwd_apply give.  The statistics come from dv_bn_stats / dv_bn_stats_from_sums as
+ * usual (save_mean / save_invstd in).  C must be V times a power of two (V = 8 for bf16, 4 for fp32), C/V <= 256. */
+typedef struct dv_bn_pool_params {
+  const void* x;        /* [N,H,W,C] conv output (BatchNorm input) */
+  void* y;              /* fwd: out [N,P,Q,C], P = (H-1)/2+1, Q = (W-1)/2+1 */
+  uint8_t* idx;         /* [N,P,Q,C] window position (0..8) of the maximum: fwd out, bwd in */
+  const void* dy;       /* bwd: [N,P,Q,C] gradient w.r.t. y */
+  void* dx;             /* bwd: [N,H,W,C] gradient w.r.t. x */
+  const float* gamma;
+  const float* beta;
+  const float* save_mean;
+  const float* save_invstd;
+  float* dgamma;        /* bwd: [C] out */
+  float* dbeta;         /* bwd: [C] out */
+  void* workspace;      /* bwd: dv_bn_pool_workspace_bytes() */
+  size_t workspace_bytes;
+  int32_t N, H, W, C;
+  int32_t dtype;
+} dv_bn_pool_params;
+int dv_bn_relu_maxpool_fwd(const dv_bn_pool_params* p, void* stream);
+int dv_bn_relu_maxpool_bwd(const dv_bn_pool_params* p, void* stream);
+size_t dv_bn_pool_workspace_bytes(const dv_bn_pool_params* p);
+
 /* stand-alone ReLU (nn.ReLU at a site that no BN precedes; not used by the four models) */
 int dv_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream);
 int dv_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);

@@ -447,3 +447,78 @@ def test_dwconv_folded_batchnorm_epilogue(stride, hw):
     assert rel_l2(w_s.cpu().numpy(), w * (gamma / np.sqrt(rv + 1e-5))[:, None, None, None]) < 1e-6
     assert rel_l2(np.transpose(yd.double().cpu().numpy(), (0, 3, 1, 2)), ref) < 1e-2
     assert lib.lib.dv_dwconv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("shape", [(2, 64, 12, 16), (3, 64, 7, 9), (1, 32, 5, 2), (2, 128, 1, 6)], ids=lambda s: "x".join(map(str, s)))
+def test_bn_relu_maxpool_fused_equals_the_three_separate_ops(shape, dtype):
+    """dv_bn_relu_maxpool_{fwd,bwd} (the ResNet stem's bn1 -> relu -> maxpool, resnet50.py:49-52): y, the argmax and dx bit for
+    bit what dv_bn_apply(relu) -> dv_maxpool_fwd and dv_maxpool_bwd -> dv_bn_bwd_reduce -> dv_bn_bwd_apply give; dgamma/dbeta to
+    summation order; and the separate ops are the ones checked against the oracle above."""
+    lib = _lib()
+    N, Cc, H, W = shape
+    M = N * H * W
+    P, Q = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    x = _rand((N, H, W, Cc), 31, dtype, scale=1.5)
+    if dtype == torch.bfloat16:
+        x = np.round(x * 4) / 4          # coarse values: ties inside pooling windows, so the argmax rule is exercised
+    xd = _dev(x, dtype)
+    f32 = lambda a: torch.from_numpy(np.asarray(a, np.float32)).cuda()
+    g_d = f32(np.random.default_rng(32).uniform(-1.5, 1.5, Cc))     # negative gammas flip the order inside a window
+    b_d = f32(np.random.default_rng(33).normal(0, 0.3, Cc))
+    sm, si = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    wsz = lib.lib.dv_bn_workspace_bytes(M, Cc)
+    ws = torch.empty(wsz, dtype=torch.uint8, device="cuda")
+    yd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+    p = lib.BnParams()
+    p.x, p.y, p.gamma, p.beta = xd.data_ptr(), yd.data_ptr(), g_d.data_ptr(), b_d.data_ptr()
+    p.save_mean, p.save_invstd, p.workspace, p.workspace_bytes = sm.data_ptr(), si.data_ptr(), ws.data_ptr(), wsz
+    p.M, p.C, p.dtype, p.relu, p.eval_mode, p.eps, p.momentum = M, Cc, _dv(dtype), 1, 0, 1e-5, 0.1
+    lib.check(lib.lib.dv_bn_stats(C.byref(p), stream_ptr()), "dv_bn_stats")
+    lib.check(lib.lib.dv_bn_apply(C.byref(p), stream_ptr()), "dv_bn_apply")
+    pool = torch.full((N, P, Q, Cc), float("nan"), device="cuda", dtype=dtype)
+    idx = torch.full((N, P, Q, Cc), 0xEE, device="cuda", dtype=torch.uint8)
+    lib.check(lib.lib.dv_maxpool_fwd(yd.data_ptr(), pool.data_ptr(), idx.data_ptr(), N, H, W, Cc, _dv(dtype), stream_ptr()), "maxpool_fwd")
+
+    pool_f = torch.full_like(pool, float("nan"))
+    idx_f = torch.full_like(idx, 0xEE)
+    q = lib.BnPoolParams()
+    q.x, q.y, q.idx = xd.data_ptr(), pool_f.data_ptr(), idx_f.data_ptr()
+    q.gamma, q.beta, q.save_mean, q.save_invstd = g_d.data_ptr(), b_d.data_ptr(), sm.data_ptr(), si.data_ptr()
+    q.N, q.H, q.W, q.C, q.dtype = N, H, W, Cc, _dv(dtype)
+    lib.check(lib.lib.dv_bn_relu_maxpool_fwd(C.byref(q), stream_ptr()), "dv_bn_relu_maxpool_fwd")
+    torch.cuda.synchronize()
+    assert torch.equal(pool_f, pool)
+    assert torch.equal(idx_f, idx)
+
+    dpool = _dev(_rand((N, P, Q, Cc), 34, dtype), dtype)
+    dyd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+    lib.check(lib.lib.dv_maxpool_bwd(dpool.data_ptr(), idx.data_ptr(), dyd.data_ptr(), N, H, W, Cc, _dv(dtype), stream_ptr()), "maxpool_bwd")
+    dxd = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=dtype)
+    dg, db = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    r = lib.BnBwdParams()
+    r.x, r.y, r.dy, r.dx = xd.data_ptr(), yd.data_ptr(), dyd.data_ptr(), dxd.data_ptr()
+    r.gamma, r.save_mean, r.save_invstd, r.dgamma, r.dbeta = g_d.data_ptr(), sm.data_ptr(), si.data_ptr(), dg.data_ptr(), db.data_ptr()
+    r.workspace, r.workspace_bytes, r.M, r.C, r.dtype, r.relu = ws.data_ptr(), wsz, M, Cc, _dv(dtype), 1
+    lib.check(lib.lib.dv_bn_bwd_reduce(C.byref(r), stream_ptr()), "dv_bn_bwd_reduce")
+    lib.check(lib.lib.dv_bn_bwd_apply(C.byref(r), stream_ptr()), "dv_bn_bwd_apply")
+
+    dx_f = torch.full_like(dxd, float("nan"))
+    dg_f, db_f = torch.full_like(dg, float("nan")), torch.full_like(db, float("nan"))
+    q.dy, q.dx, q.dgamma, q.dbeta = dpool.data_ptr(), dx_f.data_ptr(), dg_f.data_ptr(), db_f.data_ptr()
+    wsz2 = lib.lib.dv_bn_pool_workspace_bytes(C.byref(q))
+    ws2 = torch.empty(max(wsz2, 1), dtype=torch.uint8, device="cuda")
+    q.workspace, q.workspace_bytes = ws2.data_ptr(), wsz2
+    lib.check(lib.lib.dv_bn_relu_maxpool_bwd(C.byref(q), stream_ptr()), "dv_bn_relu_maxpool_bwd")
+    torch.cuda.synchronize()
+    assert rel_l2(dg_f.cpu().numpy(), dg.cpu().numpy()) < 1e-5 and rel_l2(db_f.cpu().numpy(), db.cpu().numpy()) < 1e-5
+    if torch.equal(dg_f, dg) and torch.equal(db_f, db):
+        assert torch.equal(dx_f, dxd)
+    else:   # sums differ in the last bits by summation order; dx then differs by roundings of those
+        assert rel_l2(dx_f.double().cpu().numpy(), dxd.double().cpu().numpy()) < (1e-6 if dtype == torch.float32 else 2e-3)
+    # a workspace that is too small is refused
+    q.workspace_bytes = max(wsz2 - 1, 0)
+    if wsz2:
+        assert lib.lib.dv_bn_relu_maxpool_bwd(C.byref(q), stream_ptr()) != 0
+    q.C = 24   # not a channel count the kernels take
+    assert lib.lib.dv_bn_relu_maxpool_fwd(C.byref(q), stream_ptr()) != 0

@@ -231,3 +231,47 @@ def test_captured_forward_replays_the_eager_inference_pass():
         assert torch.equal(got, want)
     with pytest.raises(RuntimeError):
         fwd(xs[0][:4])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+def test_resnet_stem_fused_bn_relu_maxpool_equals_separate_modules(dtype):
+    """set_fuse_stem_pool(True) (default): bn1 -> relu -> maxpool of the stem (resnet34.py:48-51) run as one forward pass
+    and a reduce + finalize + apply backward instead of two forward and four backward launches.  With a fixed-order forward the
+    logits are bit-identical; every gradient agrees to the summation order of dgamma/dbeta of bn1."""
+    from deep_vision_b200.lib import lib
+    dv.set_compute_dtype(dtype)
+    dv.set_fuse_bn_stats(False)      # fixed-order statistics: both runs see the same activations
+    dv.set_fuse_bn_bwd(False)        # ... and fixed-order dgamma / dbeta, so the layers behind the stem see the same gradients
+    torch.manual_seed(3)
+    ref = dv.models.ResNet34()
+    state = {k: v.clone() for k, v in ref.state_dict().items()}
+    x = torch.randn(4, 3, 96, 80, generator=torch.Generator().manual_seed(4)).cuda()
+    labels = torch.tensor([1, 500, 999, 42]).cuda()
+    out, launches = {}, {}
+    try:
+        for fuse in (False, True):
+            dv.set_fuse_stem_pool(fuse)
+            m = dv.models.ResNet34()
+            m.load_state_dict(state)
+            m = m.cuda().train()
+            n0 = lib.dv_launch_count()
+            logits = m(x)
+            loss = torch.nn.functional.cross_entropy(logits.float(), labels)
+            loss.backward()
+            torch.cuda.synchronize()
+            launches[fuse] = lib.dv_launch_count() - n0
+            out[fuse] = {"logits": logits.detach().double().cpu().numpy(), "rm": m.bn1.running_mean.double().cpu().numpy(),
+                         "rv": m.bn1.running_var.double().cpu().numpy(), "nbt": int(m.bn1.num_batches_tracked)}
+            out[fuse].update({"grad/" + k: p.grad.double().cpu().numpy() for k, p in m.named_parameters()})
+    finally:
+        dv.set_fuse_stem_pool(True)
+        dv.set_fuse_bn_stats(True)
+        dv.set_fuse_bn_bwd(True)
+    assert launches[False] - launches[True] == 2, launches     # apply + pool -> 1 forward; pool + reduce + finalize + apply -> 3 backward
+    assert np.array_equal(out[True]["logits"], out[False]["logits"])
+    assert np.array_equal(out[True]["rm"], out[False]["rm"]) and np.array_equal(out[True]["rv"], out[False]["rv"])
+    assert out[True]["nbt"] == out[False]["nbt"] == 1
+    for k in out[True]:
+        if k.startswith("grad/"):
+            bar = 1e-5 if (dtype == torch.float32 or not k.startswith("grad/conv1")) else 2e-3
+            assert rel_l2(out[True][k], out[False][k]) < bar, k
