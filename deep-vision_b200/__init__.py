@@ -10,6 +10,6 @@ alias ``deep_vision_b200.py``.
 """
 from . import checkpoint, config, evaluate, functional, inference, lib, models, nn  # noqa: F401
 from . import data, epochs  # noqa: F401,E402
-from .config import bump_weight_epoch, compute_dtype, set_compute_dtype, set_conv_algo, set_deterministic, set_fold_bn, set_fuse_bn_bwd, set_fuse_bn_stats, set_fuse_stem_pool  # noqa: F401
+from .config import bump_weight_epoch, compute_dtype, set_compute_dtype, set_conv_algo, set_deterministic, set_fold_bn, set_fuse_bn_bwd, set_fuse_bn_stats, set_fuse_shortcut_grad, set_fuse_stem_pool  # noqa: F401
 
 __version__ = "0.1.0"

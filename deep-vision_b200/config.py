@@ -12,7 +12,8 @@ _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
           "side_wgrad": os.environ.get("DV_SIDE_WGRAD", "1") == "1",
           "fuse_bn_bwd": os.environ.get("DV_FUSE_BN_BWD", "1") == "1",
           "stem_direct": os.environ.get("DV_STEM_DIRECT", "1") == "1",
-          "fuse_stem_pool": os.environ.get("DV_FUSE_STEM_POOL", "1") == "1"}
+          "fuse_stem_pool": os.environ.get("DV_FUSE_STEM_POOL", "1") == "1",
+          "fuse_shortcut_grad": os.environ.get("DV_FUSE_SHORTCUT", "0") == "1"}
 
 
 def compute_dtype():
@@ -120,3 +121,15 @@ def fuse_stem_pool():
 
 def set_fuse_stem_pool(flag):
     _state["fuse_stem_pool"] = bool(flag)
+
+
+def fuse_shortcut_grad():
+    """Identity shortcuts: the gradient `dout * (out > 0)` is added by the first convolution's dgrad epilogue
+    (dv_conv_params.ep_residual / ep_residual_mask) instead of being written by BatchNorm's backward and accumulated onto.
+    Off by default: it saves 4 bytes per element of HBM traffic per identity block, but the epilogue's extra arithmetic per
+    element costs as much on the K = 64..512 point-wise dgrads it rides on (ResNet-50 step 16.98 vs 16.86 ms, round 2)."""
+    return _state["fuse_shortcut_grad"]
+
+
+def set_fuse_shortcut_grad(flag):
+    _state["fuse_shortcut_grad"] = bool(flag)

@@ -53,9 +53,13 @@ static int run_conv(const dv_conv_params* p, int pass, void* stream, const char*
   if (rc) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const int algo = resolve_algo(p, pass);
-  const bool folded = p->ep_scale || p->ep_shift || p->ep_residual || p->ep_relu;
+  const bool folded = p->ep_scale || p->ep_shift || p->ep_relu || (p->ep_residual && pass != DV_CONV_DGRAD);
   DV_REQUIRE(!folded || (pass == DV_CONV_FPROP && algo == DV_ALGO_TC), DV_ERR_UNSUPPORTED,
              "%s: the folded-BatchNorm epilogue (ep_*) exists on the tensor-core fprop path only", who);
+  DV_REQUIRE(p->ep_residual_mask == nullptr || (p->ep_residual != nullptr && pass == DV_CONV_DGRAD), DV_ERR_ARG,
+             "%s: ep_residual_mask goes with ep_residual in dgrad", who);
+  DV_REQUIRE(p->ep_residual == nullptr || pass != DV_CONV_DGRAD || algo == DV_ALGO_TC, DV_ERR_UNSUPPORTED,
+             "%s: the shortcut-gradient epilogue (ep_residual in dgrad) exists on the tensor-core path only", who);
   DV_REQUIRE(p->bnb_x == nullptr || (pass == DV_CONV_DGRAD && algo == DV_ALGO_TC), DV_ERR_UNSUPPORTED,
              "%s: the BatchNorm-backward sums (bnb_*) exist on the tensor-core dgrad path only", who);
   return algo == DV_ALGO_TC ? conv_tc(p, pass, st) : conv_simt(p, pass, st);

@@ -283,6 +283,9 @@ struct GemmArgs {
   const float* ep_shift;
   const bf16* ep_res;
   int ep_relu;
+  // dgrad, optional: ep_scale == NULL, out = acc + (bit(ep_mask, m, n) ? ep_res[m][n] : 0) — the shortcut's share of a residual
+  // block's input gradient, ep_res = dy of the block's last ReLU and ep_mask that ReLU's one-bit-per-element mask (Nout/8 bytes per row)
+  const uint8_t* ep_mask;
   // dgrad, optional (EPI == 2): the output dx is the gradient w.r.t. a = relu(bn(x0)).  While a dx tile is still on chip the
   // epilogue fetches the matching x0 tile (tensor map tmR), recomputes the ReLU mask exactly as bn_apply computed it and adds
   //   dbeta[c] += sum_m dz,   dgamma[c] += invstd[c] * sum_m dz * (x0 - mean[c]),   dz = dx * (relu'(bn(x0)))
@@ -322,28 +325,34 @@ __device__ __forceinline__ void bnb_tile_sums(const uint8_t* my_stage, const uin
 // tile was brought into the warp's staging buffer by TMA in the layout the result is written back in ([32 rows][128 B],
 // 16-byte chunks XOR-swizzled by row), so a lane finds its row's residual exactly where its result will go: `res_row` is the
 // shared address of the lane's row (0 = no residual), `chunk0` the first of the four 16-byte chunks these columns occupy.
-__device__ __forceinline__ void apply_folded_epilogue(uint32_t* v, const GemmArgs& g, int col0, uint32_t res_row, int chunk0, int lane) {
+__device__ __forceinline__ void apply_folded_epilogue(uint32_t* v, const GemmArgs& g, int col0, const uint32_t* rr, int m) {
   if (col0 >= g.Nout) return;  // Nout is a multiple of 8 and col0 of 32: a partial group ends on an 8-column boundary
+  const bool scaled = g.ep_scale != nullptr;
+  uint32_t bits = 0xFFFFFFFFu;   // this row's mask bits of the 32 columns from col0 (col0 is a multiple of 32: one aligned word)
+  if (g.ep_mask != nullptr) bits = m < g.M ? __ldg(reinterpret_cast<const uint32_t*>(g.ep_mask + (size_t)m * (g.Nout >> 3) + (col0 >> 3))) : 0u;
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     if (col0 + j * 8 >= g.Nout) break;
-    const float4 sa = __ldg(reinterpret_cast<const float4*>(g.ep_scale + col0 + j * 8));
-    const float4 sb = __ldg(reinterpret_cast<const float4*>(g.ep_scale + col0 + j * 8 + 4));
-    const float4 ha = __ldg(reinterpret_cast<const float4*>(g.ep_shift + col0 + j * 8));
-    const float4 hb = __ldg(reinterpret_cast<const float4*>(g.ep_shift + col0 + j * 8 + 4));
-    const float sc[8] = {sa.x, sa.y, sa.z, sa.w, sb.x, sb.y, sb.z, sb.w};
-    const float sh[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
-    float r[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (res_row != 0) {
-      uint32_t w[4];
-      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3])
-                   : "r"(res_row + (uint32_t)(((chunk0 + j) ^ (lane & 7)) * 16)));
-#pragma unroll
-      for (int e = 0; e < 4; ++e) { r[2 * e] = __uint_as_float(w[e] << 16); r[2 * e + 1] = __uint_as_float(w[e] & 0xffff0000u); }
+    float sc[8] = {1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f, 1.f};
+    float sh[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (scaled) {
+      const float4 sa = __ldg(reinterpret_cast<const float4*>(g.ep_scale + col0 + j * 8));
+      const float4 sb = __ldg(reinterpret_cast<const float4*>(g.ep_scale + col0 + j * 8 + 4));
+      const float4 ha = __ldg(reinterpret_cast<const float4*>(g.ep_shift + col0 + j * 8));
+      const float4 hb = __ldg(reinterpret_cast<const float4*>(g.ep_shift + col0 + j * 8 + 4));
+      sc[0] = sa.x; sc[1] = sa.y; sc[2] = sa.z; sc[3] = sa.w; sc[4] = sb.x; sc[5] = sb.y; sc[6] = sb.z; sc[7] = sb.w;
+      sh[0] = ha.x; sh[1] = ha.y; sh[2] = ha.z; sh[3] = ha.w; sh[4] = hb.x; sh[5] = hb.y; sh[6] = hb.z; sh[7] = hb.w;
     }
+    float r[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (rr != nullptr) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) { r[2 * e] = __uint_as_float(rr[j * 4 + e] << 16); r[2 * e + 1] = __uint_as_float(rr[j * 4 + e] & 0xffff0000u); }
+    }
+    const uint32_t b8 = bits >> (j * 8);
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      float y = fmaf(__uint_as_float(v[j * 8 + e]), sc[e], sh[e]) + r[e];
+      const float acc = __uint_as_float(v[j * 8 + e]);
+      float y = (scaled ? fmaf(acc, sc[e], sh[e]) : acc) + (((b8 >> e) & 1u) ? r[e] : 0.f);
       if (g.ep_relu) y = fmaxf(y, 0.f);
       v[j * 8 + e] = __float_as_uint(y);
     }
@@ -384,7 +393,9 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     __trap();
   }
   uint8_t* stage_out = smem + STAGES * kStageBytes;  // STATS: 4 epilogue warps x [32 rows][128 B], 16-byte chunks XOR-swizzled by row
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + (STATS ? kEpiStageBytes : 0));
+  // EPI != 0: a second set of per-warp buffers for the tile the epilogue reads (identity / x0), fetched one column group ahead
+  uint8_t* stage_aux = stage_out + (STATS ? kEpiStageBytes : 0);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_aux + (EPI != 0 ? kEpiStageBytes : 0));
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
@@ -502,6 +513,15 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     const int quarter = warp & 3;
     uint8_t* my_stage = stage_out + quarter * (32 * 128);
     const uint32_t my_stage_u32 = smem_u32(my_stage);
+    uint8_t* my_aux = stage_aux + quarter * (32 * 128);
+    const uint32_t my_aux_u32 = smem_u32(my_aux);
+    (void)my_aux_u32;
+    const bool aux_wanted = (FOLD && g.ep_res != nullptr) || BNB;
+    // one elected lane asks TMA for the [32 rows][64 columns] tile of the identity / x0 tensor that column group `cgp` will read
+    auto aux_request = [&](int n_tile_, int cgp_, int m_base_) {
+      mbar_expect_tx(&res_bar[quarter], 32 * 128);
+      tma_load_2d(my_aux, &tmR, &res_bar[quarter], n_tile_ * BN + cgp_ * 64, m_base_);
+    };
     const int sub_row = lane >> 3, chunk = lane & 7;  // read-back role: row (it*4 + sub_row), 16-byte chunk `chunk`
     int acc = 0;
     uint32_t acc_phase = 0, res_phase = 0;
@@ -554,6 +574,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
         row_off[it] = off;
       }
       const int n_left = g.Nout - n_tile * BN;
+      if (EPI != 0 && aux_wanted && lane == 0 && m_base < g.M) aux_request(n_tile, 0, m_base);   // lands while the tensor core still works
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
@@ -625,30 +646,33 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           const bool group_live = cgp * 64 < n_left && m_base < g.M;
           const bool with_res = FOLD && g.ep_res != nullptr && group_live;
           const bool with_x0 = BNB && group_live;
-          if ((with_res || with_x0) && lane == 0) {  // identity / x0 tile -> staging buffer (rows / columns past the tensor are zero-filled)
-            mbar_expect_tx(&res_bar[quarter], 32 * 128);
-            tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
-          }
-          uint32_t xw[BNB ? 32 : 1];
-          if (BNB) {
-            if (with_x0) {   // (warp-uniform) the lane's two columns of x0, all 32 rows, before dy takes the buffer
-              mbar_wait(&res_bar[quarter], res_phase);
-              res_phase ^= 1;
+          uint32_t xw[EPI != 0 ? 32 : 1];   // BNB: the lane's two columns of x0, 32 rows.  FOLD: the lane's row of the identity tile, 64 columns
+          if (with_res || with_x0) {       // (warp-uniform) the tile was requested one column group earlier
+            mbar_wait(&res_bar[quarter], res_phase);
+            res_phase ^= 1;
+            if (BNB) {
               const int wch = lane >> 2, wof = (lane & 3) * 4;
 #pragma unroll
-              for (int r = 0; r < 32; ++r) xw[r] = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+              for (int r = 0; r < 32; ++r) xw[r] = *reinterpret_cast<const uint32_t*>(my_aux + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                asm volatile("ld.volatile.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(xw[4 * j]), "=r"(xw[4 * j + 1]), "=r"(xw[4 * j + 2]), "=r"(xw[4 * j + 3])
+                             : "r"(my_aux_u32 + (uint32_t)(lane * 128 + ((j ^ (lane & 7)) * 16))) : "memory");
             }
+            // Every lane has its copy, so the buffer may take the next group's tile while this one is worked on — but the refill is
+            // a write by the async proxy, which nothing orders after these generic-proxy reads except a proxy fence: without it ptxas
+            // sank the last loads of the row below the TMA issue and they returned the next tile's bytes.
+            fence_proxy_async_smem();
             __syncwarp();
+            if (lane == 0 && cgp + 1 < BN / 64 && (cgp + 1) * 64 < n_left) aux_request(n_tile, cgp + 1, m_base);
           }
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
             uint32_t v[32];
             tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
             tmem_ld_wait();
-            if (FOLD) {
-              if (with_res && half == 0) { mbar_wait(&res_bar[quarter], res_phase); res_phase ^= 1; }
-              apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? my_stage_u32 + lane * 128 : 0u, half * 4, lane);
-            }
+            if (FOLD) apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? xw + half * 16 : nullptr, m_base + lane);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint32_t w[4];
@@ -722,8 +746,10 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 // accumulator-ready barriers are signalled in both CTAs by a multicast commit; the peer's epilogue hands accumulators
 // back by a remote arrive.
 // ------------------------------------------------------------------------------------------------------------
-template <int STAGES, bool B_MN, int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads)
+// EW: epilogue warps per CTA, 4 or 8.  A warp reads the TMEM lanes of quarter (warp % 4); with 8 warps two share a quarter and take
+// alternate 64-column groups, each with its own staging / tile buffers, so two warps per scheduler hide each other's latencies.
+template <int STAGES, bool B_MN, int EPI, int EW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW)
 conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
   constexpr bool FOLD = EPI == 1, BNB = EPI == 2;
@@ -738,12 +764,16 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     __trap();
   }
   uint8_t* stage_out = smem + STAGES * kStageBytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + kEpiStageBytes);
+  static_assert(EW == 4 || EW == 8, "4 or 8 epilogue warps");
+  constexpr int kGroupStep = EW / 4;                 // column groups are dealt round-robin to the warps of a quarter
+  constexpr int kMyGroups = (BN / 64) / kGroupStep;
+  uint8_t* stage_aux = stage_out + EW * 4096;        // EPI != 0: the tile the epilogue reads (identity / x0), one column group ahead
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_aux + (EPI != 0 ? EW * 4096 : 0));
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
   uint64_t* res_bar = tempty_bar + ACC;  // one per epilogue warp: the identity tile of a folded-BN epilogue has landed
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + 4);
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(res_bar + EW);
 
   const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
@@ -763,9 +793,9 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     for (int i = 0; i < ACC; ++i) {
       mbar_init(&tfull_bar[i], 1);   // multicast commit
-      mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps of each CTA (used in CTA 0 only)
+      mbar_init(&tempty_bar[i], 2 * EW);  // the epilogue warps of both CTAs (used in CTA 0 only)
     }
-    for (int i = 0; i < 4; ++i) mbar_init(&res_bar[i], 1);
+    for (int i = 0; i < EW; ++i) mbar_init(&res_bar[i], 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc_pair(tmem_ptr, kTmemCols);
@@ -852,22 +882,33 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
     __syncwarp();
   } else {
-    const int quarter = warp & 3;
-    uint8_t* my_stage = stage_out + quarter * (32 * 128);
+    const int quarter = warp & 3;          // TMEM lanes 32*quarter .. +31: rows of the tile
+    const int ew = warp - 2;               // buffers and barriers are per warp
+    const int cg_first = ew >> 2;          // first column group of this warp (0, or 0/1 with eight warps)
+    uint8_t* my_stage = stage_out + ew * (32 * 128);
     const uint32_t my_stage_u32 = smem_u32(my_stage);
+    uint8_t* my_aux = stage_aux + ew * (32 * 128);
+    const uint32_t my_aux_u32 = smem_u32(my_aux);
+    (void)my_aux_u32;
+    const bool aux_wanted = (FOLD && g.ep_res != nullptr) || BNB;
+    // one elected lane asks TMA for the [32 rows][64 columns] tile of the identity / x0 tensor that column group `cgp` will read
+    auto aux_request = [&](int n_tile_, int cgp_, int m_base_) {
+      mbar_expect_tx(&res_bar[ew], 32 * 128);
+      tma_load_2d(my_aux, &tmR, &res_bar[ew], n_tile_ * BN + cgp_ * 64, m_base_);
+    };
     int acc = 0;
     uint32_t acc_phase = 0, res_phase = 0;
-    float s1[BN / 64][2], s2[BN / 64][2];
+    float s1[kMyGroups][2], s2[kMyGroups][2];   // entry i: column group cg_first + i * kGroupStep
     int stat_n_tile = -1;
 #pragma unroll
-    for (int i = 0; i < BN / 64; ++i) { s1[i][0] = s1[i][1] = s2[i][0] = s2[i][1] = 0.f; }
+    for (int i = 0; i < kMyGroups; ++i) { s1[i][0] = s1[i][1] = s2[i][0] = s2[i][1] = 0.f; }
     auto flush_stats = [&]() {
       if ((BNB ? (const void*)g.bnb_dgamma : (const void*)g.stat_sums) == nullptr || stat_n_tile < 0) return;
 #pragma unroll
-      for (int i = 0; i < BN / 64; ++i) {
+      for (int i = 0; i < kMyGroups; ++i) {
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
-          const int col = stat_n_tile * BN + i * 64 + 2 * lane + e;
+          const int col = stat_n_tile * BN + (cg_first + i * kGroupStep) * 64 + 2 * lane + e;
           if (col < g.Nout) {
             if (BNB) {
               atomicAdd(g.bnb_dbeta + col, s1[i][e]);
@@ -887,40 +928,42 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       if (n_tile != stat_n_tile) { flush_stats(); stat_n_tile = n_tile; }
       const int m_base = m_tile * kBlockM + quarter * 32;
       const int n_left = g.Nout - n_tile * BN;
+      if (EPI != 0 && aux_wanted && lane == 0 && m_base < g.M && cg_first * 64 < n_left) aux_request(n_tile, cg_first, m_base);   // lands while the tensor core still works
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
 #pragma unroll
-      for (int cgp = 0; cgp < BN / 64; ++cgp) {
+      for (int gi = 0; gi < kMyGroups; ++gi) {
+        const int cgp = cg_first + gi * kGroupStep;
         if (lane == 0) tma_store_wait_read();
         __syncwarp();
         const bool group_live = cgp * 64 < n_left && m_base < g.M;
         const bool with_res = FOLD && g.ep_res != nullptr && group_live;
         const bool with_x0 = BNB && group_live;
-        if ((with_res || with_x0) && lane == 0) {
-          mbar_expect_tx(&res_bar[quarter], 32 * 128);
-          tma_load_2d(my_stage, &tmR, &res_bar[quarter], n_tile * BN + cgp * 64, m_base);
-        }
-        uint32_t xw[BNB ? 32 : 1];
-        if (BNB) {
-          if (with_x0) {
-            mbar_wait(&res_bar[quarter], res_phase);
-            res_phase ^= 1;
+        uint32_t xw[EPI != 0 ? 32 : 1];   // BNB: the lane's two columns of x0, 32 rows.  FOLD: the lane's row of the identity tile, 64 columns
+        if (with_res || with_x0) {       // (warp-uniform) the tile was requested one column group earlier
+          mbar_wait(&res_bar[ew], res_phase);
+          res_phase ^= 1;
+          if (BNB) {
             const int wch = lane >> 2, wof = (lane & 3) * 4;
 #pragma unroll
-            for (int r = 0; r < 32; ++r) xw[r] = *reinterpret_cast<const uint32_t*>(my_stage + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+            for (int r = 0; r < 32; ++r) xw[r] = *reinterpret_cast<const uint32_t*>(my_aux + r * 128 + ((wch ^ (r & 7)) * 16) + wof);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              asm volatile("ld.volatile.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(xw[4 * j]), "=r"(xw[4 * j + 1]), "=r"(xw[4 * j + 2]), "=r"(xw[4 * j + 3])
+                           : "r"(my_aux_u32 + (uint32_t)(lane * 128 + ((j ^ (lane & 7)) * 16))) : "memory");
           }
+          fence_proxy_async_smem();   // orders the reads above before the async-proxy write that refills the buffer (see the persistent kernel)
           __syncwarp();
+          if (lane == 0 && gi + 1 < kMyGroups && (cgp + kGroupStep) * 64 < n_left) aux_request(n_tile, cgp + kGroupStep, m_base);
         }
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t v[32];
           tmem_ld_32x32(t_addr + (uint32_t)(cgp * 64 + half * 32), v);
           tmem_ld_wait();
-          if (FOLD) {
-            if (with_res && half == 0) { mbar_wait(&res_bar[quarter], res_phase); res_phase ^= 1; }
-            apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? my_stage_u32 + lane * 128 : 0u, half * 4, lane);
-          }
+          if (FOLD) apply_folded_epilogue(v, g, n_tile * BN + cgp * 64 + half * 32, with_res ? xw + half * 16 : nullptr, m_base + lane);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint32_t w[4];
@@ -952,8 +995,8 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             }
             float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
             bnb_tile_sums(my_stage, xw, lane, sc0, sh0, mu0, sc1, sh1, mu1, a0, a1, b0, b1);
-            s1[cgp][0] += a0; s1[cgp][1] += a1;
-            s2[cgp][0] += b0; s2[cgp][1] += b1;
+            s1[gi][0] += a0; s1[gi][1] += a1;
+            s2[gi][0] += b0; s2[gi][1] += b1;
           }
         } else if (g.stat_sums != nullptr) {
           const int wch = lane >> 2, wof = (lane & 3) * 4;
@@ -965,8 +1008,8 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             a0 += x0; a1 += x1;
             b0 = fmaf(x0, x0, b0); b1 = fmaf(x1, x1, b1);
           }
-          s1[cgp][0] += a0; s1[cgp][1] += a1;
-          s2[cgp][0] += b0; s2[cgp][1] += b1;
+          s1[gi][0] += a0; s1[gi][1] += a1;
+          s2[gi][0] += b0; s2[gi][1] += b1;
         }
       }
       tc_fence_before();
@@ -1330,20 +1373,31 @@ static int make_map_im2col(CUtensorMap* tm, const void* ptr, int N, int H, int W
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-template <int STAGES, bool B_MN, int EPI>
-static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
-                            cudaStream_t st) {
-  constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + kEpiStageBytes + 256;
+template <int STAGES, bool B_MN, int EPI, int EW>
+static int launch_gemm_pair_ew(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
+                               cudaStream_t st) {
+  constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + EW * 4096 * (EPI != 0 ? 2 : 1) + 256;
   static_assert(smem <= 227 * 1024, "pair kernel ring exceeds shared memory");
-  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int num_n = ceil_div(g.Nout, 256);
   const int pairs = ceil_div(ceil_div(g.M, kBlockM), 2) * num_n;
   int clusters = num_sms() / 2;
   if (clusters > num_n) clusters -= clusters % num_n;
   if (clusters > pairs) clusters = pairs;
-  conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI><<<2 * clusters, kThreads, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
+  conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI, EW><<<2 * clusters, 64 + 32 * EW, smem, st>>>(tmA, tmB, tmO, tmR, g);  // __cluster_dims__(2,1,1)
   DV_LAUNCH_OK("conv_tc_gemm_pair_kernel");
   return DV_OK;
+}
+
+static int env_int(const char* name, int dflt);
+// STAGES is the ring depth with four epilogue warps and no epilogue tile; eight warps (DV_TC_EW, default 8) double the staging
+// buffers, an epilogue tile doubles them again, and the ring gives up a stage when the 227 KB would be exceeded.
+template <int STAGES, bool B_MN, int EPI>
+static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
+                            cudaStream_t st) {
+  static const int ew = env_int("DV_TC_EW", 8);
+  if (ew == 8) return launch_gemm_pair_ew<(EPI != 0 ? STAGES - 1 : STAGES), B_MN, EPI, 8>(tmA, tmB, tmO, tmR, g, st);
+  return launch_gemm_pair_ew<STAGES, B_MN, EPI, 4>(tmA, tmB, tmO, tmR, g, st);
 }
 
 static int env_int(const char* name, int dflt) {
@@ -1354,7 +1408,8 @@ static int env_int(const char* name, int dflt) {
 template <int BN, int STAGES, bool STATS, bool B_MN, int EPI>
 static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                                   cudaStream_t st) {
-  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + 256;
+  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + (EPI != 0 ? kEpiStageBytes : 0) + 256;
+  static_assert(smem <= 227 * 1024, "persistent kernel ring exceeds shared memory");
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   // ask for the whole L1/shared array as shared memory: otherwise the driver sizes the carve-out for ONE CTA of this
   // kernel and a second CTA never becomes resident (measured: occupancy 1 -> 2 for the 96 KB variants)
@@ -1552,9 +1607,19 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
     DV_REQUIRE(staged && !b_mn, DV_ERR_UNSUPPORTED, "conv_tc: the folded epilogue exists on the fprop TMA-store path only");
     if (use_pair(g, bn)) return launch_gemm_pair<6, false, 1>(tmA, tmB, tmO, tmR, g, st);
     switch (bn) {
-      case 64: return launch_gemm_persistent<64, 4, true, false, 1>(tmA, tmB, tmO, tmR, g, st);
-      case 128: return launch_gemm_persistent<128, 3, true, false, 1>(tmA, tmB, tmO, tmR, g, st);
+      case 64: return launch_gemm_persistent<64, 3, true, false, 1>(tmA, tmB, tmO, tmR, g, st);    // one stage fewer: two CTAs per SM still fit
+      case 128: return launch_gemm_persistent<128, 2, true, false, 1>(tmA, tmB, tmO, tmR, g, st);
       default: return launch_gemm_persistent<256, 4, true, false, 1>(tmA, tmB, tmO, tmR, g, st);
+    }
+  }
+  if (g.ep_res != nullptr) {   // dgrad + masked shortcut gradient (conv_tc checked the preconditions): the same epilogue without scale
+    DV_REQUIRE(staged && b_mn && !g.accumulate && g.bnb_dgamma == nullptr, DV_ERR_UNSUPPORTED,
+               "conv_tc: the residual epilogue of dgrad needs the plain TMA-store path (stride 1, no accumulate, KRSC filters, no bnb_*)");
+    if (use_pair(g, bn)) return launch_gemm_pair<6, true, 1>(tmA, tmB, tmO, tmR, g, st);
+    switch (bn) {
+      case 64: return launch_gemm_persistent<64, 3, true, true, 1>(tmA, tmB, tmO, tmR, g, st);
+      case 128: return launch_gemm_persistent<128, 2, true, true, 1>(tmA, tmB, tmO, tmR, g, st);
+      default: return launch_gemm_persistent<256, 4, true, true, 1>(tmA, tmB, tmO, tmR, g, st);
     }
   }
   if (g.bnb_dgamma != nullptr) {   // dgrad with the producing layer's BatchNorm-backward sums (conv_tc checked the preconditions)
@@ -1564,8 +1629,8 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
     if (rc) return rc;
     if (use_pair(g, bn)) return launch_gemm_pair<6, true, 2>(tmA, tmB, tmO, tmR, g, st);
     switch (bn) {
-      case 64: return launch_gemm_persistent<64, 4, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
-      case 128: return launch_gemm_persistent<128, 3, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
+      case 64: return launch_gemm_persistent<64, 3, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
+      case 128: return launch_gemm_persistent<128, 2, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
       default: return launch_gemm_persistent<256, 4, true, true, 2>(tmA, tmB, tmO, tmR, g, st);
     }
   }
@@ -1637,6 +1702,15 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
       g.bnb_gamma = p->bnb_gamma; g.bnb_beta = p->bnb_beta; g.bnb_mean = p->bnb_mean; g.bnb_invstd = p->bnb_invstd;
       g.bnb_dgamma = p->bnb_dgamma; g.bnb_dbeta = p->bnb_dbeta;
       bnb_x0 = p->bnb_x;
+    }
+    if (p->ep_residual != nullptr) {
+      DV_REQUIRE(p->stride == 1 && !p->accumulate && b_mn && p->bnb_x == nullptr, DV_ERR_UNSUPPORTED,
+                 "conv_tc dgrad: ep_residual needs stride 1, accumulate == 0, w_t == NULL and no bnb_*");
+      DV_REQUIRE(!p->ep_scale && !p->ep_shift && !p->ep_relu, DV_ERR_ARG, "conv_tc dgrad: ep_scale / ep_shift / ep_relu are fprop fields");
+      DV_REQUIRE(aligned16(p->ep_residual) && (p->ep_residual_mask == nullptr || ((uintptr_t)p->ep_residual_mask & 3) == 0) && p->C % 32 == 0,
+                 DV_ERR_ARG, "conv_tc dgrad: ep_residual must be 16-byte and ep_residual_mask 4-byte aligned, C a multiple of 32");
+      g.ep_res = (const bf16*)p->ep_residual;
+      g.ep_mask = p->ep_residual_mask;
     }
     if (p->stride == 1) {
       // dx = conv(dy, w_t) with pad' = R-1-pad: an fprop whose "input" is dy [N,P,Q,K] and whose output is [N,H,W,C]

@@ -194,10 +194,13 @@ class GradSlot:
     order, and the blocks create the shortcut's nodes after the main path's, so the deposit always comes first; a
     collect without a deposit raises instead of silently dropping a gradient."""
 
-    __slots__ = ("t",)
+    __slots__ = ("t", "lazy_ok")
 
     def __init__(self):
         self.t = None
+        # set by the collecting convolution at forward time: its dgrad can add `dout * (out > 0)` in its own epilogue
+        # (dv_conv_params.ep_residual / ep_residual_mask), so the depositor hands over (dout, mask) instead of a masked copy
+        self.lazy_ok = False
 
 
 class BnBwdHandoff:
@@ -322,6 +325,9 @@ class _Conv2d(torch.autograd.Function):
         p = _conv_params(x.data_ptr(), w_c.data_ptr(), y.data_ptr(), None, N, H, W, Cc, K, R, S, stride, pad, dt, algo)
         _attach_stats(p, stats, y, DV_CONV_FPROP)
         _run_conv(lib.dv_conv_fprop, p, DV_CONV_FPROP, x.device, "dv_conv_fprop")
+        if role == "collect" and slot is not None:
+            slot.lazy_ok = bool(x.dtype == torch.bfloat16 and stride == 1 and w_t is None and Cc % 32 == 0 and config.fuse_shortcut_grad()
+                                and lib.dv_conv_algo(C.byref(p), DV_CONV_DGRAD) == DV_ALGO_TC)
         ctx.save_for_backward(x, weight)
         ctx.w_c, ctx.w_t = w_c, w_t
         ctx.geom = (stride, pad, algo)
@@ -377,15 +383,21 @@ class _Conv2d(torch.autograd.Function):
             return None, dw, None, None, None, None, None, None, None, None
         N, Cc, H, W = x.shape
         if ctx.needs_input_grad[0]:
-            acc = 0
+            acc, shortcut = 0, None
             if ctx.role == "collect":
                 if ctx.slot.t is None:
                     raise RuntimeError("deep_vision_b200: residual gradient was not deposited before the main path's dgrad")
-                dx, ctx.slot.t, acc = ctx.slot.t, None, 1
+                dep, ctx.slot.t = ctx.slot.t, None
+                if isinstance(dep, tuple):    # (dout, relu mask) of the block's merge: added by this dgrad's epilogue
+                    shortcut, dx = dep, torch.empty_like(x, memory_format=_CL)
+                else:
+                    dx, acc = dep, 1
             else:
                 dx = torch.empty_like(x, memory_format=_CL)
             p = _conv_params(dx.data_ptr(), ctx.w_c.data_ptr(), dy.data_ptr(), ctx.w_t.data_ptr() if ctx.w_t is not None else None,
                              N, H, W, Cc, K, R, S, stride, pad, dt, algo, accumulate=acc)
+            if shortcut is not None:
+                p.ep_residual, p.ep_residual_mask = shortcut[0].data_ptr(), shortcut[1].data_ptr()
             h = ctx.handoff
             fused = None
             if (h is not None and h.x is not None and h.claims == 1 and acc == 0 and stride == 1 and ctx.w_t is None
@@ -598,7 +610,9 @@ class _BatchNormAct(torch.autograd.Function):
         N, Cc, H, W = x.shape
         M = N * H * W
         dx = torch.empty_like(x, memory_format=_CL)
-        dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        # identity shortcut whose collector adds `dy * mask` in its dgrad epilogue: no masked copy of dy is written here
+        lazy = bool(ctx.has_res and ctx.needs_input_grad[1] and ctx.bit_mask and ctx.res_slot is not None and ctx.res_slot.lazy_ok)
+        dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1] and not lazy) else None
         sg, sb = grad_sink(gamma), grad_sink(beta)
         atomic = 1 if config.atomic_bn_bwd() else 0
         mk = torch.zeros if atomic else torch.empty
@@ -645,7 +659,9 @@ class _BatchNormAct(torch.autograd.Function):
         if sb:
             sb[1](beta)
             dbeta = None
-        if ctx.res_slot is not None and dres is not None:
+        if lazy:
+            ctx.res_slot.t = (dy, y)
+        elif ctx.res_slot is not None and dres is not None:
             ctx.res_slot.t, dres = dres, None   # handed to the main path's dgrad, not to autograd
         return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None, None
 

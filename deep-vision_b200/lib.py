@@ -25,7 +25,7 @@ class ConvParams(C.Structure):
         ("dtype", C.c_int32), ("algo", C.c_int32), ("y_f32", C.c_int32), ("accumulate", C.c_int32),
         ("ep_scale", C.c_void_p), ("ep_shift", C.c_void_p), ("ep_residual", C.c_void_p), ("ep_relu", C.c_int32),
         ("bnb_x", C.c_void_p), ("bnb_gamma", C.c_void_p), ("bnb_beta", C.c_void_p), ("bnb_mean", C.c_void_p),
-        ("bnb_invstd", C.c_void_p), ("bnb_dgamma", C.c_void_p), ("bnb_dbeta", C.c_void_p),
+        ("bnb_invstd", C.c_void_p), ("bnb_dgamma", C.c_void_p), ("bnb_dbeta", C.c_void_p), ("ep_residual_mask", C.c_void_p),
     ]
 
 

@@ -88,7 +88,7 @@ typedef struct dv_conv_params {
    *   y = relu( acc * ep_scale[k] + ep_shift[k] + ep_residual[n,p,q,k] )
    * with ep_scale = gamma / sqrt(running_var + eps), ep_shift = beta - running_mean * ep_scale (fp32 [K], made by the caller).
    * ep_residual (dtype [N,P,Q,K]) may be NULL; ep_relu 0/1.  All NULL/0 = plain convolution.  Any other path rejects them
-   * with DV_ERR_UNSUPPORTED rather than ignoring them. */
+   * with DV_ERR_UNSUPPORTED rather than ignoring them (dgrad gives ep_residual its own meaning: see ep_residual_mask below). */
   const float* ep_scale;
   const float* ep_shift;
   const void* ep_residual;
@@ -110,6 +110,15 @@ typedef struct dv_conv_params {
   const float* bnb_invstd;
   float* bnb_dgamma;
   float* bnb_dbeta;
+  /* dgrad on the tensor-core path only, optional — the shortcut's share of a residual block's input gradient added in the
+   * epilogue.  In  out = relu(bn3(conv3(...conv1(x)...)) + x)  (resnet50.py:147-164) the gradient of x is
+   *   dgrad(conv1) + dout * (out > 0);
+   * with ep_residual = dout [N,H,W,C] (dtype) and ep_residual_mask = the one-bit-per-element ReLU mask dv_bn_apply wrote for that
+   * block ([N*H*W][C/8] bytes, bit c%8 of byte c/8; NULL = add ep_residual unmasked), the dgrad of conv1 writes
+   *   dx = acc + (mask ? ep_residual : 0)       (one rounding to bf16)
+   * so the masked gradient is never stored by dv_bn_bwd_apply (dres == NULL there) nor read-modified-written here.
+   * Requires stride == 1, accumulate == 0, w_t == NULL, no bnb_*, C % 32 == 0; rejected with DV_ERR_UNSUPPORTED otherwise. */
+  const uint8_t* ep_residual_mask;
 } dv_conv_params;
 
 enum { DV_CONV_FPROP = 0, DV_CONV_DGRAD = 1, DV_CONV_WGRAD = 2 };

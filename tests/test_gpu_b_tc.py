@@ -483,6 +483,77 @@ def test_tc_dgrad_bn_sums_rejects_what_it_cannot_fuse():
     assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_ARG
 
 
+SHORTCUT_CASES = [c for c in BNB_CASES if c[1] % 32 == 0]
+
+
+@pytest.mark.parametrize("case", SHORTCUT_CASES, ids=lambda c: "x".join(map(str, c)))
+def test_tc_dgrad_adds_masked_shortcut_gradient(case):
+    """dv_conv_params.ep_residual / ep_residual_mask in dgrad: dx = dgrad(dy) + (mask ? dout : 0), the input gradient of an identity
+    residual block (resnet50.py:147-164) in one pass.  With dy = 0 the result must be the masked dout bit for bit (bit layout, row
+    and column addressing of the mask); with dout = 0 it must be the plain dgrad bit for bit; with both it must agree with their
+    fp32 sum to one bf16 rounding of the accumulator (the plain dgrad rounds before the add, the fused one after)."""
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    N, Cc, H, W, K, R, pad = case
+    g = torch.Generator(device="cuda").manual_seed(21)
+    dy = torch.randn((N, H + 2 * pad - R + 1, W + 2 * pad - R + 1, K), generator=g, device="cuda").to(BF)
+    w = (torch.randn((K, R, R, Cc), generator=g, device="cuda") * 0.1).to(BF)
+    dout = torch.randn((N, H, W, Cc), generator=g, device="cuda").to(BF)
+    keep = torch.rand((N * H * W, Cc), generator=g, device="cuda") < 0.6
+    # bit c%8 of byte c/8, one row of C/8 bytes per pixel: the layout dv_bn_apply writes (relu_mask)
+    weights = (2 ** torch.arange(8, device="cuda", dtype=torch.int32)).view(1, 1, 8)
+    mask = (keep.view(-1, Cc // 8, 8).to(torch.int32) * weights).sum(-1).to(torch.uint8).contiguous()
+
+    def dgrad(dy_t, res, msk):
+        dx = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=BF)
+        p = lib.ConvParams()
+        p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), dy_t.data_ptr()
+        p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, W, Cc, K, R, R, 1, pad, lib.DV_BF16, lib.DV_ALGO_TC
+        if res is not None:
+            p.ep_residual = res.data_ptr()
+            p.ep_residual_mask = msk.data_ptr() if msk is not None else None
+        lib.check(lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()), "dgrad")
+        torch.cuda.synchronize()
+        return dx
+
+    masked = torch.where(keep.view(N, H, W, Cc), dout, torch.zeros_like(dout))
+    only_res = dgrad(torch.zeros_like(dy), dout, mask)
+    assert torch.equal(only_res.view(torch.int16), (masked + 0.0).view(torch.int16))    # (+0.0: -0 + 0 accumulators give +0)
+    unmasked = dgrad(torch.zeros_like(dy), dout, None)
+    assert torch.equal(unmasked.view(torch.int16), (dout + 0.0).view(torch.int16))
+    plain = dgrad(dy, None, None)
+    assert torch.equal(dgrad(dy, torch.zeros_like(dout), mask).view(torch.int16), plain.view(torch.int16))
+    both = dgrad(dy, dout, mask)
+    want = plain.double() + masked.double()
+    err = (both.double() - want).abs()
+    # two bf16 roundings apart at most: of the accumulator (plain) and of the sum
+    assert bool((err <= 2.0 ** -8 * (plain.double().abs() + want.abs()) + 1e-30).all())
+    assert rel_l2(both.double().cpu().numpy(), want.cpu().numpy()) < 4e-3
+
+
+def test_tc_dgrad_shortcut_epilogue_rejects_what_it_cannot_fuse():
+    import ctypes as C
+    from helpers import stream_ptr
+    lib = _lib()
+    t = torch.zeros(2 * 8 * 8 * 64, device="cuda", dtype=BF)
+    m = torch.zeros(2 * 8 * 8 * 8, device="cuda", dtype=torch.uint8)
+    p = lib.ConvParams()
+    p.x, p.w, p.y = t.data_ptr(), t.data_ptr(), t.data_ptr()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = 2, 8, 8, 64, 64, 1, 1, 1, 0, lib.DV_BF16, lib.DV_ALGO_TC
+    p.ep_residual, p.ep_residual_mask = t.data_ptr(), m.data_ptr()
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_OK
+    p.accumulate = 1
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED       # either accumulate or add in the epilogue
+    p.accumulate, p.algo = 0, lib.DV_ALGO_SIMT
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED       # CUDA-core path has no such epilogue
+    p.algo, p.ep_residual = lib.DV_ALGO_TC, None
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_ARG               # a mask without the tensor it masks
+    p.ep_residual, p.stride, p.H, p.W = t.data_ptr(), 2, 16, 16
+    assert lib.lib.dv_conv_dgrad(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED       # stride 1 only
+    torch.cuda.synchronize()
+
+
 STEM_CASES = [
     # N, H, W, C, K, R, pad          stride 2
     (2, 64, 64, 3, 64, 7, 3),       # ResNet stem geometry, Q = 32

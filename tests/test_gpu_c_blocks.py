@@ -102,3 +102,35 @@ def test_block_bf16_fused_bn_backward_sums_equal_the_reduce_pass(name, fused_lay
     assert launches[False] - launches[True] == 2 * fused_layers, launches
     for k in grads[True]:
         assert rel_l2(grads[True][k], grads[False][k]) < 2e-3, k     # bf16 dx downstream of an fp32 sum that moved in its last bits
+
+
+@pytest.mark.parametrize("name", ["block_bottleneck_256_64_256", "block_basic_64_64"])
+def test_block_bf16_shortcut_gradient_in_dgrad_epilogue_equals_the_accumulate_path(name):
+    """set_fuse_shortcut_grad(True) (opt-in, DV_FUSE_SHORTCUT=1): in an identity block the last BatchNorm's backward no longer writes the masked
+    gradient of the shortcut; conv1's dgrad adds `dout * (out > 0)` in its epilogue (dv_conv_params.ep_residual[_mask]).  Every
+    parameter gradient is bit-identical (none depends on dx); dx agrees to one bf16 rounding (the accumulate path rounds the
+    dgrad before adding)."""
+    rec = load_golden(name)
+    dv.set_compute_dtype(torch.bfloat16)
+    dv.set_deterministic(True)       # fixed-order reductions: the two runs differ in the shortcut handling only
+    out = {}
+    try:
+        for fuse in (False, True):
+            dv.set_fuse_shortcut_grad(fuse)
+            m = CASES[name]()
+            m.load_state_dict(golden_state(rec))
+            m = m.cuda().train()
+            x = torch.from_numpy(rec["x"]).cuda().requires_grad_(True)
+            y = m(x)
+            y.backward(torch.from_numpy(rec["dy"]).cuda().to(torch.bfloat16))
+            torch.cuda.synchronize()
+            out[fuse] = {k: p.grad.detach().clone() for k, p in m.named_parameters()}
+            out[fuse]["dx"] = x.grad.detach().clone()
+    finally:
+        dv.set_fuse_shortcut_grad(False)
+        dv.set_deterministic(False)
+    for k in out[True]:
+        if k != "dx":
+            assert torch.equal(out[True][k], out[False][k]), k
+    assert rel_l2(out[True]["dx"].double().cpu().numpy(), out[False]["dx"].double().cpu().numpy()) < 4e-3
+    assert rel_l2(out[True]["dx"].float().cpu().numpy(), rec["dx"]) < 1.5e-1
