@@ -12,6 +12,7 @@ _state = {"compute_dtype": torch.bfloat16, "weight_epoch": 0, "conv_algo": 0,
           "side_wgrad": os.environ.get("DV_SIDE_WGRAD", "1") == "1",
           "fuse_bn_bwd": os.environ.get("DV_FUSE_BN_BWD", "1") == "1",
           "stem_direct": os.environ.get("DV_STEM_DIRECT", "1") == "1",
+          "stem_raw_input": os.environ.get("DV_STEM_RAW", "1") == "1",
           "fuse_stem_pool": os.environ.get("DV_FUSE_STEM_POOL", "1") == "1",
           "fuse_shortcut_grad": os.environ.get("DV_FUSE_SHORTCUT", "0") == "1"}
 
@@ -133,3 +134,8 @@ def fuse_shortcut_grad():
 
 def set_fuse_shortcut_grad(flag):
     _state["fuse_shortcut_grad"] = bool(flag)
+
+
+def stem_raw_input():
+    """The direct stem takes the loader's fp32 NCHW batch itself (dv_stem_pad_input_nchw) instead of a converted NHWC copy."""
+    return _state["stem_raw_input"]

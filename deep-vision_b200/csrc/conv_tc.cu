@@ -2167,6 +2167,26 @@ __global__ void stem_pad_kernel(const bf16* __restrict__ x, bf16* __restrict__ x
     reinterpret_cast<uint2*>(xp)[i] = make_uint2((uint32_t)v[0] | ((uint32_t)v[1] << 16), (uint32_t)v[2] | ((uint32_t)v[3] << 16));
   }
 }
+// The same from the batch as the reference's loader yields it (train.py:444-449: fp32 [N][C][H][W]): layout change, rounding to bf16
+// and zero border in one pass — 12 bytes read and 8 written per pixel, where dv_nchw_to_nhwc + stem_pad_kernel move 12 + 6 + 6 + 8.
+// Consecutive threads take consecutive padded columns, so each channel plane is read in whole lines.
+__global__ void stem_pad_nchw_kernel(const float* __restrict__ x, bf16* __restrict__ xp, int N, int H, int W, int C, int Hp, int Wp, int pad) {
+  const int64_t total = (int64_t)N * Hp * Wp;
+  const size_t plane = (size_t)H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int wp = (int)(i % Wp);
+    const int64_t t = i / Wp;
+    const int hp = (int)(t % Hp), n = (int)(t / Hp);
+    const int h = hp - pad, w = wp - pad;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if ((unsigned)h < (unsigned)H && (unsigned)w < (unsigned)W) {
+      const float* src = x + (size_t)n * C * plane + (size_t)h * W + w;
+      for (int c = 0; c < C; ++c) v[c] = __ldg(src + c * plane);
+    }
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+    reinterpret_cast<uint2*>(xp)[i] = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+  }
+}
 // fp32 KRSC filters -> bf16 [64][R][32]: wp[k][r][s*4 + c] = w[k][r][s][c], zero elsewhere (rows k >= K, taps s >= S, channels c >= C)
 __global__ void stem_pack_w_kernel(const float* __restrict__ w, bf16* __restrict__ wp, int K, int R, int S, int C) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -2250,6 +2270,19 @@ extern "C" int dv_stem_pad_input(const dv_stem_params* p, const void* x_nhwc, vo
   const unsigned grid = (unsigned)(ceil_div64(total, 256) < (int64_t)num_sms() * 16 ? ceil_div64(total, 256) : (int64_t)num_sms() * 16);
   stem_pad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x_nhwc, (bf16*)p->x, p->N, p->H, p->W, p->C, gm.Hp, gm.Wp, p->pad);
   DV_LAUNCH_OK("stem_pad_kernel");
+  return DV_OK;
+}
+
+extern "C" int dv_stem_pad_input_nchw(const dv_stem_params* p, const float* x_nchw, void* stream) {
+  DV_REQUIRE(p && x_nchw && p->x, DV_ERR_ARG, "dv_stem_pad_input_nchw: null pointer");
+  StemGeom gm;
+  const char* why;
+  DV_REQUIRE(stem_geometry(p, &gm, &why), DV_ERR_UNSUPPORTED, "dv_stem_pad_input_nchw: %s", why);
+  DV_REQUIRE(aligned16(p->x), DV_ERR_ARG, "dv_stem_pad_input_nchw: the padded image must be 16-byte aligned");
+  const int64_t total = (int64_t)p->N * gm.Hp * gm.Wp;
+  const unsigned grid = (unsigned)(ceil_div64(total, 256) < (int64_t)num_sms() * 16 ? ceil_div64(total, 256) : (int64_t)num_sms() * 16);
+  stem_pad_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x_nchw, (bf16*)p->x, p->N, p->H, p->W, p->C, gm.Hp, gm.Wp, p->pad);
+  DV_LAUNCH_OK("stem_pad_nchw_kernel");
   return DV_OK;
 }
 

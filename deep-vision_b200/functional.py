@@ -56,6 +56,10 @@ def _workspace(nbytes, device):
 # ----------------------------------------------------------------------------------------------------------------
 # layout change at the model entrance
 # ----------------------------------------------------------------------------------------------------------------
+class _NoCtx:
+    """Stand-in context for calling an autograd Function's forward as a plain function (nothing is saved for backward)."""
+
+
 class _ToNHWC(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, dtype):
@@ -274,27 +278,35 @@ class _Conv2d(torch.autograd.Function):
         if handoff is not None:
             handoff.claims += 1
         _require_cuda(x, "conv2d")
-        x = _nhwc(x)
+        # raw: the fp32 NCHW batch itself (nn.Conv2d.forward hands it over for a C <= 4 stem): the direct path below lays it out,
+        # rounds it and pads it in one pass; every other path converts it first, as to_compute_layout would have
+        raw = x.dtype == torch.float32 and config.compute_dtype() == torch.bfloat16 and x.is_contiguous() and not x.requires_grad
+        cdt = torch.bfloat16 if raw else x.dtype
+        if not raw:
+            x = _nhwc(x)
         N, Cc, H, W = x.shape
         K, Cw, R, S = weight.shape
         if Cw != Cc:
             raise RuntimeError(f"conv2d: input has {Cc} channels, weight expects {Cw}")
         P = (H + 2 * pad - R) // stride + 1
         Q = (W + 2 * pad - S) // stride + 1
-        dt = _dv_dtype(x.dtype)
-        y = torch.empty((N, K, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        dt = _dv_dtype(cdt)
+        y = torch.empty((N, K, P, Q), dtype=cdt, device=x.device, memory_format=_CL)
         # C=3 stems (resnet50.py:20-28, mobilenet_v1.py:30).  Direct path: padded NHWC4 image + sliding-window tensor map
         # (dv_stem_*); the 100 MB image is also what the backward pass keeps.
         ctx.patches = None
         ctx.stem = None
-        if (x.dtype == torch.bfloat16 and algo != DV_ALGO_SIMT and Cc <= 4 and config.stem_direct() and not ctx.needs_input_grad[0]):
+        if (cdt == torch.bfloat16 and algo != DV_ALGO_SIMT and Cc <= 4 and config.stem_direct() and not ctx.needs_input_grad[0]):
             sp = StemParams()
             sp.N, sp.H, sp.W, sp.C, sp.K, sp.R, sp.S, sp.stride, sp.pad = N, H, W, Cc, K, R, S, stride, pad
             hp, wp = C.c_int(0), C.c_int(0)
             if lib.dv_stem_supported(C.byref(sp), C.byref(hp), C.byref(wp)) == 1:
-                xp = torch.empty((N, hp.value, wp.value, 4), dtype=x.dtype, device=x.device)
+                xp = torch.empty((N, hp.value, wp.value, 4), dtype=cdt, device=x.device)
                 sp.x = xp.data_ptr()
-                check(lib.dv_stem_pad_input(C.byref(sp), x.data_ptr(), _stream()), "dv_stem_pad_input")
+                if raw:
+                    check(lib.dv_stem_pad_input_nchw(C.byref(sp), x.data_ptr(), _stream()), "dv_stem_pad_input_nchw")
+                else:
+                    check(lib.dv_stem_pad_input(C.byref(sp), x.data_ptr(), _stream()), "dv_stem_pad_input")
                 w_stem = cache.get_stem(weight, sp)
                 sp.w, sp.y = w_stem.data_ptr(), y.data_ptr()
                 if stats is not None:
@@ -307,6 +319,8 @@ class _Conv2d(torch.autograd.Function):
                 ctx.stem = (N, H, W, Cc, stride, pad)
                 ctx.geom = (stride, pad, algo)
                 return y
+        if raw:   # no direct path for this geometry: the layout pass after all
+            x = _ToNHWC.forward(_NoCtx(), x, cdt)
         if (x.dtype == torch.bfloat16 and algo != DV_ALGO_SIMT and Cc < 16 and R * S * Cc <= 256 and K % 8 == 0
                 and not ctx.needs_input_grad[0]):
             kp = -(-(R * S * Cc) // 64) * 64

@@ -109,6 +109,7 @@ _SIG = {
     "dv_unpad_rows": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, _P]),
     "dv_stem_supported": (C.c_int, [C.POINTER(StemParams), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "dv_stem_pad_input": (C.c_int, [C.POINTER(StemParams), _P, _P]),
+    "dv_stem_pad_input_nchw": (C.c_int, [C.POINTER(StemParams), _P, _P]),
     "dv_stem_pack_filters": (C.c_int, [C.POINTER(StemParams), _P, _P]),
     "dv_stem_fprop": (C.c_int, [C.POINTER(StemParams), _P]),
     "dv_stem_wgrad": (C.c_int, [C.POINTER(StemParams), _P]),

@@ -33,11 +33,17 @@ class Conv2d(nn.Conv2d):
         """grad_slot/role: see functional.GradSlot — used by the residual blocks to fuse the shortcut's gradient into
         this convolution's dgrad; plain callers leave them unset.  defer: the caller hands the result straight to a
         BatchNorm2d; in inference mode the launch is then left to that module (inference.PendingConv)."""
-        x = F.to_compute_layout(x)
-        if defer and inference.wanted(self, x):
+        # a C <= 4 stem in training takes the loader's fp32 NCHW batch as it is: its direct path (dv_stem_pad_input_nchw) converts
+        # while it pads, which saves the stand-alone layout pass over the batch
+        raw_stem = (self.training and self.in_channels <= 4 and not self._dv_depthwise and x.dim() == 4 and x.dtype == torch.float32
+                    and x.is_cuda and x.is_contiguous() and not x.requires_grad and config.compute_dtype() == torch.bfloat16
+                    and config.stem_direct() and config.stem_raw_input() and config.conv_algo() != 1)
+        if not raw_stem:
+            x = F.to_compute_layout(x)
+        if defer and not raw_stem and inference.wanted(self, x):
             return inference.PendingConv(x, self)
         stats = None
-        if self.training and config.fuse_bn_stats() and x.dtype == torch.bfloat16 and config.conv_algo() != 1:
+        if self.training and config.fuse_bn_stats() and (x.dtype == torch.bfloat16 or raw_stem) and config.conv_algo() != 1:
             if self._dv_stats is None or self._dv_stats.t.device != x.device:
                 self._dv_stats = F.StatSums(self.out_channels, x.device)
             stats = self._dv_stats

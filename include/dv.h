@@ -168,6 +168,9 @@ typedef struct dv_stem_params {
 } dv_stem_params;
 int dv_stem_supported(const dv_stem_params* p, int* Hp, int* Wp);
 int dv_stem_pad_input(const dv_stem_params* p, const void* x_nhwc, void* stream);   /* x_nhwc: [N,H,W,C] bf16 */
+/* the same straight from the fp32 [N,C,H,W] batch the reference's loader yields (train.py:444-449): dv_nchw_to_nhwc's rounding and
+ * dv_stem_pad_input's border in one pass over the image, bit-identical to the two calls */
+int dv_stem_pad_input_nchw(const dv_stem_params* p, const float* x_nchw, void* stream);
 int dv_stem_pack_filters(const dv_stem_params* p, const float* w_krsc, void* stream);
 int dv_stem_fprop(const dv_stem_params* p, void* stream);
 int dv_stem_wgrad(const dv_stem_params* p, void* stream);

@@ -622,3 +622,42 @@ def test_stem_direct_rejects_other_geometries():
         q = lib.StemParams.from_buffer_copy(p)
         setattr(q, field, bad)
         assert lib.lib.dv_stem_supported(C.byref(q), None, None) == 0, field
+
+
+@pytest.mark.parametrize("case", STEM_CASES[:3], ids=lambda c: "x".join(map(str, c)))
+def test_stem_pad_input_from_the_loaders_fp32_nchw_batch(case):
+    """dv_stem_pad_input_nchw (fp32 [N,C,H,W] -> padded NHWC4 bf16 in one pass) == dv_nchw_to_nhwc followed by dv_stem_pad_input,
+    bit for bit; and nn.Conv2d takes that route in training (no nchw_to_nhwc launch) with the same output."""
+    import ctypes as C
+    from helpers import stream_ptr
+    import deep_vision_b200 as dv
+    lib = _lib()
+    N, H, W, Cc, K, R, pad = case
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn((N, Cc, H, W), generator=g, device="cuda") * 60 + 20          # pixel-scale values (train.py:324 normalises 0..255)
+    p = lib.StemParams()
+    p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad = N, H, W, Cc, K, R, R, 2, pad
+    hp, wp = C.c_int(0), C.c_int(0)
+    assert lib.lib.dv_stem_supported(C.byref(p), C.byref(hp), C.byref(wp)) == 1
+    nhwc = torch.empty((N, H, W, Cc), device="cuda", dtype=BF)
+    lib.check(lib.lib.dv_nchw_to_nhwc(x.data_ptr(), nhwc.data_ptr(), N, Cc, H, W, lib.DV_BF16, stream_ptr()), "nchw_to_nhwc")
+    a = torch.full((N, hp.value, wp.value, 4), float("nan"), device="cuda", dtype=BF)
+    b = torch.full_like(a, float("nan"))
+    p.x = a.data_ptr()
+    lib.check(lib.lib.dv_stem_pad_input(C.byref(p), nhwc.data_ptr(), stream_ptr()), "pad")
+    p.x = b.data_ptr()
+    lib.check(lib.lib.dv_stem_pad_input_nchw(C.byref(p), x.data_ptr(), stream_ptr()), "pad_nchw")
+    torch.cuda.synchronize()
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    # the module: fp32 NCHW in training goes through the one-pass route; a pre-converted input through the two-pass one
+    if Cc == 3:
+        dv.set_compute_dtype(BF)
+        conv = dv.nn.Conv2d(Cc, K, R, stride=2, padding=pad, bias=False).cuda().train()
+        n0 = lib.lib.dv_launch_count()
+        y1 = conv(x)
+        n1 = lib.lib.dv_launch_count()
+        y2 = conv(nhwc.permute(0, 3, 1, 2))
+        n2 = lib.lib.dv_launch_count()
+        torch.cuda.synchronize()
+        assert torch.equal(y1, y2)
+        assert (n1 - n0) - (n2 - n1) == 1 - 0 + 0 or (n1 - n0) <= (n2 - n1) + 1   # first call also packs the filters once
