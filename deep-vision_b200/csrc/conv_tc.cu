@@ -1645,10 +1645,14 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
 #undef DV_GEMM_CASE
 }
 
+bool conv3x3_halo_supported(const dv_conv_params* p, int pass);
+int conv3x3_halo(const dv_conv_params* p, int pass, cudaStream_t st);
+
 int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
   const char* why;
   DV_REQUIRE(conv_tc_supported(p, pass, &why), DV_ERR_UNSUPPORTED, "conv_tc: %s", why);
   DV_REQUIRE(aligned16(p->x) && aligned16(p->y) && aligned16(p->w), DV_ERR_ARG, "conv_tc: pointers must be 16-byte aligned");
+  if (conv3x3_halo_supported(p, pass)) return conv3x3_halo(p, pass, st);
   const int P = (p->H + 2 * p->pad - p->R) / p->stride + 1, Q = (p->W + 2 * p->pad - p->S) / p->stride + 1;
   alignas(64) CUtensorMap tmA, tmB;
   int rc;
@@ -2378,3 +2382,269 @@ extern "C" int dv_stem_wgrad(const dv_stem_params* p, void* stream) {
   DV_LAUNCH_OK("stem_unpack_dw_kernel");
   return DV_OK;
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// 3x3 stride-1 pad-1 convolution, 64 -> 64 channels, over a halo tile resident in shared memory (fprop and dgrad).
+//
+// The im2col kernels above fetch a [128 pixels][64 channels] tile from L2 once per filter tap: nine fetches of (almost) the
+// same pixels, 1.39 GB of L2->SM traffic for a 103 MB input at 64 channels @56x56 (profiles/r02_ncu_full_3x3_64_56.csv).
+// Here ONE tiled TMA box brings rows h0-1 .. h0+2, columns -1 .. 62 of the image ([4][64 pixels][64 channels] = 32 KB, everything
+// outside the image zero-filled by the TMA unit: that is the padding) and the nine taps are nine START ADDRESSES into it: with
+// the rows of the box 64 pixels apart, output pixel m = 64*row + col of the tile reads input pixel m + 64*r + s for tap (r, s),
+// i.e. the K-major SWIZZLE_128B descriptor of the A operand starts (64*r + s) * 128 bytes into the tile.  The swizzle is a
+// function of the shared-memory address, so a start on any 128-byte row is legal (tools/probes/umma_row_offset.cu).  Output
+// columns >= W of a row are computed from wrapped-around pixels and never stored: the TMA store clips them.  The nine 64x64
+// filter taps (72 KB) stay resident for the CTA's life.  W <= 62 (W + 2 columns must fit the 64-pixel box row).
+// ------------------------------------------------------------------------------------------------------------
+namespace dv {
+namespace {
+
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* tm, uint32_t smem_addr, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(tm)),
+               "r"(smem_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+struct HaloArgs {
+  int N, H, W;
+  int tiles_h;        // ceil(H / 2): a tile is two output rows
+  int total;          // N * tiles_h
+  float* stat_sums;   // fprop, optional: [2][64] fp32 (as GemmArgs::stat_sums)
+};
+
+constexpr int kHaloWP = 64;                              // pixels per box row
+constexpr int kHaloABytes = 4 * kHaloWP * 128;           // 32 KB
+constexpr int kHaloBBytes = 9 * 64 * 128;                // 72 KB
+constexpr int kHaloStages = 3;
+
+// B_MN: dgrad — the filter tap is taken flipped and MN-major straight from the KRSC filters (rows = output channels of the
+// forward convolution = reduction, columns = input channels).  BatchNorm statistics of the output when stat_sums != NULL.  The
+// dgrad WITH BatchNorm-backward sums (bnb_*) stays on the im2col kernel: a version of this kernel that also fetched the x0 tile
+// measured 115-146 us against 111 us there (64 -> 64 @56, batch 256): the extra shared-memory traffic of its epilogue competes
+// with the operand reads of an already shared-memory-bound N = 64 MMA stream.
+constexpr int kHaloThreads = 64 + 8 * 32;   // TMA warp, MMA warp, eight epilogue warps
+template <bool B_MN>
+__global__ void __launch_bounds__(kHaloThreads)
+conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmO,
+                    const HaloArgs g) {
+  constexpr int STAGES = kHaloStages, ACC = 2, BN = 64;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("dv conv3x3_halo: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  uint8_t* sB = smem + STAGES * kHaloABytes;     // also what the last stage's wrapped-around rows (2 pixels) read: never stored
+  uint8_t* stage_out = sB + kHaloBBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + kEpiStageBytes);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint64_t* tempty_bar = tfull_bar + ACC;
+  uint64_t* bfull_bar = tempty_bar + ACC;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bfull_bar + 1);
+
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmX);
+    prefetch_tmap(&tmW);
+    prefetch_tmap(&tmO);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < ACC; ++i) {
+      mbar_init(&tfull_bar[i], 1);
+      mbar_init(&tempty_bar[i], 8);
+    }
+    mbar_init(bfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, ACC * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (elect_one()) {   // the nine filter taps, once
+      mbar_expect_tx(bfull_bar, kHaloBBytes);
+#pragma unroll
+      for (int t = 0; t < 9; ++t) tma_load_2d(sB + t * 8192, &tmW, bfull_bar, t * 64, 0);
+    }
+    __syncwarp();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < g.total; tile += gridDim.x) {
+      const int n = tile / g.tiles_h, h0 = (tile - n * g.tiles_h) * 2;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (elect_one()) {
+        mbar_expect_tx(&full_bar[stage], kHaloABytes);
+        tma_load_4d(smem + stage * kHaloABytes, &tmX, &full_bar[stage], 0, -1, h0 - 1, n);
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(kBlockM, BN, 0, B_MN ? 1 : 0);
+    constexpr uint32_t kBStep = B_MN ? (2048u >> 4) : 2u;
+    const uint32_t a_lo0 = desc_lo_kmajor(smem_u32(smem));
+    const uint32_t b_lo0 = B_MN ? desc_lo_mnmajor(smem_u32(sB)) : desc_lo_kmajor(smem_u32(sB));
+    mbar_wait(bfull_bar, 0);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < g.total; tile += gridDim.x) {
+      mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        const uint32_t a_st = a_lo0 + (uint32_t)stage * (uint32_t)(kHaloABytes >> 4);
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const int r = t / 3, s = t - 3 * r;
+          const uint32_t a_lo = a_st + (uint32_t)((r * kHaloWP + s) * 128 >> 4);
+          const uint32_t b_lo = b_lo0 + (uint32_t)((B_MN ? 8 - t : t) * (8192 >> 4));
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_f16(d_tmem, desc_pack(a_lo + k * 2u), desc_pack(b_lo + k * kBStep), idesc, (t | k) ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[stage]);
+        umma_commit(&tfull_bar[acc]);
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
+    }
+    __syncwarp();
+  } else {
+    // Eight epilogue warps.  Warp (quarter, half) owns accumulator rows 32*quarter .. +31 — output row h0 + (quarter >> 1), image
+    // columns 32*(quarter & 1) .. +31 — and output channels 32*half .. +31: one tcgen05.ld, a [32 pixels][32 channels] staging tile
+    // (64-byte rows, SWIZZLE_64B: 16-byte chunk index XOR (row >> 1) & 3), one TMA store, column sums from the staged bf16 values.
+    const int quarter = warp & 3, ew = warp - 2, col0 = (ew >> 2) * 32;
+    const int rho = quarter >> 1, kap0 = (quarter & 1) * 32;
+    uint8_t* my_stage = stage_out + ew * (32 * 64);
+    const uint32_t my_stage_u32 = smem_u32(my_stage);
+    const int nvalid_w = g.W - kap0 < 0 ? 0 : (g.W - kap0 > 32 ? 32 : g.W - kap0);   // columns of this warp inside the image
+    // column sums: lane (rh, cp) = (lane >> 4, lane & 15) walks the even (rh = 0) or odd rows of channel pair 2*cp, 2*cp+1 (one 32-bit word per row)
+    const int rh = lane >> 4, cp = lane & 15;
+    const int my_off = ((cp >> 2) * 16) + (cp & 3) * 4;   // byte offset of that channel pair in an unswizzled 64-byte row
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);   // running sums of the lane's channel pair and row half
+    for (int tile = blockIdx.x; tile < g.total; tile += gridDim.x) {
+      const int n = tile / g.tiles_h, h = (tile - n * g.tiles_h) * 2 + rho;
+      const int nvalid = h < g.H ? nvalid_w : 0;   // rows of this warp's 32 that are pixels of the image
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + col0);
+      uint32_t v[32];
+      tmem_ld_32x32(t_addr, v);
+      tmem_ld_wait();
+      // the accumulator columns are in registers: hand them back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&tempty_bar[acc]);
+        tma_store_wait_read();   // the previous tile's store has read the staging buffer
+      }
+      if (++acc == ACC) { acc = 0; acc_phase ^= 1; }
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          __nv_bfloat162 hh = __floats2bfloat162_rn(__uint_as_float(v[j * 8 + 2 * e]), __uint_as_float(v[j * 8 + 2 * e + 1]));
+          w[e] = *reinterpret_cast<uint32_t*>(&hh);
+        }
+        const int ch = j ^ ((lane >> 1) & 3);
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(my_stage_u32 + lane * 64 + ch * 16), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                     "r"(w[3])
+                     : "memory");
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0 && nvalid > 0) tma_store_4d(&tmO, my_stage_u32, col0, kap0, h, n);   // columns >= W of the box are clipped
+      if (nvalid > 0 && g.stat_sums != nullptr) {
+        float2 a = make_float2(0.f, 0.f), b = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {   // rows outside the image are skipped
+          const int r = 2 * i + rh;   // even / odd rows: the two half-warps read different banks
+          if (r < nvalid) {
+            const uint32_t word = *reinterpret_cast<const uint32_t*>(my_stage + r * 64 + (my_off ^ (((r >> 1) & 3) << 4)));
+            const float2 d = make_float2(__uint_as_float(word << 16), __uint_as_float(word & 0xffff0000u));
+            a = __fadd2_rn(a, d);
+            b = __ffma2_rn(d, d, b);
+          }
+        }
+        s1 = __fadd2_rn(s1, a);
+        s2 = __fadd2_rn(s2, b);
+      }
+    }
+    if (g.stat_sums != nullptr) {   // the two row halves of a channel pair meet, then one atomic per channel
+      s1.x += __shfl_xor_sync(0xffffffffu, s1.x, 16); s1.y += __shfl_xor_sync(0xffffffffu, s1.y, 16);
+      s2.x += __shfl_xor_sync(0xffffffffu, s2.x, 16); s2.y += __shfl_xor_sync(0xffffffffu, s2.y, 16);
+      if (rh == 0) {
+        const int col = col0 + 2 * cp;
+        atomicAdd(g.stat_sums + col, s1.x);
+        atomicAdd(g.stat_sums + col + 1, s1.y);
+        atomicAdd(g.stat_sums + 64 + col, s2.x);
+        atomicAdd(g.stat_sums + 64 + col + 1, s2.y);
+      }
+    }
+    if (lane == 0) tma_store_wait_read();   // shared memory must outlive the last bulk store's reads
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, ACC * BN);
+}
+
+}  // namespace
+
+// fprop or stride-1 dgrad of a 3x3 pad-1 convolution with 64 input and 64 output channels whose rows fit the 64-pixel box
+bool conv3x3_halo_supported(const dv_conv_params* p, int pass) {
+  static const int enabled = [] { const char* v = getenv("DV_TC_HALO"); return v ? atoi(v) : 1; }();
+  if (!enabled || (pass != DV_CONV_FPROP && pass != DV_CONV_DGRAD)) return false;
+  if (p->dtype != DV_BF16 || p->R != 3 || p->S != 3 || p->stride != 1 || p->pad != 1 || p->C != 64 || p->K != 64) return false;
+  if (p->W > kHaloWP - 2 || p->W < 24 || p->H < 2) return false;   // narrower rows waste most of the 64-pixel box
+  if (p->y_f32 || p->accumulate || p->ep_scale || p->ep_shift || p->ep_residual || p->ep_relu) return false;
+  if (pass == DV_CONV_DGRAD && p->w_t != nullptr) return false;     // KRSC filters, read MN-major
+  if (p->bnb_x != nullptr) return false;
+  return true;
+}
+
+int conv3x3_halo(const dv_conv_params* p, int pass, cudaStream_t st) {
+  const bool dgrad = pass == DV_CONV_DGRAD;
+  const void* in = dgrad ? p->y : p->x;     // dy [N,H,W,64] (stride 1, pad 1: P = H, Q = W)  /  x
+  void* out = dgrad ? p->x : p->y;          // dx / y
+  alignas(64) CUtensorMap tmX, tmW, tmO;
+  const uint64_t dims[4] = {64, (uint64_t)p->W, (uint64_t)p->H, (uint64_t)p->N};
+  const uint64_t strides[3] = {128, (uint64_t)p->W * 128, (uint64_t)p->H * p->W * 128};
+  const uint32_t box_in[4] = {64, (uint32_t)kHaloWP, 4, 1}, box_out[4] = {32, 32, 1, 1};   // out: one epilogue warp's [32 px][32 ch], SWIZZLE_64B
+  int rc = make_tiled_map_bf16(&tmX, in, 4, dims, strides, box_in, 3);
+  if (rc) return rc;
+  rc = make_tiled_map_bf16(&tmO, out, 4, dims, strides, box_out, 2);
+  if (rc) return rc;
+  rc = make_map_2d(&tmW, p->w, 64, (uint64_t)9 * 64, 64);   // KRSC [64][9*64]: one [64][64] box per tap, either way round
+  if (rc) return rc;
+  HaloArgs g{};
+  g.N = p->N; g.H = p->H; g.W = p->W;
+  g.tiles_h = (p->H + 1) / 2;
+  g.total = p->N * g.tiles_h;
+  g.stat_sums = dgrad ? nullptr : p->stat_sums;
+  const int grid = g.total < num_sms() ? g.total : num_sms();
+  constexpr int smem = kHaloStages * kHaloABytes + kHaloBBytes + kEpiStageBytes + 256;
+  static_assert(smem <= 227 * 1024, "halo kernel exceeds shared memory");
+  if (dgrad) {
+    DV_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    conv3x3_halo_kernel<true><<<grid, kHaloThreads, smem, st>>>(tmX, tmW, tmO, g);
+  } else {
+    DV_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    conv3x3_halo_kernel<false><<<grid, kHaloThreads, smem, st>>>(tmX, tmW, tmO, g);
+  }
+  DV_LAUNCH_OK("conv3x3_halo_kernel");
+  return DV_OK;
+}
+
+}  // namespace dv

@@ -30,6 +30,9 @@ TC_CASES = [
     (151, 64, 16, 8, 256, 1, 1, 0),   # CTA-pair kernel (M >= 18944, K = 256): 151 M tiles = an odd, half-empty last pair
     (149, 64, 13, 10, 256, 1, 1, 0),  # CTA-pair kernel, ragged last tile (M = 19370)
     (38, 64, 24, 24, 256, 3, 1, 1),   # CTA-pair kernel with im2col loads (M = 21888 = 171 tiles)
+    (3, 64, 30, 56, 64, 3, 1, 1),     # halo-tile kernel (3x3, 64 -> 64, 24 <= W <= 62): ResNet's conv2x row width
+    (2, 64, 7, 62, 64, 3, 1, 1),      # halo-tile kernel: widest row the 64-pixel box takes, odd height (last tile = one row)
+    (150, 64, 4, 25, 64, 3, 1, 1),    # halo-tile kernel: more tiles than SMs (ring and accumulators wrap), second warp column mostly empty
 ]
 
 
@@ -291,7 +294,8 @@ def test_tc_fp32_logits_and_dgrad_accumulate():
 
 
 @pytest.mark.parametrize("case", [(2, 64, 8, 8, 64, 3, 1, 1), (3, 128, 7, 7, 256, 1, 1, 0), (4, 64, 12, 12, 512, 1, 1, 0),
-                                  (2, 256, 9, 9, 1000, 1, 1, 0)], ids=lambda c: "x".join(map(str, c)))
+                                  (2, 256, 9, 9, 1000, 1, 1, 0), (3, 64, 9, 40, 64, 3, 1, 1), (150, 64, 4, 25, 64, 3, 1, 1)],
+                         ids=lambda c: "x".join(map(str, c)))
 def test_tc_fprop_fused_bn_sums(case):
     """The epilogue's per-channel sums (dv_conv_params.stat_sums) equal the sums of the stored bf16 output, and
     dv_bn_stats_from_sums turns them into the statistics dv_bn_stats computes from that output."""
@@ -399,6 +403,8 @@ BNB_CASES = [
     (151, 64, 16, 8, 256, 1, 0),      # many M tiles per CTA: running sums across tiles, one flush
     (38, 256, 24, 24, 64, 1, 0),      # CTA-pair kernel (M = 21888, 256 columns)
     (37, 256, 24, 23, 128, 3, 1),     # CTA-pair kernel, 3x3, odd number of M tiles (the peer's last tile is empty)
+    (3, 64, 9, 40, 64, 3, 1),         # the halo-tile geometry (its plain dgrad takes the halo kernel, the one with sums the im2col kernel), odd height
+    (150, 64, 4, 25, 64, 3, 1),       # the same, more tiles than SMs
 ]
 
 

@@ -47,8 +47,11 @@ def run_job(which, shape, iters):
     y = torch.empty(N, H, H, K, device="cuda", dtype=torch.bfloat16)
     p = ConvParams()
     p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.stride, p.pad, p.dtype, p.algo = N, H, H, Cc, K, R, R, 1, R // 2, DV_BF16, DV_ALGO_TC
-    if which == "fprop":
+    if which in ("fprop", "fprop_stats"):
         p.x, p.w, p.y = x.data_ptr(), w.data_ptr(), y.data_ptr()
+        if which == "fprop_stats":    # with the following BatchNorm's statistics from the epilogue (what the training step launches)
+            sums = torch.zeros(2 * K, device="cuda")
+            p.stat_sums = sums.data_ptr()
         fn = lambda: check(lib.dv_conv_fprop(C.byref(p), st), "fprop")
     elif which in ("dgrad", "dgrad_bnb"):
         dx = torch.empty_like(x)
