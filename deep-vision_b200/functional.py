@@ -6,6 +6,7 @@ memory; torch only owns the memory and the autograd graph, every byte of arithme
 current CUDA stream.  Nothing here falls back to torch ops or to the CPU.
 """
 import ctypes as C
+from os import environ as _environ
 
 import torch
 
@@ -480,6 +481,9 @@ def _dw_params(x_ptr, w_ptr, y_ptr, N, H, W, Cc, stride, dtype):
     return p
 
 
+_DW_SIDE = _environ.get("DV_DW_SIDE", "1") == "1"   # experiment knob: depth-wise weight gradients on the side stream
+
+
 class _DwConv3x3(torch.autograd.Function):
     """nn.Conv2d(C, C, 3, padding=1, stride, groups=C, bias=False) — mobilenet_v1.py:112-122."""
 
@@ -519,12 +523,25 @@ class _DwConv3x3(torch.autograd.Function):
             p = _dw_params(dx.data_ptr(), w.data_ptr(), dy.data_ptr(), N, H, W, Cc, stride, dt)
             check(lib.dv_dwconv_dgrad(C.byref(p), _stream()), "dv_dwconv_dgrad")
         if ctx.needs_input_grad[1]:
-            dw = torch.empty_like(w)
+            sink = grad_sink(weight)
+            dw = sink[0] if sink else torch.empty_like(w)   # the flat buffer's slice for [C,1,3,3] is [C][3][3] fp32 as well
             p = _dw_params(x.data_ptr(), dw.data_ptr(), dy.data_ptr(), N, H, W, Cc, stride, dt)
-            need = lib.dv_dwconv_workspace_bytes(C.byref(p))
-            ws = _workspace(need, x.device)
-            p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
-            check(lib.dv_dwconv_wgrad(C.byref(p), _stream()), "dv_dwconv_wgrad")
+
+            def launch():
+                need = lib.dv_dwconv_workspace_bytes(C.byref(p))
+                ws = _workspace(need, x.device)     # per stream: the side stream has its own scratch
+                p.workspace, p.workspace_bytes = ws.data_ptr(), ws.numel()
+                check(lib.dv_dwconv_wgrad(C.byref(p), _stream()), "dv_dwconv_wgrad")
+
+            side = _side_wgrad["obj"] if (sink and _DW_SIDE) else None   # nothing in the backward chain waits for a weight gradient
+            if side is not None:
+                with torch.cuda.stream(side.fork(x, dy)):
+                    launch()
+            else:
+                launch()
+            if sink:
+                sink[1](weight)
+                dw = None
         return dx, dw, None, None
 
 

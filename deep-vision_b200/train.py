@@ -201,7 +201,7 @@ class Trainer:
         noop = lambda _p: None
         for m in self.model.modules():
             targets = []
-            if isinstance(m, dvnn.Conv2d) and not m._dv_depthwise:
+            if isinstance(m, dvnn.Conv2d):     # dense and depth-wise ([C,1,3,3] is laid out [C][3][3] either way)
                 targets = [m.weight]
             elif isinstance(m, dvnn.BatchNorm2d) and m.affine:
                 targets = [m.weight, m.bias]

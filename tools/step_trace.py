@@ -17,6 +17,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--model", default="resnet50")
 ap.add_argument("--batch", type=int, default=256)
 ap.add_argument("--out", default="gpurun_out/step_trace.md")
+ap.add_argument("--launches", default="", help="also write the launch sequence of the last step: start (us), duration (us), kernel")
 args = ap.parse_args()
 import torch.distributed as dist  # noqa: E402
 rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
@@ -76,6 +77,13 @@ with open(args.out, "a") as f:
         f.write(f"* {g:.1f}  `{a}` -> `{b}`\n")
     hist = collections.Counter(min(int(g), 10) for g in gaps)
     f.write("\nGap histogram (us, 10 = 10 or more): " + ", ".join(f"{k}: {v // STEPS}" for k, v in sorted(hist.items())) + "\n")
+if args.launches:
+    last = ev[len(ev) - len(ev) // STEPS:]
+    t0 = last[0].time_range.start
+    with open(args.launches, "w") as f:
+        for e in last:
+            k = e.name.replace("(anonymous namespace)::", "").replace("void ", "").split("(")[0][:90]
+            f.write(f"{e.time_range.start - t0:10.1f} {e.time_range.end - e.time_range.start:8.1f}  {k}\n")
 print(open(args.out).read()[:3000])
 if world > 1:
     sys.stdout.flush()
