@@ -211,6 +211,15 @@ struct DwTmaArgs {
   int flip, ep_relu;
   const float* ep_shift;
   float* stat_sums;        // fprop, optional: [2][C] += per-channel sum and sum of squares of the bf16-rounded outputs (BatchNorm statistics)
+  // stride-1 dgrad, optional (template BNB): the output dx is the gradient w.r.t. relu(bn(x0)); the kernel ADDS that BatchNorm's
+  // backward sums  dbeta += sum dz,  dgamma += invstd * sum dz * (x0 - mean),  dz = dx * (bn(x0) > 0)  (as dv_conv_params.bnb_*)
+  const bf16* bnb_x;
+  const float* bnb_gamma;
+  const float* bnb_beta;
+  const float* bnb_mean;
+  const float* bnb_invstd;
+  float* bnb_dgamma;
+  float* bnb_dbeta;
 };
 
 template <int CB, int ST = 1, int RW = 1>
@@ -225,7 +234,7 @@ struct DwTile {
 
 // RW = output rows per thread (stride 1 only): with two rows a thread reads 4 input rows for 8 outputs instead of 6, and the strip
 // kernel's instruction count per output, which is what bounds the stride-1 case, drops by a third.
-template <int CB, int ST, int RW, int STAGES>
+template <int CB, int ST, int RW, int STAGES, bool BNB = false>
 __global__ void __launch_bounds__(kThreads, (ST == 1 && RW == 1) ? 2 : 1)
 dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __restrict__ w, bf16* __restrict__ out, const DwTmaArgs g) {
   static_assert(RW == 1 || ST == 1, "two rows per thread exist for stride 1 only");
@@ -263,13 +272,36 @@ dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __re
   float2 bias[H2];
 #pragma unroll
   for (int e = 0; e < H2; ++e) bias[e] = g.ep_shift != nullptr ? make_float2(g.ep_shift[c + 2 * e], g.ep_shift[c + 2 * e + 1]) : make_float2(0.f, 0.f);
-  float2 st1[H2], st2[H2];   // running sum / sum of squares of what this thread stored
+  float2 st1[H2], st2[H2];   // running sum / sum of squares of what this thread stored  (BNB: sum dz / sum dz * (x0 - mean))
 #pragma unroll
   for (int e = 0; e < H2; ++e) { st1[e] = make_float2(0.f, 0.f); st2[e] = make_float2(0.f, 0.f); }
+  float2 bsc[BNB ? H2 : 1], bsh[BNB ? H2 : 1], bnmu[BNB ? H2 : 1];   // bn_apply's expressions: the mask bits agree with its output
+  if (BNB) {
+#pragma unroll
+    for (int e = 0; e < H2; ++e) {
+      const int ch = c + 2 * e < g.C ? c + 2 * e : 0;
+      const float mu0 = g.bnb_mean[ch], mu1 = g.bnb_mean[ch + 1];
+      bsc[e] = make_float2(g.bnb_invstd[ch] * g.bnb_gamma[ch], g.bnb_invstd[ch + 1] * g.bnb_gamma[ch + 1]);
+      bsh[e] = make_float2(g.bnb_beta[ch] - mu0 * bsc[e].x, g.bnb_beta[ch + 1] - mu1 * bsc[e].y);
+      bnmu[e] = make_float2(-mu0, -mu1);
+    }
+  }
 
   for (int it = 0; it < my_tiles; ++it) {
     const int s = it % STAGES;
     const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+    if (BNB) {   // the x0 vectors this thread will need behind its stores: start them towards the L2 before the tile's arithmetic
+      const int tile_ = blockIdx.x + it * gridDim.x;
+      const int n_ = tile_ / per_img, rem_ = tile_ - n_ * per_img;
+      const int th_ = rem_ / g.tiles_w, tw_ = rem_ - th_ * g.tiles_w;
+      const int oh_ = th_ * TL::TH + row * RW, ow_ = tw_ * TL::TW + col0;
+      if (oh_ < g.OH && c < g.C) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (ow_ + j < g.OW)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(g.bnb_x + (((size_t)n_ * g.OH + oh_) * g.OW + ow_ + j) * g.C + c));
+      }
+    }
     dw_mbar_wait(&full_bar[s], ph);
     const uint8_t* tile_in = tiles + s * TL::STAGE_BYTES;
     float2 acc[RW][4][H2];
@@ -335,7 +367,20 @@ dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __re
             Vec16<bf16> ov;
             pack2(ov, acc[o][j]);
             ov.store(orow + (size_t)j * g.C);
-            if (g.stat_sums != nullptr) {   // from the rounded values: what the BatchNorm will read back
+            if (BNB) {   // dz from the rounded dx (what bn_bwd_apply will read back) and the matching x0 vector
+              Vec16<bf16> xr;
+              xr.load(g.bnb_x + (((size_t)n * g.OH + oh) * g.OW + ow0 + j) * g.C + c);
+              float2 rv[H2], x0[H2];
+              unpack2(ov, rv);
+              unpack2(xr, x0);
+#pragma unroll
+              for (int e = 0; e < H2; ++e) {
+                const float2 pre = __ffma2_rn(x0[e], bsc[e], bsh[e]);
+                const float2 z = make_float2(pre.x > 0.f ? rv[e].x : 0.f, pre.y > 0.f ? rv[e].y : 0.f);
+                st1[e] = __fadd2_rn(st1[e], z);
+                st2[e] = __ffma2_rn(z, __fadd2_rn(x0[e], bnmu[e]), st2[e]);
+              }
+            } else if (g.stat_sums != nullptr) {   // from the rounded values: what the BatchNorm will read back
               float2 rv[H2];
               unpack2(ov, rv);
 #pragma unroll
@@ -345,7 +390,7 @@ dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __re
       }
     }
   }
-  if (g.stat_sums != nullptr) {   // CTA-wide: strips of one channel group -> one pair of atomics per channel
+  if (BNB || g.stat_sums != nullptr) {   // CTA-wide: strips of one channel group -> one pair of atomics per channel
     __syncthreads();
     float* red = reinterpret_cast<float*>(dw_smem);
 #pragma unroll
@@ -359,7 +404,14 @@ dwconv_tma_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const float* __re
       float sum = 0.f;
       for (int l = 0; l < TL::NSTRIP; ++l) sum += red[(l * TL::GROUPS + grp) * 16 + k];
       const int ch = c0 + grp * V + (k & 7);
-      if (ch < g.C) atomicAdd(g.stat_sums + (k < 8 ? 0 : g.C) + ch, sum);
+      if (ch < g.C) {
+        if (BNB) {
+          if (k < 8) atomicAdd(g.bnb_dbeta + ch, sum);
+          else atomicAdd(g.bnb_dgamma + ch, sum * g.bnb_invstd[ch]);
+        } else {
+          atomicAdd(g.stat_sums + (k < 8 ? 0 : g.C) + ch, sum);
+        }
+      }
     }
   }
 }
@@ -784,7 +836,8 @@ static int wgrad_blocks(const DwDims& d, int lanes, int* per_blk) {
 // dy -> dx with flipped taps)
 template <int CB, int ST>
 static int launch_dw_tma_fwd(const void* in, const float* w, void* out, int N, int H, int W, int OH, int OW, int C, int flip,
-                             const float* ep_shift, int ep_relu, cudaStream_t st, float* stat_sums = nullptr) {
+                             const float* ep_shift, int ep_relu, cudaStream_t st, float* stat_sums = nullptr,
+                             const dv_dwconv_params* bnb = nullptr) {
   constexpr int RW = ST == 1 ? DV_DW_RW : 1;
   using TL = DwTile<CB, ST, RW>;
   constexpr int STAGES = (ST == 1 && RW == 1) ? 3 : (ST == 1 ? 3 : 2);
@@ -798,6 +851,10 @@ static int launch_dw_tma_fwd(const void* in, const float* w, void* out, int N, i
   g.N = N; g.OH = OH; g.OW = OW; g.C = C;
   g.tiles_h = ceil_div(OH, TL::TH); g.tiles_w = ceil_div(OW, TL::TW);
   g.flip = flip; g.ep_relu = ep_relu; g.ep_shift = ep_shift; g.stat_sums = stat_sums;
+  if (bnb != nullptr) {
+    g.bnb_x = (const bf16*)bnb->bnb_x; g.bnb_gamma = bnb->bnb_gamma; g.bnb_beta = bnb->bnb_beta; g.bnb_mean = bnb->bnb_mean;
+    g.bnb_invstd = bnb->bnb_invstd; g.bnb_dgamma = bnb->bnb_dgamma; g.bnb_dbeta = bnb->bnb_dbeta;
+  }
   constexpr int smem = STAGES * TL::STAGE_BYTES + 9 * CB * 4 + 2 * STAGES * 8;
   static_assert(smem <= 227 * 1024, "depth-wise tile ring exceeds shared memory");
   DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_fwd_kernel<CB, ST, RW, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -807,6 +864,14 @@ static int launch_dw_tma_fwd(const void* in, const float* w, void* out, int N, i
   int gx = ((ST == 1 && RW == 1) ? 2 : 1) * num_sms() / cblocks;
   if (gx < 1) gx = 1;
   if (gx > ntiles) gx = (int)ntiles;
+  if constexpr (ST == 1) {
+    if (bnb != nullptr) {
+      DV_CUDA_OK(cudaFuncSetAttribute(dwconv_tma_fwd_kernel<CB, ST, RW, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+      dwconv_tma_fwd_kernel<CB, ST, RW, STAGES, true><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, w, (bf16*)out, g);
+      DV_LAUNCH_OK("dwconv_tma_fwd_kernel<bnb>");
+      return DV_OK;
+    }
+  }
   dwconv_tma_fwd_kernel<CB, ST, RW, STAGES><<<dim3((unsigned)gx, (unsigned)cblocks), kThreads, smem, st>>>(tm, w, (bf16*)out, g);
   DV_LAUNCH_OK("dwconv_tma_fwd_kernel");
   return DV_OK;
@@ -879,9 +944,16 @@ static int run_dgrad(const dv_dwconv_params* p, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   DV_REQUIRE(p->C % V == 0, DV_ERR_UNSUPPORTED, "dwconv: C=%d must be a multiple of %d", p->C, V);
   DwDims d = dims_of(p);
-  if (sizeof(T) == 2 && d.stride == 1 && dw_tma_ok(p))
-    return p->C % 64 == 0 ? launch_dw_tma_fwd<64, 1>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.H, d.W, d.C, 1, nullptr, 0, st)
-                          : launch_dw_tma_fwd<32, 1>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.H, d.W, d.C, 1, nullptr, 0, st);
+  if (sizeof(T) == 2 && d.stride == 1 && dw_tma_ok(p)) {
+    const dv_dwconv_params* bnb = p->bnb_x != nullptr ? p : nullptr;
+    if (bnb != nullptr)
+      DV_REQUIRE(p->bnb_gamma && p->bnb_beta && p->bnb_mean && p->bnb_invstd && p->bnb_dgamma && p->bnb_dbeta && ((uintptr_t)p->bnb_x & 15) == 0,
+                 DV_ERR_ARG, "dwconv dgrad: bnb_x given but one of bnb_gamma/beta/mean/invstd/dgamma/dbeta is null (or bnb_x is not 16-byte aligned)");
+    return p->C % 64 == 0 ? launch_dw_tma_fwd<64, 1>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.H, d.W, d.C, 1, nullptr, 0, st, nullptr, bnb)
+                          : launch_dw_tma_fwd<32, 1>(p->y, (const float*)p->w, p->x, d.N, d.H, d.W, d.H, d.W, d.C, 1, nullptr, 0, st, nullptr, bnb);
+  }
+  DV_REQUIRE(p->bnb_x == nullptr, DV_ERR_UNSUPPORTED,
+             "dwconv dgrad: bnb_* (BatchNorm-backward sums) is honoured by the TMA-staged stride-1 kernel only (ask dv_dwconv_fuses_bn_bwd)");
   DwPlan pl = dw_plan(p->C, V);
   int nb, per;
   if (d.stride == 1) {
@@ -1019,9 +1091,14 @@ extern "C" int dv_dwconv_fuses_stats(const dv_dwconv_params* p) {
   if (!p || (p->stride != 1 && p->stride != 2) || p->dtype != DV_BF16 || !dw_tma_ok(p)) return 0;
   return dims_of(p).Q >= 8 ? 1 : 0;
 }
+extern "C" int dv_dwconv_fuses_bn_bwd(const dv_dwconv_params* p) {
+  if (!p || p->stride != 1 || p->dtype != DV_BF16 || !dw_tma_ok(p)) return 0;
+  return 1;
+}
 extern "C" int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_fprop");
   if (rc) return rc;
+  DV_REQUIRE(p->bnb_x == nullptr, DV_ERR_UNSUPPORTED, "dv_dwconv_fprop: bnb_* belongs to dgrad");
   return p->dtype == DV_BF16 ? run_fprop<bf16>(p, (cudaStream_t)stream) : run_fprop<float>(p, (cudaStream_t)stream);
 }
 extern "C" int dv_dwconv_dgrad(const dv_dwconv_params* p, void* stream) {
@@ -1034,5 +1111,6 @@ extern "C" int dv_dwconv_wgrad(const dv_dwconv_params* p, void* stream) {
   int rc = check(p, "dv_dwconv_wgrad");
   if (rc) return rc;
   DV_REQUIRE(p->ep_shift == nullptr && p->ep_relu == 0, DV_ERR_UNSUPPORTED, "dv_dwconv_wgrad: the folded epilogue is fprop-only");
+  DV_REQUIRE(p->bnb_x == nullptr, DV_ERR_UNSUPPORTED, "dv_dwconv_wgrad: bnb_* belongs to dgrad");
   return p->dtype == DV_BF16 ? run_wgrad<bf16>(p, (cudaStream_t)stream) : run_wgrad<float>(p, (cudaStream_t)stream);
 }

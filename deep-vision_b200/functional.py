@@ -481,6 +481,10 @@ def _dw_params(x_ptr, w_ptr, y_ptr, N, H, W, Cc, stride, dtype):
     return p
 
 
+# BatchNorm-backward sums from the stride-1 depth-wise dgrad (dv_dwconv_params.bnb_*): correct and tested, but that kernel is bound
+# by its fp32 arithmetic, and the extra x0 vector + mask + two sums per output cost what the saved reduce pass gains
+# (MobileNetV1 step 7.51 vs 7.48 ms) — opt-in.
+_DW_BNB = _environ.get("DV_DW_FUSE_BN_BWD", "0") == "1"
 _DW_SIDE = _environ.get("DV_DW_SIDE", "1") == "1"   # experiment knob: depth-wise weight gradients on the side stream
 
 
@@ -488,7 +492,10 @@ class _DwConv3x3(torch.autograd.Function):
     """nn.Conv2d(C, C, 3, padding=1, stride, groups=C, bias=False) — mobilenet_v1.py:112-122."""
 
     @staticmethod
-    def forward(ctx, x, weight, stride, stats=None):
+    def forward(ctx, x, weight, stride, stats=None, handoff=None):
+        ctx.handoff = handoff
+        if handoff is not None:
+            handoff.claims += 1
         _require_cuda(x, "dwconv3x3")
         x = _nhwc(x)
         N, Cc, H, W = x.shape
@@ -521,7 +528,20 @@ class _DwConv3x3(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x, memory_format=_CL)
             p = _dw_params(dx.data_ptr(), w.data_ptr(), dy.data_ptr(), N, H, W, Cc, stride, dt)
+            h, fused = ctx.handoff, None
+            if (h is not None and h.x is not None and h.claims == 1 and config.fuse_bn_bwd() and _DW_BNB
+                    and lib.dv_dwconv_fuses_bn_bwd(C.byref(p)) == 1):
+                # this dx is dy of the BatchNorm that produced x (pw.bn -> relu -> dw): the kernel adds that layer's dgamma / dbeta
+                sg, sb = grad_sink(h.gamma), grad_sink(h.beta)
+                dgamma = sg[0] if sg else torch.zeros(Cc, dtype=torch.float32, device=x.device)
+                dbeta = sb[0] if sb else torch.zeros(Cc, dtype=torch.float32, device=x.device)
+                p.bnb_x, p.bnb_gamma, p.bnb_beta = h.x.data_ptr(), h.gamma.data_ptr(), h.beta.data_ptr()
+                p.bnb_mean, p.bnb_invstd = h.mean.data_ptr(), h.invstd.data_ptr()
+                p.bnb_dgamma, p.bnb_dbeta = dgamma.data_ptr(), dbeta.data_ptr()
+                fused = (dgamma, dbeta)
             check(lib.dv_dwconv_dgrad(C.byref(p), _stream()), "dv_dwconv_dgrad")
+            if fused is not None:
+                h.result = (dx, fused[0], fused[1])
         if ctx.needs_input_grad[1]:
             sink = grad_sink(weight)
             dw = sink[0] if sink else torch.empty_like(w)   # the flat buffer's slice for [C,1,3,3] is [C][3][3] fp32 as well
@@ -542,11 +562,11 @@ class _DwConv3x3(torch.autograd.Function):
             if sink:
                 sink[1](weight)
                 dw = None
-        return dx, dw, None, None
+        return dx, dw, None, None, None
 
 
 def dwconv3x3(x, weight, stride=1, stats=None):
-    y = _DwConv3x3.apply(x, weight, int(stride), stats)
+    y = _DwConv3x3.apply(x, weight, int(stride), stats, getattr(x, "_dv_bn_handoff", None))
     if stats is not None and stats.pending:
         y._dv_stat_sums = stats   # picked up by the BatchNorm that consumes y
     return y
@@ -703,7 +723,7 @@ def batch_norm_act(x, residual, gamma, beta, running_mean, running_var, training
     y = _BatchNormAct.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum), float(eps),
                             bool(relu), res_slot, sums, handoff)
     if handoff is not None and handoff.x is not None:
-        y._dv_bn_handoff = handoff      # claimed by the dense convolution that consumes y (functional.conv2d)
+        y._dv_bn_handoff = handoff      # claimed by the convolution that consumes y (functional.conv2d / dwconv3x3)
     return y
 
 

@@ -44,6 +44,8 @@ class DwConvParams(C.Structure):
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t),
         ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("C", C.c_int32), ("stride", C.c_int32),
         ("dtype", C.c_int32), ("ep_shift", C.c_void_p), ("ep_relu", C.c_int32), ("stat_sums", C.c_void_p),
+        ("bnb_x", C.c_void_p), ("bnb_gamma", C.c_void_p), ("bnb_beta", C.c_void_p), ("bnb_mean", C.c_void_p),
+        ("bnb_invstd", C.c_void_p), ("bnb_dgamma", C.c_void_p), ("bnb_dbeta", C.c_void_p),
     ]
 
 
@@ -115,6 +117,7 @@ _SIG = {
     "dv_stem_wgrad": (C.c_int, [C.POINTER(StemParams), _P]),
     "dv_stem_workspace_bytes": (C.c_size_t, [C.POINTER(StemParams)]),
     "dv_dwconv_fuses_stats": (C.c_int, [C.POINTER(DwConvParams)]),
+    "dv_dwconv_fuses_bn_bwd": (C.c_int, [C.POINTER(DwConvParams)]),
     "dv_dwconv_fprop": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_dgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),
     "dv_dwconv_wgrad": (C.c_int, [C.POINTER(DwConvParams), _P]),

@@ -199,8 +199,21 @@ typedef struct dv_dwconv_params {
                          output to — the statistics pass of the BatchNorm that follows (mobilenet_v1.py:126), see dv_bn_stats_from_sums.
                          Honoured by the TMA-staged stride-1 kernel only: dv_dwconv_fuses_stats() answers 1 for such parameters, any
                          other path rejects a non-NULL stat_sums */
+  /* dgrad only, optional — the backward sums of the BatchNorm whose OUTPUT is this convolution's input (pw.bn -> relu -> dw of the
+   * next block, mobilenet_v1.py:129-133,152-156), exactly as dv_conv_params.bnb_*: with bnb_x = that BatchNorm's input x0 [N,H,W,C]
+   * the kernel ADDS dbeta = sum dz and dgamma = sum dz * xhat (dz = dx masked by bn(x0) > 0, from the bf16-rounded dx it stores)
+   * into bnb_dbeta / bnb_dgamma, so dv_bn_bwd_reduce is skipped for that layer.  Honoured by the TMA-staged stride-1 kernel only:
+   * dv_dwconv_fuses_bn_bwd() answers 1 for such parameters, any other path rejects a non-NULL bnb_x. */
+  const void* bnb_x;
+  const float* bnb_gamma;
+  const float* bnb_beta;
+  const float* bnb_mean;
+  const float* bnb_invstd;
+  float* bnb_dgamma;
+  float* bnb_dbeta;
 } dv_dwconv_params;
 int dv_dwconv_fuses_stats(const dv_dwconv_params* p);
+int dv_dwconv_fuses_bn_bwd(const dv_dwconv_params* p);
 
 int dv_dwconv_fprop(const dv_dwconv_params* p, void* stream);
 int dv_dwconv_dgrad(const dv_dwconv_params* p, void* stream);

@@ -522,3 +522,62 @@ def test_bn_relu_maxpool_fused_equals_the_three_separate_ops(shape, dtype):
         assert lib.lib.dv_bn_relu_maxpool_bwd(C.byref(q), stream_ptr()) != 0
     q.C = 24   # not a channel count the kernels take
     assert lib.lib.dv_bn_relu_maxpool_fwd(C.byref(q), stream_ptr()) != 0
+
+
+@pytest.mark.parametrize("case", [(2, 64, 18, 21), (3, 32, 14, 14), (5, 128, 9, 30), (40, 512, 14, 14)], ids=lambda c: "x".join(map(str, c)))
+def test_dwconv_dgrad_fused_bn_backward_sums(case):
+    """dv_dwconv_params.bnb_*: the stride-1 depth-wise dgrad adds dbeta = sum dz and dgamma = sum dz*xhat of the BatchNorm that
+    produced the convolution's input (dz = dx masked by bn(x0) > 0).  dx is unchanged by the option (bit for bit); the sums equal
+    fp64 sums over the kernel's own bf16 dx and dv_bn_bwd_reduce's on the same tensors; they are ADDED to what was there; paths
+    that cannot honour the option reject it."""
+    lib = _lib()
+    N, Cc, H, W = case
+    g = torch.Generator(device="cuda").manual_seed(17)
+    dy = torch.randn((N, H, W, Cc), generator=g, device="cuda").bfloat16()
+    w = (torch.randn((Cc, 1, 3, 3), generator=g, device="cuda") * 0.3).contiguous()
+    x0 = (torch.randn((N, H, W, Cc), generator=g, device="cuda") * 1.5 + 0.3).bfloat16()
+    gamma = torch.rand(Cc, generator=g, device="cuda") + 0.5
+    beta = torch.randn(Cc, generator=g, device="cuda") * 0.3
+    xf = x0.float().reshape(-1, Cc)
+    mean = xf.mean(0)
+    invstd = 1.0 / torch.sqrt(xf.var(0, unbiased=False) + 1e-5)
+
+    def dgrad(with_sums):
+        dx = torch.full((N, H, W, Cc), float("nan"), device="cuda", dtype=torch.bfloat16)
+        dgamma, dbeta = torch.full((Cc,), 2.0, device="cuda"), torch.full((Cc,), -3.0, device="cuda")
+        p = lib.DwConvParams()
+        p.x, p.w, p.y, p.N, p.H, p.W, p.C, p.stride, p.dtype = dx.data_ptr(), w.data_ptr(), dy.data_ptr(), N, H, W, Cc, 1, lib.DV_BF16
+        assert lib.lib.dv_dwconv_fuses_bn_bwd(C.byref(p)) == 1
+        if with_sums:
+            p.bnb_x, p.bnb_gamma, p.bnb_beta, p.bnb_mean, p.bnb_invstd = x0.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr()
+            p.bnb_dgamma, p.bnb_dbeta = dgamma.data_ptr(), dbeta.data_ptr()
+        lib.check(lib.lib.dv_dwconv_dgrad(C.byref(p), stream_ptr()), "dv_dwconv_dgrad")
+        torch.cuda.synchronize()
+        return dx, dgamma, dbeta, p
+
+    dx_plain, _, _, _ = dgrad(False)
+    dx, dgamma, dbeta, p = dgrad(True)
+    assert torch.equal(dx.view(torch.int16), dx_plain.view(torch.int16))
+    sc = (invstd * gamma).double()
+    pre = x0.double().reshape(-1, Cc) * sc + (beta.double() - mean.double() * sc)
+    dz = dx.double().reshape(-1, Cc) * (pre > 0)
+    xhat = (x0.double().reshape(-1, Cc) - mean.double()) * invstd.double()
+    want_b, want_g = dz.sum(0), (dz * xhat).sum(0)
+    scale_b, scale_g = dz.abs().sum(0) + 1e-6, (dz * xhat).abs().sum(0) + 1e-6
+    assert float(((dbeta.double() + 3.0 - want_b).abs() / scale_b).max()) < 1e-4
+    assert float(((dgamma.double() - 2.0 - want_g).abs() / scale_g).max()) < 1e-4
+    q = lib.BnBwdParams()
+    dg2, db2 = torch.empty(Cc, device="cuda"), torch.empty(Cc, device="cuda")
+    M = N * H * W
+    ws = torch.empty(lib.lib.dv_bn_workspace_bytes(M, Cc), dtype=torch.uint8, device="cuda")
+    q.x, q.dy, q.gamma, q.beta, q.save_mean, q.save_invstd = x0.data_ptr(), dx.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), invstd.data_ptr()
+    q.dgamma, q.dbeta, q.workspace, q.workspace_bytes = dg2.data_ptr(), db2.data_ptr(), ws.data_ptr(), ws.numel()
+    q.M, q.C, q.dtype, q.relu = M, Cc, lib.DV_BF16, 1
+    lib.check(lib.lib.dv_bn_bwd_reduce(C.byref(q), stream_ptr()), "bwd_reduce")
+    torch.cuda.synchronize()
+    assert float(((dbeta + 3.0 - db2).double().abs() / scale_b).max()) < 1e-4
+    assert float(((dgamma - 2.0 - dg2).double().abs() / scale_g).max()) < 1e-4
+    # not honoured elsewhere: forward, weight gradient, stride 2
+    assert lib.lib.dv_dwconv_fprop(C.byref(p), stream_ptr()) == lib.DV_ERR_UNSUPPORTED
+    p.stride = 2
+    assert lib.lib.dv_dwconv_fuses_bn_bwd(C.byref(p)) == 0
