@@ -53,6 +53,13 @@ def run_job(which, shape, iters):
             sums = torch.zeros(2 * K, device="cuda")
             p.stat_sums = sums.data_ptr()
         fn = lambda: check(lib.dv_conv_fprop(C.byref(p), st), "fprop")
+    elif which == "dgrad_s2":         # 1x1 stride-2 dgrad (Bottleneck conv1 / projection of a down-sampling block): strided row scatter
+        dx = torch.empty_like(x)
+        dy2 = torch.randn(N, H // 2, H // 2, K, device="cuda").to(torch.bfloat16)
+        p.stride, p.pad = 2, 0
+        p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), dy2.data_ptr()
+        keep = dy2
+        fn = lambda: check(lib.dv_conv_dgrad(C.byref(p), st), "dgrad_s2")
     elif which in ("dgrad", "dgrad_bnb"):
         dx = torch.empty_like(x)
         p.x, p.w, p.y = dx.data_ptr(), w.data_ptr(), y.normal_().data_ptr()
