@@ -1647,6 +1647,8 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
 
 bool conv3x3_halo_supported(const dv_conv_params* p, int pass);
 int conv3x3_halo(const dv_conv_params* p, int pass, cudaStream_t st);
+bool conv3x3_halo_wgrad_supported(const dv_conv_params* p);
+int conv3x3_halo_wgrad(const dv_conv_params* p, cudaStream_t st);
 
 int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
   const char* why;
@@ -1783,6 +1785,7 @@ int conv_tc(const dv_conv_params* p, int pass, cudaStream_t st) {
   }
 
   // wgrad
+  if (conv3x3_halo_wgrad_supported(p)) return conv3x3_halo_wgrad(p, st);
   WgradPlan w = plan_wgrad(p);
   const size_t need = p->accumulate ? 0 : (size_t)w.splits * p->K * p->R * p->S * p->C * sizeof(float);
   DV_REQUIRE(need == 0 || (p->workspace != nullptr && p->workspace_bytes >= need), DV_ERR_WORKSPACE,
@@ -2600,6 +2603,130 @@ conv3x3_halo_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_consta
   if (warp == 1) tmem_dealloc(tmem_base, ACC * BN);
 }
 
+// Weight gradient of the same layer over the same halo tile: dW[k][r][s][c] = sum over pixels of dy[pix][k] * x[pix + (r, s)][c].
+// Both operands are MN-major (a shared-memory row = one pixel = one K index, 128 bytes = 64 channels), so the shifted windows of x are
+// again start addresses, now along K.  The accumulator is kept TRANSPOSED — D[c][k], A = x, B = dy — because then M can be filled:
+// M = 128 is two 64-channel chunks of A whose distance is the descriptor's leading-dimension byte offset, and with that offset set to
+// (offset of tap b - offset of tap a) * 128 bytes ONE MMA produces two taps (rows 0-63: tap a, rows 64-127: tap b; any distance and
+// any start row are legal, tools/probes/umma_row_offset.cu).  The im2col kernel spends an M = 128 MMA per tap with half of its rows
+// on zero-filled output channels and fetches the dy tile and a shifted x tile per tap: 2.77 GB of L2->SM traffic per launch.
+// Here: 5 MMAs per 16 pixels (taps 0+1, 2+3, 4+5, 6+7, 8), one x box + one dy box per two output rows (columns >= W and rows >= H of
+// dy are zero-filled by the TMA unit, so the wrapped-around pixels of x meet zeros), five accumulators (320 TMEM columns) that live
+// for the CTA's whole share of the image, and at the end 18 fp32 [32 k][32 c] tiles per warp added into dW by TMA reduce-add.
+constexpr int kHaloWgStages = 4;
+constexpr int kHaloDyBytes = 2 * kHaloWP * 128;   // 16 KB: two output rows of dy
+
+__global__ void __launch_bounds__(kThreads)
+conv3x3_halo_wgrad_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmDW,
+                          const HaloArgs g) {
+  constexpr int STAGES = kHaloWgStages, kStage = kHaloABytes + kHaloDyBytes;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0) {
+    if (threadIdx.x == 0) printf("dv conv3x3_halo_wgrad: dynamic shared memory is not 1024-byte aligned\n");
+    __trap();
+  }
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * kStage);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tfull_bar + 1);
+  const int warp = uniform_warp_idx(), lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmX);
+    prefetch_tmap(&tmDY);
+    prefetch_tmap(&tmDW);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < g.total; tile += gridDim.x) {
+      const int n = tile / g.tiles_h, h0 = (tile - n * g.tiles_h) * 2;
+      mbar_wait(&empty_bar[stage], phase ^ 1);
+      if (elect_one()) {
+        uint8_t* sX = smem + stage * kStage;
+        mbar_expect_tx(&full_bar[stage], kStage);
+        tma_load_4d(sX, &tmX, &full_bar[stage], 0, -1, h0 - 1, n);
+        tma_load_4d(sX + kHaloABytes, &tmDY, &full_bar[stage], 0, 0, h0, n);
+      }
+      __syncwarp();
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc(128, 64, 1, 1);
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first = true;
+    for (int tile = blockIdx.x; tile < g.total; tile += gridDim.x) {
+      mbar_wait(&full_bar[stage], phase);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t x0 = (smem_u32(smem + stage * kStage) & 0x3FFFFu) >> 4;
+        const uint32_t b_lo0 = desc_lo_mnmajor(smem_u32(smem + stage * kStage + kHaloABytes));
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+          const int ta = 2 * j, tb = j < 4 ? 2 * j + 1 : 2 * j;                       // taps of rows 0-63 / 64-127 (the last one twice)
+          const int offa = (ta / 3) * kHaloWP + ta % 3, offb = (tb / 3) * kHaloWP + tb % 3;
+          const uint32_t lbo = (uint32_t)((offb - offa) * 128) >> 4;                 // chunk distance, 16-byte units
+          const uint32_t a_lo0 = (x0 + (uint32_t)(offa * 128 >> 4)) | (lbo << 16);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)   // 128 pixels of the tile, 16 per MMA (+2048 bytes)
+            umma_f16(tmem_base + (uint32_t)(j * 64), desc_pack(a_lo0 + (uint32_t)(k * 128)), desc_pack(b_lo0 + (uint32_t)(k * 128)), idesc,
+                     (first && k == 0) ? 0u : 1u);
+        }
+        umma_commit(&empty_bar[stage]);
+      }
+      __syncwarp();
+      first = false;
+      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
+    if (elect_one()) umma_commit(tfull_bar);
+    __syncwarp();
+  } else {
+    const int quarter = warp & 3;
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    // every MMA has completed: the operand ring is free for the fp32 tiles ([32 k][32 c], 128-byte rows, SWIZZLE_128B as tmDW wants)
+    uint8_t* tiles = smem + (size_t)quarter * (10 * 4096);
+    const int c0 = (quarter & 1) * 32;
+#pragma unroll 1
+    for (int j = 0; j < 5; ++j) {
+      const int tap = quarter < 2 ? 2 * j : 2 * j + 1;
+      if (tap > 8) break;   // the fifth accumulator holds tap 8 twice
+#pragma unroll 1
+      for (int kh = 0; kh < 2; ++kh) {
+        uint32_t v[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(j * 64 + kh * 32), v);
+        tmem_ld_wait();
+        uint8_t* tile = tiles + (j * 2 + kh) * 4096;
+        // lane = channel c0 + lane holds 32 output channels k: transposed into rows k
+#pragma unroll
+        for (int kk = 0; kk < 32; ++kk)
+          *reinterpret_cast<uint32_t*>(tile + kk * 128 + (((lane >> 2) ^ (kk & 7)) * 16) + (lane & 3) * 4) = v[kk];
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) tma_reduce_add_3d(&tmDW, smem_u32(tile), c0, tap, kh * 32);
+      }
+    }
+    if (lane == 0) tma_store_wait_read();
+    __syncwarp();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
 }  // namespace
 
 // fprop or stride-1 dgrad of a 3x3 pad-1 convolution with 64 input and 64 output channels whose rows fit the 64-pixel box
@@ -2644,6 +2771,40 @@ int conv3x3_halo(const dv_conv_params* p, int pass, cudaStream_t st) {
     conv3x3_halo_kernel<false><<<grid, kHaloThreads, smem, st>>>(tmX, tmW, tmO, g);
   }
   DV_LAUNCH_OK("conv3x3_halo_kernel");
+  return DV_OK;
+}
+
+
+// weight gradient of the same geometry, added into dW (fp32 KRSC) by TMA reduce-add: the accumulate mode of dv_conv_wgrad
+bool conv3x3_halo_wgrad_supported(const dv_conv_params* p) {
+  static const int enabled = [] { const char* v = getenv("DV_TC_HALO_WGRAD"); return v ? atoi(v) : 1; }();
+  if (!enabled || p->dtype != DV_BF16 || p->R != 3 || p->S != 3 || p->stride != 1 || p->pad != 1 || p->C != 64 || p->K != 64) return false;
+  if (p->W > kHaloWP - 2 || p->W < 24 || p->H < 2) return false;
+  if (!p->accumulate || p->y_f32 || p->ep_scale || p->ep_shift || p->ep_residual || p->ep_relu || p->bnb_x) return false;
+  return aligned16(p->w);
+}
+
+int conv3x3_halo_wgrad(const dv_conv_params* p, cudaStream_t st) {
+  alignas(64) CUtensorMap tmX, tmDY, tmDW;
+  const uint64_t dims[4] = {64, (uint64_t)p->W, (uint64_t)p->H, (uint64_t)p->N};
+  const uint64_t strides[3] = {128, (uint64_t)p->W * 128, (uint64_t)p->H * p->W * 128};
+  const uint32_t box_x[4] = {64, (uint32_t)kHaloWP, 4, 1}, box_dy[4] = {64, (uint32_t)kHaloWP, 2, 1};
+  int rc = make_tiled_map_bf16(&tmX, p->x, 4, dims, strides, box_x, 3);
+  if (rc) return rc;
+  rc = make_tiled_map_bf16(&tmDY, p->y, 4, dims, strides, box_dy, 3);
+  if (rc) return rc;
+  rc = make_map_dw(&tmDW, (float*)p->w, 64, 9, 64);
+  if (rc) return rc;
+  HaloArgs g{};
+  g.N = p->N; g.H = p->H; g.W = p->W;
+  g.tiles_h = (p->H + 1) / 2;
+  g.total = p->N * g.tiles_h;
+  const int grid = g.total < num_sms() ? g.total : num_sms();
+  constexpr int smem = kHaloWgStages * (kHaloABytes + kHaloDyBytes) + 256;
+  static_assert(smem <= 227 * 1024, "halo wgrad kernel exceeds shared memory");
+  DV_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  conv3x3_halo_wgrad_kernel<<<grid, kThreads, smem, st>>>(tmX, tmDY, tmDW, g);
+  DV_LAUNCH_OK("conv3x3_halo_wgrad_kernel");
   return DV_OK;
 }
 
