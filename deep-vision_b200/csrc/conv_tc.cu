@@ -372,12 +372,13 @@ __device__ __forceinline__ void apply_folded_epilogue(uint32_t* v, const GemmArg
 // B_MN: the B operand is taken as [64 reduction rows][64 output columns] boxes straight from KRSC filters and consumed
 // MN-major — the dgrad case, where the reduction runs over K (filter rows) and the output over C (contiguous), with the
 // tap flipped by index.  No transposed copy of the filters is needed.
-// EPI: 0 = plain, 1 = folded BatchNorm (inference fprop), 2 = BatchNorm-backward sums of the producing layer (dgrad)
+// EPI: 0 = plain, 1 = folded BatchNorm (inference fprop) with an identity tile, 3 = the same without one, 2 = BatchNorm-backward sums of
+// the producing layer (dgrad)
 template <int BN, int STAGES, bool STATS, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kThreads)
 conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                                const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
-  constexpr bool FOLD = EPI == 1, BNB = EPI == 2;
+  constexpr bool FOLD = EPI == 1 || EPI == 3, BNB = EPI == 2, AUX = EPI == 1 || EPI == 2;   // AUX: the epilogue reads a tile (identity / x0)
   static_assert(!BNB || STATS, "the BatchNorm-backward sums ride on the staged (TMA store) epilogue");
   constexpr int ACC = 2;
   constexpr int kBBytes = BN * kBlockK * 2;
@@ -393,9 +394,9 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     __trap();
   }
   uint8_t* stage_out = smem + STAGES * kStageBytes;  // STATS: 4 epilogue warps x [32 rows][128 B], 16-byte chunks XOR-swizzled by row
-  // EPI != 0: a second set of per-warp buffers for the tile the epilogue reads (identity / x0), fetched one column group ahead
+  // AUX: a second set of per-warp buffers for the tile the epilogue reads (identity / x0), fetched one column group ahead
   uint8_t* stage_aux = stage_out + (STATS ? kEpiStageBytes : 0);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_aux + (EPI != 0 ? kEpiStageBytes : 0));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_aux + (AUX ? kEpiStageBytes : 0));
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
@@ -516,7 +517,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     uint8_t* my_aux = stage_aux + quarter * (32 * 128);
     const uint32_t my_aux_u32 = smem_u32(my_aux);
     (void)my_aux_u32;
-    const bool aux_wanted = (FOLD && g.ep_res != nullptr) || BNB;
+    const bool aux_wanted = AUX && ((FOLD && g.ep_res != nullptr) || BNB);
     // one elected lane asks TMA for the [32 rows][64 columns] tile of the identity / x0 tensor that column group `cgp` will read
     auto aux_request = [&](int n_tile_, int cgp_, int m_base_) {
       mbar_expect_tx(&res_bar[quarter], 32 * 128);
@@ -574,7 +575,7 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
         row_off[it] = off;
       }
       const int n_left = g.Nout - n_tile * BN;
-      if (EPI != 0 && aux_wanted && lane == 0 && m_base < g.M) aux_request(n_tile, 0, m_base);   // lands while the tensor core still works
+      if (AUX && aux_wanted && lane == 0 && m_base < g.M) aux_request(n_tile, 0, m_base);   // lands while the tensor core still works
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
@@ -644,9 +645,9 @@ conv_tc_gemm_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
           if (lane == 0) tma_store_wait_read();
           __syncwarp();
           const bool group_live = cgp * 64 < n_left && m_base < g.M;
-          const bool with_res = FOLD && g.ep_res != nullptr && group_live;
+          const bool with_res = AUX && FOLD && g.ep_res != nullptr && group_live;
           const bool with_x0 = BNB && group_live;
-          uint32_t xw[EPI != 0 ? 32 : 1];   // BNB: the lane's two columns of x0, 32 rows.  FOLD: the lane's row of the identity tile, 64 columns
+          uint32_t xw[AUX ? 32 : 1];   // BNB: the lane's two columns of x0, 32 rows.  FOLD: the lane's row of the identity tile, 64 columns
           if (with_res || with_x0) {       // (warp-uniform) the tile was requested one column group earlier
             mbar_wait(&res_bar[quarter], res_phase);
             res_phase ^= 1;
@@ -752,7 +753,7 @@ template <int STAGES, bool B_MN, int EPI, int EW>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(64 + 32 * EW)
 conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmArgs g) {
-  constexpr bool FOLD = EPI == 1, BNB = EPI == 2;
+  constexpr bool FOLD = EPI == 1 || EPI == 3, BNB = EPI == 2, AUX = EPI == 1 || EPI == 2;   // AUX: the epilogue reads a tile (identity / x0)
   constexpr int BN = 256, ACC = 2;
   constexpr int kBHalfBytes = (BN / 2) * kBlockK * 2;  // 16 KB: this CTA's half of the filter tile
   constexpr int kStageBytes = kABytes + kBHalfBytes;    // 32 KB
@@ -767,8 +768,8 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   static_assert(EW == 4 || EW == 8, "4 or 8 epilogue warps");
   constexpr int kGroupStep = EW / 4;                 // column groups are dealt round-robin to the warps of a quarter
   constexpr int kMyGroups = (BN / 64) / kGroupStep;
-  uint8_t* stage_aux = stage_out + EW * 4096;        // EPI != 0: the tile the epilogue reads (identity / x0), one column group ahead
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_aux + (EPI != 0 ? EW * 4096 : 0));
+  uint8_t* stage_aux = stage_out + EW * 4096;        // AUX: the tile the epilogue reads (identity / x0), one column group ahead
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_aux + (AUX ? EW * 4096 : 0));
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tfull_bar = empty_bar + STAGES;
   uint64_t* tempty_bar = tfull_bar + ACC;
@@ -890,7 +891,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     uint8_t* my_aux = stage_aux + ew * (32 * 128);
     const uint32_t my_aux_u32 = smem_u32(my_aux);
     (void)my_aux_u32;
-    const bool aux_wanted = (FOLD && g.ep_res != nullptr) || BNB;
+    const bool aux_wanted = AUX && ((FOLD && g.ep_res != nullptr) || BNB);
     // one elected lane asks TMA for the [32 rows][64 columns] tile of the identity / x0 tensor that column group `cgp` will read
     auto aux_request = [&](int n_tile_, int cgp_, int m_base_) {
       mbar_expect_tx(&res_bar[ew], 32 * 128);
@@ -928,7 +929,7 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       if (n_tile != stat_n_tile) { flush_stats(); stat_n_tile = n_tile; }
       const int m_base = m_tile * kBlockM + quarter * 32;
       const int n_left = g.Nout - n_tile * BN;
-      if (EPI != 0 && aux_wanted && lane == 0 && m_base < g.M && cg_first * 64 < n_left) aux_request(n_tile, cg_first, m_base);   // lands while the tensor core still works
+      if (AUX && aux_wanted && lane == 0 && m_base < g.M && cg_first * 64 < n_left) aux_request(n_tile, cg_first, m_base);   // lands while the tensor core still works
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
@@ -938,9 +939,9 @@ conv_tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         if (lane == 0) tma_store_wait_read();
         __syncwarp();
         const bool group_live = cgp * 64 < n_left && m_base < g.M;
-        const bool with_res = FOLD && g.ep_res != nullptr && group_live;
+        const bool with_res = AUX && FOLD && g.ep_res != nullptr && group_live;
         const bool with_x0 = BNB && group_live;
-        uint32_t xw[EPI != 0 ? 32 : 1];   // BNB: the lane's two columns of x0, 32 rows.  FOLD: the lane's row of the identity tile, 64 columns
+        uint32_t xw[AUX ? 32 : 1];   // BNB: the lane's two columns of x0, 32 rows.  FOLD: the lane's row of the identity tile, 64 columns
         if (with_res || with_x0) {       // (warp-uniform) the tile was requested one column group earlier
           mbar_wait(&res_bar[ew], res_phase);
           res_phase ^= 1;
@@ -1376,7 +1377,7 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 template <int STAGES, bool B_MN, int EPI, int EW>
 static int launch_gemm_pair_ew(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                                cudaStream_t st) {
-  constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + EW * 4096 * (EPI != 0 ? 2 : 1) + 256;
+  constexpr int smem = STAGES * (kABytes + 128 * kBlockK * 2) + EW * 4096 * ((EPI == 1 || EPI == 2) ? 2 : 1) + 256;
   static_assert(smem <= 227 * 1024, "pair kernel ring exceeds shared memory");
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_pair_kernel<STAGES, B_MN, EPI, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int num_n = ceil_div(g.Nout, 256);
@@ -1396,7 +1397,7 @@ template <int STAGES, bool B_MN, int EPI>
 static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                             cudaStream_t st) {
   static const int ew = env_int("DV_TC_EW", 8);
-  if (ew == 8) return launch_gemm_pair_ew<(EPI != 0 ? STAGES - 1 : STAGES), B_MN, EPI, 8>(tmA, tmB, tmO, tmR, g, st);
+  if (ew == 8) return launch_gemm_pair_ew<((EPI == 1 || EPI == 2) ? STAGES - 1 : STAGES), B_MN, EPI, 8>(tmA, tmB, tmO, tmR, g, st);
   return launch_gemm_pair_ew<STAGES, B_MN, EPI, 4>(tmA, tmB, tmO, tmR, g, st);
 }
 
@@ -1408,7 +1409,7 @@ static int env_int(const char* name, int dflt) {
 template <int BN, int STAGES, bool STATS, bool B_MN, int EPI>
 static int launch_gemm_persistent(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmO, const CUtensorMap& tmR, const GemmArgs& g,
                                   cudaStream_t st) {
-  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + (EPI != 0 ? kEpiStageBytes : 0) + 256;
+  constexpr int smem = STAGES * (kABytes + BN * kBlockK * 2) + (STATS ? kEpiStageBytes : 0) + ((EPI == 1 || EPI == 2) ? kEpiStageBytes : 0) + 256;
   static_assert(smem <= 227 * 1024, "persistent kernel ring exceeds shared memory");
   DV_CUDA_OK(cudaFuncSetAttribute(conv_tc_gemm_persistent_kernel<BN, STAGES, STATS, B_MN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   // ask for the whole L1/shared array as shared memory: otherwise the driver sizes the carve-out for ONE CTA of this
@@ -1605,6 +1606,14 @@ static int gemm_dispatch(const CUtensorMap& tmA, const CUtensorMap& tmB, const G
   const bool fold = g.ep_scale != nullptr;  // fprop only (conv_tc checks): staged, K-major B
   if (fold) {
     DV_REQUIRE(staged && !b_mn, DV_ERR_UNSUPPORTED, "conv_tc: the folded epilogue exists on the fprop TMA-store path only");
+    if (g.ep_res == nullptr) {   // no identity tile to fetch (EPI 3): no tile buffers, the plain kernels' ring depth
+      if (use_pair(g, bn)) return launch_gemm_pair<6, false, 3>(tmA, tmB, tmO, tmR, g, st);
+      switch (bn) {
+        case 64: return launch_gemm_persistent<64, 4, true, false, 3>(tmA, tmB, tmO, tmR, g, st);
+        case 128: return launch_gemm_persistent<128, 3, true, false, 3>(tmA, tmB, tmO, tmR, g, st);
+        default: return launch_gemm_persistent<256, 4, true, false, 3>(tmA, tmB, tmO, tmR, g, st);
+      }
+    }
     if (use_pair(g, bn)) return launch_gemm_pair<6, false, 1>(tmA, tmB, tmO, tmR, g, st);
     switch (bn) {
       case 64: return launch_gemm_persistent<64, 3, true, false, 1>(tmA, tmB, tmO, tmR, g, st);    // one stage fewer: two CTAs per SM still fit
